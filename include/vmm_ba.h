@@ -1,0 +1,210 @@
+/* vmm_ba.h — C ABI of the B200-native bundle-adjustment engine (libvmm_ba.so).
+ *
+ * This is the drop-in boundary for ONE path of schmidtniko/visual_marker_mapping: the joint
+ * Levenberg-Marquardt refinement of camera and marker poses,
+ *     TagReconstructor::doBundleAdjustment            src/TagReconstructor.cpp:646-784
+ * with its cost functor
+ *     TagReconstructionCostFunction::operator()       include/visual_marker_mapping/TagReconstructionCostFunction.h:101-159
+ * and the reprojection statistics that gate it
+ *     computeReprojectionErrorPerImg / PerTag         src/TagReconstructor.cpp:340-428.
+ *
+ * The reference has no FFI of its own (the seam is that one protected member function); the C++
+ * facade in visual_marker_mapping_b200/csrc/host/ flattens its std::map state into the dense arrays
+ * below and calls these entry points (INTEGRATION.md shows the binding).  Plain pointers and sizes
+ * only; every function returns a vmm_ba_status (0 = ok) and never throws.  All pointer arguments
+ * are HOST memory unless the name ends in _dev.  There is no CPU fallback: every entry point that
+ * computes needs a CUDA device (sm_100a) and fails with VMM_BA_ERR_CUDA otherwise.
+ *
+ * Conventions
+ *   quaternions (w,x,y,z)                               Camera.h:13, TagReconstructor.h:19
+ *   camera pose maps world -> camera, marker pose maps marker -> world   TagReconstructionCostFunction.h:107-122
+ *   tag observation = 4 corners (LL, LR, UR, UL), u,v interleaved: to_uv[8*k + 2*c + {0,1}]   TagReconstructor.h:44-52
+ *   indices are dense 0-based positions; ids stay on the host side
+ *   tangent vectors / gradients: camera i at [6i, 6i+6) = (t, delta), marker j at 6*Nc + [6j, 6j+6)
+ *   local Jacobian of one corner: 2 x 12 row-major, columns (t_c, delta_c, t_m, delta_m)  — parameter
+ *   block order of AddResidualBlock at src/TagReconstructor.cpp:720-722, delta = the 3-vector of
+ *   ceres::QuaternionParameterization (src/TagReconstructor.cpp:661).
+ */
+#ifndef VMM_BA_H_
+#define VMM_BA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VMM_BA_ABI_VERSION 1
+
+typedef struct vmm_ba_engine* vmm_ba_handle;
+
+typedef enum {
+    VMM_BA_OK = 0,
+    VMM_BA_ERR_INVALID_ARGUMENT = 1,
+    VMM_BA_ERR_CUDA = 2,          /* no device / CUDA runtime failure */
+    VMM_BA_ERR_STATE = 3,         /* call order (no problem set, ...) */
+    VMM_BA_ERR_NCCL = 4,
+    VMM_BA_ERR_NUMERIC = 5
+} vmm_ba_status;
+
+/* replaces: new ceres::HuberLoss(1.0) / nullptr / (commented) CauchyLoss(3)   src/TagReconstructor.cpp:721 */
+typedef enum { VMM_BA_LOSS_NONE = 0, VMM_BA_LOSS_HUBER = 1, VMM_BA_LOSS_CAUCHY = 2 } vmm_ba_loss;
+
+/* same numbering as ceres::TerminationType, which the reference prints at src/TagReconstructor.cpp:740 */
+typedef enum { VMM_BA_CONVERGENCE = 0, VMM_BA_NO_CONVERGENCE = 1, VMM_BA_FAILURE = 2 } vmm_ba_termination;
+
+typedef enum { VMM_BA_PRECOND_JACOBI = 0, VMM_BA_PRECOND_SCHUR_JACOBI = 1 } vmm_ba_preconditioner;
+
+/* replaces: ceres::Solver::Options as configured at src/TagReconstructor.cpp:725-735
+ * (everything the reference leaves at the Ceres default is a field here with that default). */
+typedef struct {
+    int max_num_iterations;               /* reference: 400 / 1500 */
+    int loss_kind;                        /* vmm_ba_loss; reference: HUBER when robustify */
+    double loss_scale;                    /* reference: 1.0 */
+    double function_tolerance;            /* 1e-6  */
+    double gradient_tolerance;            /* 1e-10 */
+    double parameter_tolerance;           /* 1e-8  */
+    double initial_trust_region_radius;   /* 1e4   */
+    double max_trust_region_radius;       /* 1e16  */
+    double min_trust_region_radius;       /* 1e-32 */
+    double min_relative_decrease;         /* 1e-3  */
+    double min_lm_diagonal;               /* 1e-6  */
+    double max_lm_diagonal;               /* 1e32  */
+    int max_num_consecutive_invalid_steps;/* 5     */
+    int jacobi_scaling;                   /* 1     */
+    /* linear solver: block-Jacobi PCG on the reduced camera system (markers eliminated) */
+    int preconditioner;                   /* vmm_ba_preconditioner, default SCHUR_JACOBI */
+    double pcg_tolerance;                 /* stop when sqrt(r.M^-1 r / r0.M^-1 r0) <= tol; default 1e-2 */
+    int pcg_max_iterations;               /* default 500 */
+    int pcg_min_iterations;               /* default 1 */
+    int parity_mode;                      /* 1: solve every LM step to pcg_parity_tolerance so that the
+                                             iterates track an exact-Cholesky (Ceres) trajectory */
+    double pcg_parity_tolerance;          /* default 1e-13 */
+    int pcg_parity_max_iterations;        /* default 20000 */
+    int verbose;                          /* 1: one line per LM iteration on stderr */
+} vmm_ba_options;
+
+/* replaces: ceres::Solver::Summary (the reference only prints termination_type / FullReport) */
+typedef struct {
+    int termination_type;                 /* vmm_ba_termination */
+    double initial_cost;
+    double final_cost;
+    int num_successful_steps;
+    int num_unsuccessful_steps;
+    int num_iterations;                   /* LM iterations performed, iteration 0 excluded */
+    int64_t num_linearizations;           /* residual+Jacobian(+Schur blocks) passes */
+    int64_t num_cost_evaluations;         /* residual-only passes */
+    int64_t pcg_iterations;               /* total over the solve */
+    int64_t kernel_launches;              /* launches of this library's kernels during the solve */
+    double time_total_s;                  /* host wall clock of vmm_ba_solve */
+    double time_linearize_s;              /* CUDA-event time on the engine's stream */
+    double time_linear_solver_s;
+    double time_cost_eval_s;
+    double gradient_max_norm;
+    double trust_region_radius;
+    char message[256];
+} vmm_ba_summary;
+
+/* Fill with the Ceres defaults in force at src/TagReconstructor.cpp:725-735. */
+void vmm_ba_options_init(vmm_ba_options* options);
+
+int vmm_ba_abi_version(void);
+
+/* Number of visible CUDA devices (0 when there is none; never fails). */
+int vmm_ba_device_count(void);
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+
+/* Single-GPU engine on CUDA device `device`. */
+int vmm_ba_create(int device, vmm_ba_handle* out);
+
+/* One engine per process per GPU; `nccl_unique_id` is the 128-byte ncclUniqueId that rank 0 got
+ * from vmm_ba_nccl_unique_id() and broadcast out of band.  Cameras and their observations are
+ * sharded over ranks, markers are replicated; partial marker blocks, gradients and the PCG
+ * reductions travel by ncclAllReduce over NVLink. */
+int vmm_ba_create_distributed(int device, int rank, int world_size, const void* nccl_unique_id, size_t id_bytes,
+                              vmm_ba_handle* out);
+int vmm_ba_nccl_unique_id(void* out_id, size_t id_bytes);
+int vmm_ba_destroy(vmm_ba_handle h);
+
+/* Error text of the last failing call on this handle (or of the last failing create when h == NULL). */
+const char* vmm_ba_last_error(vmm_ba_handle h);
+
+/* Run on the caller's CUDA stream (a cudaStream_t passed as void*) instead of the engine's own. */
+int vmm_ba_set_stream(vmm_ba_handle h, void* cuda_stream);
+
+/* ---- problem ------------------------------------------------------------------------------- */
+
+/* replaces: camModel.getK() / distortionCoefficients copied per corner   src/TagReconstructor.cpp:710-711
+ * dist = k1, k2, p1, p2, k3 (src/CameraUtilities.cpp:45-58). */
+int vmm_ba_set_intrinsics(vmm_ba_handle h, double fx, double fy, double cx, double cy, const double dist[5]);
+
+/* replaces: the problem assembly loop   src/TagReconstructor.cpp:663-724
+ * Every rank passes the SAME full problem; a distributed engine keeps only its camera shard.
+ * fixed_tag_index: the origin tag (SetParameterBlockConstant, :669-673) or -1.
+ * Tag observations may come in any order; they are stably sorted by camera internally. */
+int vmm_ba_set_problem(vmm_ba_handle h, int64_t num_cameras, const double* cam_q, const double* cam_t,
+                       int64_t num_markers, const double* tag_q, const double* tag_t, const double* tag_wh,
+                       int64_t fixed_tag_index, int64_t num_tag_obs, const int32_t* to_cam, const int32_t* to_tag,
+                       const double* to_uv);
+
+/* Overwrite the current poses (same sizes as in set_problem). */
+int vmm_ba_set_poses(vmm_ba_handle h, const double* cam_q, const double* cam_t, const double* tag_q,
+                     const double* tag_t);
+
+/* replaces: the in-place write-back through the pointers handed to Ceres   src/TagReconstructor.cpp:665-666,692-693
+ * Full-size outputs on every rank (a distributed engine gathers the camera shards). */
+int vmm_ba_get_poses(vmm_ba_handle h, double* cam_q, double* cam_t, double* tag_q, double* tag_t);
+
+/* ---- the hot path -------------------------------------------------------------------------- */
+
+/* replaces: ceres::Solve(options, &markerBAProblem, &summary)   src/TagReconstructor.cpp:737-738 */
+int vmm_ba_solve(vmm_ba_handle h, const vmm_ba_options* options, vmm_ba_summary* summary);
+
+/* replaces: one ProgramEvaluator::Evaluate over all residual blocks (AutoDiffCostFunction<...,2,3,4,3,4>
+ * of TagReconstructionCostFunction.h:163-170 + QuaternionParameterization + loss Corrector).
+ * Outputs (any may be NULL), in the CALLER's tag-observation order:
+ *   cost        sum over corners of 0.5*rho(|r|^2)
+ *   residuals   [4*num_tag_obs][2]        corrected residuals
+ *   jacobians   [4*num_tag_obs][2][12]    corrected local Jacobians
+ *   gradient    [6*(num_cameras+num_markers)]   J^T r, zeros for the fixed tag
+ * Distributed engines return the cost/gradient of the whole problem and fill residuals/jacobians
+ * only for their own shard (other entries untouched). */
+int vmm_ba_evaluate(vmm_ba_handle h, int loss_kind, double loss_scale, double* cost, double* residuals,
+                    double* jacobians, double* gradient);
+
+/* Device-resident residual+Jacobian pass (what the HBM roofline is quoted on): launches the
+ * materialising kernel `iterations` times on the engine's stream into device buffers
+ * (component-major: res_dev[2][Nobs_local], jac_dev[24][Nobs_local]) and returns the CUDA-event
+ * time per launch in milliseconds.  No host transfer. */
+int vmm_ba_evaluate_device(vmm_ba_handle h, int loss_kind, double loss_scale, int iterations, double* ms_per_launch);
+
+/* replaces: computeReprojectionErrorPerImg / PerTag   src/TagReconstructor.cpp:340-428 (projection of
+ * src/CameraModel.cpp:6-26, quirk included).  per_tag_obs_sum[k] = sum over the 4 corners of the
+ * Euclidean reprojection error of tag observation k at the current poses (caller's order). */
+int vmm_ba_reprojection_error_sums(vmm_ba_handle h, double* per_tag_obs_sum);
+
+/* ---- introspection for tests / benchmarks -------------------------------------------------- */
+
+/* Camera range [begin,end) and tag-observation count owned by this engine. */
+int vmm_ba_shard_info(vmm_ba_handle h, int64_t* cam_begin, int64_t* cam_end, int64_t* num_local_tag_obs);
+
+/* Host-side partition used by distributed engines: cameras split into `world_size` contiguous
+ * ranges balanced by tag-observation count.  cam_begin has world_size+1 entries.  Needs no GPU. */
+int vmm_ba_partition_cameras(int64_t num_cameras, int64_t num_tag_obs, const int32_t* to_cam, int world_size,
+                             int64_t* cam_begin);
+
+/* Number of kernel launches issued by this library on this handle since creation. */
+int64_t vmm_ba_kernel_launches(vmm_ba_handle h);
+
+/* Measured DFMA throughput of the device (TFLOP/s, 2 flops per FMA) — the FP64 roofline denominator. */
+int vmm_ba_measure_fp64_peak(vmm_ba_handle h, double* tflops);
+
+/* Measured device-to-device copy bandwidth (GB/s, read+write bytes) with this library's own copy kernel. */
+int vmm_ba_measure_copy_bandwidth(vmm_ba_handle h, size_t bytes, double* gbps);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VMM_BA_H_ */

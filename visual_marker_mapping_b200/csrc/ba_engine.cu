@@ -1,0 +1,944 @@
+// ba_engine.cu — host side of libvmm_ba.so: device memory, the Levenberg-Marquardt loop with Ceres
+// trust-region semantics, the block-Jacobi PCG on the reduced camera system, NCCL reductions, and the
+// C ABI declared in include/vmm_ba.h.
+//
+// Replaces TagReconstructor::doBundleAdjustment -> ceres::Solve (src/TagReconstructor.cpp:646-738).
+// Semantics follow SURVEY.md Appendix A; the structure (Schur elimination of the marker blocks,
+// matrix-free PCG, camera-sharded multi-GPU) is new.  There is no CPU fallback in this file.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "../../include/vmm_ba.h"
+#include "ba_kernels.cuh"
+#include "nccl_dyn.h"
+
+using namespace vmm;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        release();
+        n = count;
+        if (count == 0) return cudaSuccess;
+        return cudaMalloc(&p, count * sizeof(T));
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    ~DevBuf() { release(); }
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+};
+
+inline int nblocks(int64_t n, int threads) { return (int)std::max<int64_t>(1, (n + threads - 1) / threads); }
+
+}  // namespace
+
+struct vmm_ba_engine {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t own_stream = nullptr;
+    int rank = 0, world = 1;
+    nccl_comm_t comm = nullptr;
+    std::string last_error;
+    int64_t launches = 0;
+
+    bool have_intrinsics = false, have_problem = false;
+    Intrinsics intr{};
+
+    // global problem sizes
+    int64_t Nc = 0, Nm = 0, Nto = 0, fixed_tag = -1;
+    // local shard (camera range, tag observations in camera-sorted order)
+    int64_t cam0 = 0, cam1 = 0, Ncl = 0, to0 = 0, Ntol = 0;
+    std::vector<int64_t> perm_c;      // sorted position -> caller's tag-observation index (global)
+    bool perm_identity = true;
+    int64_t n_active_cams_local = 0;
+
+    // observations
+    DevBuf<double2> uv;
+    DevBuf<int> ocam, otag, pos_m, mo_cam, mo_tag;
+    DevBuf<unsigned char> cam_active, tag_active;
+    // poses: current and candidate (pointer-swapped on acceptance)
+    DevBuf<double> cam_q[2], cam_t[2], tag_q[2], tag_t[2], camP[2], mkP[2], tag_wh;
+    int cur = 0;
+    // linearisation
+    DevBuf<double> Ec, Em, Bt, gc, B, C, lin_m /* Ct(21Nm) | gm(6Nm) | tail(8) */;
+    DevBuf<double> hdiag_c, hdiag_m, scale_c, scale_m, lmd_c, lmd_m, lam_c, lam_m;
+    DevBuf<double> Cinv, Minv, Sd;
+    // PCG
+    DevBuf<double> px, pr, pz, pp, pq, w /* 6Nm + 2 (pbp slots) */, zm, dm, sc;
+    DevBuf<double> partials, st;
+    DevBuf<int> fail;
+    double* h_st = nullptr;   // pinned mirror of st (64) + sc (8)
+    int* h_fail = nullptr;
+    int n_cost_blocks = 0, n_lin_blocks = 0;
+    // materialised evaluation buffers
+    DevBuf<double> res_dev, jac_dev, rj_partials;
+    DevBuf<double> sums_dev;
+    // gather buffer for distributed get_poses / gradient
+    DevBuf<double> gather;
+
+    cudaEvent_t ev[8] = { nullptr };
+
+    double* Ct() { return lin_m.p; }
+    double* gm() { return lin_m.p + 21 * Nm; }
+    double* lin_tail() { return lin_m.p + 27 * Nm; }
+    double* pbp() { return w.p + 6 * Nm; }
+};
+
+namespace {
+
+int fail_with(vmm_ba_engine* e, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (e) e->last_error = buf; else g_create_error = buf;
+    return code;
+}
+
+#define CU(call)                                                                                                  \
+    do {                                                                                                          \
+        cudaError_t _err = (call);                                                                                \
+        if (_err != cudaSuccess)                                                                                  \
+            return fail_with(e, VMM_BA_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_err), __FILE__, \
+                             __LINE__);                                                                           \
+    } while (0)
+
+#define LAUNCH(kernel, grid, block, ...)                        \
+    do {                                                        \
+        kernel<<<(grid), (block), 0, e->stream>>>(__VA_ARGS__); \
+        ++e->launches;                                          \
+    } while (0)
+
+int nccl_check(vmm_ba_engine* e, int rc, const char* what) {
+    if (rc == 0) return VMM_BA_OK;
+    return fail_with(e, VMM_BA_ERR_NCCL, "%s failed: %s", what, nccl_api().GetErrorString(rc));
+}
+
+int allreduce(vmm_ba_engine* e, double* dev, size_t n, int op) {
+    if (e->world == 1 || n == 0) return VMM_BA_OK;
+    return nccl_check(e, nccl_api().AllReduce(dev, dev, n, NCCL_FLOAT64, op, e->comm, e->stream), "ncclAllReduce");
+}
+
+// Contiguous camera ranges balanced by tag-observation count.
+void partition_cameras(int64_t Nc, const std::vector<int64_t>& cam_count, int world, std::vector<int64_t>& begin) {
+    begin.assign(world + 1, 0);
+    int64_t total = 0;
+    for (int64_t c : cam_count) total += c;
+    begin[world] = Nc;
+    if (total == 0) {
+        for (int k = 0; k <= world; ++k) begin[k] = (Nc * k) / world;
+        return;
+    }
+    int64_t prefix = 0, i = 0;
+    for (int r = 1; r < world; ++r) {
+        // smallest i whose prefix of tag observations reaches r/world of the total
+        while (i < Nc && prefix * world < total * r) prefix += cam_count[i++];
+        begin[r] = i;
+    }
+}
+
+int prepare_poses(vmm_ba_engine* e, int slot) {
+    if (e->Ncl > 0)
+        LAUNCH(k_prep_cameras, nblocks(e->Ncl, 128), 128, (int)e->Ncl, e->cam_q[slot].p, e->cam_t[slot].p, e->camP[slot].p);
+    LAUNCH(k_prep_markers, nblocks(e->Nm, 128), 128, (int)e->Nm, e->tag_q[slot].p, e->tag_t[slot].p, e->tag_wh.p,
+           e->mkP[slot].p);
+    return VMM_BA_OK;
+}
+
+// st layout (doubles)
+enum {
+    ST_COST = 0, ST_GMAX_CAM = 1, ST_XN_CAM = 2, ST_GMAX_MARK = 3, ST_XN_MARK = 4,
+    ST_CAND_CAM = 8 /* 5 values */, ST_CAND_COST = 13, ST_CAND_MARK = 16 /* 5 values */,
+    ST_SC = 32 /* copy of PCG scalars, 8 values */, ST_N = 64
+};
+
+// Linearise at pose slot `slot`: E (both orders), B, gc, C, gm, cost, gradient norms.
+int linearize(vmm_ba_engine* e, int slot, int loss_kind, double loss_a) {
+    CU(cudaMemsetAsync(e->Bt.p, 0, sizeof(double) * 21 * e->Ncl, e->stream));
+    CU(cudaMemsetAsync(e->gc.p, 0, sizeof(double) * 6 * e->Ncl, e->stream));
+    CU(cudaMemsetAsync(e->lin_m.p, 0, sizeof(double) * (27 * e->Nm + 8), e->stream));
+    CU(cudaMemsetAsync(e->st.p, 0, sizeof(double) * 8, e->stream));
+    if (e->Ntol > 0) {
+        LAUNCH(k_linearize, e->n_lin_blocks, 128, e->intr, (int)e->Ntol, e->uv.p, e->ocam.p, e->otag.p, e->pos_m.p,
+               e->tag_active.p, e->camP[slot].p, e->mkP[slot].p, loss_kind, loss_a, e->Ec.p, e->Em.p, e->Bt.p, e->gc.p,
+               e->Ct(), e->gm(), e->partials.p);
+        LAUNCH(k_sum_partials, 1, 256, e->n_lin_blocks, e->partials.p, e->lin_tail());
+    }
+    if (e->Ncl > 0) {
+        LAUNCH(k_expand_blocks, nblocks(e->Ncl, 128), 128, (int)e->Ncl, e->Bt.p, e->B.p, e->hdiag_c.p);
+        LAUNCH(k_gradient_norm, nblocks(e->Ncl, kThreads), kThreads, (int)e->Ncl, e->cam_active.p, e->cam_q[slot].p,
+               e->cam_t[slot].p, e->gc.p, e->st.p + ST_GMAX_CAM);
+    }
+    if (e->world > 1) {
+        // one sum all-reduce: marker blocks, marker gradient, cost, camera x-norm; one max: camera gmax
+        CU(cudaMemcpyAsync(e->lin_tail() + 1, e->st.p + ST_XN_CAM, sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
+        int rc = allreduce(e, e->lin_m.p, 27 * e->Nm + 2, NCCL_SUM);
+        if (rc) return rc;
+        rc = allreduce(e, e->st.p + ST_GMAX_CAM, 1, NCCL_MAX);
+        if (rc) return rc;
+        CU(cudaMemcpyAsync(e->st.p + ST_XN_CAM, e->lin_tail() + 1, sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
+    }
+    CU(cudaMemcpyAsync(e->st.p + ST_COST, e->lin_tail(), sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
+    LAUNCH(k_expand_blocks, nblocks(e->Nm, 128), 128, (int)e->Nm, e->Ct(), e->C.p, e->hdiag_m.p);
+    LAUNCH(k_gradient_norm, nblocks(e->Nm, kThreads), kThreads, (int)e->Nm, e->tag_active.p, e->tag_q[slot].p,
+           e->tag_t[slot].p, e->gm(), e->st.p + ST_GMAX_MARK);
+    return VMM_BA_OK;
+}
+
+int read_stats(vmm_ba_engine* e) {
+    CU(cudaMemcpyAsync(e->h_st, e->st.p, sizeof(double) * ST_N, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(e->h_fail, e->fail.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return VMM_BA_OK;
+}
+
+// out (camera space) += sign * E * vin (marker space)
+void matvec_cam(vmm_ba_engine* e, const double* vin_m, double sign, double* out_c) {
+    if (e->Ntol > 0)
+        LAUNCH(k_block_matvec<false>, nblocks(e->Ntol, kThreads), kThreads, (int)e->Ntol, e->Ec.p, e->ocam.p, e->otag.p,
+               vin_m, sign, out_c);
+}
+// out (marker space) += sign * E^T * vin (camera space)
+void matvec_mark(vmm_ba_engine* e, const double* vin_c, double sign, double* out_m) {
+    if (e->Ntol > 0)
+        LAUNCH(k_block_matvec<true>, nblocks(e->Ntol, kThreads), kThreads, (int)e->Ntol, e->Em.p, e->mo_tag.p, e->mo_cam.p,
+               vin_c, sign, out_m);
+}
+
+struct PcgResult { int iterations; bool ok; double rel; };
+
+// Solve (B_l - E C_l^-1 E^T) x = r0 (r0 in e->pr on entry). x -> e->px, final residual in e->pr.
+int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* out) {
+    const int nc = (int)e->Ncl;
+    const int gb = nblocks(std::max<int64_t>(nc, 1), kThreads);
+    CU(cudaMemsetAsync(e->sc.p, 0, sizeof(double) * 8, e->stream));
+    CU(cudaMemsetAsync(e->pbp(), 0, sizeof(double) * 2, e->stream));
+    LAUNCH(k_pcg_init, gb, kThreads, nc, e->Minv.p, e->B.p, e->lam_c.p, e->pr.p, e->px.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p,
+           e->pbp());
+    if (e->world > 1) {
+        // rz0 (sc[0], sc[4]) are local partials
+        int rc = allreduce(e, e->sc.p, 5, NCCL_SUM);
+        if (rc) return rc;
+    }
+    double rz0 = 0.0;
+    out->iterations = 0;
+    out->ok = true;
+    out->rel = 1.0;
+    const int check_every = 1;
+    for (int it = 0; it < max_it; ++it) {
+        const int s = it & 1, o = s ^ 1;
+        // w = E^T p  (+ pbp partial rides in the tail in distributed mode)
+        CU(cudaMemsetAsync(e->w.p, 0, sizeof(double) * 6 * e->Nm, e->stream));
+        matvec_mark(e, e->pp.p, 1.0, e->w.p);
+        if (e->world > 1) {
+            int rc = allreduce(e, e->w.p, 6 * e->Nm + 2, NCCL_SUM);
+            if (rc) return rc;
+        }
+        // zm = Cinv w ; wz[s] += w.zm ; recycle slot o
+        LAUNCH(k_marker_solve, nblocks(e->Nm, kThreads), kThreads, (int)e->Nm, e->Cinv.p, e->w.p, (const double*)nullptr, 1.0,
+               e->zm.p, e->sc.p + 2 + s, e->sc.p + o, e->sc.p + 2 + o, e->pbp() + o);
+        // q -= E zm   (q holds (B+lam) p)
+        matvec_cam(e, e->zm.p, -1.0, e->pq.p);
+        LAUNCH(k_pcg_update, gb, kThreads, nc, s, e->Minv.p, e->pp.p, e->pq.p, e->px.p, e->pr.p, e->pz.p, e->sc.p, e->pbp());
+        if (e->world > 1) {
+            int rc = allreduce(e, e->sc.p + o, 1, NCCL_SUM);
+            if (rc) return rc;
+        }
+        out->iterations = it + 1;
+        bool stop = false;
+        if ((it + 1) % check_every == 0 || it + 1 == max_it) {
+            CU(cudaMemcpyAsync(e->h_st + ST_SC, e->sc.p, sizeof(double) * 8, cudaMemcpyDeviceToHost, e->stream));
+            CU(cudaStreamSynchronize(e->stream));
+            rz0 = e->h_st[ST_SC + 4];
+            const double rz = e->h_st[ST_SC + o];
+            if (!std::isfinite(rz) || !std::isfinite(rz0)) { out->ok = false; return VMM_BA_OK; }
+            if (rz0 <= 0.0) { out->rel = 0.0; return VMM_BA_OK; }
+            out->rel = std::sqrt(std::max(rz, 0.0) / rz0);
+            if (it + 1 >= min_it && out->rel <= tol) stop = true;
+        }
+        if (stop) break;
+        LAUNCH(k_pcg_direction, gb, kThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, e->pbp());
+    }
+    return VMM_BA_OK;
+}
+
+double elapsed_s(std::chrono::steady_clock::time_point a) {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
+}
+
+int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
+    const auto t_start = std::chrono::steady_clock::now();
+    const int64_t launches0 = e->launches;
+    std::memset(sum, 0, sizeof(*sum));
+    const int loss = opt->loss_kind;
+    const double loss_a = opt->loss_scale;
+    const int nc = (int)e->Ncl, nm = (int)e->Nm;
+    const int gc_b = nblocks(std::max(6 * nc, 1), kThreads), gm_b = nblocks(std::max(6 * nm, 1), kThreads);
+    float ms = 0.f;
+    double t_lin = 0.0, t_solve = 0.0, t_cost = 0.0;
+
+    CU(cudaMemsetAsync(e->fail.p, 0, sizeof(int), e->stream));
+    // ---------------- iteration 0 ----------------
+    CU(cudaEventRecord(e->ev[0], e->stream));
+    prepare_poses(e, e->cur);
+    int rc = linearize(e, e->cur, loss, loss_a);
+    if (rc) return rc;
+    if (nc > 0) LAUNCH(k_jacobi_scale, gc_b, kThreads, 6 * nc, e->hdiag_c.p, e->scale_c.p, opt->jacobi_scaling);
+    LAUNCH(k_jacobi_scale, gm_b, kThreads, 6 * nm, e->hdiag_m.p, e->scale_m.p, opt->jacobi_scaling);
+    CU(cudaEventRecord(e->ev[1], e->stream));
+    rc = read_stats(e);
+    if (rc) return rc;
+    CU(cudaEventElapsedTime(&ms, e->ev[0], e->ev[1]));
+    t_lin += ms * 1e-3;
+    sum->num_linearizations = 1;
+
+    double x_cost = e->h_st[ST_COST];
+    double gmax = std::max(e->h_st[ST_GMAX_CAM], e->h_st[ST_GMAX_MARK]);
+    double x_norm = std::sqrt(e->h_st[ST_XN_CAM] + e->h_st[ST_XN_MARK]);
+    sum->initial_cost = x_cost;
+    double radius = opt->initial_trust_region_radius;
+    double decrease_factor = 2.0;
+    bool reuse_diagonal = false;
+    int num_consecutive_invalid = 0;
+    int iteration = 0;
+    int termination = VMM_BA_NO_CONVERGENCE;
+    const char* msg = "";
+    if (!std::isfinite(x_cost)) {
+        termination = VMM_BA_FAILURE;
+        msg = "Initial cost is not finite.";
+    }
+    if (opt->verbose)
+        fprintf(stderr, "[vmm_ba] it %3d cost %.9e gmax %.3e radius %.3e\n", 0, x_cost, gmax, radius);
+
+    while (termination != VMM_BA_FAILURE) {
+        if (iteration >= opt->max_num_iterations) { termination = VMM_BA_NO_CONVERGENCE; msg = "Maximum number of iterations reached."; break; }
+        if (gmax <= opt->gradient_tolerance) { termination = VMM_BA_CONVERGENCE; msg = "Gradient tolerance reached."; break; }
+        if (radius < opt->min_trust_region_radius) { termination = VMM_BA_CONVERGENCE; msg = "Minimum trust region radius reached."; break; }
+        ++iteration;
+
+        // ---- trust-region step ----
+        CU(cudaEventRecord(e->ev[2], e->stream));
+        if (!reuse_diagonal) {
+            if (nc > 0) LAUNCH(k_lm_diagonal, gc_b, kThreads, 6 * nc, e->hdiag_c.p, e->scale_c.p, opt->min_lm_diagonal, opt->max_lm_diagonal, e->lmd_c.p);
+            LAUNCH(k_lm_diagonal, gm_b, kThreads, 6 * nm, e->hdiag_m.p, e->scale_m.p, opt->min_lm_diagonal, opt->max_lm_diagonal, e->lmd_m.p);
+        }
+        reuse_diagonal = false;
+        if (nc > 0) LAUNCH(k_lambda, gc_b, kThreads, 6 * nc, e->lmd_c.p, e->scale_c.p, radius, e->lam_c.p);
+        LAUNCH(k_lambda, gm_b, kThreads, 6 * nm, e->lmd_m.p, e->scale_m.p, radius, e->lam_m.p);
+        LAUNCH(k_invert_blocks, nblocks(nm, 128), 128, nm, e->C.p, e->lam_m.p, e->tag_active.p, e->Cinv.p, e->fail.p);
+        if (nc > 0) {
+            if (opt->preconditioner == VMM_BA_PRECOND_SCHUR_JACOBI) {
+                LAUNCH(k_schur_diag_init, nblocks((int64_t)nc * 36, kThreads), kThreads, nc, e->B.p, e->lam_c.p, e->Sd.p);
+                if (e->Ntol > 0)
+                    LAUNCH(k_schur_diag, nblocks(e->Ntol, 128), 128, (int)e->Ntol, e->ocam.p, e->otag.p, e->Ec.p, e->Cinv.p, e->Sd.p);
+                LAUNCH(k_mirror_blocks, nblocks(nc, 128), 128, nc, e->Sd.p);
+                LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->Sd.p, (const double*)nullptr, e->cam_active.p, e->Minv.p, e->fail.p);
+            } else {
+                LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->B.p, e->lam_c.p, e->cam_active.p, e->Minv.p, e->fail.p);
+            }
+        }
+        // rhs: r = -gc + E Cinv gm
+        LAUNCH(k_marker_solve, nblocks(nm, kThreads), kThreads, nm, e->Cinv.p, e->gm(), (const double*)nullptr, 1.0, e->zm.p,
+               (double*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr);
+        if (nc > 0) LAUNCH(k_negate, gc_b, kThreads, 6 * nc, e->gc.p, e->pr.p);
+        matvec_cam(e, e->zm.p, 1.0, e->pr.p);
+        PcgResult pr{};
+        const double tol = opt->parity_mode ? opt->pcg_parity_tolerance : opt->pcg_tolerance;
+        const int max_it = opt->parity_mode ? opt->pcg_parity_max_iterations : opt->pcg_max_iterations;
+        rc = pcg_solve(e, tol, std::max(1, max_it), std::max(1, opt->pcg_min_iterations), &pr);
+        if (rc) return rc;
+        sum->pcg_iterations += pr.iterations;
+        // back-substitution: dm = -Cinv (gm + E^T dc)
+        CU(cudaMemsetAsync(e->w.p, 0, sizeof(double) * (6 * nm + 2), e->stream));
+        matvec_mark(e, e->px.p, 1.0, e->w.p);
+        rc = allreduce(e, e->w.p, 6 * (size_t)nm, NCCL_SUM);
+        if (rc) return rc;
+        LAUNCH(k_marker_solve, nblocks(nm, kThreads), kThreads, nm, e->Cinv.p, e->w.p, (const double*)e->gm(), -1.0, e->dm.p,
+               (double*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr);
+        CU(cudaEventRecord(e->ev[3], e->stream));
+
+        // ---- candidate point and its cost ----
+        const int cand = e->cur ^ 1;
+        CU(cudaMemsetAsync(e->st.p + ST_CAND_CAM, 0, sizeof(double) * 16, e->stream));
+        if (nc > 0)
+            LAUNCH(k_candidate, nblocks(nc, kThreads), kThreads, nc, e->cam_active.p, e->cam_q[e->cur].p, e->cam_t[e->cur].p,
+                   e->px.p, e->gc.p, e->lam_c.p, (const double*)e->pr.p, e->cam_q[cand].p, e->cam_t[cand].p, e->st.p + ST_CAND_CAM);
+        LAUNCH(k_candidate, nblocks(nm, kThreads), kThreads, nm, e->tag_active.p, e->tag_q[e->cur].p, e->tag_t[e->cur].p, e->dm.p,
+               (const double*)e->gm(), e->lam_m.p, (const double*)nullptr, e->tag_q[cand].p, e->tag_t[cand].p, e->st.p + ST_CAND_MARK);
+        prepare_poses(e, cand);
+        if (e->Ntol > 0) {
+            LAUNCH(k_cost, e->n_cost_blocks, kThreads, e->intr, e->Ntol, e->uv.p, e->ocam.p, e->otag.p, e->camP[cand].p,
+                   e->mkP[cand].p, loss, loss_a, e->partials.p);
+            LAUNCH(k_sum_partials, 1, 256, e->n_cost_blocks, e->partials.p, e->st.p + ST_CAND_COST);
+        }
+        rc = allreduce(e, e->st.p + ST_CAND_CAM, 6, NCCL_SUM);   // 5 camera stats + candidate cost
+        if (rc) return rc;
+        CU(cudaEventRecord(e->ev[4], e->stream));
+        rc = read_stats(e);
+        if (rc) return rc;
+        CU(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); t_solve += ms * 1e-3;
+        CU(cudaEventElapsedTime(&ms, e->ev[3], e->ev[4])); t_cost += ms * 1e-3;
+        sum->num_cost_evaluations += 1;
+
+        const double* cs = e->h_st + ST_CAND_CAM;
+        const double* msx = e->h_st + ST_CAND_MARK;
+        const double step_norm = std::sqrt(cs[0] + msx[0]);
+        const double dg = cs[1] + msx[1], dld = cs[2] + msx[2], dr = cs[3];
+        const double model_cost_change = -0.5 * dg + 0.5 * dr + 0.5 * dld;
+        double cand_cost = e->h_st[ST_CAND_COST];
+        const bool solver_failed = (*e->h_fail != 0) || !pr.ok || !std::isfinite(step_norm) || !std::isfinite(model_cost_change);
+        if (*e->h_fail) CU(cudaMemsetAsync(e->fail.p, 0, sizeof(int), e->stream));
+        const bool step_valid = !solver_failed && model_cost_change > 0.0;
+        if (opt->verbose)
+            fprintf(stderr, "[vmm_ba] it %3d pcg %4d rel %.2e model %.6e cand %.9e step %.3e radius %.3e%s\n", iteration,
+                    pr.iterations, pr.rel, model_cost_change, cand_cost, step_norm, radius, step_valid ? "" : " INVALID");
+        if (!step_valid) {
+            if (++num_consecutive_invalid >= opt->max_num_consecutive_invalid_steps) {
+                termination = VMM_BA_FAILURE;
+                msg = "Number of consecutive invalid steps more than max_num_consecutive_invalid_steps.";
+                break;
+            }
+            radius /= decrease_factor; decrease_factor *= 2.0; reuse_diagonal = true;
+            ++sum->num_unsuccessful_steps;
+            continue;
+        }
+        num_consecutive_invalid = 0;
+        if (!std::isfinite(cand_cost)) cand_cost = std::numeric_limits<double>::max();
+        if (step_norm <= opt->parameter_tolerance * (x_norm + opt->parameter_tolerance)) {
+            termination = VMM_BA_CONVERGENCE; msg = "Parameter tolerance reached."; break;
+        }
+        const double cost_change = x_cost - cand_cost;
+        if (std::fabs(cost_change) <= opt->function_tolerance * x_cost) {
+            termination = VMM_BA_CONVERGENCE; msg = "Function tolerance reached."; break;
+        }
+        const double relative_decrease = cost_change / model_cost_change;
+        if (relative_decrease > opt->min_relative_decrease) {
+            e->cur = cand;   // accept: candidate poses (and their prepared blocks) become current
+            x_norm = std::sqrt(cs[4] + msx[4]);
+            CU(cudaEventRecord(e->ev[0], e->stream));
+            rc = linearize(e, e->cur, loss, loss_a);
+            if (rc) return rc;
+            CU(cudaEventRecord(e->ev[1], e->stream));
+            rc = read_stats(e);
+            if (rc) return rc;
+            CU(cudaEventElapsedTime(&ms, e->ev[0], e->ev[1])); t_lin += ms * 1e-3;
+            sum->num_linearizations += 1;
+            x_cost = e->h_st[ST_COST];
+            gmax = std::max(e->h_st[ST_GMAX_CAM], e->h_st[ST_GMAX_MARK]);
+            radius = radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * relative_decrease - 1.0, 3));
+            radius = std::min(opt->max_trust_region_radius, radius);
+            decrease_factor = 2.0;
+            ++sum->num_successful_steps;
+        } else {
+            radius /= decrease_factor; decrease_factor *= 2.0; reuse_diagonal = true;
+            ++sum->num_unsuccessful_steps;
+        }
+    }
+    sum->termination_type = termination;
+    sum->final_cost = x_cost;
+    sum->num_iterations = iteration;
+    sum->gradient_max_norm = gmax;
+    sum->trust_region_radius = radius;
+    sum->kernel_launches = e->launches - launches0;
+    sum->time_linearize_s = t_lin;
+    sum->time_linear_solver_s = t_solve;
+    sum->time_cost_eval_s = t_cost;
+    sum->time_total_s = elapsed_s(t_start);
+    snprintf(sum->message, sizeof(sum->message), "%s", msg);
+    return VMM_BA_OK;
+}
+
+int ensure_rj_buffers(vmm_ba_engine* e) {
+    const size_t nobs = (size_t)4 * e->Ntol;
+    if (e->res_dev.n != 2 * nobs || !e->res_dev.p) {
+        CU(e->res_dev.alloc(std::max<size_t>(2 * nobs, 1)));
+        CU(e->jac_dev.alloc(std::max<size_t>(24 * nobs, 1)));
+        CU(e->rj_partials.alloc((size_t)nblocks(nobs, kThreads) + 1));
+    }
+    return VMM_BA_OK;
+}
+
+int launch_rj(vmm_ba_engine* e, int loss_kind, double loss_a, bool with_cost) {
+    const int64_t nobs = 4 * e->Ntol;
+    if (nobs == 0) return VMM_BA_OK;
+    LAUNCH(k_residual_jacobian, nblocks(nobs, kThreads), kThreads, e->intr, nobs, e->uv.p, e->ocam.p, e->otag.p,
+           e->camP[e->cur].p, e->mkP[e->cur].p, loss_kind, loss_a, e->res_dev.p, e->jac_dev.p,
+           with_cost ? e->rj_partials.p : (double*)nullptr);
+    return VMM_BA_OK;
+}
+
+}  // namespace
+
+// =====================================================================================
+// C ABI
+// =====================================================================================
+extern "C" {
+
+void vmm_ba_options_init(vmm_ba_options* o) {
+    std::memset(o, 0, sizeof(*o));
+    o->max_num_iterations = 50;   // Ceres default; the reference passes 400 / 1500
+    o->loss_kind = VMM_BA_LOSS_NONE;
+    o->loss_scale = 1.0;
+    o->function_tolerance = 1e-6;
+    o->gradient_tolerance = 1e-10;
+    o->parameter_tolerance = 1e-8;
+    o->initial_trust_region_radius = 1e4;
+    o->max_trust_region_radius = 1e16;
+    o->min_trust_region_radius = 1e-32;
+    o->min_relative_decrease = 1e-3;
+    o->min_lm_diagonal = 1e-6;
+    o->max_lm_diagonal = 1e32;
+    o->max_num_consecutive_invalid_steps = 5;
+    o->jacobi_scaling = 1;
+    o->preconditioner = VMM_BA_PRECOND_SCHUR_JACOBI;
+    o->pcg_tolerance = 1e-2;
+    o->pcg_max_iterations = 500;
+    o->pcg_min_iterations = 1;
+    o->parity_mode = 0;
+    o->pcg_parity_tolerance = 1e-13;
+    o->pcg_parity_max_iterations = 20000;
+    o->verbose = 0;
+}
+
+int vmm_ba_abi_version(void) { return VMM_BA_ABI_VERSION; }
+
+int vmm_ba_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* vmm_ba_last_error(vmm_ba_handle h) { return h ? h->last_error.c_str() : g_create_error.c_str(); }
+
+static int create_common(int device, vmm_ba_engine** out) {
+    vmm_ba_engine* e = nullptr;
+    if (!out) return fail_with(nullptr, VMM_BA_ERR_INVALID_ARGUMENT, "out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t err = cudaGetDeviceCount(&n);
+    if (err != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail_with(nullptr, VMM_BA_ERR_CUDA, "no CUDA device available (%s); this library has no CPU fallback",
+                         err != cudaSuccess ? cudaGetErrorString(err) : "device count is 0");
+    }
+    if (device < 0 || device >= n) return fail_with(nullptr, VMM_BA_ERR_INVALID_ARGUMENT, "device %d out of range [0,%d)", device, n);
+    cudaDeviceProp prop;
+    if ((err = cudaGetDeviceProperties(&prop, device)) != cudaSuccess)
+        return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(err));
+    if (prop.major != 10)
+        return fail_with(nullptr, VMM_BA_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    if ((err = cudaSetDevice(device)) != cudaSuccess) return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(err));
+    e = new vmm_ba_engine();
+    e->device = device;
+    if ((err = cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        delete e;
+        return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(err));
+    }
+    e->stream = e->own_stream;
+    for (auto& ev : e->ev) cudaEventCreate(&ev);
+    cudaMallocHost(&e->h_st, sizeof(double) * ST_N);
+    cudaMallocHost(&e->h_fail, sizeof(int));
+    e->st.alloc(ST_N);
+    e->sc.alloc(8);
+    e->fail.alloc(1);
+    cudaMemset(e->st.p, 0, sizeof(double) * ST_N);
+    cudaMemset(e->fail.p, 0, sizeof(int));
+    *out = e;
+    return VMM_BA_OK;
+}
+
+int vmm_ba_create(int device, vmm_ba_handle* out) { return create_common(device, out); }
+
+int vmm_ba_nccl_unique_id(void* out_id, size_t id_bytes) {
+    if (!out_id || id_bytes < sizeof(nccl_unique_id)) return fail_with(nullptr, VMM_BA_ERR_INVALID_ARGUMENT, "id buffer must hold 128 bytes");
+    if (!nccl_api().load()) return fail_with(nullptr, VMM_BA_ERR_NCCL, "%s", nccl_api().error);
+    nccl_unique_id id;
+    const int rc = nccl_api().GetUniqueId(&id);
+    if (rc) return fail_with(nullptr, VMM_BA_ERR_NCCL, "ncclGetUniqueId: %s", nccl_api().GetErrorString(rc));
+    std::memcpy(out_id, &id, sizeof(id));
+    return VMM_BA_OK;
+}
+
+int vmm_ba_create_distributed(int device, int rank, int world_size, const void* nccl_id, size_t id_bytes, vmm_ba_handle* out) {
+    if (world_size < 1 || rank < 0 || rank >= world_size) return fail_with(nullptr, VMM_BA_ERR_INVALID_ARGUMENT, "bad rank/world_size");
+    if (world_size > 1 && (!nccl_id || id_bytes < sizeof(nccl_unique_id)))
+        return fail_with(nullptr, VMM_BA_ERR_INVALID_ARGUMENT, "nccl_unique_id must hold 128 bytes");
+    int rc = create_common(device, out);
+    if (rc) return rc;
+    vmm_ba_engine* e = *out;
+    e->rank = rank;
+    e->world = world_size;
+    if (world_size > 1) {
+        if (!nccl_api().load()) { std::string m = nccl_api().error; vmm_ba_destroy(e); *out = nullptr; return fail_with(nullptr, VMM_BA_ERR_NCCL, "%s", m.c_str()); }
+        nccl_unique_id id;
+        std::memcpy(&id, nccl_id, sizeof(id));
+        const int nrc = nccl_api().CommInitRank(&e->comm, world_size, id, rank);
+        if (nrc) {
+            std::string m = nccl_api().GetErrorString(nrc);
+            vmm_ba_destroy(e);
+            *out = nullptr;
+            return fail_with(nullptr, VMM_BA_ERR_NCCL, "ncclCommInitRank: %s", m.c_str());
+        }
+    }
+    return VMM_BA_OK;
+}
+
+int vmm_ba_destroy(vmm_ba_handle e) {
+    if (!e) return VMM_BA_OK;
+    cudaSetDevice(e->device);
+    cudaDeviceSynchronize();
+    if (e->comm) nccl_api().CommDestroy(e->comm);
+    for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
+    if (e->h_st) cudaFreeHost(e->h_st);
+    if (e->h_fail) cudaFreeHost(e->h_fail);
+    if (e->own_stream) cudaStreamDestroy(e->own_stream);
+    delete e;
+    return VMM_BA_OK;
+}
+
+int vmm_ba_set_stream(vmm_ba_handle e, void* cuda_stream) {
+    if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
+    e->stream = cuda_stream ? (cudaStream_t)cuda_stream : e->own_stream;
+    return VMM_BA_OK;
+}
+
+int vmm_ba_set_intrinsics(vmm_ba_handle e, double fx, double fy, double cx, double cy, const double dist[5]) {
+    if (!e || !dist) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null argument");
+    e->intr = Intrinsics{ fx, fy, cx, cy, dist[0], dist[1], dist[2], dist[3], dist[4] };
+    e->have_intrinsics = true;
+    return VMM_BA_OK;
+}
+
+int vmm_ba_partition_cameras(int64_t num_cameras, int64_t num_tag_obs, const int32_t* to_cam, int world_size, int64_t* cam_begin) {
+    if (num_cameras < 0 || num_tag_obs < 0 || world_size < 1 || !cam_begin || (num_tag_obs > 0 && !to_cam)) return VMM_BA_ERR_INVALID_ARGUMENT;
+    std::vector<int64_t> cnt(num_cameras, 0);
+    for (int64_t k = 0; k < num_tag_obs; ++k) {
+        if (to_cam[k] < 0 || to_cam[k] >= num_cameras) return VMM_BA_ERR_INVALID_ARGUMENT;
+        cnt[to_cam[k]]++;
+    }
+    std::vector<int64_t> begin;
+    partition_cameras(num_cameras, cnt, world_size, begin);
+    for (int r = 0; r <= world_size; ++r) cam_begin[r] = begin[r];
+    return VMM_BA_OK;
+}
+
+int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const double* cam_t, int64_t Nm, const double* tag_q,
+                       const double* tag_t, const double* tag_wh, int64_t fixed_tag, int64_t Nto, const int32_t* to_cam,
+                       const int32_t* to_tag, const double* to_uv) {
+    if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
+    if (Nc < 0 || Nm < 1 || Nto < 0) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "sizes must be non-negative and num_markers >= 1");
+    if ((Nc > 0 && (!cam_q || !cam_t)) || !tag_q || !tag_t || !tag_wh || (Nto > 0 && (!to_cam || !to_tag || !to_uv)))
+        return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null array");
+    if (fixed_tag >= Nm) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "fixed_tag_index out of range");
+    if (Nc > (int64_t)1 << 28 || Nm > (int64_t)1 << 28 || Nto > (int64_t)1 << 28)
+        return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "problem too large for 32-bit block indices");
+    CU(cudaSetDevice(e->device));
+    e->have_problem = false;
+    std::vector<int64_t> cam_count(Nc, 0), tag_count(Nm, 0);
+    bool sorted = true;
+    for (int64_t k = 0; k < Nto; ++k) {
+        const int32_t c = to_cam[k], m = to_tag[k];
+        if (c < 0 || c >= Nc || m < 0 || m >= Nm) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "tag observation %lld has an index out of range", (long long)k);
+        cam_count[c]++;
+        tag_count[m]++;
+        if (k > 0 && to_cam[k - 1] > c) sorted = false;
+    }
+    e->Nc = Nc; e->Nm = Nm; e->Nto = Nto; e->fixed_tag = fixed_tag;
+    // stable counting sort by camera
+    std::vector<int64_t> cam_ptr(Nc + 1, 0);
+    for (int64_t i = 0; i < Nc; ++i) cam_ptr[i + 1] = cam_ptr[i] + cam_count[i];
+    e->perm_c.resize(Nto);
+    e->perm_identity = sorted;
+    if (sorted) {
+        for (int64_t k = 0; k < Nto; ++k) e->perm_c[k] = k;
+    } else {
+        std::vector<int64_t> fill(cam_ptr.begin(), cam_ptr.end() - 1);
+        for (int64_t k = 0; k < Nto; ++k) e->perm_c[fill[to_cam[k]]++] = k;
+    }
+    // shard
+    std::vector<int64_t> begin;
+    partition_cameras(Nc, cam_count, e->world, begin);
+    e->cam0 = begin[e->rank]; e->cam1 = begin[e->rank + 1];
+    e->Ncl = e->cam1 - e->cam0;
+    e->to0 = cam_ptr[e->cam0];
+    e->Ntol = cam_ptr[e->cam1] - e->to0;
+    const int64_t Ncl = e->Ncl, Ntol = e->Ntol;
+
+    // host staging of the local shard
+    std::vector<double2> h_uv((size_t)4 * Ntol);
+    std::vector<int> h_ocam(Ntol), h_otag(Ntol), h_posm(Ntol), h_mocam(Ntol), h_motag(Ntol);
+    for (int64_t s = 0; s < Ntol; ++s) {
+        const int64_t k = e->perm_c[e->to0 + s];
+        h_ocam[s] = (int)(to_cam[k] - e->cam0);
+        h_otag[s] = to_tag[k];
+        for (int c = 0; c < 4; ++c) h_uv[4 * s + c] = make_double2(to_uv[8 * k + 2 * c], to_uv[8 * k + 2 * c + 1]);
+    }
+    // marker order of the local tag observations (stable counting sort by marker)
+    {
+        std::vector<int64_t> mptr(Nm + 1, 0);
+        for (int64_t s = 0; s < Ntol; ++s) mptr[h_otag[s] + 1]++;
+        for (int64_t j = 0; j < Nm; ++j) mptr[j + 1] += mptr[j];
+        for (int64_t s = 0; s < Ntol; ++s) {
+            const int64_t pos = mptr[h_otag[s]]++;
+            h_posm[s] = (int)pos;
+            h_mocam[pos] = h_ocam[s];
+            h_motag[pos] = h_otag[s];
+        }
+    }
+    std::vector<unsigned char> h_cact(std::max<int64_t>(Ncl, 1), 0), h_tact(Nm, 0);
+    e->n_active_cams_local = 0;
+    for (int64_t i = 0; i < Ncl; ++i) { h_cact[i] = cam_count[e->cam0 + i] > 0; e->n_active_cams_local += h_cact[i]; }
+    for (int64_t j = 0; j < Nm; ++j) h_tact[j] = (tag_count[j] > 0) && (j != fixed_tag);
+
+    const size_t ncl1 = (size_t)std::max<int64_t>(Ncl, 1), nto1 = (size_t)std::max<int64_t>(Ntol, 1);
+    CU(e->uv.alloc(4 * nto1));
+    CU(e->ocam.alloc(nto1)); CU(e->otag.alloc(nto1)); CU(e->pos_m.alloc(nto1)); CU(e->mo_cam.alloc(nto1)); CU(e->mo_tag.alloc(nto1));
+    CU(e->cam_active.alloc(ncl1)); CU(e->tag_active.alloc(Nm));
+    for (int s = 0; s < 2; ++s) {
+        CU(e->cam_q[s].alloc(4 * ncl1)); CU(e->cam_t[s].alloc(3 * ncl1)); CU(e->tag_q[s].alloc(4 * Nm)); CU(e->tag_t[s].alloc(3 * Nm));
+        CU(e->camP[s].alloc(CAM_PREP * ncl1)); CU(e->mkP[s].alloc((size_t)MARK_PREP * Nm));
+    }
+    CU(e->tag_wh.alloc(2 * Nm));
+    CU(e->Ec.alloc(36 * nto1)); CU(e->Em.alloc(36 * nto1));
+    CU(e->Bt.alloc(21 * ncl1)); CU(e->gc.alloc(6 * ncl1)); CU(e->B.alloc(36 * ncl1)); CU(e->C.alloc((size_t)36 * Nm));
+    CU(e->lin_m.alloc((size_t)27 * Nm + 8));
+    CU(e->hdiag_c.alloc(6 * ncl1)); CU(e->scale_c.alloc(6 * ncl1)); CU(e->lmd_c.alloc(6 * ncl1)); CU(e->lam_c.alloc(6 * ncl1));
+    CU(e->hdiag_m.alloc((size_t)6 * Nm)); CU(e->scale_m.alloc((size_t)6 * Nm)); CU(e->lmd_m.alloc((size_t)6 * Nm)); CU(e->lam_m.alloc((size_t)6 * Nm));
+    CU(e->Cinv.alloc((size_t)36 * Nm)); CU(e->Minv.alloc(36 * ncl1)); CU(e->Sd.alloc(36 * ncl1));
+    CU(e->px.alloc(6 * ncl1)); CU(e->pr.alloc(6 * ncl1)); CU(e->pz.alloc(6 * ncl1)); CU(e->pp.alloc(6 * ncl1)); CU(e->pq.alloc(6 * ncl1));
+    CU(e->w.alloc((size_t)6 * Nm + 2)); CU(e->zm.alloc((size_t)6 * Nm)); CU(e->dm.alloc((size_t)6 * Nm));
+    e->n_cost_blocks = nblocks(Ntol, kThreads);
+    e->n_lin_blocks = nblocks(Ntol, 128);
+    CU(e->partials.alloc((size_t)std::max(e->n_cost_blocks, e->n_lin_blocks) + 1));
+    CU(e->sums_dev.alloc(nto1));
+    e->res_dev.release(); e->jac_dev.release(); e->rj_partials.release();
+
+    auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
+    CU(up(e->uv.p, h_uv.data(), sizeof(double2) * 4 * Ntol));
+    CU(up(e->ocam.p, h_ocam.data(), sizeof(int) * Ntol));
+    CU(up(e->otag.p, h_otag.data(), sizeof(int) * Ntol));
+    CU(up(e->pos_m.p, h_posm.data(), sizeof(int) * Ntol));
+    CU(up(e->mo_cam.p, h_mocam.data(), sizeof(int) * Ntol));
+    CU(up(e->mo_tag.p, h_motag.data(), sizeof(int) * Ntol));
+    CU(up(e->cam_active.p, h_cact.data(), Ncl));
+    CU(up(e->tag_active.p, h_tact.data(), Nm));
+    CU(up(e->tag_wh.p, tag_wh, sizeof(double) * 2 * Nm));
+    e->cur = 0;
+    CU(up(e->cam_q[0].p, cam_q + 4 * e->cam0, sizeof(double) * 4 * Ncl));
+    CU(up(e->cam_t[0].p, cam_t + 3 * e->cam0, sizeof(double) * 3 * Ncl));
+    CU(up(e->tag_q[0].p, tag_q, sizeof(double) * 4 * Nm));
+    CU(up(e->tag_t[0].p, tag_t, sizeof(double) * 3 * Nm));
+    CU(cudaStreamSynchronize(e->stream));   // host staging vectors go out of scope
+    e->have_problem = true;
+    return VMM_BA_OK;
+}
+
+int vmm_ba_set_poses(vmm_ba_handle e, const double* cam_q, const double* cam_t, const double* tag_q, const double* tag_t) {
+    if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
+    if (!e->have_problem) return fail_with(e, VMM_BA_ERR_STATE, "set_problem has not been called");
+    if ((e->Nc > 0 && (!cam_q || !cam_t)) || !tag_q || !tag_t) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null array");
+    CU(cudaSetDevice(e->device));
+    const int s = e->cur;
+    if (e->Ncl > 0) {
+        CU(cudaMemcpyAsync(e->cam_q[s].p, cam_q + 4 * e->cam0, sizeof(double) * 4 * e->Ncl, cudaMemcpyHostToDevice, e->stream));
+        CU(cudaMemcpyAsync(e->cam_t[s].p, cam_t + 3 * e->cam0, sizeof(double) * 3 * e->Ncl, cudaMemcpyHostToDevice, e->stream));
+    }
+    CU(cudaMemcpyAsync(e->tag_q[s].p, tag_q, sizeof(double) * 4 * e->Nm, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(e->tag_t[s].p, tag_t, sizeof(double) * 3 * e->Nm, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return VMM_BA_OK;
+}
+
+// gather a camera-sharded array (per-camera `width` doubles) into a full host array
+static int gather_cameras(vmm_ba_engine* e, const double* local_dev, int width, double* host_out) {
+    if (e->world == 1) {
+        if (e->Ncl > 0) CU(cudaMemcpyAsync(host_out, local_dev, sizeof(double) * width * e->Ncl, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        return VMM_BA_OK;
+    }
+    const size_t n = (size_t)width * e->Nc;
+    if (e->gather.n < n) CU(e->gather.alloc(n));
+    CU(cudaMemsetAsync(e->gather.p, 0, sizeof(double) * n, e->stream));
+    if (e->Ncl > 0)
+        CU(cudaMemcpyAsync(e->gather.p + (size_t)width * e->cam0, local_dev, sizeof(double) * width * e->Ncl, cudaMemcpyDeviceToDevice, e->stream));
+    int rc = allreduce(e, e->gather.p, n, NCCL_SUM);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(host_out, e->gather.p, sizeof(double) * n, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return VMM_BA_OK;
+}
+
+int vmm_ba_get_poses(vmm_ba_handle e, double* cam_q, double* cam_t, double* tag_q, double* tag_t) {
+    if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
+    if (!e->have_problem) return fail_with(e, VMM_BA_ERR_STATE, "set_problem has not been called");
+    CU(cudaSetDevice(e->device));
+    const int s = e->cur;
+    int rc;
+    if (cam_q && e->Nc > 0) { rc = gather_cameras(e, e->cam_q[s].p, 4, cam_q); if (rc) return rc; }
+    if (cam_t && e->Nc > 0) { rc = gather_cameras(e, e->cam_t[s].p, 3, cam_t); if (rc) return rc; }
+    if (tag_q) CU(cudaMemcpyAsync(tag_q, e->tag_q[s].p, sizeof(double) * 4 * e->Nm, cudaMemcpyDeviceToHost, e->stream));
+    if (tag_t) CU(cudaMemcpyAsync(tag_t, e->tag_t[s].p, sizeof(double) * 3 * e->Nm, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return VMM_BA_OK;
+}
+
+int vmm_ba_solve(vmm_ba_handle e, const vmm_ba_options* options, vmm_ba_summary* summary) {
+    if (!e || !options || !summary) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null argument");
+    if (!e->have_problem || !e->have_intrinsics) return fail_with(e, VMM_BA_ERR_STATE, "set_intrinsics and set_problem must be called before solve");
+    if (options->loss_kind < 0 || options->loss_kind > 2 || !(options->loss_scale > 0)) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "bad loss");
+    CU(cudaSetDevice(e->device));
+    return do_solve(e, options, summary);
+}
+
+int vmm_ba_evaluate(vmm_ba_handle e, int loss_kind, double loss_scale, double* cost, double* residuals, double* jacobians, double* gradient) {
+    if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
+    if (!e->have_problem || !e->have_intrinsics) return fail_with(e, VMM_BA_ERR_STATE, "set_intrinsics and set_problem must be called before evaluate");
+    if (loss_kind < 0 || loss_kind > 2 || !(loss_scale > 0)) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "bad loss");
+    CU(cudaSetDevice(e->device));
+    int rc = ensure_rj_buffers(e);
+    if (rc) return rc;
+    prepare_poses(e, e->cur);
+    const int64_t nobs = 4 * e->Ntol;
+    rc = launch_rj(e, loss_kind, loss_scale, true);
+    if (rc) return rc;
+    CU(cudaMemsetAsync(e->st.p, 0, sizeof(double) * 8, e->stream));
+    if (nobs > 0) LAUNCH(k_sum_partials, 1, 256, nblocks(nobs, kThreads), e->rj_partials.p, e->st.p + ST_COST);
+    rc = allreduce(e, e->st.p + ST_COST, 1, NCCL_SUM);
+    if (rc) return rc;
+    rc = read_stats(e);
+    if (rc) return rc;
+    if (cost) *cost = e->h_st[ST_COST];
+    if ((residuals || jacobians) && nobs > 0) {
+        std::vector<double> hr, hj;
+        if (residuals) { hr.resize(2 * nobs); CU(cudaMemcpy(hr.data(), e->res_dev.p, sizeof(double) * 2 * nobs, cudaMemcpyDeviceToHost)); }
+        if (jacobians) { hj.resize(24 * nobs); CU(cudaMemcpy(hj.data(), e->jac_dev.p, sizeof(double) * 24 * nobs, cudaMemcpyDeviceToHost)); }
+        // component-major device layout -> caller's order, row-major per corner
+        for (int64_t s = 0; s < e->Ntol; ++s) {
+            const int64_t k = e->perm_c[e->to0 + s];
+            for (int c = 0; c < 4; ++c) {
+                const int64_t src = 4 * s + c, dst = 4 * k + c;
+                if (residuals) { residuals[2 * dst] = hr[src]; residuals[2 * dst + 1] = hr[nobs + src]; }
+                if (jacobians) for (int el = 0; el < 24; ++el) jacobians[24 * dst + el] = hj[(size_t)el * nobs + src];
+            }
+        }
+    }
+    if (gradient) {
+        rc = linearize(e, e->cur, loss_kind, loss_scale);
+        if (rc) return rc;
+        if (e->Nc > 0) { rc = gather_cameras(e, e->gc.p, 6, gradient); if (rc) return rc; }
+        CU(cudaMemcpyAsync(gradient + 6 * e->Nc, e->gm(), sizeof(double) * 6 * e->Nm, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+    }
+    return VMM_BA_OK;
+}
+
+int vmm_ba_evaluate_device(vmm_ba_handle e, int loss_kind, double loss_scale, int iterations, double* ms_per_launch) {
+    if (!e || iterations < 1) return VMM_BA_ERR_INVALID_ARGUMENT;
+    if (!e->have_problem || !e->have_intrinsics) return fail_with(e, VMM_BA_ERR_STATE, "set_intrinsics and set_problem must be called first");
+    CU(cudaSetDevice(e->device));
+    int rc = ensure_rj_buffers(e);
+    if (rc) return rc;
+    prepare_poses(e, e->cur);
+    CU(cudaEventRecord(e->ev[5], e->stream));
+    for (int i = 0; i < iterations; ++i) launch_rj(e, loss_kind, loss_scale, false);
+    CU(cudaEventRecord(e->ev[6], e->stream));
+    CU(cudaEventSynchronize(e->ev[6]));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, e->ev[5], e->ev[6]));
+    if (ms_per_launch) *ms_per_launch = (double)ms / iterations;
+    return VMM_BA_OK;
+}
+
+int vmm_ba_reprojection_error_sums(vmm_ba_handle e, double* out) {
+    if (!e || !out) return VMM_BA_ERR_INVALID_ARGUMENT;
+    if (!e->have_problem || !e->have_intrinsics) return fail_with(e, VMM_BA_ERR_STATE, "set_intrinsics and set_problem must be called first");
+    CU(cudaSetDevice(e->device));
+    const int s = e->cur;
+    if (e->Ntol > 0) {
+        LAUNCH(k_reprojection_sums, nblocks(e->Ntol, kThreads), kThreads, e->intr, (int)e->Ntol, e->uv.p, e->ocam.p, e->otag.p,
+               e->cam_q[s].p, e->cam_t[s].p, e->tag_q[s].p, e->tag_t[s].p, e->tag_wh.p, e->sums_dev.p);
+        std::vector<double> h(e->Ntol);
+        CU(cudaMemcpyAsync(h.data(), e->sums_dev.p, sizeof(double) * e->Ntol, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        for (int64_t i = 0; i < e->Ntol; ++i) out[e->perm_c[e->to0 + i]] = h[i];
+    }
+    return VMM_BA_OK;
+}
+
+int vmm_ba_shard_info(vmm_ba_handle e, int64_t* cam_begin, int64_t* cam_end, int64_t* ntol) {
+    if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
+    if (!e->have_problem) return fail_with(e, VMM_BA_ERR_STATE, "set_problem has not been called");
+    if (cam_begin) *cam_begin = e->cam0;
+    if (cam_end) *cam_end = e->cam1;
+    if (ntol) *ntol = e->Ntol;
+    return VMM_BA_OK;
+}
+
+int64_t vmm_ba_kernel_launches(vmm_ba_handle e) { return e ? e->launches : 0; }
+
+int vmm_ba_measure_fp64_peak(vmm_ba_handle e, double* tflops) {
+    if (!e || !tflops) return VMM_BA_ERR_INVALID_ARGUMENT;
+    CU(cudaSetDevice(e->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, e->device));
+    const int iters = 1 << 14;
+    const int grid = prop.multiProcessorCount * 8;
+    DevBuf<double> out;
+    CU(out.alloc(1));
+    LAUNCH(k_dfma_peak, grid, 256, 256, 1.0, out.p);   // warm-up
+    CU(cudaEventRecord(e->ev[5], e->stream));
+    LAUNCH(k_dfma_peak, grid, 256, iters, 1.0, out.p);
+    CU(cudaEventRecord(e->ev[6], e->stream));
+    CU(cudaEventSynchronize(e->ev[6]));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, e->ev[5], e->ev[6]));
+    const double flops = 2.0 * 8.0 * (double)iters * 256.0 * grid;
+    *tflops = flops / (ms * 1e-3) / 1e12;
+    return VMM_BA_OK;
+}
+
+int vmm_ba_measure_copy_bandwidth(vmm_ba_handle e, size_t bytes, double* gbps) {
+    if (!e || !gbps || bytes < 1024) return VMM_BA_ERR_INVALID_ARGUMENT;
+    CU(cudaSetDevice(e->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, e->device));
+    const size_t n16 = bytes / 16;
+    DevBuf<double2> a, b;
+    CU(a.alloc(n16));
+    CU(b.alloc(n16));
+    CU(cudaMemsetAsync(a.p, 0, n16 * 16, e->stream));
+    const int grid = prop.multiProcessorCount * 16;
+    float best = 1e30f;
+    for (int rep = 0; rep < 6; ++rep) {
+        CU(cudaEventRecord(e->ev[5], e->stream));
+        LAUNCH(k_copy16, grid, 256, n16, a.p, b.p);
+        CU(cudaEventRecord(e->ev[6], e->stream));
+        CU(cudaEventSynchronize(e->ev[6]));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, e->ev[5], e->ev[6]));
+        if (rep > 0) best = std::min(best, ms);
+    }
+    *gbps = 2.0 * (double)n16 * 16.0 / (best * 1e-3) / 1e9;
+    return VMM_BA_OK;
+}
+
+}  // extern "C"
