@@ -198,6 +198,14 @@ int vmm_ba_partition_cameras(int64_t num_cameras, int64_t num_tag_obs, const int
 /* Number of kernel launches issued by this library on this handle since creation. */
 int64_t vmm_ba_kernel_launches(vmm_ba_handle h);
 
+/* Per-kernel device time: when enabled every kernel this library launches on the handle is bracketed
+ * by a CUDA-event pair on the launching stream.  enable(…) also clears the counters.  Kernel indices
+ * run over [0, vmm_ba_profile_num_kernels()); a kernel appears once it has been launched. */
+int vmm_ba_profile_enable(vmm_ba_handle h, int on);
+int vmm_ba_profile_num_kernels(void);
+const char* vmm_ba_profile_kernel_name(int index);
+int vmm_ba_profile_get(vmm_ba_handle h, int index, int64_t* launches, double* total_ms);
+
 /* Measured DFMA throughput of the device (TFLOP/s, 2 flops per FMA) — the FP64 roofline denominator. */
 int vmm_ba_measure_fp64_peak(vmm_ba_handle h, double* tflops);
 

@@ -96,6 +96,14 @@ struct vmm_ba_engine {
 
     cudaEvent_t ev[8] = { nullptr };
 
+    // per-kernel profiling
+    struct ProfPending { int kid; cudaEvent_t a, b; };
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_free;
+    std::vector<ProfPending> prof_pending;
+    std::vector<double> prof_ms;
+    std::vector<int64_t> prof_n;
+
     double* Ct() { return lin_m.p; }
     double* gm() { return lin_m.p + 21 * Nm; }
     double* lin_tail() { return lin_m.p + 27 * Nm; }
@@ -103,6 +111,61 @@ struct vmm_ba_engine {
 };
 
 namespace {
+
+// ---- per-kernel profiling (CUDA events on the launching stream) --------------------------------
+struct KernelRegistry {
+    std::vector<std::string> names;
+};
+KernelRegistry& registry() {
+    static KernelRegistry r;
+    return r;
+}
+int register_kernel(const char* name) {
+    auto& r = registry();
+    std::string n(name);
+    const size_t lt = n.find('<');   // k_block_matvec<true> keeps its template argument
+    (void)lt;
+    for (size_t i = 0; i < r.names.size(); ++i)
+        if (r.names[i] == n) return (int)i;
+    r.names.push_back(n);
+    return (int)r.names.size() - 1;
+}
+cudaEvent_t profile_event(vmm_ba_engine* e) {
+    if (!e->prof_free.empty()) {
+        cudaEvent_t ev = e->prof_free.back();
+        e->prof_free.pop_back();
+        return ev;
+    }
+    cudaEvent_t ev = nullptr;
+    cudaEventCreate(&ev);
+    return ev;
+}
+cudaEvent_t profile_begin(vmm_ba_engine* e) {
+    cudaEvent_t a = profile_event(e);
+    cudaEventRecord(a, e->stream);
+    return a;
+}
+void profile_end(vmm_ba_engine* e, int kid, cudaEvent_t a) {
+    cudaEvent_t b = profile_event(e);
+    cudaEventRecord(b, e->stream);
+    e->prof_pending.push_back({ kid, a, b });
+}
+// call only after the stream has been synchronised
+void profile_resolve(vmm_ba_engine* e) {
+    for (auto& p : e->prof_pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+            if ((size_t)p.kid >= e->prof_ms.size()) { e->prof_ms.resize(p.kid + 1, 0.0); e->prof_n.resize(p.kid + 1, 0); }
+            e->prof_ms[p.kid] += ms;
+            e->prof_n[p.kid] += 1;
+        } else {
+            cudaGetLastError();
+        }
+        e->prof_free.push_back(p.a);
+        e->prof_free.push_back(p.b);
+    }
+    e->prof_pending.clear();
+}
 
 int fail_with(vmm_ba_engine* e, int code, const char* fmt, ...) {
     char buf[512];
@@ -122,10 +185,16 @@ int fail_with(vmm_ba_engine* e, int code, const char* fmt, ...) {
                              __LINE__);                                                                           \
     } while (0)
 
-#define LAUNCH(kernel, grid, block, ...)                        \
-    do {                                                        \
-        kernel<<<(grid), (block), 0, e->stream>>>(__VA_ARGS__); \
-        ++e->launches;                                          \
+// Every kernel launch goes through here: counts it and, when profiling is on, brackets it with a
+// CUDA-event pair on the engine's stream (resolved at the next host synchronisation).
+#define LAUNCH(kernel, grid, block, ...)                                   \
+    do {                                                                   \
+        static const int _kid = register_kernel(#kernel);                  \
+        cudaEvent_t _eb = nullptr;                                         \
+        if (e->profiling) _eb = profile_begin(e);                          \
+        kernel<<<(grid), (block), 0, e->stream>>>(__VA_ARGS__);            \
+        if (_eb) profile_end(e, _kid, _eb);                                \
+        ++e->launches;                                                     \
     } while (0)
 
 int nccl_check(vmm_ba_engine* e, int rc, const char* what) {
@@ -208,6 +277,7 @@ int read_stats(vmm_ba_engine* e) {
     CU(cudaMemcpyAsync(e->h_st, e->st.p, sizeof(double) * ST_N, cudaMemcpyDeviceToHost, e->stream));
     CU(cudaMemcpyAsync(e->h_fail, e->fail.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
+    if (e->profiling) profile_resolve(e);
     return VMM_BA_OK;
 }
 
@@ -608,6 +678,8 @@ int vmm_ba_destroy(vmm_ba_handle e) {
     cudaDeviceSynchronize();
     if (e->comm) nccl_api().CommDestroy(e->comm);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
+    for (auto& p : e->prof_pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto& ev : e->prof_free) cudaEventDestroy(ev);
     if (e->h_st) cudaFreeHost(e->h_st);
     if (e->h_fail) cudaFreeHost(e->h_fail);
     if (e->own_stream) cudaStreamDestroy(e->own_stream);
@@ -894,6 +966,37 @@ int vmm_ba_shard_info(vmm_ba_handle e, int64_t* cam_begin, int64_t* cam_end, int
 }
 
 int64_t vmm_ba_kernel_launches(vmm_ba_handle e) { return e ? e->launches : 0; }
+
+int vmm_ba_profile_enable(vmm_ba_handle e, int on) {
+    if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
+    CU(cudaSetDevice(e->device));
+    CU(cudaStreamSynchronize(e->stream));
+    profile_resolve(e);
+    e->profiling = on != 0;
+    std::fill(e->prof_ms.begin(), e->prof_ms.end(), 0.0);
+    std::fill(e->prof_n.begin(), e->prof_n.end(), 0);
+    return VMM_BA_OK;
+}
+
+int vmm_ba_profile_num_kernels(void) { return (int)registry().names.size(); }
+
+const char* vmm_ba_profile_kernel_name(int index) {
+    auto& r = registry();
+    return (index >= 0 && (size_t)index < r.names.size()) ? r.names[index].c_str() : "";
+}
+
+int vmm_ba_profile_get(vmm_ba_handle e, int index, int64_t* launches, double* total_ms) {
+    if (!e || index < 0) return VMM_BA_ERR_INVALID_ARGUMENT;
+    CU(cudaSetDevice(e->device));
+    if (!e->prof_pending.empty()) {
+        CU(cudaStreamSynchronize(e->stream));
+        profile_resolve(e);
+    }
+    const bool have = (size_t)index < e->prof_ms.size();
+    if (launches) *launches = have ? e->prof_n[index] : 0;
+    if (total_ms) *total_ms = have ? e->prof_ms[index] : 0.0;
+    return VMM_BA_OK;
+}
 
 int vmm_ba_measure_fp64_peak(vmm_ba_handle e, double* tflops) {
     if (!e || !tflops) return VMM_BA_ERR_INVALID_ARGUMENT;

@@ -27,6 +27,7 @@ ABI_SYMBOLS = [
     "vmm_ba_get_poses", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
     "vmm_ba_reprojection_error_sums", "vmm_ba_shard_info", "vmm_ba_partition_cameras",
     "vmm_ba_kernel_launches", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
+    "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
 ]
 
 
@@ -129,6 +130,10 @@ def load_library():
     lib.vmm_ba_measure_fp64_peak.argtypes = [C.c_void_p, dp]
     lib.vmm_ba_measure_copy_bandwidth.argtypes = [C.c_void_p, C.c_size_t, dp]
     lib.vmm_ba_nccl_unique_id.argtypes = [C.c_void_p, C.c_size_t]
+    lib.vmm_ba_profile_enable.argtypes = [C.c_void_p, C.c_int]
+    lib.vmm_ba_profile_kernel_name.restype = C.c_char_p
+    lib.vmm_ba_profile_kernel_name.argtypes = [C.c_int]
+    lib.vmm_ba_profile_get.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), dp]
     _lib = lib
     return lib
 
@@ -284,6 +289,20 @@ class BundleAdjuster:
 
     def kernel_launches(self) -> int:
         return int(self._lib.vmm_ba_kernel_launches(self._h))
+
+    def profile_enable(self, on: bool = True):
+        """Bracket every kernel launch with CUDA events on the launching stream (clears the counters)."""
+        self._check(self._lib.vmm_ba_profile_enable(self._h, 1 if on else 0))
+
+    def profile(self) -> dict:
+        """{kernel name: (launches, total device ms)} since profile_enable()."""
+        out = {}
+        for i in range(self._lib.vmm_ba_profile_num_kernels()):
+            n, ms = C.c_int64(0), C.c_double(0)
+            self._check(self._lib.vmm_ba_profile_get(self._h, i, C.byref(n), C.byref(ms)))
+            if n.value:
+                out[self._lib.vmm_ba_profile_kernel_name(i).decode()] = (n.value, ms.value)
+        return out
 
     def measure_fp64_peak(self) -> float:
         v = C.c_double(0)
