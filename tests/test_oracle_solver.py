@@ -1,0 +1,124 @@
+"""Properties of the CPU oracle's Ceres-semantics LM (oracle/vmm_oracle.cpp) that
+do not need Ceres to check: convergence to ground truth on zero-noise scenes, invariances, the loss
+limits, the analytic/dual-number Jacobian against central differences through Plus."""
+import numpy as np
+import pytest
+
+from visual_marker_mapping_b200 import synth
+
+
+def small_scene(**kw):
+    args = dict(n_markers=10, n_cameras=24, markers_per_camera=8, seed=42)
+    args.update(kw)
+    return synth.make_scene(**args)
+
+
+def test_zero_noise_returns_to_ground_truth(oracle):
+    s = small_scene(noise_px=0.0, float32_round=False)
+    assert oracle.evaluate(s.at_ground_truth()).cost < 1e-12
+    r = oracle.solve(s, max_num_iterations=100, function_tolerance=1e-16, parameter_tolerance=1e-14)
+    assert r.summary.final_cost < 1e-14
+    obs = np.unique(s.to_tag)
+    assert np.abs(r.tag_t - s.tag_t_gt)[obs].max() < 1e-8
+    assert np.abs(r.cam_t - s.cam_t_gt).max() < 1e-8
+    assert synth.quat_angle(r.cam_q, s.cam_q_gt).max() < 1e-8
+    # the origin tag is constant (src/TagReconstructor.cpp:669-673)
+    assert np.array_equal(r.tag_q[0], s.tag_q[0]) and np.array_equal(r.tag_t[0], s.tag_t[0])
+
+
+def test_default_options_are_the_ceres_defaults(oracle):
+    o = oracle.default_options()
+    assert (o.function_tolerance, o.gradient_tolerance, o.parameter_tolerance) == (1e-6, 1e-10, 1e-8)
+    assert o.initial_trust_region_radius == 1e4 and o.min_relative_decrease == 1e-3 and o.jacobi_scaling == 1
+
+
+def test_trace_is_monotone_and_terminates_by_function_tolerance(oracle, scene_c1):
+    r = oracle.solve(scene_c1, max_num_iterations=50, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+    assert r.summary.termination_type == 0 and b"tolerance" in r.summary.message
+    costs = r.trace[r.trace[:, 5] == 1, 0]
+    assert np.all(np.diff(costs) < 0)
+    assert r.summary.final_cost == costs[-1]
+    assert r.summary.num_iterations == r.summary.num_successful_steps + r.summary.num_unsuccessful_steps + 1 or \
+        r.summary.num_iterations == r.summary.num_successful_steps + r.summary.num_unsuccessful_steps + 2
+
+
+def test_huber_with_huge_scale_is_no_loss(oracle, scene_c1):
+    a = oracle.solve(scene_c1, max_num_iterations=30)
+    b = oracle.solve(scene_c1, max_num_iterations=30, loss_kind=oracle.LOSS_HUBER, loss_scale=1e9)
+    assert abs(a.summary.final_cost - b.summary.final_cost) <= 1e-12 * a.summary.final_cost
+    assert np.abs(a.cam_t - b.cam_t).max() < 1e-12
+
+
+def test_observation_order_does_not_matter(oracle, scene_c1):
+    s = scene_c1.copy()
+    perm = np.random.default_rng(1).permutation(s.n_tag_obs)
+    s.to_cam, s.to_tag, s.to_uv = s.to_cam[perm].copy(), s.to_tag[perm].copy(), s.to_uv[perm].copy()
+    a = oracle.solve(scene_c1, max_num_iterations=30, loss_kind=oracle.LOSS_HUBER)
+    b = oracle.solve(s, max_num_iterations=30, loss_kind=oracle.LOSS_HUBER)
+    assert abs(a.summary.final_cost - b.summary.final_cost) <= 1e-9 * a.summary.final_cost
+    assert np.abs(a.tag_t - b.tag_t).max() < 1e-8
+
+
+def test_quaternion_scale_invariance(oracle, scene_c1):
+    """QuaternionRotatePoint normalises: cost and local Jacobian do not depend on |q|."""
+    s = scene_c1.copy()
+    s.cam_q = s.cam_q * 1.7
+    s.tag_q = s.tag_q * 0.4
+    a, b = oracle.evaluate(scene_c1), oracle.evaluate(s)
+    assert abs(a.cost - b.cost) <= 1e-12 * a.cost
+    # local Jacobian of a scaled quaternion: Plus keeps |q|, tangent columns scale with nothing
+    assert np.abs(a.jac_local[:, :, :3] - b.jac_local[:, :, :3]).max() <= 1e-9 * np.abs(a.jac_local).max()
+
+
+@pytest.mark.parametrize("loss,scale", [(0, 1.0), (1, 1.0), (2, 3.0)])
+def test_gradient_matches_central_differences_through_plus(oracle, loss, scale):
+    s = small_scene(n_markers=6, n_cameras=8, markers_per_camera=5, outlier_frac=0.2)
+    ev = oracle.evaluate(s, loss, scale)
+    n = 6 * (s.n_cameras + s.n_markers)
+    rng = np.random.default_rng(3)
+    for idx in rng.choice(n, 25, replace=False):
+        blk = idx // 6
+        if blk >= s.n_cameras and blk - s.n_cameras == s.fixed_tag:
+            continue
+        h = 1e-6
+        d = np.zeros(n)
+        d[idx] = h
+        sp, sm = s.copy(), s.copy()
+        sp.cam_q, sp.cam_t, sp.tag_q, sp.tag_t = oracle.plus(s, d)
+        sm.cam_q, sm.cam_t, sm.tag_q, sm.tag_t = oracle.plus(s, -d)
+        fd = (oracle.evaluate(sp, loss, scale).cost - oracle.evaluate(sm, loss, scale).cost) / (2 * h)
+        assert abs(fd - ev.gradient[idx]) <= 2e-5 * max(abs(ev.gradient[idx]), 1.0), (idx, fd, ev.gradient[idx])
+
+
+def test_fixed_tag_and_unobserved_blocks_have_zero_gradient(oracle):
+    s = small_scene()
+    keep = s.to_tag != 3
+    s.to_cam, s.to_tag, s.to_uv = s.to_cam[keep].copy(), s.to_tag[keep].copy(), s.to_uv[keep].copy()
+    g = oracle.evaluate(s).gradient.reshape(-1, 6)
+    assert not g[s.n_cameras + 0].any() and not g[s.n_cameras + 3].any()
+    r = oracle.solve(s, max_num_iterations=20)
+    assert np.array_equal(r.tag_t[3], s.tag_t[3]) and np.array_equal(r.tag_q[3], s.tag_q[3])
+
+
+def test_reprojection_error_sums_follow_cameramodel_quirk(oracle):
+    """CameraModel::projectPoint reuses the distorted x in the y formula (src/CameraModel.cpp:20-23):
+    the statistic differs slightly from the functor's residual norm, and matches a numpy restatement."""
+    s = small_scene()
+    sums = oracle.reprojection_error_sums(s)
+    fx, fy, cx, cy, k1, k2, p1, p2, k3 = s.intr
+    Rm = synth.quat_to_rot(s.tag_q)[s.to_tag]
+    Rc = synth.quat_to_rot(s.cam_q)[s.to_cam]
+    ref = np.zeros(s.n_tag_obs)
+    for c in range(4):
+        p = np.zeros((s.n_tag_obs, 3))
+        p[:, 0] = synth.CORNER_SIGNS[c, 0] * s.tag_wh[s.to_tag, 0] / 2
+        p[:, 1] = synth.CORNER_SIGNS[c, 1] * s.tag_wh[s.to_tag, 1] / 2
+        pw = np.einsum("nij,nj->ni", Rm, p) + s.tag_t[s.to_tag]
+        pc = np.einsum("nij,nj->ni", Rc, pw) + s.cam_t[s.to_cam]
+        x, y = pc[:, 0] / pc[:, 2], pc[:, 1] / pc[:, 2]
+        r2 = x * x + y * y
+        rad = 1 + r2 * (k1 + r2 * (k2 + r2 * k3))
+        xd = x * rad + 2 * p1 * x * y + p2 * (r2 + 2 * x * x)
+        yd = y * rad + 2 * p2 * xd * y + p1 * (r2 + 2 * y * y)      # quirk: distorted x
+        ref += np.hypot(fx * xd + cx - s.to_uv[:, 2 * c], fy * yd + cy - s.to_uv[:, 2 * c + 1])
+    assert np.abs(sums - ref).max() < 1e-9

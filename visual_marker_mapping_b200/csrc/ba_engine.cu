@@ -17,6 +17,7 @@
 
 #include "../../include/vmm_ba.h"
 #include "ba_kernels.cuh"
+#include "ba_schur.cuh"
 #include "nccl_dyn.h"
 
 using namespace vmm;
@@ -70,15 +71,16 @@ struct vmm_ba_engine {
     bool perm_identity = true;
     int64_t n_active_cams_local = 0;
 
-    // observations
-    DevBuf<double2> uv;
-    DevBuf<int> ocam, otag, pos_m, mo_cam, mo_tag;
+    // observations: camera order (uv AoS, ocam, otag) and marker order (uvm corner planes, mo_cam, CSR mptr)
+    DevBuf<double2> uv, uvm, Et;
+    size_t uv_stride = 0;
+    DevBuf<int> ocam, otag, mo_cam, mptr;
     DevBuf<unsigned char> cam_active, tag_active;
     // poses: current and candidate (pointer-swapped on acceptance)
     DevBuf<double> cam_q[2], cam_t[2], tag_q[2], tag_t[2], camP[2], mkP[2], tag_wh;
     int cur = 0;
     // linearisation
-    DevBuf<double> Ec, Em, Bt, gc, B, C, lin_m /* Ct(21Nm) | gm(6Nm) | tail(8) */;
+    DevBuf<double> Bt, gc, B, C, lin_m /* Ct(21Nm) | gm(6Nm) | tail(8) */;
     DevBuf<double> hdiag_c, hdiag_m, scale_c, scale_m, lmd_c, lmd_m, lam_c, lam_m;
     DevBuf<double> Cinv, Minv, Sd;
     // PCG
@@ -247,10 +249,11 @@ int linearize(vmm_ba_engine* e, int slot, int loss_kind, double loss_a) {
     CU(cudaMemsetAsync(e->lin_m.p, 0, sizeof(double) * (27 * e->Nm + 8), e->stream));
     CU(cudaMemsetAsync(e->st.p, 0, sizeof(double) * 8, e->stream));
     if (e->Ntol > 0) {
-        LAUNCH(k_linearize, e->n_lin_blocks, 128, e->intr, (int)e->Ntol, e->uv.p, e->ocam.p, e->otag.p, e->pos_m.p,
-               e->tag_active.p, e->camP[slot].p, e->mkP[slot].p, loss_kind, loss_a, e->Ec.p, e->Em.p, e->Bt.p, e->gc.p,
-               e->Ct(), e->gm(), e->partials.p);
+        LAUNCH(k_linearize_cameras, e->n_lin_blocks, 128, e->intr, (int)e->Ntol, e->uv.p, e->ocam.p, e->otag.p, e->camP[slot].p,
+               e->mkP[slot].p, loss_kind, loss_a, e->Bt.p, e->gc.p, e->partials.p);
         LAUNCH(k_sum_partials, 1, 256, e->n_lin_blocks, e->partials.p, e->lin_tail());
+        LAUNCH(k_linearize_markers, (int)e->Nm, kLinThreads, e->intr, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->uvm.p,
+               e->uv_stride, e->camP[slot].p, e->mkP[slot].p, loss_kind, loss_a, e->Et.p, e->Ct(), e->gm());
     }
     if (e->Ncl > 0) {
         LAUNCH(k_expand_blocks, nblocks(e->Ncl, 128), 128, (int)e->Ncl, e->Bt.p, e->B.p, e->hdiag_c.p);
@@ -281,72 +284,81 @@ int read_stats(vmm_ba_engine* e) {
     return VMM_BA_OK;
 }
 
-// out (camera space) += sign * E * vin (marker space)
-void matvec_cam(vmm_ba_engine* e, const double* vin_m, double sign, double* out_c) {
+// out (camera space) += sign * E * mvec (marker space)
+void schur_scatter(vmm_ba_engine* e, double* mvec, double sign, double* out_c, const double* done) {
     if (e->Ntol > 0)
-        LAUNCH(k_block_matvec<false>, nblocks(e->Ntol, kThreads), kThreads, (int)e->Ntol, e->Ec.p, e->ocam.p, e->otag.p,
-               vin_m, sign, out_c);
+        LAUNCH(k_schur_product<SP_SCATTER>, (int)e->Nm, kSpThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->Et.p, e->Cinv.p,
+               (const double*)nullptr, mvec, sign, out_c, (double*)nullptr, done, (double*)nullptr, (double*)nullptr,
+               (double*)nullptr);
 }
-// out (marker space) += sign * E^T * vin (camera space)
-void matvec_mark(vmm_ba_engine* e, const double* vin_c, double sign, double* out_m) {
-    if (e->Ntol > 0)
-        LAUNCH(k_block_matvec<true>, nblocks(e->Ntol, kThreads), kThreads, (int)e->Ntol, e->Em.p, e->mo_tag.p, e->mo_cam.p,
-               vin_c, sign, out_m);
+// mvec (marker space) = E^T * vin (camera space), this rank's observations only
+void schur_gather(vmm_ba_engine* e, const double* vin_c, double* mvec, const double* done) {
+    LAUNCH(k_schur_product<SP_GATHER>, (int)e->Nm, kSpThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->Et.p, e->Cinv.p, vin_c,
+           mvec, 1.0, (double*)nullptr, (double*)nullptr, done, (double*)nullptr, (double*)nullptr, (double*)nullptr);
 }
 
 struct PcgResult { int iterations; bool ok; double rel; };
 
 // Solve (B_l - E C_l^-1 E^T) x = r0 (r0 in e->pr on entry). x -> e->px, final residual in e->pr.
+// The stopping test runs on the device (k_pcg_direction raises sc[SC_DONE], which turns every later
+// PCG launch into a no-op); the host only looks every `check_every` iterations.
 int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* out) {
     const int nc = (int)e->Ncl;
+    const int nm = (int)e->Nm;
     const int gb = nblocks(std::max<int64_t>(nc, 1), kThreads);
-    CU(cudaMemsetAsync(e->sc.p, 0, sizeof(double) * 8, e->stream));
+    const int check_every = 8;
+    double* done = e->sc.p + SC_DONE;
+    CU(cudaMemsetAsync(e->sc.p, 0, sizeof(double) * SC_N, e->stream));
     CU(cudaMemsetAsync(e->pbp(), 0, sizeof(double) * 2, e->stream));
     LAUNCH(k_pcg_init, gb, kThreads, nc, e->Minv.p, e->B.p, e->lam_c.p, e->pr.p, e->px.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p,
            e->pbp());
     if (e->world > 1) {
-        // rz0 (sc[0], sc[4]) are local partials
-        int rc = allreduce(e, e->sc.p, 5, NCCL_SUM);
+        int rc = allreduce(e, e->sc.p, 5, NCCL_SUM);   // rz0 (sc[0], sc[4]) are local partials
         if (rc) return rc;
     }
-    double rz0 = 0.0;
     out->iterations = 0;
     out->ok = true;
     out->rel = 1.0;
-    const int check_every = 1;
+    const double tol2 = tol * tol;
     for (int it = 0; it < max_it; ++it) {
         const int s = it & 1, o = s ^ 1;
-        // w = E^T p  (+ pbp partial rides in the tail in distributed mode)
-        CU(cudaMemsetAsync(e->w.p, 0, sizeof(double) * 6 * e->Nm, e->stream));
-        matvec_mark(e, e->pp.p, 1.0, e->w.p);
-        if (e->world > 1) {
-            int rc = allreduce(e, e->w.p, 6 * e->Nm + 2, NCCL_SUM);
+        if (e->world == 1) {
+            // q -= E Cinv E^T p in one pass over the E blocks; wz[s] += w.z ; recycle slot o
+            LAUNCH(k_schur_product<SP_FULL>, nm, kSpThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->Et.p, e->Cinv.p,
+                   (const double*)e->pp.p, (double*)nullptr, -1.0, e->pq.p, e->sc.p + SC_WZ + s, (const double*)done,
+                   e->sc.p + SC_RZ + o, e->sc.p + SC_WZ + o, e->pbp() + o);
+        } else {
+            // w = E^T p per rank, summed over ranks together with the local p.(B+lam)p partials in its tail
+            schur_gather(e, e->pp.p, e->w.p, done);
+            int rc = allreduce(e, e->w.p, 6 * (size_t)nm + 2, NCCL_SUM);
             if (rc) return rc;
+            LAUNCH(k_marker_solve, nblocks(nm, kThreads), kThreads, nm, e->Cinv.p, e->w.p, (const double*)nullptr, 1.0, e->zm.p,
+                   e->sc.p + SC_WZ + s, e->sc.p + SC_RZ + o, e->sc.p + SC_WZ + o, e->pbp() + o, (const double*)done);
+            schur_scatter(e, e->zm.p, -1.0, e->pq.p, done);
         }
-        // zm = Cinv w ; wz[s] += w.zm ; recycle slot o
-        LAUNCH(k_marker_solve, nblocks(e->Nm, kThreads), kThreads, (int)e->Nm, e->Cinv.p, e->w.p, (const double*)nullptr, 1.0,
-               e->zm.p, e->sc.p + 2 + s, e->sc.p + o, e->sc.p + 2 + o, e->pbp() + o);
-        // q -= E zm   (q holds (B+lam) p)
-        matvec_cam(e, e->zm.p, -1.0, e->pq.p);
         LAUNCH(k_pcg_update, gb, kThreads, nc, s, e->Minv.p, e->pp.p, e->pq.p, e->px.p, e->pr.p, e->pz.p, e->sc.p, e->pbp());
         if (e->world > 1) {
-            int rc = allreduce(e, e->sc.p + o, 1, NCCL_SUM);
+            int rc = allreduce(e, e->sc.p + SC_RZ + o, 1, NCCL_SUM);
             if (rc) return rc;
         }
+        LAUNCH(k_pcg_direction, gb, kThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, e->pbp(), it + 1,
+               min_it, tol2);
         out->iterations = it + 1;
-        bool stop = false;
         if ((it + 1) % check_every == 0 || it + 1 == max_it) {
-            CU(cudaMemcpyAsync(e->h_st + ST_SC, e->sc.p, sizeof(double) * 8, cudaMemcpyDeviceToHost, e->stream));
+            CU(cudaMemcpyAsync(e->h_st + ST_SC, e->sc.p, sizeof(double) * SC_N, cudaMemcpyDeviceToHost, e->stream));
             CU(cudaStreamSynchronize(e->stream));
-            rz0 = e->h_st[ST_SC + 4];
-            const double rz = e->h_st[ST_SC + o];
-            if (!std::isfinite(rz) || !std::isfinite(rz0)) { out->ok = false; return VMM_BA_OK; }
-            if (rz0 <= 0.0) { out->rel = 0.0; return VMM_BA_OK; }
-            out->rel = std::sqrt(std::max(rz, 0.0) / rz0);
-            if (it + 1 >= min_it && out->rel <= tol) stop = true;
+            if (e->profiling) profile_resolve(e);
+            const double* h = e->h_st + ST_SC;
+            if (!std::isfinite(h[SC_REL2]) || !std::isfinite(h[SC_RZ0]) || !std::isfinite(h[SC_RZ]) || !std::isfinite(h[SC_RZ + 1])) {
+                out->ok = false;
+                return VMM_BA_OK;
+            }
+            out->rel = std::sqrt(std::max(h[SC_REL2], 0.0));
+            if (h[SC_DONE] != 0.0) {
+                out->iterations = (int)h[SC_ITERS];
+                break;
+            }
         }
-        if (stop) break;
-        LAUNCH(k_pcg_direction, gb, kThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, e->pbp());
     }
     return VMM_BA_OK;
 }
@@ -419,7 +431,7 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
             if (opt->preconditioner == VMM_BA_PRECOND_SCHUR_JACOBI) {
                 LAUNCH(k_schur_diag_init, nblocks((int64_t)nc * 36, kThreads), kThreads, nc, e->B.p, e->lam_c.p, e->Sd.p);
                 if (e->Ntol > 0)
-                    LAUNCH(k_schur_diag, nblocks(e->Ntol, 128), 128, (int)e->Ntol, e->ocam.p, e->otag.p, e->Ec.p, e->Cinv.p, e->Sd.p);
+                    LAUNCH(k_schur_diag, nm, kSpThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->Et.p, e->Cinv.p, e->Sd.p);
                 LAUNCH(k_mirror_blocks, nblocks(nc, 128), 128, nc, e->Sd.p);
                 LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->Sd.p, (const double*)nullptr, e->cam_active.p, e->Minv.p, e->fail.p);
             } else {
@@ -428,9 +440,9 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         }
         // rhs: r = -gc + E Cinv gm
         LAUNCH(k_marker_solve, nblocks(nm, kThreads), kThreads, nm, e->Cinv.p, e->gm(), (const double*)nullptr, 1.0, e->zm.p,
-               (double*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr);
+               (double*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr, (const double*)nullptr);
         if (nc > 0) LAUNCH(k_negate, gc_b, kThreads, 6 * nc, e->gc.p, e->pr.p);
-        matvec_cam(e, e->zm.p, 1.0, e->pr.p);
+        schur_scatter(e, e->zm.p, 1.0, e->pr.p, nullptr);
         PcgResult pr{};
         const double tol = opt->parity_mode ? opt->pcg_parity_tolerance : opt->pcg_tolerance;
         const int max_it = opt->parity_mode ? opt->pcg_parity_max_iterations : opt->pcg_max_iterations;
@@ -438,12 +450,11 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         if (rc) return rc;
         sum->pcg_iterations += pr.iterations;
         // back-substitution: dm = -Cinv (gm + E^T dc)
-        CU(cudaMemsetAsync(e->w.p, 0, sizeof(double) * (6 * nm + 2), e->stream));
-        matvec_mark(e, e->px.p, 1.0, e->w.p);
+        schur_gather(e, e->px.p, e->w.p, nullptr);
         rc = allreduce(e, e->w.p, 6 * (size_t)nm, NCCL_SUM);
         if (rc) return rc;
         LAUNCH(k_marker_solve, nblocks(nm, kThreads), kThreads, nm, e->Cinv.p, e->w.p, (const double*)e->gm(), -1.0, e->dm.p,
-               (double*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr);
+               (double*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr, (const double*)nullptr);
         CU(cudaEventRecord(e->ev[3], e->stream));
 
         // ---- candidate point and its cost ----
@@ -755,25 +766,26 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     e->Ntol = cam_ptr[e->cam1] - e->to0;
     const int64_t Ncl = e->Ncl, Ntol = e->Ntol;
 
-    // host staging of the local shard
+    // host staging of the local shard: camera order ...
     std::vector<double2> h_uv((size_t)4 * Ntol);
-    std::vector<int> h_ocam(Ntol), h_otag(Ntol), h_posm(Ntol), h_mocam(Ntol), h_motag(Ntol);
+    std::vector<int> h_ocam(Ntol), h_otag(Ntol), h_mocam(Ntol), h_mptr(Nm + 1, 0);
     for (int64_t s = 0; s < Ntol; ++s) {
         const int64_t k = e->perm_c[e->to0 + s];
         h_ocam[s] = (int)(to_cam[k] - e->cam0);
         h_otag[s] = to_tag[k];
         for (int c = 0; c < 4; ++c) h_uv[4 * s + c] = make_double2(to_uv[8 * k + 2 * c], to_uv[8 * k + 2 * c + 1]);
     }
-    // marker order of the local tag observations (stable counting sort by marker)
+    // ... and marker order (stable counting sort by marker; corners as four planes of stride uv_stride)
+    const size_t uv_stride = ((size_t)std::max<int64_t>(Ntol, 1) + 31) / 32 * 32;
+    std::vector<double2> h_uvm(4 * uv_stride, make_double2(0.0, 0.0));
     {
-        std::vector<int64_t> mptr(Nm + 1, 0);
-        for (int64_t s = 0; s < Ntol; ++s) mptr[h_otag[s] + 1]++;
-        for (int64_t j = 0; j < Nm; ++j) mptr[j + 1] += mptr[j];
+        for (int64_t s = 0; s < Ntol; ++s) h_mptr[h_otag[s] + 1]++;
+        for (int64_t j = 0; j < Nm; ++j) h_mptr[j + 1] += h_mptr[j];
+        std::vector<int> fill(h_mptr.begin(), h_mptr.end() - 1);
         for (int64_t s = 0; s < Ntol; ++s) {
-            const int64_t pos = mptr[h_otag[s]]++;
-            h_posm[s] = (int)pos;
+            const int pos = fill[h_otag[s]]++;
             h_mocam[pos] = h_ocam[s];
-            h_motag[pos] = h_otag[s];
+            for (int c = 0; c < 4; ++c) h_uvm[c * uv_stride + pos] = h_uv[4 * s + c];
         }
     }
     std::vector<unsigned char> h_cact(std::max<int64_t>(Ncl, 1), 0), h_tact(Nm, 0);
@@ -783,14 +795,16 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
 
     const size_t ncl1 = (size_t)std::max<int64_t>(Ncl, 1), nto1 = (size_t)std::max<int64_t>(Ntol, 1);
     CU(e->uv.alloc(4 * nto1));
-    CU(e->ocam.alloc(nto1)); CU(e->otag.alloc(nto1)); CU(e->pos_m.alloc(nto1)); CU(e->mo_cam.alloc(nto1)); CU(e->mo_tag.alloc(nto1));
+    CU(e->ocam.alloc(nto1)); CU(e->otag.alloc(nto1)); CU(e->mo_cam.alloc(nto1)); CU(e->mptr.alloc(Nm + 1));
+    CU(e->uvm.alloc(4 * uv_stride));
+    e->uv_stride = uv_stride;
+    CU(e->Et.alloc((size_t)18 * uv_stride));
     CU(e->cam_active.alloc(ncl1)); CU(e->tag_active.alloc(Nm));
     for (int s = 0; s < 2; ++s) {
         CU(e->cam_q[s].alloc(4 * ncl1)); CU(e->cam_t[s].alloc(3 * ncl1)); CU(e->tag_q[s].alloc(4 * Nm)); CU(e->tag_t[s].alloc(3 * Nm));
         CU(e->camP[s].alloc(CAM_PREP * ncl1)); CU(e->mkP[s].alloc((size_t)MARK_PREP * Nm));
     }
     CU(e->tag_wh.alloc(2 * Nm));
-    CU(e->Ec.alloc(36 * nto1)); CU(e->Em.alloc(36 * nto1));
     CU(e->Bt.alloc(21 * ncl1)); CU(e->gc.alloc(6 * ncl1)); CU(e->B.alloc(36 * ncl1)); CU(e->C.alloc((size_t)36 * Nm));
     CU(e->lin_m.alloc((size_t)27 * Nm + 8));
     CU(e->hdiag_c.alloc(6 * ncl1)); CU(e->scale_c.alloc(6 * ncl1)); CU(e->lmd_c.alloc(6 * ncl1)); CU(e->lam_c.alloc(6 * ncl1));
@@ -808,9 +822,9 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(up(e->uv.p, h_uv.data(), sizeof(double2) * 4 * Ntol));
     CU(up(e->ocam.p, h_ocam.data(), sizeof(int) * Ntol));
     CU(up(e->otag.p, h_otag.data(), sizeof(int) * Ntol));
-    CU(up(e->pos_m.p, h_posm.data(), sizeof(int) * Ntol));
     CU(up(e->mo_cam.p, h_mocam.data(), sizeof(int) * Ntol));
-    CU(up(e->mo_tag.p, h_motag.data(), sizeof(int) * Ntol));
+    CU(up(e->mptr.p, h_mptr.data(), sizeof(int) * (Nm + 1)));
+    CU(up(e->uvm.p, h_uvm.data(), sizeof(double2) * 4 * uv_stride));
     CU(up(e->cam_active.p, h_cact.data(), Ncl));
     CU(up(e->tag_active.p, h_tact.data(), Nm));
     CU(up(e->tag_wh.p, tag_wh, sizeof(double) * 2 * Nm));

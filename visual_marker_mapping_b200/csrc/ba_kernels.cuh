@@ -194,100 +194,7 @@ __global__ void k_sum_partials(int n, const double* __restrict__ partials, doubl
     if (threadIdx.x == 0) out[0] = s;
 }
 
-// ------------------------------------------------------------------------------------------
-// Fused linearisation (Schur builder): per tag observation, the four corners' residuals and
-// Jacobians stay in registers and are contracted straight into
-//   E_k = Jc^T Jm (written twice: camera order and marker order),
-//   B_i += Jc^T Jc, gc_i += Jc^T r   (warp-segmented reduction, observations sorted by camera),
-//   C_j += Jm^T Jm, gm_j += Jm^T r   (atomics; marker-sorted segmented pass is k_linearize_markers),
-// and the robust cost.  Only the upper triangles of B and C are accumulated (21 values).
-// ------------------------------------------------------------------------------------------
 __device__ __forceinline__ int tri_index(int a, int b) { return a * 6 - a * (a - 1) / 2 + (b - a); }   // a <= b
-
-__global__ void __launch_bounds__(128)
-k_linearize(Intrinsics in, int nto, const double2* __restrict__ uv, const int* __restrict__ ocam,
-            const int* __restrict__ otag, const int* __restrict__ pos_m, const unsigned char* __restrict__ tag_active,
-            const double* __restrict__ camP, const double* __restrict__ mkP, int loss_kind, double loss_a,
-            double* __restrict__ Ec, double* __restrict__ Em, double* __restrict__ Bt, double* __restrict__ gc,
-            double* __restrict__ Ct, double* __restrict__ gm, double* __restrict__ cost_partials) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool valid = k < nto;
-    double cost = 0.0;
-    double E[36];
-    double Bv[27];   // 21 upper-triangular + 6 gradient
-    double Cv[27];
-#pragma unroll
-    for (int i = 0; i < 36; ++i) E[i] = 0.0;
-#pragma unroll
-    for (int i = 0; i < 27; ++i) { Bv[i] = 0.0; Cv[i] = 0.0; }
-    int ci = -1, mi = 0;
-    bool mact = false;
-    if (valid) {
-        ci = __ldg(ocam + k);
-        mi = __ldg(otag + k);
-        mact = tag_active[mi] != 0;
-        double cam[12], mk[12];
-        load12(camP + (size_t)ci * CAM_PREP, cam);
-        load12(mkP + (size_t)mi * MARK_PREP, mk);
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-            const double2 o = __ldcs(uv + 4 * (size_t)k + c);
-            double r[2], J[24];
-            cost += corner_full(in, cam, mk, c, o.x, o.y, loss_kind, loss_a, r, J);
-#pragma unroll
-            for (int row = 0; row < 2; ++row) {
-                const double* Jc = J + row * 12;
-                const double* Jm = J + row * 12 + 6;
-#pragma unroll
-                for (int a = 0; a < 6; ++a) {
-#pragma unroll
-                    for (int b = 0; b < 6; ++b) E[a * 6 + b] += Jc[a] * Jm[b];
-                }
-                int t = 0;
-#pragma unroll
-                for (int a = 0; a < 6; ++a) {
-#pragma unroll
-                    for (int b = a; b < 6; ++b) { Bv[t] += Jc[a] * Jc[b]; Cv[t] += Jm[a] * Jm[b]; ++t; }
-                }
-#pragma unroll
-                for (int a = 0; a < 6; ++a) { Bv[21 + a] += Jc[a] * r[row]; Cv[21 + a] += Jm[a] * r[row]; }
-            }
-        }
-        if (!mact) {
-#pragma unroll
-            for (int i = 0; i < 36; ++i) E[i] = 0.0;   // constant / unobserved marker: no columns
-        }
-        double2* e1 = reinterpret_cast<double2*>(Ec + (size_t)k * 36);
-        double2* e2 = reinterpret_cast<double2*>(Em + (size_t)__ldg(pos_m + k) * 36);
-#pragma unroll
-        for (int i = 0; i < 18; ++i) {
-            const double2 v = make_double2(E[2 * i], E[2 * i + 1]);
-            e1[i] = v;
-            e2[i] = v;
-        }
-        if (mact) {
-            double* co = Ct + (size_t)mi * 21;
-#pragma unroll
-            for (int i = 0; i < 21; ++i) atomicAdd(co + i, Cv[i]);
-            double* go = gm + (size_t)mi * 6;
-#pragma unroll
-            for (int i = 0; i < 6; ++i) atomicAdd(go + i, Cv[21 + i]);
-        }
-    }
-    // camera side: segmented by camera (sorted) -> few atomics
-    {
-        double Bh[21];
-#pragma unroll
-        for (int i = 0; i < 21; ++i) Bh[i] = Bv[i];
-        warp_segmented_add<21>(Bh, ci, Bt, 21);
-        double gh[6];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) gh[i] = Bv[21 + i];
-        warp_segmented_add<6>(gh, ci, gc, 6);
-    }
-    const double s = block_sum(cost);
-    if (threadIdx.x == 0) cost_partials[blockIdx.x] = s;
-}
 
 // Expand packed upper triangles (21) into full symmetric 6x6 blocks (36) and extract the diagonal.
 __global__ void k_expand_blocks(int n, const double* __restrict__ tri, double* __restrict__ full,
@@ -356,132 +263,13 @@ __global__ void k_invert_blocks(int n, const double* __restrict__ A, const doubl
     for (int k = 0; k < 36; ++k) out[(size_t)i * 36 + k] = M[k];
 }
 
-// Sd_i = B_i + diag(lam_c)  (start of the Schur-Jacobi diagonal)
-__global__ void k_schur_diag_init(int n, const double* __restrict__ B, const double* __restrict__ lam,
-                                  double* __restrict__ Sd) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n * 36) return;
-    const int blk = i / 36, e = i % 36;
-    const int a = e / 6, b = e % 6;
-    Sd[i] = B[i] + ((a == b) ? lam[(size_t)blk * 6 + a] : 0.0);
-}
-// Sd_i -= sum_k E_k Cinv_{m(k)} E_k^T   (upper triangle accumulated, mirrored by k_mirror_blocks)
-__global__ void __launch_bounds__(128)
-k_schur_diag(int nto, const int* __restrict__ ocam, const int* __restrict__ otag, const double* __restrict__ Ec,
-             const double* __restrict__ Cinv, double* __restrict__ Sd) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    int ci = -1;
-    double T[21];
-#pragma unroll
-    for (int i = 0; i < 21; ++i) T[i] = 0.0;
-    if (k < nto) {
-        ci = __ldg(ocam + k);
-        const int mi = __ldg(otag + k);
-        double E[36];
-        const double2* e2 = reinterpret_cast<const double2*>(Ec + (size_t)k * 36);
-#pragma unroll
-        for (int i = 0; i < 18; ++i) { const double2 v = __ldcs(e2 + i); E[2 * i] = v.x; E[2 * i + 1] = v.y; }
-        const double* Ci = Cinv + (size_t)mi * 36;
-        // W = E Cinv (row a), T[a][b] = W[a] . E[b]
-#pragma unroll
-        for (int a = 0; a < 6; ++a) {
-            double W[6];
-#pragma unroll
-            for (int j = 0; j < 6; ++j) {
-                double s = 0.0;
-#pragma unroll
-                for (int l = 0; l < 6; ++l) s += E[a * 6 + l] * __ldg(Ci + l * 6 + j);
-                W[j] = s;
-            }
-#pragma unroll
-            for (int b = a; b < 6; ++b) {
-                double s = 0.0;
-#pragma unroll
-                for (int j = 0; j < 6; ++j) s += W[j] * E[b * 6 + j];
-                T[tri_index(a, b)] = -s;
-            }
-        }
-    }
-    // scatter as upper-triangle entries of the full 6x6 block
-    // (segmented by camera; the stride-36 destination uses explicit positions)
-    const int lane = threadIdx.x & 31;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int kup = __shfl_up_sync(0xffffffffu, ci, d);
-        const bool take = (lane >= d) && (kup == ci);
-#pragma unroll
-        for (int i = 0; i < 21; ++i) {
-            const double up = shfl_up_d(T[i], d);
-            if (take) T[i] += up;
-        }
-    }
-    const int knext = __shfl_down_sync(0xffffffffu, ci, 1);
-    const bool tail = (lane == 31) || (knext != ci);
-    if (tail && ci >= 0) {
-        double* o = Sd + (size_t)ci * 36;
-        int idx = 0;
-#pragma unroll
-        for (int a = 0; a < 6; ++a)
-#pragma unroll
-            for (int b = a; b < 6; ++b) atomicAdd(o + a * 6 + b, T[idx++]);
-    }
-}
-__global__ void k_mirror_blocks(int n, double* __restrict__ M) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    double* f = M + (size_t)i * 36;
-    for (int a = 0; a < 6; ++a)
-        for (int b = a + 1; b < 6; ++b) f[b * 6 + a] = f[a * 6 + b];
-}
-
-// ------------------------------------------------------------------------------------------
-// Block-sparse products with the E blocks (the PCG hot loop).
-//   TRANSPOSE = false, camera order :  out[cam(k)] += sign * E_k   * vin[tag(k)]
-//   TRANSPOSE = true,  marker order :  out[tag(k)] += sign * E_k^T * vin[cam(k)]
-// key_out is sorted (segmented reduction), idx_in gathers the 6-vector.  One thread per block.
-// ------------------------------------------------------------------------------------------
-template <bool TRANSPOSE>
-__global__ void __launch_bounds__(kThreads)
-k_block_matvec(int nto, const double* __restrict__ E, const int* __restrict__ key_out, const int* __restrict__ idx_in,
-               const double* __restrict__ vin, double sign, double* __restrict__ out) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    int key = -1;
-    double y[6] = { 0, 0, 0, 0, 0, 0 };
-    if (k < nto) {
-        key = __ldg(key_out + k);
-        const int in_idx = __ldg(idx_in + k);
-        double x[6];
-        const double2* x2 = reinterpret_cast<const double2*>(vin + (size_t)in_idx * 6);
-#pragma unroll
-        for (int i = 0; i < 3; ++i) { const double2 v = __ldg(x2 + i); x[2 * i] = v.x; x[2 * i + 1] = v.y; }
-        const double2* e2 = reinterpret_cast<const double2*>(E + (size_t)k * 36);
-#pragma unroll
-        for (int a = 0; a < 6; ++a) {
-            double row[6];
-#pragma unroll
-            for (int i = 0; i < 3; ++i) { const double2 v = __ldcs(e2 + a * 3 + i); row[2 * i] = v.x; row[2 * i + 1] = v.y; }
-            if (TRANSPOSE) {
-#pragma unroll
-                for (int b = 0; b < 6; ++b) y[b] += row[b] * x[a];
-            } else {
-                double s = 0.0;
-#pragma unroll
-                for (int b = 0; b < 6; ++b) s += row[b] * x[b];
-                y[a] = s;
-            }
-        }
-#pragma unroll
-        for (int a = 0; a < 6; ++a) y[a] *= sign;
-    }
-    warp_segmented_add<6>(y, key, out, 6);
-}
-
 // zm = Cinv w (per marker), optional dot accumulation  acc += w . zm ; optionally negates input
 // and adds an offset vector first:  zm = Cinv (alpha * (w + add)).
 __global__ void __launch_bounds__(kThreads)
 k_marker_solve(int nm, const double* __restrict__ Cinv, const double* __restrict__ w, const double* __restrict__ add,
                double alpha, double* __restrict__ zm, double* __restrict__ dot_acc, double* z0, double* z1,
-               double* z2) {
+               double* z2, const double* __restrict__ done) {
+    if (done && *done != 0.0) return;
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (blockIdx.x == 0 && threadIdx.x == 0) {   // recycle the other parity's PCG accumulators
         if (z0) *z0 = 0.0;
@@ -511,7 +299,10 @@ k_marker_solve(int nm, const double* __restrict__ Cinv, const double* __restrict
 
 // PCG scalars, device resident. Slot parity s = iteration & 1.
 //   sc[0+s] rz = r.M^-1 r   sc[2+s] wz = w.Cinv w   sc[4] rz0      pbp[s] = p.(B+lam)p
+//   sc[5] done flag (set on device when rz <= tol^2 rz0; every later PCG launch is then a no-op)
+//   sc[6] iterations performed when the flag was set      sc[7] last rz / rz0
 // (pbp lives at the tail of the marker-space vector w so that one all-reduce carries both).
+enum { SC_RZ = 0, SC_WZ = 2, SC_RZ0 = 4, SC_DONE = 5, SC_ITERS = 6, SC_REL2 = 7, SC_N = 8 };
 
 // r = b (already in r), x = 0, z = Minv r, p = z, q = (B + lam) p, rz[0] = r.z, pBp[0] = p.q
 __global__ void __launch_bounds__(kThreads)
@@ -556,10 +347,11 @@ __global__ void __launch_bounds__(kThreads)
 k_pcg_update(int nc, int s, const double* __restrict__ Minv, const double* __restrict__ p,
              const double* __restrict__ q, double* __restrict__ x, double* __restrict__ r, double* __restrict__ z,
              double* __restrict__ sc, const double* __restrict__ pbp) {
+    if (sc[SC_DONE] != 0.0) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int o = s ^ 1;
     const double denom = pbp[s] - sc[2 + s];
-    const double alpha = sc[0 + s] / denom;
+    const double alpha = (sc[0 + s] != 0.0) ? sc[0 + s] / denom : 0.0;
     double rz = 0.0;
     if (i < nc) {
         double rv[6];
@@ -588,10 +380,22 @@ k_pcg_update(int nc, int s, const double* __restrict__ Minv, const double* __res
 __global__ void __launch_bounds__(kThreads)
 k_pcg_direction(int nc, int s, const double* __restrict__ B, const double* __restrict__ lam,
                 const double* __restrict__ z, double* __restrict__ p, double* __restrict__ q,
-                const double* __restrict__ sc, double* __restrict__ pbp) {
+                double* __restrict__ sc, double* __restrict__ pbp, int iters_done, int min_iters, double tol2) {
+    if (sc[SC_DONE] != 0.0) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int o = s ^ 1;
-    const double beta = sc[0 + o] / sc[0 + s];
+    // device-side stopping test: every block evaluates the same predicate on the same (complete) sums
+    const double rz_new = sc[0 + o], rz0 = sc[SC_RZ0];
+    const bool stop = (iters_done >= min_iters) && (rz_new <= tol2 * rz0);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        sc[SC_REL2] = (rz0 > 0.0) ? rz_new / rz0 : 0.0;
+        if (stop) sc[SC_ITERS] = (double)iters_done;
+    }
+    if (stop) {   // blocks that start after the flag is up leave at the top: same effect
+        if (blockIdx.x == 0 && threadIdx.x == 0) sc[SC_DONE] = 1.0;
+        return;
+    }
+    const double beta = (sc[0 + s] != 0.0) ? rz_new / sc[0 + s] : 0.0;
     double pq = 0.0;
     if (i < nc) {
         double pv[6];
@@ -615,7 +419,7 @@ k_pcg_direction(int nc, int s, const double* __restrict__ B, const double* __res
     if (threadIdx.x == 0) atomicAdd(pbp + o, s1);
 }
 
-// r = -gc (right-hand side start); the E Cinv gm term is added by k_block_matvec
+// r = -gc (right-hand side start); the E Cinv gm term is added by k_schur_product<SP_SCATTER>
 __global__ void k_negate(int n, const double* __restrict__ a, double* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = -a[i];

@@ -178,6 +178,36 @@ VMM_HD double corner_full(const Intrinsics& in, const double* cam, const double*
     return 0.5 * rho0;
 }
 
+// Camera-side half of corner_full: corrected residual and the six camera columns (t_c, delta_c) of
+// both rows, Jc[row*6 + k].  Same arithmetic, the marker columns are simply not formed.
+VMM_HD double corner_camera_side(const Intrinsics& in, const double* cam, const double* mk, int c, double u, double v,
+                                 int loss_kind, double loss_a, double r[2], double Jc[12]) {
+    CornerGeom g;
+    corner_geometry(in, cam, mk, c, u, v, g);
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+    for (int row = 0; row < 2; ++row) {
+        const double* j = g.JX + 3 * row;
+        double* o = Jc + 6 * row;
+        o[0] = j[0]; o[1] = j[1]; o[2] = j[2];
+        o[3] = 2.0 * (g.vc[1] * j[2] - g.vc[2] * j[1]);
+        o[4] = 2.0 * (g.vc[2] * j[0] - g.vc[0] * j[2]);
+        o[5] = 2.0 * (g.vc[0] * j[1] - g.vc[1] * j[0]);
+    }
+    const double s = g.r[0] * g.r[0] + g.r[1] * g.r[1];
+    double rho0 = s, rho1 = 1.0;
+    if (loss_kind != LOSS_NONE) {
+        loss_eval(loss_kind, loss_a, s, &rho0, &rho1);
+        const double w = sqrt(rho1);
+        r[0] = w * g.r[0]; r[1] = w * g.r[1];
+        for (int k = 0; k < 12; ++k) Jc[k] *= w;
+    } else {
+        r[0] = g.r[0]; r[1] = g.r[1];
+    }
+    return 0.5 * rho0;
+}
+
 VMM_HD double corner_cost(const Intrinsics& in, const double* cam, const double* mk, int c, double u, double v,
                           int loss_kind, double loss_a) {
     double r[2];

@@ -21,7 +21,7 @@ from typing import Optional
 
 import numpy as np
 
-GENERATOR_VERSION = "vmm-synth-1"
+GENERATOR_VERSION = "vmm-synth-2"
 
 # README.md:132-145 — fx, fy, cx, cy, k1, k2, p1, p2, k3
 README_INTRINSICS = np.array(
@@ -258,6 +258,12 @@ def make_scene(
     jit = max(0.0, 0.5 * (cell - 0.20))
     mx = (gx + 0.5) * cell + rng.uniform(-jit, jit, n_markers)
     my = (gy + 0.5) * cell + rng.uniform(-jit, jit, n_markers)
+    # the origin tag (index 0, fixed at the identity pose) must be one the cameras actually see — the
+    # reference picks it from the start image (src/TagReconstructor.cpp:115-141) — otherwise the gauge
+    # is free: take the marker nearest the centre of the sheet.
+    centre = int(np.argmin((mx - 0.5 * L) ** 2 + (my - 0.5 * L) ** 2))
+    for arr in (mx, my):
+        arr[0], arr[centre] = arr[centre], arr[0]
     mz = relief * np.sin(mx * 1.3) * np.cos(my * 0.9) + rng.uniform(-0.05, 0.05, n_markers)
     tag_t = np.stack([mx, my, mz], axis=1)
     tilt = np.deg2rad(marker_tilt_deg) * np.sqrt(rng.uniform(0, 1, n_markers))
