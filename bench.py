@@ -216,8 +216,8 @@ def run_b200(args):
 
     scene = synth.make_config(args.workload)
     ba = pkg.BundleAdjuster(device=local_rank, rank=rank, world_size=world, nccl_id=nccl_id)
-    stream = torch.cuda.current_stream()
-    ba.set_stream(stream.cuda_stream)          # torch.cuda.Event only sees torch's current stream
+    stream = torch.cuda.Stream()               # torch.cuda.Event only sees the stream it is recorded on:
+    ba.set_stream(stream.cuda_stream)          # run the engine on a torch stream and record on that one
     ba.set_scene(scene)
     opts = dict(loss_kind=pkg.LOSS_HUBER, loss_scale=1.0)
     init = (scene.cam_q, scene.cam_t, scene.tag_q, scene.tag_t)

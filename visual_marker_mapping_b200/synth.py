@@ -21,7 +21,7 @@ from typing import Optional
 
 import numpy as np
 
-GENERATOR_VERSION = "vmm-synth-2"
+GENERATOR_VERSION = "vmm-synth-3"
 
 # README.md:132-145 — fx, fy, cx, cy, k1, k2, p1, p2, k3
 README_INTRINSICS = np.array(
@@ -370,21 +370,27 @@ def make_scene(
         to_uv = to_uv.astype(np.float32).astype(np.float64)
 
     # initial guess = ground truth perturbed (stands in for the PnP initialisation)
-    def perturb(q, t, fixed=None):
+    def perturb(q, t, fixed=None, about_centre=False):
         n = q.shape[0]
         rv = rng.normal(0.0, np.deg2rad(rot_sigma_deg), (n, 3))
         dt = rng.normal(0.0, trans_sigma, (n, 3))
         if fixed is not None:
             rv[fixed] = 0.0
             dt[fixed] = 0.0
-        Rn = rotvec_to_rot(rv) @ quat_to_rot(q)
+        R = quat_to_rot(q)
+        Rn = rotvec_to_rot(rv) @ R
         qn = rot_to_quat(Rn)
         if fixed is not None:
             qn[fixed] = q[fixed]
+        if about_centre:
+            # world->camera pose: rotate about the camera centre C = -R^T t and move the centre by dt,
+            # which is what a PnP initialisation gets wrong (not a rotation about the far world origin)
+            C = -np.einsum("nji,nj->ni", R, t)
+            return qn, -np.einsum("nij,nj->ni", Rn, C + dt)
         return qn, t + dt
 
     if rot_sigma_deg > 0 or trans_sigma > 0:
-        cam_q, cam_t = perturb(cam_q_gt, cam_t_gt)
+        cam_q, cam_t = perturb(cam_q_gt, cam_t_gt, about_centre=True)
         tag_q, tag_t0 = perturb(tag_q_gt, tag_t_gt, fixed=0)
     else:
         cam_q, cam_t, tag_q, tag_t0 = cam_q_gt.copy(), cam_t_gt.copy(), tag_q_gt.copy(), tag_t_gt.copy()
