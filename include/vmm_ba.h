@@ -74,7 +74,7 @@ typedef struct {
     int max_num_consecutive_invalid_steps;/* 5     */
     int jacobi_scaling;                   /* 1     */
     /* linear solver: block-Jacobi PCG on the reduced camera system (markers eliminated) */
-    int preconditioner;                   /* vmm_ba_preconditioner, default SCHUR_JACOBI */
+    int preconditioner;                   /* vmm_ba_preconditioner, default JACOBI */
     double pcg_tolerance;                 /* stop when sqrt(r.M^-1 r / r0.M^-1 r0) <= tol; default 1e-2 */
     int pcg_max_iterations;               /* default 500 */
     int pcg_min_iterations;               /* default 1 */

@@ -1,0 +1,172 @@
+"""The C++ host side of the drop-in (visual_marker_mapping_b200/csrc/host/): TagReconstructor facade, the
+readers/writers of the three project files in the reference's boost::property_tree JSON dialect, and the
+visual_marker_mapping-compatible CLI.  CPU tests cover formats and error behaviour; the GPU test runs the
+reference's closing sequence BA(Huber) -> cull 2 px -> BA (src/TagReconstructor.cpp:271-277) through the
+CLI and compares reconstruction.json with the same sequence done by the oracle."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from visual_marker_mapping_b200 import _build, project_io, synth
+
+HOST = _build.HOST_DIR
+CLI = os.path.join(HOST, "visual_marker_mapping")
+DRIVER = os.path.join(HOST, "vmm_host_test")
+
+
+@pytest.fixture(scope="module")
+def host(lib):
+    _build.build_host()
+    assert os.path.exists(CLI) and os.path.exists(DRIVER)
+    return HOST
+
+
+def culled_scene():
+    """C1-like scene in which marker 5 is badly detected in most images: the cull step must drop it."""
+    s = synth.make_scene(n_markers=12, n_cameras=40, markers_per_camera=12, seed=0x564D4D01)
+    rng = np.random.default_rng(4)
+    idx = np.nonzero(s.to_tag == 5)[0]
+    bad = idx[rng.random(idx.size) < 0.7]
+    s.to_uv[bad] += rng.uniform(8, 20, (bad.size, 1)) * np.tile(rng.choice([-1.0, 1.0], (bad.size, 2)), (1, 4))
+    return s
+
+
+def test_roundtrip_is_byte_exact(host, tmp_path, scene_c1):
+    src, dst = tmp_path / "src", tmp_path / "dst"
+    dst.mkdir()
+    project_io.write_project(scene_c1, str(src), image_id_offset=3, tag_id_offset=100)
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert f"images 40 tags 12 observations {scene_c1.n_tag_obs} rec_tags 12 rec_cams 40" in r.stdout
+    assert (src / "marker_detections.json").read_bytes() == (dst / "marker_detections.json").read_bytes()
+    a = (src / "initial_reconstruction.json").read_text().splitlines()
+    b = (dst / "initial_reconstruction.json").read_text().splitlines()
+    assert len(a) == len(b)
+    for x, y in zip(a, b):
+        if x != y:   # only the derived world corners may differ, in the last digit
+            fx, fy = float(x.strip().strip('",')), float(y.strip().strip('",'))
+            assert abs(fx - fy) <= 4e-16 * max(abs(fx), 1.0)
+
+
+def test_dialect_literals(tmp_path, scene_c1):
+    """boost write_json: quoted leaves, 17 significant digits, 4-space indent, '/' escaped, empty array = \"\"."""
+    project_io.write_project(scene_c1, str(tmp_path))
+    text = (tmp_path / "marker_detections.json").read_text()
+    assert text.startswith('{\n    "images": [\n        {\n            "filename": "images\\/img_000000.jpg",\n            "id": "0"\n        },')
+    assert '"tag_type": "apriltag_36h11"' in text and '"width": "0.1285"' in text and '"height": "0.1295"' in text
+    assert text.endswith("}\n")
+    intr = (tmp_path / "camera_intrinsics.json").read_text()
+    assert '"fx": "8075.2937867635346"' in intr and '"horizontal_resolution": "6000"' in intr
+    assert project_io.dumps_ptree({"tag_observations": [], "tags": {}}) == '{\n    "tag_observations": "",\n    "tags": ""\n}\n'
+    json.loads(text)   # it is still JSON
+
+
+def test_reader_accepts_bare_numbers_and_empty_arrays(host, tmp_path, scene_c1):
+    src, dst = tmp_path / "src", tmp_path / "dst"
+    dst.mkdir()
+    project_io.write_project(scene_c1, str(src))
+    det = json.loads((src / "marker_detections.json").read_text())
+    det["tag_observations"] = ""
+    for t in det["tags"]:
+        t["id"], t["width"] = int(t["id"]), float(t["width"])
+    (src / "marker_detections.json").write_text(json.dumps(det))
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "tags 12 observations 0" in r.stdout
+    assert '"tag_observations": ""' in (dst / "marker_detections.json").read_text()
+
+
+def test_reader_error_messages(host, tmp_path, scene_c1):
+    src, dst = tmp_path / "src", tmp_path / "dst"
+    dst.mkdir()
+    project_io.write_project(scene_c1, str(src))
+    good = (src / "marker_detections.json").read_text()
+    det = json.loads(good)
+    det["tag_observations"][0]["observations"].pop()           # 3 corners (src/DetectionIO.cpp:50-51)
+    (src / "marker_detections.json").write_text(json.dumps(det))
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 1 and "Unexpected number of values" in r.stderr
+    (src / "marker_detections.json").write_text(good)
+    intr = json.loads((src / "camera_intrinsics.json").read_text())
+    intr["distortion_coefficients"].pop()                       # PropertyTreeUtilities.h:118-121
+    (src / "camera_intrinsics.json").write_text(json.dumps(intr))
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 1 and "Not enough many parameters in vector. Expected 5, got 4!" in r.stderr
+
+
+def test_cli_without_device_reports_and_returns_zero(host, tmp_path, scene_c1, have_gpu):
+    """No CPU fallback; like the reference's main the exception is printed and the exit code stays 0."""
+    if have_gpu:
+        pytest.skip("a CUDA device is present")
+    project_io.write_project(scene_c1, str(tmp_path))
+    r = subprocess.run([CLI, "--project_path", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0
+    assert "no CUDA device" in r.stderr and "no CPU fallback" in r.stderr
+    assert not (tmp_path / "reconstruction.json").exists()
+    r = subprocess.run([CLI], capture_output=True, text=True)
+    assert "--project_path" in r.stderr
+
+
+def oracle_closing_sequence(oracle, s):
+    """BA(Huber, 1500) -> removeBadMarkers(2) -> removeBadCameras(2) -> BA(no loss, 1500) with the oracle."""
+    o1 = oracle.solve(s, max_num_iterations=1500, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+    s1 = s.copy()
+    s1.cam_q, s1.cam_t, s1.tag_q, s1.tag_t = o1.cam_q, o1.cam_t, o1.tag_q, o1.tag_t
+    sums = oracle.reprojection_error_sums(s1)
+    tag_err = np.bincount(s1.to_tag, sums, s.n_markers) / np.maximum(4 * np.bincount(s1.to_tag, minlength=s.n_markers), 1)
+    keep_tag = ~((tag_err > 2.0) & (np.arange(s.n_markers) != s.fixed_tag))
+    ko = keep_tag[s1.to_tag]
+    cam_n = np.bincount(s1.to_cam[ko], minlength=s.n_cameras)
+    cam_err = np.where(cam_n > 0, np.bincount(s1.to_cam[ko], sums[ko], s.n_cameras) / np.maximum(4 * cam_n, 1), -1.0)
+    keep_cam = ~((cam_err > 2.0) | (cam_err < 0))
+    ko &= keep_cam[s1.to_cam]
+    tmap = np.cumsum(keep_tag) - 1
+    cmap = np.cumsum(keep_cam) - 1
+    s2 = synth.Scene(intr=s.intr, cam_q=o1.cam_q[keep_cam], cam_t=o1.cam_t[keep_cam], tag_q=o1.tag_q[keep_tag], tag_t=o1.tag_t[keep_tag],
+                     tag_wh=s.tag_wh[keep_tag], fixed_tag=int(tmap[s.fixed_tag]), to_cam=cmap[s1.to_cam[ko]].astype(np.int32),
+                     to_tag=tmap[s1.to_tag[ko]].astype(np.int32), to_uv=s1.to_uv[ko])
+    o2 = oracle.solve(s2, max_num_iterations=1500)
+    return np.nonzero(keep_tag)[0], np.nonzero(keep_cam)[0], o2
+
+
+@pytest.mark.gpu
+def test_cli_closing_sequence_matches_oracle(host, oracle, tmp_path):
+    s = culled_scene()
+    project_io.write_project(s, str(tmp_path), image_id_offset=7, tag_id_offset=20)
+    r = subprocess.run([CLI, "--project_path", str(tmp_path), "--start_tag_id", "20", "--parity", "--overwrite"], capture_output=True, text=True)
+    assert r.returncode == 0 and "Error" not in r.stderr, r.stderr
+    assert "Solution 0" in r.stdout and "Removing bad marker with id 25" in r.stdout
+    tags, cams = project_io.read_reconstruction(str(tmp_path / "reconstruction.json"))
+    keep_tag, keep_cam, o2 = oracle_closing_sequence(oracle, s)
+    assert 5 not in keep_tag
+    assert sorted(tags) == [int(t) + 20 for t in keep_tag] and sorted(cams) == [int(c) + 7 for c in keep_cam]
+    for j, t in enumerate(keep_tag):
+        assert np.abs(tags[int(t) + 20]["t"] - o2.tag_t[j]).max() < 1e-6
+        assert synth.quat_angle(tags[int(t) + 20]["q"], o2.tag_q[j]) < 1e-6
+    for i, c in enumerate(keep_cam):
+        assert np.abs(cams[int(c) + 7]["t"] - o2.cam_t[i]).max() < 1e-6
+        assert synth.quat_angle(cams[int(c) + 7]["q"], o2.cam_q[i]) < 1e-6
+    # reconstruction.json carries the derived world corners and the camera model as the reference writes them
+    root = json.loads((tmp_path / "reconstruction.json").read_text())
+    assert list(root) == ["reconstructed_tags", "reconstructed_marker_corners", "reconstructed_cameras", "camera_model"]
+    assert len(root["reconstructed_marker_corners"]) == 4 * len(keep_tag)
+
+
+@pytest.mark.gpu
+def test_facade_reprojection_statistics(host, oracle, tmp_path, scene_c1):
+    project_io.write_project(scene_c1, str(tmp_path))
+    r = subprocess.run([DRIVER, "stats", str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = json.loads(r.stdout)
+    sums = oracle.reprojection_error_sums(scene_c1)
+    n_tag = np.bincount(scene_c1.to_tag, minlength=scene_c1.n_markers)
+    per_tag = np.bincount(scene_c1.to_tag, sums, scene_c1.n_markers) / (4 * n_tag)
+    for j in range(scene_c1.n_markers):
+        assert abs(float(got["per_tag"][str(j)]) - per_tag[j]) < 1e-9 * max(per_tag[j], 1.0)
+    assert abs(float(got["avg"]) - sums.sum() / (4 * scene_c1.n_tag_obs)) < 1e-9 * float(got["avg"])
+    per_img = np.bincount(scene_c1.to_cam, sums, scene_c1.n_cameras) / (4 * np.bincount(scene_c1.to_cam, minlength=scene_c1.n_cameras))
+    for i in range(scene_c1.n_cameras):
+        assert abs(float(got["per_img"][str(i)]) - per_img[i]) < 1e-9 * max(per_img[i], 1.0)

@@ -63,6 +63,15 @@ def quat_to_rot(q: np.ndarray) -> np.ndarray:
     return R
 
 
+def quat_to_rot_raw(q: np.ndarray) -> np.ndarray:
+    """Eigen::Quaterniond::toRotationMatrix: no normalisation (computeMarkerCorners3D, TagReconstructor.h:33-43)."""
+    q = np.asarray(q, dtype=np.float64)
+    n2 = np.sum(q * q, axis=-1, keepdims=True)
+    # R_raw = I + (R_unit - I) * |q|^2  for the 2*q_i*q_j form used by Eigen
+    R = quat_to_rot(q)
+    return np.eye(3) + (R - np.eye(3)) * n2[..., None]
+
+
 def rot_to_quat(R: np.ndarray) -> np.ndarray:
     """Batch rotation matrix -> unit quaternion (w,x,y,z), w >= 0."""
     R = np.asarray(R, dtype=np.float64)
