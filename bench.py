@@ -33,10 +33,12 @@ UNIT = "LM iterations/s"
 RJ_BYTES_PER_CORNER = 226.0          # 16 uv + 2 idx + 16 r + 192 J
 # algorithmic HBM bytes per tag observation of the solver kernels
 KERNEL_BYTES_PER_TAG_OBS = {
-    "k_linearize": 64 + 8 + 4 + 2 * 288,
-    "k_block_matvec<false>": 288 + 8,
-    "k_block_matvec<true>": 288 + 8,
-    "k_schur_diag": 288 + 8,
+    "k_linearize_cameras": 64 + 8,
+    "k_linearize_markers": 64 + 4 + 288,
+    "k_schur_product<SP_FULL>": 288 + 4,
+    "k_schur_product<SP_GATHER>": 288 + 4,
+    "k_schur_product<SP_SCATTER>": 288 + 4,
+    "k_schur_diag": 288 + 4,
     "k_cost": 64 + 8,
     "k_residual_jacobian": 4 * RJ_BYTES_PER_CORNER,
 }
