@@ -35,6 +35,7 @@ RJ_BYTES_PER_CORNER = 226.0          # 16 uv + 2 idx + 16 r + 192
 KERNEL_BYTES_PER_TAG_OBS = {
     "k_linearize_cameras": 64 + 8,
     "k_linearize_markers": 64 + 4 + 288,
+    "k_scale_e": 2 * 288,
     "k_schur_product<SP_FULL>": 288 + 4,
     "k_schur_product<SP_GATHER>": 288 + 4,
     "k_schur_product<SP_SCATTER>": 288 + 4,

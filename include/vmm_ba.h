@@ -187,6 +187,14 @@ int vmm_ba_reprojection_error_sums(vmm_ba_handle h, double* per_tag_obs_sum);
 
 /* ---- introspection for tests / benchmarks -------------------------------------------------- */
 
+/* One product with the reduced camera system at the current poses (single-GPU handles only):
+ *   y = (B + diag(lambda_c)) x - E (C + diag(lambda_m))^-1 E^T x,   x, y: 6 doubles per camera,
+ * with B, C, E of the normal equations of src/TagReconstructor.cpp:699-724 under the given loss and the
+ * LM damping that vmm_ba_solve would use at trust-region radius `radius` (Jacobi scaling on).
+ * path 0: the one-pass kernel the PCG uses on one GPU; path 1: gather / marker solve / scatter (the
+ * sharded form).  The parity tests check both against the product formed from the oracle's Jacobian. */
+int vmm_ba_schur_multiply(vmm_ba_handle h, int loss_kind, double loss_scale, double radius, int path, const double* x, double* y);
+
 /* Camera range [begin,end) and tag-observation count owned by this engine. */
 int vmm_ba_shard_info(vmm_ba_handle h, int64_t* cam_begin, int64_t* cam_end, int64_t* num_local_tag_obs);
 

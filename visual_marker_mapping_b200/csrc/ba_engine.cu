@@ -72,9 +72,20 @@ struct vmm_ba_engine {
     int64_t n_active_cams_local = 0;
 
     // observations: camera order (uv AoS, ocam, otag) and marker order (uvm corner planes, mo_cam, CSR mptr)
-    DevBuf<double2> uv, uvm, Et;
+    DevBuf<double2> uv, uvm;
+    DevBuf<unsigned char> Et, Es;     // E and scaled-E streams: 8-observation tiles (ba_schur.cuh)
     size_t uv_stride = 0;
-    DevBuf<int> ocam, otag, mo_cam, mptr;
+    DevBuf<int> ocam, otag, mo_cam, mptr, mtile;
+    // segment lists of the streamed Schur product: whole markers (SP_FULL), the sub-segments of the
+    // markers too big for it, and all markers as sub-segments (SP_GATHER / SP_SCATTER)
+    struct SegList {
+        DevBuf<SpSeg> segs;
+        DevBuf<int> cta_seg;
+        DevBuf<int2> slots;   // per ring slot: first tile, number of tiles
+        int count = 0, nslots = 0;
+    };
+    SegList seg_full, seg_big, seg_all;
+    int sp_grid = 1;
     DevBuf<unsigned char> cam_active, tag_active;
     // poses: current and candidate (pointer-swapped on acceptance)
     DevBuf<double> cam_q[2], cam_t[2], tag_q[2], tag_t[2], camP[2], mkP[2], tag_wh;
@@ -82,7 +93,7 @@ struct vmm_ba_engine {
     // linearisation
     DevBuf<double> Bt, gc, B, C, lin_m /* Ct(21Nm) | gm(6Nm) | tail(8) */;
     DevBuf<double> hdiag_c, hdiag_m, scale_c, scale_m, lmd_c, lmd_m, lam_c, lam_m;
-    DevBuf<double> Cinv, Minv, Sd;
+    DevBuf<double> Linv /* inverse Cholesky factors of the damped marker blocks */, Minv, Sd;
     // PCG
     DevBuf<double> px, pr, pz, pp, pq, w /* 6Nm + 2 (pbp slots) */, zm, dm, sc;
     DevBuf<double> partials, st;
@@ -189,15 +200,16 @@ int fail_with(vmm_ba_engine* e, int code, const char* fmt, ...) {
 
 // Every kernel launch goes through here: counts it and, when profiling is on, brackets it with a
 // CUDA-event pair on the engine's stream (resolved at the next host synchronisation).
-#define LAUNCH(kernel, grid, block, ...)                                   \
+#define LAUNCH_NAMED(name, kernel, grid, block, smem, ...)                 \
     do {                                                                   \
-        static const int _kid = register_kernel(#kernel);                  \
+        static const int _kid = register_kernel(name);                     \
         cudaEvent_t _eb = nullptr;                                         \
         if (e->profiling) _eb = profile_begin(e);                          \
-        kernel<<<(grid), (block), 0, e->stream>>>(__VA_ARGS__);            \
+        kernel<<<(grid), (block), (smem), e->stream>>>(__VA_ARGS__);       \
         if (_eb) profile_end(e, _kid, _eb);                                \
         ++e->launches;                                                     \
     } while (0)
+#define LAUNCH(kernel, grid, block, ...) LAUNCH_NAMED(#kernel, kernel, grid, block, 0, __VA_ARGS__)
 
 int nccl_check(vmm_ba_engine* e, int rc, const char* what) {
     if (rc == 0) return VMM_BA_OK;
@@ -253,7 +265,7 @@ int linearize(vmm_ba_engine* e, int slot, int loss_kind, double loss_a) {
                e->mkP[slot].p, loss_kind, loss_a, e->Bt.p, e->gc.p, e->partials.p);
         LAUNCH(k_sum_partials, 1, 256, e->n_lin_blocks, e->partials.p, e->lin_tail());
         LAUNCH(k_linearize_markers, (int)e->Nm, kLinThreads, e->intr, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->uvm.p,
-               e->uv_stride, e->camP[slot].p, e->mkP[slot].p, loss_kind, loss_a, e->Et.p, e->Ct(), e->gm());
+               e->uv_stride, e->camP[slot].p, e->mkP[slot].p, loss_kind, loss_a, e->mtile.p, e->Et.p, e->Ct(), e->gm());
     }
     if (e->Ncl > 0) {
         LAUNCH(k_expand_blocks, nblocks(e->Ncl, 128), 128, (int)e->Ncl, e->Bt.p, e->B.p, e->hdiag_c.p);
@@ -284,17 +296,52 @@ int read_stats(vmm_ba_engine* e) {
     return VMM_BA_OK;
 }
 
+// One pass of the streamed Schur product over a segment list (see ba_schur.cuh).
+template <int MODE>
+void schur_launch(vmm_ba_engine* e, const vmm_ba_engine::SegList& L, const double* vin_c, double* mvec, double sign, double* out_c,
+                  double* dot_acc, const double* done, double* z0, double* z1, double* z2) {
+    constexpr const char* name = MODE == SP_FULL ? "k_schur_product<SP_FULL>" : MODE == SP_GATHER ? "k_schur_product<SP_GATHER>" : "k_schur_product<SP_SCATTER>";
+    LAUNCH_NAMED(name, k_schur_product<MODE>, e->sp_grid, kSpThreads, kSpSmemBytes, L.segs.p, L.cta_seg.p, L.count, L.slots.p, L.nslots,
+                e->Es.p, e->mo_cam.p, vin_c, mvec, sign, out_c, dot_acc, done, z0, z1, z2);
+}
 // out (camera space) += sign * E * mvec (marker space)
 void schur_scatter(vmm_ba_engine* e, double* mvec, double sign, double* out_c, const double* done) {
-    if (e->Ntol > 0)
-        LAUNCH(k_schur_product<SP_SCATTER>, (int)e->Nm, kSpThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->Et.p, e->Cinv.p,
-               (const double*)nullptr, mvec, sign, out_c, (double*)nullptr, done, (double*)nullptr, (double*)nullptr,
-               (double*)nullptr);
+    if (e->seg_all.count > 0)
+        schur_launch<SP_SCATTER>(e, e->seg_all, nullptr, mvec, sign, out_c, nullptr, done, nullptr, nullptr, nullptr);
 }
 // mvec (marker space) = E^T * vin (camera space), this rank's observations only
-void schur_gather(vmm_ba_engine* e, const double* vin_c, double* mvec, const double* done) {
-    LAUNCH(k_schur_product<SP_GATHER>, (int)e->Nm, kSpThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->Et.p, e->Cinv.p, vin_c,
-           mvec, 1.0, (double*)nullptr, (double*)nullptr, done, (double*)nullptr, (double*)nullptr, (double*)nullptr);
+int schur_gather(vmm_ba_engine* e, const double* vin_c, double* mvec, const double* done, double* z0 = nullptr, double* z1 = nullptr,
+                 double* z2 = nullptr) {
+    CU(cudaMemsetAsync(mvec, 0, sizeof(double) * 6 * e->Nm, e->stream));
+    schur_launch<SP_GATHER>(e, e->seg_all, vin_c, mvec, 1.0, nullptr, nullptr, done, z0, z1, z2);
+    return VMM_BA_OK;
+}
+
+// out -= Es Es^T v (= E Cinv E^T v) on one GPU: one pass over the scaled E blocks; dot_acc += w.w;
+// z0..z2 are zeroed (the other parity's PCG accumulators, which nobody touches during this product).
+int schur_offdiag(vmm_ba_engine* e, const double* v, double* out, double* dot_acc, const double* done, double* z0, double* z1, double* z2) {
+    const int nm = (int)e->Nm;
+#ifdef VMM_SP_TIMING
+    schur_launch<SP_FULL>(e, e->seg_full, v, e->dm.p, -1.0, out, dot_acc, done, z0, z1, z2);   // dm: phase time stamps (debug build)
+#else
+    schur_launch<SP_FULL>(e, e->seg_full, v, nullptr, -1.0, out, dot_acc, done, z0, z1, z2);
+#endif
+    if (e->seg_big.count > 0) {   // markers with more observations than one segment holds: two passes over their blocks
+        CU(cudaMemsetAsync(e->w.p, 0, sizeof(double) * 6 * nm, e->stream));
+        schur_launch<SP_GATHER>(e, e->seg_big, v, e->w.p, 1.0, nullptr, nullptr, done, nullptr, nullptr, nullptr);
+        if (dot_acc) LAUNCH(k_sum_squares, nblocks(6 * nm, kThreads), kThreads, 6 * nm, e->w.p, dot_acc, done);
+        schur_launch<SP_SCATTER>(e, e->seg_big, nullptr, e->w.p, -1.0, out, nullptr, done, nullptr, nullptr, nullptr);
+    }
+    return VMM_BA_OK;
+}
+
+// (C + L_m)^-1 = Linv^T Linv per marker, then Es = E Linv^T: once per damping value.
+int factor_and_scale(vmm_ba_engine* e) {
+    const int nm = (int)e->Nm;
+    LAUNCH(k_factor_markers, nblocks(nm, 128), 128, nm, e->C.p, e->lam_m.p, e->tag_active.p, e->Linv.p, e->fail.p);
+    if (e->Ntol > 0)
+        LAUNCH(k_scale_e, nm, kScaleThreads, e->mptr.p, e->tag_active.p, e->mtile.p, e->Linv.p, e->Et.p, e->Es.p);
+    return VMM_BA_OK;
 }
 
 struct PcgResult { int iterations; bool ok; double rel; };
@@ -323,18 +370,16 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
     for (int it = 0; it < max_it; ++it) {
         const int s = it & 1, o = s ^ 1;
         if (e->world == 1) {
-            // q -= E Cinv E^T p in one pass over the E blocks; wz[s] += w.z ; recycle slot o
-            LAUNCH(k_schur_product<SP_FULL>, nm, kSpThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->Et.p, e->Cinv.p,
-                   (const double*)e->pp.p, (double*)nullptr, -1.0, e->pq.p, e->sc.p + SC_WZ + s, (const double*)done,
-                   e->sc.p + SC_RZ + o, e->sc.p + SC_WZ + o, e->pbp() + o);
-        } else {
-            // w = E^T p per rank, summed over ranks together with the local p.(B+lam)p partials in its tail
-            schur_gather(e, e->pp.p, e->w.p, done);
-            int rc = allreduce(e, e->w.p, 6 * (size_t)nm + 2, NCCL_SUM);
+            int rc = schur_offdiag(e, e->pp.p, e->pq.p, e->sc.p + SC_WZ + s, done, e->sc.p + SC_RZ + o, e->sc.p + SC_WZ + o, e->pbp() + o);
             if (rc) return rc;
-            LAUNCH(k_marker_solve, nblocks(nm, kThreads), kThreads, nm, e->Cinv.p, e->w.p, (const double*)nullptr, 1.0, e->zm.p,
-                   e->sc.p + SC_WZ + s, e->sc.p + SC_RZ + o, e->sc.p + SC_WZ + o, e->pbp() + o, (const double*)done);
-            schur_scatter(e, e->zm.p, -1.0, e->pq.p, done);
+        } else {
+            // w = Es^T p per rank, summed over ranks together with the local p.(B+lam)p partials in its tail
+            int rc = schur_gather(e, e->pp.p, e->w.p, done, e->sc.p + SC_RZ + o, e->sc.p + SC_WZ + o, e->pbp() + o);
+            if (rc) return rc;
+            rc = allreduce(e, e->w.p, 6 * (size_t)nm + 2, NCCL_SUM);
+            if (rc) return rc;
+            LAUNCH(k_sum_squares, nblocks(6 * nm, kThreads), kThreads, 6 * nm, e->w.p, e->sc.p + SC_WZ + s, (const double*)done);
+            schur_scatter(e, e->w.p, -1.0, e->pq.p, done);
         }
         LAUNCH(k_pcg_update, gb, kThreads, nc, s, e->Minv.p, e->pp.p, e->pq.p, e->px.p, e->pr.p, e->pz.p, e->sc.p, e->pbp());
         if (e->world > 1) {
@@ -426,21 +471,21 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         reuse_diagonal = false;
         if (nc > 0) LAUNCH(k_lambda, gc_b, kThreads, 6 * nc, e->lmd_c.p, e->scale_c.p, radius, e->lam_c.p);
         LAUNCH(k_lambda, gm_b, kThreads, 6 * nm, e->lmd_m.p, e->scale_m.p, radius, e->lam_m.p);
-        LAUNCH(k_invert_blocks, nblocks(nm, 128), 128, nm, e->C.p, e->lam_m.p, e->tag_active.p, e->Cinv.p, e->fail.p);
+        rc = factor_and_scale(e);
+        if (rc) return rc;
         if (nc > 0) {
             if (opt->preconditioner == VMM_BA_PRECOND_SCHUR_JACOBI) {
                 LAUNCH(k_schur_diag_init, nblocks((int64_t)nc * 36, kThreads), kThreads, nc, e->B.p, e->lam_c.p, e->Sd.p);
                 if (e->Ntol > 0)
-                    LAUNCH(k_schur_diag, nm, kSpThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->Et.p, e->Cinv.p, e->Sd.p);
+                    LAUNCH(k_schur_diag, nm, kDiagThreads, e->mptr.p, e->tag_active.p, e->mo_cam.p, e->mtile.p, e->Es.p, e->Sd.p);
                 LAUNCH(k_mirror_blocks, nblocks(nc, 128), 128, nc, e->Sd.p);
                 LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->Sd.p, (const double*)nullptr, e->cam_active.p, e->Minv.p, e->fail.p);
             } else {
                 LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->B.p, e->lam_c.p, e->cam_active.p, e->Minv.p, e->fail.p);
             }
         }
-        // rhs: r = -gc + E Cinv gm
-        LAUNCH(k_marker_solve, nblocks(nm, kThreads), kThreads, nm, e->Cinv.p, e->gm(), (const double*)nullptr, 1.0, e->zm.p,
-               (double*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr, (const double*)nullptr);
+        // rhs: r = -gc + E Cinv gm = -gc + Es (Linv gm); zm = Linv gm is kept for the back-substitution
+        LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 0, (const double*)e->gm(), (const double*)nullptr, 1.0, e->zm.p);
         if (nc > 0) LAUNCH(k_negate, gc_b, kThreads, 6 * nc, e->gc.p, e->pr.p);
         schur_scatter(e, e->zm.p, 1.0, e->pr.p, nullptr);
         PcgResult pr{};
@@ -449,12 +494,12 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         rc = pcg_solve(e, tol, std::max(1, max_it), std::max(1, opt->pcg_min_iterations), &pr);
         if (rc) return rc;
         sum->pcg_iterations += pr.iterations;
-        // back-substitution: dm = -Cinv (gm + E^T dc)
-        schur_gather(e, e->px.p, e->w.p, nullptr);
+        // back-substitution: dm = -Cinv (gm + E^T dc) = -Linv^T (zm + Es^T dc)
+        rc = schur_gather(e, e->px.p, e->w.p, nullptr);
+        if (rc) return rc;
         rc = allreduce(e, e->w.p, 6 * (size_t)nm, NCCL_SUM);
         if (rc) return rc;
-        LAUNCH(k_marker_solve, nblocks(nm, kThreads), kThreads, nm, e->Cinv.p, e->w.p, (const double*)e->gm(), -1.0, e->dm.p,
-               (double*)nullptr, (double*)nullptr, (double*)nullptr, (double*)nullptr, (const double*)nullptr);
+        LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 1, (const double*)e->w.p, (const double*)e->zm.p, -1.0, e->dm.p);
         CU(cudaEventRecord(e->ev[3], e->stream));
 
         // ---- candidate point and its cost ----
@@ -548,6 +593,60 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
     return VMM_BA_OK;
 }
 
+// Segment lists of the streamed Schur product and their per-CTA ranges (balanced by ring slots).
+struct HostSeg { SpSeg d; int tile0; };
+
+int upload_seglist(vmm_ba_engine* e, vmm_ba_engine::SegList& L, std::vector<HostSeg>& hs) {
+    std::vector<int2> desc;
+    std::vector<SpSeg> segs(hs.size());
+    // a segment costs its slots (HBM time) plus a fixed latency chain: balance the CTAs on both
+    const int kFixed = 3;
+    std::vector<int64_t> cost(hs.size() + 1, 0);
+    for (size_t i = 0; i < hs.size(); ++i) {
+        hs[i].d.slot0 = (int)desc.size();
+        const int ntiles = (hs[i].d.nobs + kTileObs - 1) / kTileObs;
+        for (int t = 0; t < ntiles; t += kSlotTiles) desc.push_back(make_int2(hs[i].tile0 + t, std::min(kSlotTiles, ntiles - t)));
+        segs[i] = hs[i].d;
+        cost[i + 1] = cost[i] + ((int)desc.size() - hs[i].d.slot0) + kFixed;
+    }
+    L.nslots = (int)desc.size();
+    const int G = e->sp_grid;
+    std::vector<int> cta(G + 1, (int)segs.size());
+    size_t s = 0;
+    for (int c = 0; c < G; ++c) {
+        const int64_t want = cost[hs.size()] * c / G;
+        while (s < segs.size() && cost[s] < want) ++s;
+        cta[c] = (int)s;
+    }
+    L.count = (int)segs.size();
+    CU(L.segs.alloc(std::max<size_t>(segs.size(), 1)));
+    CU(L.cta_seg.alloc(G + 1));
+    CU(L.slots.alloc(std::max<size_t>(desc.size(), 1)));
+    if (!desc.empty()) CU(cudaMemcpyAsync(L.slots.p, desc.data(), sizeof(int2) * desc.size(), cudaMemcpyHostToDevice, e->stream));
+    if (!segs.empty()) CU(cudaMemcpyAsync(L.segs.p, segs.data(), sizeof(SpSeg) * segs.size(), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(L.cta_seg.p, cta.data(), sizeof(int) * (G + 1), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaStreamSynchronize(e->stream));   // host vectors go out of scope
+    return VMM_BA_OK;
+}
+
+int build_segments(vmm_ba_engine* e, const std::vector<int>& mptr, const std::vector<int>& mtile, const std::vector<unsigned char>& active) {
+    std::vector<HostSeg> full, big, all;
+    for (int64_t j = 0; j < e->Nm; ++j) {
+        const int n = mptr[j + 1] - mptr[j];
+        if (!active[j] || n == 0) continue;
+        if (n <= kSegMaxObs) full.push_back(HostSeg{ SpSeg{ (int)j, 0, n, mptr[j] }, mtile[j] });
+        for (int o = 0; o < n; o += kSegRegObs) {
+            const HostSeg d{ SpSeg{ (int)j, 0, std::min(kSegRegObs, n - o), mptr[j] + o }, mtile[j] + o / kTileObs };
+            all.push_back(d);
+            if (n > kSegMaxObs) big.push_back(d);
+        }
+    }
+    int rc = upload_seglist(e, e->seg_full, full);
+    if (!rc) rc = upload_seglist(e, e->seg_big, big);
+    if (!rc) rc = upload_seglist(e, e->seg_all, all);
+    return rc;
+}
+
 int ensure_rj_buffers(vmm_ba_engine* e) {
     const size_t nobs = (size_t)4 * e->Ntol;
     if (e->res_dev.n != 2 * nobs || !e->res_dev.p) {
@@ -628,8 +727,12 @@ static int create_common(int device, vmm_ba_engine** out) {
     if (prop.major != 10)
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
     if ((err = cudaSetDevice(device)) != cudaSuccess) return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(err));
+    for (const void* f : { (const void*)k_schur_product<SP_FULL>, (const void*)k_schur_product<SP_GATHER>, (const void*)k_schur_product<SP_SCATTER> })
+        if ((err = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmemBytes)) != cudaSuccess)
+            return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaFuncSetAttribute(shared memory %zu): %s", kSpSmemBytes, cudaGetErrorString(err));
     e = new vmm_ba_engine();
     e->device = device;
+    e->sp_grid = prop.multiProcessorCount;   // persistent kernel: one CTA per SM
     if ((err = cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
         delete e;
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(err));
@@ -798,7 +901,15 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(e->ocam.alloc(nto1)); CU(e->otag.alloc(nto1)); CU(e->mo_cam.alloc(nto1)); CU(e->mptr.alloc(Nm + 1));
     CU(e->uvm.alloc(4 * uv_stride));
     e->uv_stride = uv_stride;
-    CU(e->Et.alloc((size_t)18 * uv_stride));
+    // E stream: every marker's observation count padded to a multiple of 8 (tile), tiles contiguous per marker
+    std::vector<int> h_mtile(Nm + 1, 0);
+    for (int64_t j = 0; j < Nm; ++j) h_mtile[j + 1] = h_mtile[j] + (h_mptr[j + 1] - h_mptr[j] + kTileObs - 1) / kTileObs;
+    const size_t et_bytes = (size_t)std::max(h_mtile[Nm], 1) * kTileBytes;
+    CU(e->Et.alloc(et_bytes));
+    CU(e->Es.alloc(et_bytes));
+    CU(cudaMemsetAsync(e->Et.p, 0, et_bytes, e->stream));   // padding rows stay zero: no kernel writes them
+    CU(cudaMemsetAsync(e->Es.p, 0, et_bytes, e->stream));
+    CU(e->mtile.alloc(Nm + 1));
     CU(e->cam_active.alloc(ncl1)); CU(e->tag_active.alloc(Nm));
     for (int s = 0; s < 2; ++s) {
         CU(e->cam_q[s].alloc(4 * ncl1)); CU(e->cam_t[s].alloc(3 * ncl1)); CU(e->tag_q[s].alloc(4 * Nm)); CU(e->tag_t[s].alloc(3 * Nm));
@@ -809,7 +920,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(e->lin_m.alloc((size_t)27 * Nm + 8));
     CU(e->hdiag_c.alloc(6 * ncl1)); CU(e->scale_c.alloc(6 * ncl1)); CU(e->lmd_c.alloc(6 * ncl1)); CU(e->lam_c.alloc(6 * ncl1));
     CU(e->hdiag_m.alloc((size_t)6 * Nm)); CU(e->scale_m.alloc((size_t)6 * Nm)); CU(e->lmd_m.alloc((size_t)6 * Nm)); CU(e->lam_m.alloc((size_t)6 * Nm));
-    CU(e->Cinv.alloc((size_t)36 * Nm)); CU(e->Minv.alloc(36 * ncl1)); CU(e->Sd.alloc(36 * ncl1));
+    CU(e->Linv.alloc((size_t)36 * Nm)); CU(e->Minv.alloc(36 * ncl1)); CU(e->Sd.alloc(36 * ncl1));
     CU(e->px.alloc(6 * ncl1)); CU(e->pr.alloc(6 * ncl1)); CU(e->pz.alloc(6 * ncl1)); CU(e->pp.alloc(6 * ncl1)); CU(e->pq.alloc(6 * ncl1));
     CU(e->w.alloc((size_t)6 * Nm + 2)); CU(e->zm.alloc((size_t)6 * Nm)); CU(e->dm.alloc((size_t)6 * Nm));
     e->n_cost_blocks = nblocks(Ntol, kThreads);
@@ -828,6 +939,12 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(up(e->cam_active.p, h_cact.data(), Ncl));
     CU(up(e->tag_active.p, h_tact.data(), Nm));
     CU(up(e->tag_wh.p, tag_wh, sizeof(double) * 2 * Nm));
+    CU(up(e->mtile.p, h_mtile.data(), sizeof(int) * (Nm + 1)));
+    {
+        // segment lists (active markers only: the constant origin tag and unobserved tags have no columns)
+        int rc = build_segments(e, h_mptr, h_mtile, h_tact);
+        if (rc) return rc;
+    }
     e->cur = 0;
     CU(up(e->cam_q[0].p, cam_q + 4 * e->cam0, sizeof(double) * 4 * Ncl));
     CU(up(e->cam_t[0].p, cam_t + 3 * e->cam0, sizeof(double) * 3 * Ncl));
@@ -967,6 +1084,60 @@ int vmm_ba_reprojection_error_sums(vmm_ba_handle e, double* out) {
         CU(cudaStreamSynchronize(e->stream));
         for (int64_t i = 0; i < e->Ntol; ++i) out[e->perm_c[e->to0 + i]] = h[i];
     }
+    return VMM_BA_OK;
+}
+
+int vmm_ba_schur_multiply(vmm_ba_handle e, int loss_kind, double loss_scale, double radius, int path, const double* x, double* y) {
+    if (!e || !x || !y) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null argument");
+    if (!e->have_problem || !e->have_intrinsics) return fail_with(e, VMM_BA_ERR_STATE, "set_intrinsics and set_problem must be called first");
+    if (e->world != 1) return fail_with(e, VMM_BA_ERR_STATE, "vmm_ba_schur_multiply is a single-GPU test entry");
+    if (loss_kind < 0 || loss_kind > 2 || !(loss_scale > 0) || !(radius > 0)) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "bad loss or radius");
+    CU(cudaSetDevice(e->device));
+    const int nc = (int)e->Ncl, nm = (int)e->Nm;
+    if (nc == 0) return VMM_BA_OK;
+    vmm_ba_options o;
+    vmm_ba_options_init(&o);
+    const int gc_b = nblocks(6 * nc, kThreads), gm_b = nblocks(6 * nm, kThreads);
+    prepare_poses(e, e->cur);
+    int rc = linearize(e, e->cur, loss_kind, loss_scale);
+    if (rc) return rc;
+    LAUNCH(k_jacobi_scale, gc_b, kThreads, 6 * nc, e->hdiag_c.p, e->scale_c.p, 1);
+    LAUNCH(k_jacobi_scale, gm_b, kThreads, 6 * nm, e->hdiag_m.p, e->scale_m.p, 1);
+    LAUNCH(k_lm_diagonal, gc_b, kThreads, 6 * nc, e->hdiag_c.p, e->scale_c.p, o.min_lm_diagonal, o.max_lm_diagonal, e->lmd_c.p);
+    LAUNCH(k_lm_diagonal, gm_b, kThreads, 6 * nm, e->hdiag_m.p, e->scale_m.p, o.min_lm_diagonal, o.max_lm_diagonal, e->lmd_m.p);
+    LAUNCH(k_lambda, gc_b, kThreads, 6 * nc, e->lmd_c.p, e->scale_c.p, radius, e->lam_c.p);
+    LAUNCH(k_lambda, gm_b, kThreads, 6 * nm, e->lmd_m.p, e->scale_m.p, radius, e->lam_m.p);
+    rc = factor_and_scale(e);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(e->pp.p, x, sizeof(double) * 6 * nc, cudaMemcpyHostToDevice, e->stream));
+    LAUNCH(k_block_multiply, nblocks(nc, kThreads), kThreads, nc, e->B.p, e->lam_c.p, e->pp.p, e->pq.p);
+    if (path == 0) {
+        rc = schur_offdiag(e, e->pp.p, e->pq.p, nullptr, nullptr, nullptr, nullptr, nullptr);
+        if (rc) return rc;
+    } else {
+        rc = schur_gather(e, e->pp.p, e->w.p, nullptr);
+        if (rc) return rc;
+        schur_scatter(e, e->w.p, -1.0, e->pq.p, nullptr);
+    }
+    CU(cudaMemcpyAsync(y, e->pq.p, sizeof(double) * 6 * nc, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+#ifdef VMM_SP_TIMING
+    {
+        std::vector<double> ts((size_t)e->sp_grid * 2 * 8 * 8);
+        CU(cudaMemcpy(ts.data(), e->dm.p, sizeof(double) * ts.size(), cudaMemcpyDeviceToHost));
+        double acc[8] = { 0 }; int n = 0;
+        for (int c = 0; c < e->sp_grid; ++c) for (int g = 0; g < 2; ++g) for (int i = 0; i < 8; ++i) {
+            const double* t = &ts[(((size_t)c * 2 + g) * 8 + i) * 8];
+            if (t[0] <= 0 || t[7] <= t[0]) continue;
+            for (int k = 1; k < 8; ++k) acc[k] += t[k] - t[k - 1];
+            if (i > 0) acc[0] += t[0] - ts[(((size_t)c * 2 + g) * 8 + i - 1) * 8 + 7];
+            ++n;
+        }
+        fprintf(stderr, "[sp timing] n=%d loop-top %.0f | wait %.0f | lds %.0f | x+fma %.0f | warp_sum %.0f | bar1 %.0f | z+bar2 %.0f | scatter %.0f clks\n", n,
+                acc[0] / n, acc[1] / n, acc[2] / n, acc[3] / n, acc[4] / n, acc[5] / n, acc[6] / n, acc[7] / n);
+    }
+#endif
+    if (e->profiling) profile_resolve(e);
     return VMM_BA_OK;
 }
 

@@ -263,42 +263,64 @@ __global__ void k_invert_blocks(int n, const double* __restrict__ A, const doubl
     for (int k = 0; k < 36; ++k) out[(size_t)i * 36 + k] = M[k];
 }
 
-// zm = Cinv w (per marker), optional dot accumulation  acc += w . zm ; optionally negates input
-// and adds an offset vector first:  zm = Cinv (alpha * (w + add)).
-__global__ void __launch_bounds__(kThreads)
-k_marker_solve(int nm, const double* __restrict__ Cinv, const double* __restrict__ w, const double* __restrict__ add,
-               double alpha, double* __restrict__ zm, double* __restrict__ dot_acc, double* z0, double* z1,
-               double* z2, const double* __restrict__ done) {
-    if (done && *done != 0.0) return;
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {   // recycle the other parity's PCG accumulators
-        if (z0) *z0 = 0.0;
-        if (z1) *z1 = 0.0;
-        if (z2) *z2 = 0.0;
-    }
-    double dot = 0.0;
-    if (j < nm) {
-        double v[6];
+// Marker blocks: Linv_j = G_j^-1 with C_j + diag(lam) = G_j G_j^T, so (C_j + diag(lam))^-1 = Linv^T Linv.
+// Inactive blocks (constant origin tag, unobserved tags) -> 0.  fail flag set on a non-PD block.
+__global__ void k_factor_markers(int n, const double* __restrict__ C, const double* __restrict__ lam,
+                                 const unsigned char* __restrict__ active, double* __restrict__ Linv,
+                                 int* __restrict__ fail) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double M[36], L[36];
 #pragma unroll
-        for (int a = 0; a < 6; ++a) v[a] = alpha * (w[(size_t)j * 6 + a] + (add ? add[(size_t)j * 6 + a] : 0.0));
-        const double* Ci = Cinv + (size_t)j * 36;
+    for (int k = 0; k < 36; ++k) L[k] = 0.0;
+    if (active[i]) {
 #pragma unroll
-        for (int a = 0; a < 6; ++a) {
-            double s = 0.0;
+        for (int k = 0; k < 36; ++k) M[k] = C[(size_t)i * 36 + k];
 #pragma unroll
-            for (int b = 0; b < 6; ++b) s += Ci[a * 6 + b] * v[b];
-            zm[(size_t)j * 6 + a] = s;
-            dot += s * v[a];
+        for (int a = 0; a < 6; ++a) M[a * 6 + a] += lam[(size_t)i * 6 + a];
+        if (!spd_inverse6(M, L)) {
+            atomicExch(fail, 1);
+#pragma unroll
+            for (int k = 0; k < 36; ++k) L[k] = 0.0;
         }
     }
-    if (dot_acc) {
-        const double s = block_sum(dot);
-        if (threadIdx.x == 0) atomicAdd(dot_acc, s);
+#pragma unroll
+    for (int k = 0; k < 36; ++k) Linv[(size_t)i * 36 + k] = L[k];
+}
+
+// out = alpha * op(Linv) (v + add) per marker; op = transpose when `transposed`.
+//   rhs:                z = Linv gm                 (E Cinv gm = Es z)
+//   back-substitution:  dm = -Linv^T (z + Es^T dc)  (= -Cinv (gm + E^T dc))
+__global__ void __launch_bounds__(kThreads)
+k_marker_apply(int nm, const double* __restrict__ Linv, int transposed, const double* __restrict__ v,
+               const double* __restrict__ add, double alpha, double* __restrict__ out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nm) return;
+    double x[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) x[a] = alpha * (v[(size_t)j * 6 + a] + (add ? add[(size_t)j * 6 + a] : 0.0));
+    const double* L = Linv + (size_t)j * 36;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+        double s = 0.0;
+#pragma unroll
+        for (int b = 0; b < 6; ++b) s += (transposed ? L[b * 6 + a] : L[a * 6 + b]) * x[b];
+        out[(size_t)j * 6 + a] = s;
     }
 }
 
+// acc += sum v_i^2 (the w.w term of the sharded PCG, after the all-reduce of w)
+__global__ void __launch_bounds__(kThreads)
+k_sum_squares(int n, const double* __restrict__ v, double* __restrict__ acc, const double* __restrict__ done) {
+    if (done && *done != 0.0) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const double x = (i < n) ? v[i] : 0.0;
+    const double s = block_sum(x * x);
+    if (threadIdx.x == 0) atomicAdd(acc, s);
+}
+
 // PCG scalars, device resident. Slot parity s = iteration & 1.
-//   sc[0+s] rz = r.M^-1 r   sc[2+s] wz = w.Cinv w   sc[4] rz0      pbp[s] = p.(B+lam)p
+//   sc[0+s] rz = r.M^-1 r   sc[2+s] wz = w.w (w = Es^T p)   sc[4] rz0      pbp[s] = p.(B+lam)p
 //   sc[5] done flag (set on device when rz <= tol^2 rz0; every later PCG launch is then a no-op)
 //   sc[6] iterations performed when the flag was set      sc[7] last rz / rz0
 // (pbp lives at the tail of the marker-space vector w so that one all-reduce carries both).
@@ -419,6 +441,23 @@ k_pcg_direction(int nc, int s, const double* __restrict__ B, const double* __res
     if (threadIdx.x == 0) atomicAdd(pbp + o, s1);
 }
 
+// y = (B + diag(lam)) x per 6x6 block (test entry vmm_ba_schur_multiply)
+__global__ void k_block_multiply(int n, const double* __restrict__ B, const double* __restrict__ lam,
+                                 const double* __restrict__ x, double* __restrict__ y) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double xv[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) xv[a] = x[(size_t)i * 6 + a];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+        double t = lam[(size_t)i * 6 + a] * xv[a];
+#pragma unroll
+        for (int b = 0; b < 6; ++b) t += B[(size_t)i * 36 + a * 6 + b] * xv[b];
+        y[(size_t)i * 6 + a] = t;
+    }
+}
+
 // r = -gc (right-hand side start); the E Cinv gm term is added by k_schur_product<SP_SCATTER>
 __global__ void k_negate(int n, const double* __restrict__ a, double* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -505,7 +544,6 @@ k_gradient_norm(int n, const unsigned char* __restrict__ active, const double* _
     if (threadIdx.x == 0) { atomic_max_nonneg(out + 0, bm); atomicAdd(out + 1, bx); }
 }
 
-// marker step: dm = -Cinv (gm + w)   handled by k_marker_solve(alpha = -1, add = gm)
 
 // ------------------------------------------------------------------------------------------
 // Reprojection statistics (src/TagReconstructor.cpp:340-428): per tag observation, the sum of the

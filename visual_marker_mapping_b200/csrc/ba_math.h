@@ -235,7 +235,9 @@ VMM_HD void quat_plus(const double x[4], const double d[3], double out[4]) {
 
 // In-place inverse of a symmetric positive definite 6x6 (row-major, full storage) by Cholesky.
 // Returns false (and leaves A unspecified) if a pivot is not positive.
-VMM_HD bool spd_inverse6(double* A) {
+// If Linv_out != nullptr it receives G^-1 (G = Cholesky factor of the input, lower triangular, row-major
+// 6x6 with zeros above the diagonal): A^-1 = Linv^T Linv.
+VMM_HD bool spd_inverse6(double* A, double* Linv_out = nullptr) {
     double L[21];   // packed lower: L[i*(i+1)/2 + j]
 #define VMM_L(i, j) L[(i) * ((i) + 1) / 2 + (j)]
     for (int j = 0; j < 6; ++j) {
@@ -259,6 +261,10 @@ VMM_HD bool spd_inverse6(double* A) {
             for (int p = j; p < i; ++p) s -= VMM_L(i, p) * VMM_L(p, j);
             VMM_L(i, j) = s / VMM_L(i, i);
         }
+    }
+    if (Linv_out) {
+        for (int i = 0; i < 6; ++i)
+            for (int j = 0; j < 6; ++j) Linv_out[i * 6 + j] = (j <= i) ? VMM_L(i, j) : 0.0;
     }
     // A^-1 = L^-T L^-1
     for (int i = 0; i < 6; ++i)

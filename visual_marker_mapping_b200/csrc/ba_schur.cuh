@@ -4,22 +4,38 @@
 //     [ B   E ] [dc]   [gc]        B_i = sum Jc^T Jc (cameras, 6x6)   C_j = sum Jm^T Jm (markers, 6x6)
 //     [ E^T C ] [dm] = -[gm]       E_k = Jc^T Jm of tag observation k (4 corners = 8 residual rows)
 // The marker blocks are eliminated: S = (B+L_c) - E (C+L_m)^-1 E^T acts on camera space only and is
-// never formed; one product with S streams the E blocks ONCE from HBM.
+// never formed.  With (C_j+L_m)^-1 = U_j U_j^T (U_j = G_j^-T from the Cholesky factor G_j) and the
+// scaled blocks  Es_k = E_k U_j  the off-diagonal part is a plain Gram product,
+//     E (C+L_m)^-1 E^T p = Es (Es^T p),
+// so one product with S streams the Es blocks ONCE from HBM, needs no 6x6 solve between its two
+// halves and costs one group barrier per marker.  Es is rebuilt (k_scale_e) whenever the damping
+// changes, i.e. once per LM iteration against hundreds of products.
 //
 // Two device orders of the tag observations exist side by side (both built in vmm_ba_set_problem):
 //   camera order  — sorted by camera: B_i / g_c / cost by warp-segmented reduction (no hot atomics)
-//   marker order  — sorted by marker, CSR offsets mptr[]: one CTA owns one marker, so C_j / g_m are
-//                   plain stores and w_j = sum_k E_k^T p needs no atomics at all
-// E is stored in marker order as 32-observation tiles of 18 double2 planes ("tile-SoA"): lane l of a
-// warp reading plane c touches Et[(tile*18 + c)*32 + l], i.e. every load/store instruction of a warp
-// is one contiguous 512 B run.
+//   marker order  — sorted by marker, CSR offsets mptr[]: one CTA (or consumer group) owns one marker,
+//                   so C_j / g_m are plain stores and w_j = sum_k Es_k^T p needs no atomics at all
+// E and Es are stored in marker order as byte streams of 8-observation tiles: 18 double2 planes of 8
+// entries (2304 B).  A marker's tiles are contiguous and its observation count is padded to a
+// multiple of 8 (padding: zeros), so that the observations of any run of markers are ONE contiguous
+// byte range that cp.async.bulk can move, and 8 consecutive lanes touch 128 contiguous bytes in every
+// plane (shared-memory conflict free, whole sectors in HBM).
 #pragma once
 #include "ba_kernels.cuh"
 
 namespace vmm {
 
-__device__ __forceinline__ size_t e_index(int k, int plane) {
-    return ((size_t)(k >> 5) * 18 + plane) * 32 + (k & 31);
+constexpr int kTileObs = 8;
+constexpr int kTileBytes = 18 * kTileObs * 16;           // 2304
+constexpr int kSlotTiles = 4;                            // a ring slot: 32 observations = one warp task
+constexpr int kSlotBytes = kSlotTiles * kTileBytes;      // 9216
+
+// E plane `plane` of observation i (0-based inside its marker) of a marker whose first tile is tile0
+__device__ __forceinline__ double2* e_entry(unsigned char* Et, int tile0, int i, int plane) {
+    return reinterpret_cast<double2*>(Et + (size_t)(tile0 + (i >> 3)) * kTileBytes + plane * (kTileObs * 16) + (i & 7) * 16);
+}
+__device__ __forceinline__ const double2* e_entry(const unsigned char* Et, int tile0, int i, int plane) {
+    return reinterpret_cast<const double2*>(Et + (size_t)(tile0 + (i >> 3)) * kTileBytes + plane * (kTileObs * 16) + (i & 7) * 16);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -83,10 +99,11 @@ __global__ void __launch_bounds__(kLinThreads)
 k_linearize_markers(Intrinsics in, const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active,
                     const int* __restrict__ mo_cam, const double2* __restrict__ uvm, size_t uv_stride,
                     const double* __restrict__ camP, const double* __restrict__ mkP, int loss_kind, double loss_a,
-                    double2* __restrict__ Et, double* __restrict__ Ct, double* __restrict__ gm) {
+                    const int* __restrict__ mtile, unsigned char* __restrict__ Et, double* __restrict__ Ct,
+                    double* __restrict__ gm) {
     const int j = blockIdx.x;
     if (!tag_active[j]) return;   // constant origin tag / unobserved tag: no columns (Ct, gm stay zero)
-    const int kb = mptr[j], ke = mptr[j + 1];
+    const int kb = mptr[j], ke = mptr[j + 1], t0 = mtile[j];
     __shared__ double red[27][kLinThreads + 1];
     double mk[12];
     load12(mkP + (size_t)j * MARK_PREP, mk);
@@ -124,7 +141,7 @@ k_linearize_markers(Intrinsics in, const int* __restrict__ mptr, const unsigned 
             }
         }
 #pragma unroll
-        for (int i = 0; i < 18; ++i) Et[e_index(k, i)] = make_double2(E[2 * i], E[2 * i + 1]);
+        for (int i = 0; i < 18; ++i) *e_entry(Et, t0, k - kb, i) = make_double2(E[2 * i], E[2 * i + 1]);
     }
     // CTA reduction of the 27 marker-side sums through shared memory
 #pragma unroll
@@ -145,21 +162,118 @@ k_linearize_markers(Intrinsics in, const int* __restrict__ mptr, const unsigned 
 }
 
 // ------------------------------------------------------------------------------------------
-// Products with the E blocks, one CTA per marker (marker order).
-//   SP_FULL    w_j = sum_k E_k^T v[cam(k)];  z_j = Cinv_j w_j;  out[cam(k)] += sign * E_k z_j;  dot += w_j.z_j
-//              (the whole off-diagonal part of S*p; E is read from HBM once and kept in registers)
-//   SP_GATHER  w_j = sum_k E_k^T v[cam(k)]  stored to mvec[j]          (multi-GPU: all-reduced next)
-//   SP_SCATTER out[cam(k)] += sign * E_k mvec[j]
-// Algorithmic bytes per tag observation: 288 (E) + 4 (camera index); the camera-space vectors
-// (48 B per camera) live in L2.  `done` != 0 turns the launch into a no-op (device-side PCG stop).
+// Es_k = E_k U_j with U_j = Linv_j^T (Linv_j: inverse Cholesky factor of C_j + L_m, lower triangular,
+// row-major 6x6 with zeros above the diagonal; k_factor_markers).  One CTA per marker, one thread per
+// tag observation; reads and writes whole tiles.  Algorithmic bytes per tag observation: 2 x 288.
+// ------------------------------------------------------------------------------------------
+constexpr int kScaleThreads = 128;
+__global__ void __launch_bounds__(kScaleThreads)
+k_scale_e(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active, const int* __restrict__ mtile,
+          const double* __restrict__ Linv, const unsigned char* __restrict__ Et, unsigned char* __restrict__ Es) {
+    const int j = blockIdx.x;
+    if (!tag_active[j]) return;
+    __shared__ double s_l[36];
+    if (threadIdx.x < 36) s_l[threadIdx.x] = Linv[(size_t)j * 36 + threadIdx.x];
+    __syncthreads();
+    const int n = mptr[j + 1] - mptr[j], t0 = mtile[j];
+    for (int i = threadIdx.x; i < n; i += kScaleThreads) {
+        double E[36];
+#pragma unroll
+        for (int p = 0; p < 18; ++p) {
+            const double2 v = __ldcs(e_entry(Et, t0, i, p));
+            E[2 * p] = v.x; E[2 * p + 1] = v.y;
+        }
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            double o[6];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+                double s = 0.0;
+#pragma unroll
+                for (int b = 0; b <= c; ++b) s += E[a * 6 + b] * s_l[c * 6 + b];   // (E U)[a][c] = sum_b E[a][b] Linv[c][b]
+                o[c] = s;
+            }
+#pragma unroll
+            for (int h = 0; h < 3; ++h) *e_entry(Es, t0, i, 3 * a + h) = make_double2(o[2 * h], o[2 * h + 1]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Products with the scaled E blocks: a persistent, TMA-fed kernel (one CTA per SM).
+//
+//   SP_FULL    w_j = sum_k Es_k^T v[cam(k)];  out[cam(k)] += sign * Es_k w_j;  dot += w_j.w_j
+//              (the whole off-diagonal part of S*p with ONE pass over Es)
+//   SP_GATHER  mvec[j] += sum_k Es_k^T v[cam(k)]                        (multi-GPU: all-reduced next)
+//   SP_SCATTER out[cam(k)] += sign * Es_k mvec[j]
+//
+// The unit of work is a *segment*: up to kSegMaxObs tag observations of one marker (a whole marker in
+// SP_FULL).  Every CTA owns a contiguous range of segments.  A producer warp moves their tiles through
+// a ring of shared-memory slots with cp.async.bulk (one slot = 32 observations = the task of one
+// consumer warp; lane r of the producer owns ring position r) under full/empty mbarriers; two
+// consumer groups work on alternate segments, each thread keeping the Es block of its observation
+// in registers from the gather pass to the scatter pass, so a slot is released as soon as it has been
+// consumed and the ring mostly holds data that is still in flight.  A segment longer than the group
+// has lanes keeps its tail in the ring slot for both passes.  One named group barrier per segment.
+// The camera indices and the camera-space vector entries of the NEXT segment are requested while
+// the current one is processed, so no global-memory latency sits between the slot and the FMAs.
+// Algorithmic bytes per tag observation: 288 (Es) + 4 (camera index).
 // ------------------------------------------------------------------------------------------
 enum { SP_FULL = 0, SP_GATHER = 1, SP_SCATTER = 2 };
-constexpr int kSpThreads = 256;
+constexpr int kSpGroups = 2;
+#ifndef VMM_SP_GROUP_WARPS
+#define VMM_SP_GROUP_WARPS 7   // 2 x 7 consumer warps + producer = 15 warps: 128 registers per thread (17 warps: 96, spills)
+#endif
+constexpr int kSpGroupWarps = VMM_SP_GROUP_WARPS;
+constexpr int kSpConsumerThreads = kSpGroups * kSpGroupWarps * 32;
+constexpr int kSpThreads = kSpConsumerThreads + 32;                  // + producer warp
+constexpr int kSpRing = 20;                                          // slots of kSlotBytes: 184,320 B
+constexpr int kSegRegObs = kSpGroupWarps * 32;                       // observations of a segment held in registers
+constexpr int kSegMaxObs = 2 * kSegRegObs;                           // the second half stays in its ring slot
+constexpr size_t kSpSmemBytes = (size_t)kSpRing * kSlotBytes;
 
-__device__ __forceinline__ void load_e_tile(const double2* __restrict__ Et, int k, double2 (&E)[18]) {
-#pragma unroll
-    for (int i = 0; i < 18; ++i) E[i] = __ldcs(Et + e_index(k, i));
+struct __align__(16) SpSeg {
+    int marker;   // marker index j
+    int slot0;    // sequence number of the segment's first slot in its list
+    int nobs;     // observations in this segment (<= kSegMaxObs; <= kSegRegObs outside SP_FULL)
+    int k0;       // marker-order index of the segment's first observation (mo_cam[k0 + i])
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
 }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+    asm volatile(
+        "{\n.reg .pred p;\nWAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_u32(b)), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+// Slot release.  The arrive is RELAXED: a releasing arrive makes ptxas track every earlier global
+// atomic of the thread (ATOMG with a scoreboard instead of fire-and-forget RED), which serialises the
+// scatter pass.  What the release really needs — the LDS reads of the slot being complete before the
+// async proxy overwrites it (measured otherwise: an arrive issued right behind the loads lets the next
+// bulk copy land under them) — is guaranteed by where it is placed: behind a store / reduction whose
+// operands depend on every loaded value.
+__device__ __forceinline__ void mbar_arrive_relaxed(uint64_t* b) {
+    asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void red_add(double* addr, double v) {
+    asm volatile("red.relaxed.gpu.global.add.f64 [%0], %1;" ::"l"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ void group_barrier(int g) {
+    asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kSpGroupWarps * 32) : "memory");
+}
+
 __device__ __forceinline__ void et_times_x(const double2 (&E)[18], const double (&x)[6], double (&y)[6]) {
 #pragma unroll
     for (int a = 0; a < 6; ++a) {
@@ -177,111 +291,209 @@ __device__ __forceinline__ void scatter_e_z(const double2 (&E)[18], const double
         double s = 0.0;
 #pragma unroll
         for (int h = 0; h < 3; ++h) s += E[3 * a + h].x * z[2 * h] + E[3 * a + h].y * z[2 * h + 1];
-        atomicAdd(out + a, sign * s);
+        red_add(out + a, sign * s);
     }
+}
+__device__ __forceinline__ void load_x6(const double* __restrict__ v, int cam, double (&x)[6]) {
+    const double2* x2 = reinterpret_cast<const double2*>(v + (size_t)cam * 6);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { const double2 t = __ldg(x2 + i); x[2 * i] = t.x; x[2 * i + 1] = t.y; }
+}
+// lane's block inside a ring slot (tile = lane / 8, row = lane % 8)
+__device__ __forceinline__ void slot_load_e(const unsigned char* slot, int lane, double2 (&E)[18]) {
+    const unsigned char* b = slot + (lane >> 3) * kTileBytes + (lane & 7) * 16;
+#pragma unroll
+    for (int i = 0; i < 18; ++i) E[i] = *reinterpret_cast<const double2*>(b + i * (kTileObs * 16));
+}
+
+// Sum of 6 values over the 32 lanes with 9 exchanges instead of 30: every stage halves the number of
+// values a lane carries (it keeps the half selected by one bit of its lane index and hands the other
+// half to its partner).  Returns the total of component warp_reduce6_index(lane) — every component
+// < 6 ends up, complete, in four lanes.
+__device__ __forceinline__ int warp_reduce6_index(int lane) { return ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1); }
+__device__ __forceinline__ double warp_reduce6(const double (&y)[6], int lane) {
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+    double a[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const double lo = y[i], hi = (i + 4 < 6) ? y[i + 4] : 0.0;
+        a[i] = (h16 ? hi : lo) + shfl_xor_d(h16 ? lo : hi, 16);
+    }
+    double b[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) b[i] = (h8 ? a[i + 2] : a[i]) + shfl_xor_d(h8 ? a[i] : a[i + 2], 8);
+    double c = (h4 ? b[1] : b[0]) + shfl_xor_d(h4 ? b[0] : b[1], 4);
+    c += shfl_xor_d(c, 2);
+    c += shfl_xor_d(c, 1);
+    return c;
+}
+
+// Consumer side of the ring: slot sequence number q -> ring position, after its data has landed.
+// Two groups (and, without group barriers, the warps of a group) consume out of order, so a warp can
+// be a whole lap ahead of the slot it maps to; an mbarrier parity only distinguishes adjacent phases,
+// hence the wait on the full barrier starts only once the producer has issued lap q / kSpRing of that
+// ring position (then the barrier is in the phase of q or the next one).  No fence: shared memory has
+// one copy and the try_wait is control-dependent on the load of s_lap.
+__device__ __forceinline__ int ring_acquire(int q, uint64_t* s_full, const volatile int* s_lap) {
+    const int ring = q % kSpRing, lap = q / kSpRing;
+    if ((threadIdx.x & 31) == 0) {
+        while (s_lap[ring] <= lap) { }
+    }
+    __syncwarp();
+    mbar_wait(&s_full[ring], (uint32_t)lap & 1);
+    return ring;
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kSpThreads, 2)
-k_schur_product(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active,
-                const int* __restrict__ mo_cam, const double2* __restrict__ Et, const double* __restrict__ Cinv,
+__global__ void __launch_bounds__(kSpThreads, 1)
+k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg, int nseg, const int2* __restrict__ slot_desc,
+                int nslots_total, const unsigned char* __restrict__ Es, const int* __restrict__ mo_cam,
                 const double* __restrict__ vin_c, double* __restrict__ mvec, double sign, double* __restrict__ out_c,
-                double* __restrict__ dot_acc, const double* __restrict__ done, double* zero0, double* zero1,
-                double* zero2) {
+                double* __restrict__ dot_acc, const double* __restrict__ done, double* zero0, double* zero1, double* zero2) {
     if (done && *done != 0.0) return;
-    const int j = blockIdx.x;
+    extern __shared__ __align__(128) unsigned char sp_ring[];
+    __shared__ uint64_t s_full[kSpRing], s_empty[kSpRing];
+    __shared__ double s_part[2][kSpGroups][kSpGroupWarps][6];
+    __shared__ volatile int s_lap[kSpRing];   // laps the producer has issued per ring position (see ring_acquire)
     const int tid = threadIdx.x;
-    if (j == 0 && tid == 0) {   // recycle the other parity's PCG accumulators (nobody touches them in this launch)
+    if (blockIdx.x == 0 && tid == 0) {   // recycle the other parity's PCG accumulators (nobody touches them in this launch)
         if (zero0) *zero0 = 0.0;
         if (zero1) *zero1 = 0.0;
         if (zero2) *zero2 = 0.0;
     }
-    if (!tag_active[j]) {
-        if (MODE == SP_GATHER && tid < 6) mvec[(size_t)j * 6 + tid] = 0.0;
+    const int sb = cta_seg[blockIdx.x], se = cta_seg[blockIdx.x + 1];
+    if (sb >= se) return;
+    if (tid == 0) {
+        for (int s = 0; s < kSpRing; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 1); s_lap[s] = 0; }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int4* seg4 = reinterpret_cast<const int4*>(segs);
+    const int slot_base = __ldg(seg4 + sb).y;
+
+    if (tid >= kSpConsumerThreads) {
+        // ---------------- producer warp: lane r owns ring position r and feeds it slot r, r + kSpRing, ... ----------------
+        const int lane = tid & 31;
+        if (lane < kSpRing) {
+            const int nslots = ((se < nseg) ? __ldg(seg4 + se).y : nslots_total) - slot_base;
+            const int2* desc = slot_desc + slot_base;
+            unsigned char* dst = sp_ring + (size_t)lane * kSlotBytes;
+            int2 sd = (lane < nslots) ? __ldg(desc + lane) : make_int2(0, 0);
+            int lap = 0;
+            for (int q = lane; q < nslots; q += kSpRing, ++lap) {
+                const int2 cur = sd;
+                if (q + kSpRing < nslots) sd = __ldg(desc + q + kSpRing);
+                if (lap > 0) mbar_wait(&s_empty[lane], (uint32_t)(lap - 1) & 1);
+                const uint32_t bytes = (uint32_t)cur.y * kTileBytes;
+                mbar_expect_tx(&s_full[lane], bytes);
+                bulk_g2s(dst, Es + (size_t)cur.x * kTileBytes, bytes, &s_full[lane]);
+                __threadfence_block();
+                s_lap[lane] = lap + 1;
+            }
+        }
         return;
     }
-    const int kb = mptr[j], ke = mptr[j + 1];
-    __shared__ double s_part[kSpThreads / 32][6];
-    __shared__ double s_w[6], s_z[6];
-    double2 Er[18];
-    const int k0 = kb + tid;
-    int cam0 = 0;
-    if (MODE != SP_SCATTER) {
+
+    // ---------------- consumers ----------------
+    const int g = tid / (kSpGroupWarps * 32);        // group
+    const int gt = tid - g * (kSpGroupWarps * 32);   // thread within group
+    const int wg = gt >> 5, lane = tid & 31;
+    const int o0 = wg * 32 + lane;                   // observation of the segment held in registers
+    const int o1 = o0 + kSegRegObs;                  // observation that stays in its slot (long segments, SP_FULL only)
+    const int ridx = warp_reduce6_index(lane);
+    double dacc = 0.0;
+    // software pipeline: descriptor two segments ahead, camera indices one segment ahead
+    const int s0 = sb + g;
+    int4 d_cur = (s0 < se) ? __ldg(seg4 + s0) : make_int4(0, 0, 0, 0);
+    int4 d_nxt = (s0 + kSpGroups < se) ? __ldg(seg4 + s0 + kSpGroups) : make_int4(0, 0, 0, 0);
+    int cam0 = (o0 < d_cur.z) ? __ldg(mo_cam + d_cur.w + o0) : 0;
+    int cam1 = (o1 < d_cur.z) ? __ldg(mo_cam + d_cur.w + o1) : 0;
+    int it = 0;
+    for (int s = s0; s < se; s += kSpGroups, ++it) {
+        const SpSeg d{ d_cur.x, d_cur.y, d_cur.z, d_cur.w };
+        const int j = d.marker;
+        const bool has0 = wg * 32 < d.nobs, has1 = wg * 32 + kSegRegObs < d.nobs;   // warp-uniform
+        const bool v0 = o0 < d.nobs, v1 = o1 < d.nobs;
+        // ---- requests that must not wait for the slot: this segment's vector entries, the next one's indices ----
+        double x0[6], x1[6], z[6];
+        const int c0 = cam0, c1 = cam1;
+        if (MODE != SP_SCATTER) {
+            if (v0) load_x6(vin_c, c0, x0);
+            if (v1) load_x6(vin_c, c1, x1);
+        } else {
+#pragma unroll
+            for (int b = 0; b < 6; ++b) z[b] = __ldg(mvec + (size_t)j * 6 + b);
+        }
+        d_cur = d_nxt;
+        if (s + 2 * kSpGroups < se) d_nxt = __ldg(seg4 + s + 2 * kSpGroups);
+        cam0 = (o0 < d_cur.z && s + kSpGroups < se) ? __ldg(mo_cam + d_cur.w + o0) : 0;
+        cam1 = (o1 < d_cur.z && s + kSpGroups < se) ? __ldg(mo_cam + d_cur.w + o1) : 0;
+
+        // ---- gather pass ----
+        double2 Er[18];
+        const unsigned char* slot1 = nullptr;
+        int ring0 = 0, ring1 = 0;
         double y[6] = { 0, 0, 0, 0, 0, 0 };
-        if (k0 < ke) {
-            cam0 = __ldg(mo_cam + k0);
-            load_e_tile(Et, k0, Er);
-            double x[6];
-            const double2* x2 = reinterpret_cast<const double2*>(vin_c + (size_t)cam0 * 6);
-#pragma unroll
-            for (int i = 0; i < 3; ++i) { const double2 t = __ldg(x2 + i); x[2 * i] = t.x; x[2 * i + 1] = t.y; }
-            et_times_x(Er, x, y);
+        if (has0) {
+            ring0 = ring_acquire(d.slot0 - slot_base + wg, s_full, s_lap);
+            if (v0) {
+                slot_load_e(sp_ring + (size_t)ring0 * kSlotBytes, lane, Er);
+                if (MODE != SP_SCATTER) et_times_x(Er, x0, y);
+            }
         }
-        for (int k = k0 + kSpThreads; k < ke; k += kSpThreads) {   // markers with more than 256 observations
-            const int cam = __ldg(mo_cam + k);
-            double2 Ek[18];
-#pragma unroll
-            for (int i = 0; i < 18; ++i) Ek[i] = __ldg(Et + e_index(k, i));
-            double x[6];
-            const double2* x2 = reinterpret_cast<const double2*>(vin_c + (size_t)cam * 6);
-#pragma unroll
-            for (int i = 0; i < 3; ++i) { const double2 t = __ldg(x2 + i); x[2 * i] = t.x; x[2 * i + 1] = t.y; }
-            et_times_x(Ek, x, y);
+        if (has1) {
+            ring1 = ring_acquire(d.slot0 - slot_base + wg + kSpGroupWarps, s_full, s_lap);
+            slot1 = sp_ring + (size_t)ring1 * kSlotBytes;
+            if (MODE != SP_SCATTER && v1) {
+                double2 Ek[18];
+                slot_load_e(slot1, lane, Ek);
+                et_times_x(Ek, x1, y);
+            }
         }
-#pragma unroll
-        for (int b = 0; b < 6; ++b) y[b] = warp_sum(y[b]);
-        if ((tid & 31) == 0) {
-#pragma unroll
-            for (int b = 0; b < 6; ++b) s_part[tid >> 5][b] = y[b];
-        }
-        __syncthreads();
-        if (tid < 6) {
+        if (MODE != SP_SCATTER) {
+            const double part = warp_reduce6(y, lane);
+            if ((lane & 3) == 0 && ridx < 6) s_part[it & 1][g][wg][ridx] = part;
+            // the stored values depend on every E entry of every lane: the slot's loads are complete
+            if (has0 && lane == 0) mbar_arrive_relaxed(&s_empty[ring0]);
+            group_barrier(g);
             double w = 0.0;
+            if (lane < 6) {
 #pragma unroll
-            for (int q = 0; q < kSpThreads / 32; ++q) w += s_part[q][tid];
-            if (MODE == SP_GATHER) mvec[(size_t)j * 6 + tid] = w;
-            else s_w[tid] = w;
-        }
-        if (MODE == SP_GATHER) return;
-        __syncthreads();
-        if (tid < 6) {
-            const double* Ci = Cinv + (size_t)j * 36 + tid * 6;
-            double z = 0.0;
+                for (int q = 0; q < kSpGroupWarps; ++q) w += s_part[it & 1][g][q][lane];
+            }
+            if (MODE == SP_GATHER) {
+                if (wg == 0 && lane < 6) red_add(mvec + (size_t)j * 6 + lane, w);   // segments of a split marker meet here
+                continue;
+            }
+            if (wg == 0) dacc += w * w;   // lanes 0..5 of the group's first warp
 #pragma unroll
-            for (int b = 0; b < 6; ++b) z += Ci[b] * s_w[b];
-            s_z[tid] = z;
+            for (int b = 0; b < 6; ++b) z[b] = __shfl_sync(0xffffffffu, w, b);
         }
-        __syncthreads();
-        if (tid == 0 && dot_acc) {
-            double d = 0.0;
-#pragma unroll
-            for (int b = 0; b < 6; ++b) d += s_w[b] * s_z[b];
-            atomicAdd(dot_acc, d);
+        // ---- scatter pass ----
+        if (v0) scatter_e_z(Er, z, sign, out_c + (size_t)c0 * 6);
+        if (MODE == SP_SCATTER) {
+            __syncwarp();
+            if (has0 && lane == 0) mbar_arrive_relaxed(&s_empty[ring0]);   // behind the reductions that consumed E
         }
-    } else {
-        if (tid < 6) s_z[tid] = mvec[(size_t)j * 6 + tid];
-        __syncthreads();
-        if (k0 < ke) {
-            cam0 = __ldg(mo_cam + k0);
-            load_e_tile(Et, k0, Er);
+        if (has1) {
+            if (v1) {
+                double2 Ek[18];
+                slot_load_e(slot1, lane, Ek);
+                scatter_e_z(Ek, z, sign, out_c + (size_t)c1 * 6);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive_relaxed(&s_empty[ring1]);
         }
     }
-    double z[6];
-#pragma unroll
-    for (int b = 0; b < 6; ++b) z[b] = s_z[b];
-    if (k0 < ke) scatter_e_z(Er, z, sign, out_c + (size_t)cam0 * 6);
-    for (int k = k0 + kSpThreads; k < ke; k += kSpThreads) {
-        const int cam = __ldg(mo_cam + k);
-        double2 Ek[18];
-#pragma unroll
-        for (int i = 0; i < 18; ++i) Ek[i] = __ldg(Et + e_index(k, i));   // L2 hit: read moments ago
-        scatter_e_z(Ek, z, sign, out_c + (size_t)cam * 6);
+    if (MODE == SP_FULL && dot_acc && wg == 0) {
+        const double dsum = warp_sum(lane < 6 ? dacc : 0.0);
+        if (lane == 0) red_add(dot_acc, dsum);
     }
 }
 
 // ------------------------------------------------------------------------------------------
 // Block diagonal of the reduced camera system (the SCHUR_JACOBI preconditioner):
-//   Sd_i = B_i + diag(lam_c) - sum_k E_k Cinv_{m(k)} E_k^T     (upper triangle; mirrored afterwards)
+//   Sd_i = B_i + diag(lam_c) - sum_k Es_k Es_k^T     (upper triangle; mirrored afterwards)
 // ------------------------------------------------------------------------------------------
 __global__ void k_schur_diag_init(int n, const double* __restrict__ B, const double* __restrict__ lam,
                                   double* __restrict__ Sd) {
@@ -292,36 +504,27 @@ __global__ void k_schur_diag_init(int n, const double* __restrict__ B, const dou
     Sd[i] = B[i] + ((a == b) ? lam[(size_t)blk * 6 + a] : 0.0);
 }
 
-__global__ void __launch_bounds__(kSpThreads, 2)
+constexpr int kDiagThreads = 256;
+__global__ void __launch_bounds__(kDiagThreads, 2)
 k_schur_diag(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active, const int* __restrict__ mo_cam,
-             const double2* __restrict__ Et, const double* __restrict__ Cinv, double* __restrict__ Sd) {
+             const int* __restrict__ mtile, const unsigned char* __restrict__ Es, double* __restrict__ Sd) {
     const int j = blockIdx.x;
     if (!tag_active[j]) return;
-    __shared__ double s_c[36];
-    if (threadIdx.x < 36) s_c[threadIdx.x] = Cinv[(size_t)j * 36 + threadIdx.x];
-    __syncthreads();
-    const int kb = mptr[j], ke = mptr[j + 1];
-    for (int k = kb + threadIdx.x; k < ke; k += kSpThreads) {
+    const int kb = mptr[j], ke = mptr[j + 1], t0 = mtile[j];
+    for (int k = kb + threadIdx.x; k < ke; k += kDiagThreads) {
         const int cam = __ldg(mo_cam + k);
         double2 E2[18];
-        load_e_tile(Et, k, E2);
+#pragma unroll
+        for (int i = 0; i < 18; ++i) E2[i] = __ldcs(e_entry(Es, t0, k - kb, i));
         const double* E = reinterpret_cast<const double*>(E2);
         double* o = Sd + (size_t)cam * 36;
 #pragma unroll
         for (int a = 0; a < 6; ++a) {
-            double W[6];
-#pragma unroll
-            for (int c = 0; c < 6; ++c) {
-                double s = 0.0;
-#pragma unroll
-                for (int l = 0; l < 6; ++l) s += E[a * 6 + l] * s_c[l * 6 + c];
-                W[c] = s;
-            }
 #pragma unroll
             for (int b = a; b < 6; ++b) {
                 double s = 0.0;
 #pragma unroll
-                for (int c = 0; c < 6; ++c) s += W[c] * E[b * 6 + c];
+                for (int c = 0; c < 6; ++c) s += E[a * 6 + c] * E[b * 6 + c];   // (Es Es^T)[a][b]
                 atomicAdd(o + a * 6 + b, -s);
             }
         }

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "vmm_ba_create_distributed", "vmm_ba_nccl_unique_id", "vmm_ba_destroy", "vmm_ba_last_error",
     "vmm_ba_set_stream", "vmm_ba_set_intrinsics", "vmm_ba_set_problem", "vmm_ba_set_poses",
     "vmm_ba_get_poses", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
-    "vmm_ba_reprojection_error_sums", "vmm_ba_shard_info", "vmm_ba_partition_cameras",
+    "vmm_ba_reprojection_error_sums", "vmm_ba_schur_multiply", "vmm_ba_shard_info", "vmm_ba_partition_cameras",
     "vmm_ba_kernel_launches", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
     "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
 ]
@@ -101,7 +101,7 @@ def load_library():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB_PATH
+    path = os.environ.get("VMM_BA_LIBRARY", _build.LIB_PATH)   # override: kernel-variant experiments (tools/)
     if not os.path.exists(path):
         raise VmmBaError(
             f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
@@ -125,6 +125,7 @@ def load_library():
     lib.vmm_ba_evaluate.argtypes = [C.c_void_p, C.c_int, C.c_double, dp, dp, dp, dp]
     lib.vmm_ba_evaluate_device.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp]
     lib.vmm_ba_reprojection_error_sums.argtypes = [C.c_void_p, dp]
+    lib.vmm_ba_schur_multiply.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.vmm_ba_shard_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.vmm_ba_partition_cameras.argtypes = [C.c_int64, C.c_int64, ip, C.c_int, C.POINTER(C.c_int64)]
     lib.vmm_ba_measure_fp64_peak.argtypes = [C.c_void_p, dp]
@@ -281,6 +282,14 @@ class BundleAdjuster:
         out = np.zeros(self.n_tag_obs)
         self._check(self._lib.vmm_ba_reprojection_error_sums(self._h, _dp(out)))
         return out
+
+    def schur_multiply(self, x, loss_kind=LOSS_NONE, loss_scale=1.0, radius=1e4, path=0) -> np.ndarray:
+        """y = S x with the reduced camera system at the current poses (test entry, one GPU)."""
+        x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1)
+        assert x.size == 6 * self.n_cameras
+        y = np.zeros_like(x)
+        self._check(self._lib.vmm_ba_schur_multiply(self._h, loss_kind, loss_scale, radius, path, _dp(x), _dp(y)))
+        return y
 
     def shard_info(self):
         a, b, n = C.c_int64(0), C.c_int64(0), C.c_int64(0)
