@@ -1133,7 +1133,7 @@ int vmm_ba_schur_multiply(vmm_ba_handle e, int loss_kind, double loss_scale, dou
             if (i > 0) acc[0] += t[0] - ts[(((size_t)c * 2 + g) * 8 + i - 1) * 8 + 7];
             ++n;
         }
-        fprintf(stderr, "[sp timing] n=%d loop-top %.0f | wait %.0f | lds %.0f | x+fma %.0f | warp_sum %.0f | bar1 %.0f | z+bar2 %.0f | scatter %.0f clks\n", n,
+        fprintf(stderr, "[sp timing] n=%d between %.0f | issue-prefetch %.0f | ring wait %.0f | lds+fma %.0f | warp_reduce %.0f | barrier %.0f | sum+bcast %.0f | scatter %.0f clks\n", n,
                 acc[0] / n, acc[1] / n, acc[2] / n, acc[3] / n, acc[4] / n, acc[5] / n, acc[6] / n, acc[7] / n);
     }
 #endif

@@ -253,6 +253,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
         "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_u32(b)), "r"(parity)
         : "memory");
 }
+__device__ __forceinline__ bool mbar_test(uint64_t* b, uint32_t parity) {   // non-blocking
+    uint32_t ok;
+    asm volatile(
+        "{\n.reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n}" : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
@@ -291,11 +299,19 @@ __device__ __forceinline__ void scatter_e_z(const double2 (&E)[18], const double
         double s = 0.0;
 #pragma unroll
         for (int h = 0; h < 3; ++h) s += E[3 * a + h].x * z[2 * h] + E[3 * a + h].y * z[2 * h + 1];
+#ifdef VMM_SP_NO_RED   // timing experiment only (tools/): results are wrong
+        if (s == 1.2345e300) red_add(out + a, sign * s);
+#else
         red_add(out + a, sign * s);
+#endif
     }
 }
 __device__ __forceinline__ void load_x6(const double* __restrict__ v, int cam, double (&x)[6]) {
+#ifdef VMM_SP_NO_X    // timing experiment only (tools/): results are wrong
+    const double2* x2 = reinterpret_cast<const double2*>(v + (size_t)(cam & 31) * 6);
+#else
     const double2* x2 = reinterpret_cast<const double2*>(v + (size_t)cam * 6);
+#endif
 #pragma unroll
     for (int i = 0; i < 3; ++i) { const double2 t = __ldg(x2 + i); x[2 * i] = t.x; x[2 * i + 1] = t.y; }
 }
@@ -373,22 +389,24 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
 
     if (tid >= kSpConsumerThreads) {
         // ---------------- producer warp: lane r owns ring position r and feeds it slot r, r + kSpRing, ... ----------------
+        // The lanes poll their empty barriers together (test_wait, non-blocking): a lane parked in a
+        // blocking try_wait would hold up the copies of the 19 other ring positions.
         const int lane = tid & 31;
-        if (lane < kSpRing) {
-            const int nslots = ((se < nseg) ? __ldg(seg4 + se).y : nslots_total) - slot_base;
-            const int2* desc = slot_desc + slot_base;
-            unsigned char* dst = sp_ring + (size_t)lane * kSlotBytes;
-            int2 sd = (lane < nslots) ? __ldg(desc + lane) : make_int2(0, 0);
-            int lap = 0;
-            for (int q = lane; q < nslots; q += kSpRing, ++lap) {
-                const int2 cur = sd;
-                if (q + kSpRing < nslots) sd = __ldg(desc + q + kSpRing);
-                if (lap > 0) mbar_wait(&s_empty[lane], (uint32_t)(lap - 1) & 1);
-                const uint32_t bytes = (uint32_t)cur.y * kTileBytes;
+        const int nslots = ((se < nseg) ? __ldg(seg4 + se).y : nslots_total) - slot_base;
+        const int2* desc = slot_desc + slot_base;
+        unsigned char* dst = sp_ring + (size_t)(lane < kSpRing ? lane : 0) * kSlotBytes;
+        int q = (lane < kSpRing) ? lane : nslots;
+        int lap = 0;
+        int2 sd = (q < nslots) ? __ldg(desc + q) : make_int2(0, 0);
+        while (__any_sync(0xffffffffu, q < nslots)) {
+            const bool ready = (q < nslots) && (lap == 0 || mbar_test(&s_empty[lane], (uint32_t)(lap - 1) & 1));
+            if (ready) {
+                const uint32_t bytes = (uint32_t)sd.y * kTileBytes;
                 mbar_expect_tx(&s_full[lane], bytes);
-                bulk_g2s(dst, Es + (size_t)cur.x * kTileBytes, bytes, &s_full[lane]);
-                __threadfence_block();
-                s_lap[lane] = lap + 1;
+                bulk_g2s(dst, Es + (size_t)sd.x * kTileBytes, bytes, &s_full[lane]);
+                s_lap[lane] = ++lap;   // after the expect_tx in this thread's shared-memory order
+                q += kSpRing;
+                if (q < nslots) sd = __ldg(desc + q);
             }
         }
         return;
@@ -402,6 +420,12 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
     const int o1 = o0 + kSegRegObs;                  // observation that stays in its slot (long segments, SP_FULL only)
     const int ridx = warp_reduce6_index(lane);
     double dacc = 0.0;
+#ifdef VMM_SP_TIMING   // debug build: phase time stamps of warp 0 of each group into mvec (tools/, not the product)
+#define SP_TS(k, dep) do { if (MODE == SP_FULL && mvec && wg == 0 && lane == 0 && it >= 8 && it < 16) \
+        mvec[(((size_t)blockIdx.x * 2 + g) * 8 + (it - 8)) * 8 + (k)] = (double)(clock64() + ((dep) == 1.2345e300 ? 1 : 0)); } while (0)
+#else
+#define SP_TS(k, dep) do { } while (0)
+#endif
     // software pipeline: descriptor two segments ahead, camera indices one segment ahead
     const int s0 = sb + g;
     int4 d_cur = (s0 < se) ? __ldg(seg4 + s0) : make_int4(0, 0, 0, 0);
@@ -414,12 +438,12 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
         const int j = d.marker;
         const bool has0 = wg * 32 < d.nobs, has1 = wg * 32 + kSegRegObs < d.nobs;   // warp-uniform
         const bool v0 = o0 < d.nobs, v1 = o1 < d.nobs;
+        SP_TS(0, 0.0);
         // ---- requests that must not wait for the slot: this segment's vector entries, the next one's indices ----
-        double x0[6], x1[6], z[6];
+        double x0[6], z[6];
         const int c0 = cam0, c1 = cam1;
         if (MODE != SP_SCATTER) {
             if (v0) load_x6(vin_c, c0, x0);
-            if (v1) load_x6(vin_c, c1, x1);
         } else {
 #pragma unroll
             for (int b = 0; b < 6; ++b) z[b] = __ldg(mvec + (size_t)j * 6 + b);
@@ -434,28 +458,35 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
         const unsigned char* slot1 = nullptr;
         int ring0 = 0, ring1 = 0;
         double y[6] = { 0, 0, 0, 0, 0, 0 };
-        if (has0) {
-            ring0 = ring_acquire(d.slot0 - slot_base + wg, s_full, s_lap);
-            if (v0) {
-                slot_load_e(sp_ring + (size_t)ring0 * kSlotBytes, lane, Er);
-                if (MODE != SP_SCATTER) et_times_x(Er, x0, y);
-            }
-        }
-        if (has1) {
+        SP_TS(1, 0.0);
+        if (has1) {   // the tail first: its vector entries die before the register-resident block is loaded
             ring1 = ring_acquire(d.slot0 - slot_base + wg + kSpGroupWarps, s_full, s_lap);
             slot1 = sp_ring + (size_t)ring1 * kSlotBytes;
             if (MODE != SP_SCATTER && v1) {
+                double x1[6];
+                load_x6(vin_c, c1, x1);   // requested here: prefetching it as well costs more in spills than it hides
                 double2 Ek[18];
                 slot_load_e(slot1, lane, Ek);
                 et_times_x(Ek, x1, y);
             }
         }
+        if (has0) {
+            ring0 = ring_acquire(d.slot0 - slot_base + wg, s_full, s_lap);
+            SP_TS(2, 0.0);
+            if (v0) {
+                slot_load_e(sp_ring + (size_t)ring0 * kSlotBytes, lane, Er);
+                if (MODE != SP_SCATTER) et_times_x(Er, x0, y);
+            }
+        }
         if (MODE != SP_SCATTER) {
+            SP_TS(3, y[0] + y[1] + y[2] + y[3] + y[4] + y[5]);
             const double part = warp_reduce6(y, lane);
+            SP_TS(4, part);
             if ((lane & 3) == 0 && ridx < 6) s_part[it & 1][g][wg][ridx] = part;
             // the stored values depend on every E entry of every lane: the slot's loads are complete
             if (has0 && lane == 0) mbar_arrive_relaxed(&s_empty[ring0]);
             group_barrier(g);
+            SP_TS(5, 0.0);
             double w = 0.0;
             if (lane < 6) {
 #pragma unroll
@@ -468,6 +499,7 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
             if (wg == 0) dacc += w * w;   // lanes 0..5 of the group's first warp
 #pragma unroll
             for (int b = 0; b < 6; ++b) z[b] = __shfl_sync(0xffffffffu, w, b);
+            SP_TS(6, z[5]);
         }
         // ---- scatter pass ----
         if (v0) scatter_e_z(Er, z, sign, out_c + (size_t)c0 * 6);
@@ -484,6 +516,7 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
             __syncwarp();
             if (lane == 0) mbar_arrive_relaxed(&s_empty[ring1]);
         }
+        SP_TS(7, 0.0);
     }
     if (MODE == SP_FULL && dot_acc && wg == 0) {
         const double dsum = warp_sum(lane < 6 ? dacc : 0.0);
