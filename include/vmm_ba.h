@@ -54,7 +54,10 @@ typedef enum { VMM_BA_LOSS_NONE = 0, VMM_BA_LOSS_HUBER = 1, VMM_BA_LOSS_CAUCHY =
 /* same numbering as ceres::TerminationType, which the reference prints at src/TagReconstructor.cpp:740 */
 typedef enum { VMM_BA_CONVERGENCE = 0, VMM_BA_NO_CONVERGENCE = 1, VMM_BA_FAILURE = 2 } vmm_ba_termination;
 
-typedef enum { VMM_BA_PRECOND_JACOBI = 0, VMM_BA_PRECOND_SCHUR_JACOBI = 1 } vmm_ba_preconditioner;
+/* JACOBI: inverse of B_i + lambda per camera.  SCHUR_JACOBI: inverse of the diagonal block of the reduced system.
+ * TWO_LEVEL (default): JACOBI plus a coarse space of rigid motions of camera clusters (additive Schwarz); what
+ * the "block-Jacobi-preconditioned CG" of the path needs to stay at tens of iterations on site-sized maps. */
+typedef enum { VMM_BA_PRECOND_JACOBI = 0, VMM_BA_PRECOND_SCHUR_JACOBI = 1, VMM_BA_PRECOND_TWO_LEVEL = 2 } vmm_ba_preconditioner;
 
 /* replaces: ceres::Solver::Options as configured at src/TagReconstructor.cpp:725-735
  * (everything the reference leaves at the Ceres default is a field here with that default). */
@@ -74,7 +77,7 @@ typedef struct {
     int max_num_consecutive_invalid_steps;/* 5     */
     int jacobi_scaling;                   /* 1     */
     /* linear solver: block-Jacobi PCG on the reduced camera system (markers eliminated) */
-    int preconditioner;                   /* vmm_ba_preconditioner, default JACOBI */
+    int preconditioner;                   /* vmm_ba_preconditioner, default TWO_LEVEL */
     double pcg_tolerance;                 /* stop when sqrt(r.M^-1 r / r0.M^-1 r0) <= tol; default 1e-2 */
     int pcg_max_iterations;               /* default 500 */
     int pcg_min_iterations;               /* default 1 */
@@ -184,6 +187,11 @@ int vmm_ba_evaluate_device(vmm_ba_handle h, int loss_kind, double loss_scale, in
  * src/CameraModel.cpp:6-26, quirk included).  per_tag_obs_sum[k] = sum over the 4 corners of the
  * Euclidean reprojection error of tag observation k at the current poses (caller's order). */
 int vmm_ba_reprojection_error_sums(vmm_ba_handle h, double* per_tag_obs_sum);
+
+/* Target number of cameras per cluster of the two-level preconditioner's coarse space (default 192; the
+ * coarse matrix is 6 x clusters squared and dense, the library caps it at 768 clusters).  Takes effect at
+ * the next vmm_ba_set_problem. */
+int vmm_ba_set_coarse_cluster_size(vmm_ba_handle h, int cameras_per_cluster);
 
 /* ---- introspection for tests / benchmarks -------------------------------------------------- */
 

@@ -24,7 +24,7 @@ NVCC_FLAGS = [
 ]
 
 CUDA_SOURCES = ["ba_engine.cu"]
-CUDA_HEADERS = ["ba_kernels.cuh", "ba_schur.cuh", "ba_math.h", "nccl_dyn.h", os.path.join(REPO, "include", "vmm_ba.h")]
+CUDA_HEADERS = ["ba_kernels.cuh", "ba_schur.cuh", "ba_coarse.cuh", "ba_math.h", "nccl_dyn.h", os.path.join(REPO, "include", "vmm_ba.h")]
 
 
 def _nvcc() -> str:
@@ -45,7 +45,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     srcs = [os.path.join(CSRC, s) for s in CUDA_SOURCES]
     deps = srcs + [h if os.path.isabs(h) else os.path.join(CSRC, h) for h in CUDA_HEADERS]
     if force or _stale(LIB_PATH, deps):
-        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB_PATH] + srcs + ["-ldl"]
+        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB_PATH] + srcs + ["-ldl", "-lcusolver"]
         res = subprocess.run(cmd, capture_output=True, text=True, cwd=CSRC)
         if res.returncode != 0:
             raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)

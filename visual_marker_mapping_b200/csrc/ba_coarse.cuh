@@ -1,0 +1,245 @@
+// ba_coarse.cuh — the coarse level of the two-level preconditioner of the reduced camera system.
+//
+// Block-Jacobi PCG on S = (B + L_c) - Es Es^T needs O(site diameter / camera footprint) iterations:
+// the smooth modes of a large marker map (whole regions drifting rigidly against each other) are
+// invisible to a per-camera preconditioner.  Cameras are grouped into spatial clusters
+// (vmm_ba_set_problem, k-d splits of the camera centres); cluster c contributes the six rigid motions
+// of its part of the world to a coarse space,
+//     P_i y_c = [ -R_i (y_tau + xbar_c x y_theta) ;  -1/2 R_i y_theta ]        (camera i in cluster c)
+// in the solver's tangent coordinates (translation, then the half-angle rotation increment of
+// ceres::QuaternionParameterization, src/TagReconstructor.cpp:661): the pose change of a camera that
+// rides along when the world around it is moved by (y_tau, y_theta) about the cluster centroid.  The
+// preconditioner is additive,  M^-1 r = blockdiag(S)^-1 r + P (P^T S P)^-1 P^T r,  with the dense
+// coarse matrix A_c = P^T S P (6 n_clusters squared, a few thousand) assembled and inverted once per
+// LM iteration and applied as one dense matrix-vector product per PCG iteration.
+#pragma once
+#include "ba_kernels.cuh"
+#include "ba_schur.cuh"
+
+namespace vmm {
+
+// P_i y for one camera: R row-major (camP), xbar the cluster centroid
+__device__ __forceinline__ void coarse_prolong(const double* __restrict__ R, const double* __restrict__ xb,
+                                               const double (&y)[6], double (&out)[6]) {
+    const double ux = y[0] + (xb[1] * y[5] - xb[2] * y[4]);
+    const double uy = y[1] + (xb[2] * y[3] - xb[0] * y[5]);
+    const double uz = y[2] + (xb[0] * y[4] - xb[1] * y[3]);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        out[a] = -(R[3 * a] * ux + R[3 * a + 1] * uy + R[3 * a + 2] * uz);
+        out[3 + a] = -0.5 * (R[3 * a] * y[3] + R[3 * a + 1] * y[4] + R[3 * a + 2] * y[5]);
+    }
+}
+// the 6x6 matrix P_i (row-major): columns = coarse dofs
+__device__ __forceinline__ void coarse_basis(const double* __restrict__ R, const double* __restrict__ xb, double (&P)[36]) {
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+        double y[6] = { 0, 0, 0, 0, 0, 0 }, o[6];
+        y[c] = 1.0;
+        coarse_prolong(R, xb, y, o);
+#pragma unroll
+        for (int a = 0; a < 6; ++a) P[a * 6 + c] = o[a];
+    }
+}
+
+// P_i^T r, formed from the same basis as the prolongation (exact transpose by construction)
+__device__ __forceinline__ void coarse_restrict(const double* __restrict__ R, const double* __restrict__ xb,
+                                                const double (&r)[6], double (&out)[6]) {
+    double P[36];
+    coarse_basis(R, xb, P);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+        double s = 0.0;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) s += P[a * 6 + c] * r[a];
+        out[c] = s;
+    }
+}
+
+// v += P_i yc[cluster(i)]  (declared in ba_kernels.cuh for k_pcg_direction)
+__device__ __forceinline__ void coarse_add(const CoarseView& cv, int i, double (&v)[6]) {
+    const int c = cv.cl_of_cam[i];
+    if (c < 0) return;
+    double y[6], o[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) y[a] = cv.yc[(size_t)c * 6 + a];
+    coarse_prolong(cv.camP + (size_t)i * CAM_PREP, cv.xbar + 3 * (size_t)c, y, o);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) v[a] += o[a];
+}
+
+constexpr int kCoarseThreads = 128;
+
+// A_c[c,c] += sum_{i in c} P_i^T (B_i + diag(lam_i)) P_i.  One CTA per cluster.
+__global__ void __launch_bounds__(kCoarseThreads)
+k_coarse_diag(const int* __restrict__ cl_ptr, const int* __restrict__ cl_cams, const double* __restrict__ xbar,
+              const double* __restrict__ camP, const double* __restrict__ B, const double* __restrict__ lam, int nC,
+              double* __restrict__ Ac) {
+    const int c = blockIdx.x;
+    __shared__ double s_acc[36];
+    if (threadIdx.x < 36) s_acc[threadIdx.x] = 0.0;
+    __syncthreads();
+    double acc[36];
+#pragma unroll
+    for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+    const double xb[3] = { xbar[3 * c], xbar[3 * c + 1], xbar[3 * c + 2] };
+    for (int q = cl_ptr[c] + threadIdx.x; q < cl_ptr[c + 1]; q += kCoarseThreads) {
+        const int i = cl_cams[q];
+        double P[36], T[36];
+        coarse_basis(camP + (size_t)i * CAM_PREP, xb, P);
+        const double* Bi = B + (size_t)i * 36;
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int col = 0; col < 6; ++col) {
+                double s = lam[(size_t)i * 6 + a] * P[a * 6 + col];
+#pragma unroll
+                for (int b = 0; b < 6; ++b) s += Bi[a * 6 + b] * P[b * 6 + col];
+                T[a * 6 + col] = s;
+            }
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int col = 0; col < 6; ++col) {
+                double s = 0.0;
+#pragma unroll
+                for (int a = 0; a < 6; ++a) s += P[a * 6 + r] * T[a * 6 + col];
+                acc[r * 6 + col] += s;
+            }
+    }
+#pragma unroll
+    for (int k = 0; k < 36; ++k) {
+        const double s = warp_sum(acc[k]);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&s_acc[k], s);
+    }
+    __syncthreads();
+    if (threadIdx.x < 36) {
+        const int r = threadIdx.x / 6, col = threadIdx.x % 6;
+        atomicAdd(Ac + (size_t)(6 * c + r) * nC + 6 * c + col, s_acc[threadIdx.x]);
+    }
+}
+
+// A_c -= W^T W with W = Es^T P: per marker j the blocks W_{j,c} = sum_{k in j, cam(k) in c} Es_k^T P_cam(k)
+// are accumulated in shared memory (the clusters a marker touches are few: mcl_ptr/mcl list them,
+// mo_lc[k] is the position of observation k's cluster in that list), then every pair of touched
+// clusters receives -W_a^T W_b.  One CTA per marker.
+constexpr int kCoarseMaxTouched = 24;
+__global__ void __launch_bounds__(kCoarseThreads)
+k_coarse_offdiag(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active, const int* __restrict__ mtile,
+                 const int* __restrict__ mo_cam, const unsigned char* __restrict__ mo_lc, const int* __restrict__ mcl_ptr,
+                 const int* __restrict__ mcl, const int* __restrict__ cl_of_cam, const double* __restrict__ xbar,
+                 const double* __restrict__ camP, const unsigned char* __restrict__ Es, int nC, double* __restrict__ Ac) {
+    const int j = blockIdx.x;
+    if (!tag_active[j]) return;
+    const int tb = mcl_ptr[j], nt = mcl_ptr[j + 1] - tb;
+    __shared__ double s_w[kCoarseMaxTouched][36];
+    for (int i = threadIdx.x; i < nt * 36; i += kCoarseThreads) (&s_w[0][0])[i] = 0.0;
+    __syncthreads();
+    const int kb = mptr[j], n = mptr[j + 1] - kb, t0 = mtile[j];
+    for (int i = threadIdx.x; i < n; i += kCoarseThreads) {
+        const int cam = __ldg(mo_cam + kb + i);
+        const int lc = mo_lc[kb + i];
+        const int c = __ldg(cl_of_cam + cam);
+        const double xb[3] = { xbar[3 * c], xbar[3 * c + 1], xbar[3 * c + 2] };
+        double P[36], E[36];
+        coarse_basis(camP + (size_t)cam * CAM_PREP, xb, P);
+#pragma unroll
+        for (int p = 0; p < 18; ++p) {
+            const double2 v = __ldcs(e_entry(Es, t0, i, p));
+            E[2 * p] = v.x; E[2 * p + 1] = v.y;
+        }
+        // G = Es^T P  (marker dof x coarse dof)
+#pragma unroll
+        for (int m = 0; m < 6; ++m)
+#pragma unroll
+            for (int col = 0; col < 6; ++col) {
+                double s = 0.0;
+#pragma unroll
+                for (int a = 0; a < 6; ++a) s += E[a * 6 + m] * P[a * 6 + col];
+                atomicAdd(&s_w[lc][m * 6 + col], s);
+            }
+    }
+    __syncthreads();
+    // pairs of touched clusters: A_c[6a.., 6b..] -= W_a^T W_b
+    for (int t = threadIdx.x; t < nt * nt * 36; t += kCoarseThreads) {
+        const int pair = t / 36, e = t % 36;
+        const int ia = pair / nt, ib = pair % nt;
+        const int r = e / 6, col = e % 6;
+        double s = 0.0;
+#pragma unroll
+        for (int m = 0; m < 6; ++m) s += s_w[ia][m * 6 + r] * s_w[ib][m * 6 + col];
+        atomicAdd(Ac + (size_t)(6 * mcl[tb + ia] + r) * nC + 6 * mcl[tb + ib] + col, -s);
+    }
+}
+
+// potri leaves the inverse in one triangle: mirror it (column-major lower == row-major upper).
+__global__ void k_symmetrize(int n, double* __restrict__ A) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)n * n) return;
+    const int r = (int)(idx / n), c = (int)(idx % n);
+    if (c > r) A[(size_t)c * n + r] = A[(size_t)r * n + c];   // row-major view: upper triangle is valid
+}
+
+// rc = P^T r restricted per cluster (one CTA per cluster, no atomics).
+__global__ void __launch_bounds__(kCoarseThreads)
+k_coarse_restrict(const int* __restrict__ cl_ptr, const int* __restrict__ cl_cams, const double* __restrict__ xbar,
+                  const double* __restrict__ camP, const double* __restrict__ r, double* __restrict__ rc,
+                  const double* __restrict__ done) {
+    if (done && *done != 0.0) return;
+    const int c = blockIdx.x;
+    const double xb[3] = { xbar[3 * c], xbar[3 * c + 1], xbar[3 * c + 2] };
+    double acc[6] = { 0, 0, 0, 0, 0, 0 };
+    for (int q = cl_ptr[c] + threadIdx.x; q < cl_ptr[c + 1]; q += kCoarseThreads) {
+        const int i = cl_cams[q];
+        double rv[6], o[6];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) rv[a] = r[(size_t)i * 6 + a];
+        coarse_restrict(camP + (size_t)i * CAM_PREP, xb, rv, o);
+#pragma unroll
+        for (int a = 0; a < 6; ++a) acc[a] += o[a];
+    }
+    __shared__ double s_p[kCoarseThreads / 32][6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+        const double s = warp_sum(acc[a]);
+        if ((threadIdx.x & 31) == 0) s_p[threadIdx.x >> 5][a] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kCoarseThreads / 32; ++w) s += s_p[w][threadIdx.x];
+        rc[(size_t)c * 6 + threadIdx.x] = s;
+    }
+}
+
+// yc = Ainv rc (dense symmetric, row-major), one warp per row; dot_acc += rc . yc (the coarse part of r.z)
+__global__ void __launch_bounds__(256)
+k_coarse_apply(int n, const double* __restrict__ Ainv, const double* __restrict__ rc, double* __restrict__ yc,
+               double* __restrict__ dot_acc, double* __restrict__ dot_acc2, const double* __restrict__ done) {
+    if (done && *done != 0.0) return;
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    double s = 0.0;
+    if (row < n) {
+        const double2* a2 = reinterpret_cast<const double2*>(Ainv + (size_t)row * n);
+        const double2* x2 = reinterpret_cast<const double2*>(rc);
+        for (int k = lane; k < n / 2; k += 32) {
+            const double2 a = __ldg(a2 + k), x = __ldg(x2 + k);
+            s += a.x * x.x + a.y * x.y;
+        }
+        s = warp_sum(s);
+        if (lane == 0) yc[row] = s;
+    }
+    __shared__ double s_d[8];
+    if (lane == 0) s_d[threadIdx.x >> 5] = (row < n) ? s * rc[row] : 0.0;
+    __syncthreads();
+    if (threadIdx.x == 0 && dot_acc) {
+        double d = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) d += s_d[w];
+        atomicAdd(dot_acc, d);
+        if (dot_acc2) atomicAdd(dot_acc2, d);
+    }
+}
+
+}  // namespace vmm

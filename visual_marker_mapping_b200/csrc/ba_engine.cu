@@ -18,7 +18,9 @@
 #include "../../include/vmm_ba.h"
 #include "ba_kernels.cuh"
 #include "ba_schur.cuh"
+#include "ba_coarse.cuh"
 #include "nccl_dyn.h"
+#include <cusolverDn.h>
 
 using namespace vmm;
 
@@ -86,6 +88,17 @@ struct vmm_ba_engine {
     };
     SegList seg_full, seg_big, seg_all;
     int sp_grid = 1;
+    // coarse level of the two-level preconditioner (ba_coarse.cuh); single-GPU handles only
+    struct Coarse {
+        bool available = false;   // clusters exist for this problem
+        bool active = false;      // A_c^-1 is valid for the current LM iteration
+        int ncl = 0, nC = 0, lwork = 0;
+        DevBuf<int> cl_of_cam, cl_ptr, cl_cams, mcl_ptr, mcl, info;
+        DevBuf<unsigned char> mo_lc;
+        DevBuf<double> xbar, Ac, rc, yc, work;
+    } coarse;
+    cusolverDnHandle_t cusolver = nullptr;
+    int coarse_cams_per_cluster = 192;
     DevBuf<unsigned char> cam_active, tag_active;
     // poses: current and candidate (pointer-swapped on acceptance)
     DevBuf<double> cam_q[2], cam_t[2], tag_q[2], tag_t[2], camP[2], mkP[2], tag_wh;
@@ -344,6 +357,41 @@ int factor_and_scale(vmm_ba_engine* e) {
     return VMM_BA_OK;
 }
 
+// yc = A_c^-1 P^T r (r in e->pr); acc (+ acc2) += (P^T r) . yc, the coarse part of r.z
+void coarse_correction(vmm_ba_engine* e, double* acc, double* acc2, const double* done) {
+    auto& c = e->coarse;
+    LAUNCH(k_coarse_restrict, c.ncl, kCoarseThreads, c.cl_ptr.p, c.cl_cams.p, c.xbar.p, e->camP[e->cur].p, e->pr.p, c.rc.p, done);
+    LAUNCH(k_coarse_apply, (c.nC + 7) / 8, 256, c.nC, c.Ac.p, c.rc.p, c.yc.p, acc, acc2, done);
+}
+
+// A_c = P^T S P at the current linearisation and damping, then its inverse (dense, cuSOLVER potrf + potri:
+// a plain library factorisation of a few-thousand-square matrix, once per LM iteration).
+int coarse_setup(vmm_ba_engine* e, int slot) {
+    auto& c = e->coarse;
+    c.active = false;
+    if (!c.available || e->world != 1) return VMM_BA_OK;
+    const size_t n = (size_t)c.nC;
+    CU(cudaMemsetAsync(c.Ac.p, 0, sizeof(double) * n * n, e->stream));
+    LAUNCH(k_coarse_diag, c.ncl, kCoarseThreads, c.cl_ptr.p, c.cl_cams.p, c.xbar.p, e->camP[slot].p, e->B.p, e->lam_c.p, c.nC, c.Ac.p);
+    if (e->Ntol > 0)
+        LAUNCH(k_coarse_offdiag, (int)e->Nm, kCoarseThreads, e->mptr.p, e->tag_active.p, e->mtile.p, e->mo_cam.p, c.mo_lc.p, c.mcl_ptr.p,
+               c.mcl.p, c.cl_of_cam.p, c.xbar.p, e->camP[slot].p, e->Es.p, c.nC, c.Ac.p);
+    if (cusolverDnSetStream(e->cusolver, e->stream) != CUSOLVER_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cusolverDnSetStream failed");
+    if (cusolverDnDpotrf(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) != CUSOLVER_STATUS_SUCCESS)
+        return fail_with(e, VMM_BA_ERR_CUDA, "cusolverDnDpotrf failed");
+    int h_info[2] = { 0, 0 };
+    CU(cudaMemcpyAsync(&h_info[0], c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    if (cusolverDnDpotri(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) != CUSOLVER_STATUS_SUCCESS)
+        return fail_with(e, VMM_BA_ERR_CUDA, "cusolverDnDpotri failed");
+    CU(cudaMemcpyAsync(&h_info[1], c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    e->launches += 2;
+    LAUNCH(k_symmetrize, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Ac.p);
+    CU(cudaStreamSynchronize(e->stream));
+    if (e->profiling) profile_resolve(e);
+    c.active = (h_info[0] == 0 && h_info[1] == 0);   // not positive definite: this iteration runs block-Jacobi only
+    return VMM_BA_OK;
+}
+
 struct PcgResult { int iterations; bool ok; double rel; };
 
 // Solve (B_l - E C_l^-1 E^T) x = r0 (r0 in e->pr on entry). x -> e->px, final residual in e->pr.
@@ -357,12 +405,17 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
     double* done = e->sc.p + SC_DONE;
     CU(cudaMemsetAsync(e->sc.p, 0, sizeof(double) * SC_N, e->stream));
     CU(cudaMemsetAsync(e->pbp(), 0, sizeof(double) * 2, e->stream));
-    LAUNCH(k_pcg_init, gb, kThreads, nc, e->Minv.p, e->B.p, e->lam_c.p, e->pr.p, e->px.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p,
-           e->pbp());
+    const bool two_level = e->coarse.active;
+    CoarseView cv{ nullptr, nullptr, nullptr, nullptr };
+    if (two_level) cv = CoarseView{ e->coarse.cl_of_cam.p, e->coarse.xbar.p, e->camP[e->cur].p, e->coarse.yc.p };
+    LAUNCH(k_pcg_init, gb, kThreads, nc, e->Minv.p, e->pr.p, e->px.p, e->pz.p, e->pp.p, e->sc.p);
+    if (two_level) coarse_correction(e, e->sc.p + SC_RZ, e->sc.p + SC_RZ0, nullptr);
     if (e->world > 1) {
         int rc = allreduce(e, e->sc.p, 5, NCCL_SUM);   // rz0 (sc[0], sc[4]) are local partials
         if (rc) return rc;
     }
+    // first direction: p = z (+ P yc), q = (B + lam) p, pBp[0]
+    LAUNCH(k_pcg_direction, gb, kThreads, nc, 1, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, e->pbp(), 0, 1, tol * tol, cv);
     out->iterations = 0;
     out->ok = true;
     out->rel = 1.0;
@@ -386,8 +439,9 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
             int rc = allreduce(e, e->sc.p + SC_RZ + o, 1, NCCL_SUM);
             if (rc) return rc;
         }
+        if (two_level) coarse_correction(e, e->sc.p + SC_RZ + o, nullptr, done);
         LAUNCH(k_pcg_direction, gb, kThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, e->pbp(), it + 1,
-               min_it, tol2);
+               min_it, tol2, cv);
         out->iterations = it + 1;
         if ((it + 1) % check_every == 0 || it + 1 == max_it) {
             CU(cudaMemcpyAsync(e->h_st + ST_SC, e->sc.p, sizeof(double) * SC_N, cudaMemcpyDeviceToHost, e->stream));
@@ -483,6 +537,12 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
             } else {
                 LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->B.p, e->lam_c.p, e->cam_active.p, e->Minv.p, e->fail.p);
             }
+        }
+        if (opt->preconditioner == VMM_BA_PRECOND_TWO_LEVEL) {
+            rc = coarse_setup(e, e->cur);
+            if (rc) return rc;
+        } else {
+            e->coarse.active = false;
         }
         // rhs: r = -gc + E Cinv gm = -gc + Es (Linv gm); zm = Linv gm is kept for the back-substitution
         LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 0, (const double*)e->gm(), (const double*)nullptr, 1.0, e->zm.p);
@@ -647,6 +707,105 @@ int build_segments(vmm_ba_engine* e, const std::vector<int>& mptr, const std::ve
     return rc;
 }
 
+// Camera clusters of the coarse space: k-d median splits of the (active) camera centres C = -R^T t at the
+// initial poses, the clusters every marker touches and, per marker-order observation, the position of its
+// camera's cluster in that marker's list.  Host side, once per problem.
+int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, const std::vector<unsigned char>& cam_active,
+                   const std::vector<int>& mptr, const std::vector<int>& mocam, const std::vector<unsigned char>& tag_active) {
+    auto& c = e->coarse;
+    c.available = false;
+    c.active = false;
+    const int64_t Ncl = e->Ncl, Nm = e->Nm;
+    if (e->world != 1 || Ncl == 0) return VMM_BA_OK;
+    std::vector<int> act;
+    for (int64_t i = 0; i < Ncl; ++i) if (cam_active[i]) act.push_back((int)i);
+    const int kMaxClusters = 768;
+    int target = std::max(8, e->coarse_cams_per_cluster);
+    target = std::max<int>(target, (int)((act.size() + kMaxClusters - 1) / kMaxClusters) * 2);   // the k-d leaves hold target/2 .. target cameras
+    if ((int64_t)act.size() < 2 * (int64_t)target) return VMM_BA_OK;   // one cluster = the gauge mode of a single block: nothing to gain
+    std::vector<double> ctr(3 * Ncl, 0.0);
+    for (int i : act) {
+        const double* q = cam_q + 4 * (e->cam0 + i);
+        const double* t = cam_t + 3 * (e->cam0 + i);
+        double R[9];
+        quat_to_rot(q, R);
+        for (int a = 0; a < 3; ++a) ctr[3 * i + a] = -(R[a] * t[0] + R[3 + a] * t[1] + R[6 + a] * t[2]);
+    }
+    // iterative k-d splitting of index ranges of `act`
+    std::vector<std::pair<int, int>> stack{ { 0, (int)act.size() } }, leaves;
+    while (!stack.empty()) {
+        auto [lo, hi] = stack.back();
+        stack.pop_back();
+        if (hi - lo <= target) { leaves.push_back({ lo, hi }); continue; }
+        double mn[3] = { 1e300, 1e300, 1e300 }, mx[3] = { -1e300, -1e300, -1e300 };
+        for (int k = lo; k < hi; ++k)
+            for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], ctr[3 * act[k] + a]); mx[a] = std::max(mx[a], ctr[3 * act[k] + a]); }
+        int ax = 0;
+        for (int a = 1; a < 3; ++a) if (mx[a] - mn[a] > mx[ax] - mn[ax]) ax = a;
+        const int mid = lo + (hi - lo) / 2;
+        std::nth_element(act.begin() + lo, act.begin() + mid, act.begin() + hi, [&](int a, int b) { return ctr[3 * a + ax] < ctr[3 * b + ax]; });
+        stack.push_back({ lo, mid });
+        stack.push_back({ mid, hi });
+    }
+    const int ncl = (int)leaves.size();
+    if (ncl < 2) return VMM_BA_OK;
+    std::vector<int> cl_of(Ncl, -1), cl_ptr(ncl + 1, 0), cl_cams(act.size());
+    std::vector<double> xbar(3 * (size_t)ncl, 0.0);
+    std::sort(leaves.begin(), leaves.end());
+    for (int cidx = 0; cidx < ncl; ++cidx) {
+        const auto [lo, hi] = leaves[cidx];
+        cl_ptr[cidx] = lo;
+        for (int k = lo; k < hi; ++k) {
+            cl_of[act[k]] = cidx;
+            cl_cams[k] = act[k];
+            for (int a = 0; a < 3; ++a) xbar[3 * cidx + a] += ctr[3 * act[k] + a] / (hi - lo);
+        }
+    }
+    cl_ptr[ncl] = (int)act.size();
+    // clusters touched per marker, local position per marker-order observation
+    std::vector<int> mcl_ptr(Nm + 1, 0), mcl;
+    std::vector<unsigned char> mo_lc(std::max<size_t>(mocam.size(), 1), 0);
+    for (int64_t j = 0; j < Nm; ++j) {
+        const size_t base = mcl.size();
+        if (tag_active[j]) {
+            for (int k = mptr[j]; k < mptr[j + 1]; ++k) {
+                const int cc = cl_of[mocam[k]];
+                size_t pos = base;
+                while (pos < mcl.size() && mcl[pos] != cc) ++pos;
+                if (pos == mcl.size()) {
+                    if ((int)(mcl.size() - base) >= kCoarseMaxTouched) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
+                    mcl.push_back(cc);
+                }
+                mo_lc[k] = (unsigned char)(pos - base);
+            }
+        }
+        mcl_ptr[j + 1] = (int)mcl.size();
+    }
+    c.ncl = ncl;
+    c.nC = 6 * ncl;
+    const size_t n = (size_t)c.nC;
+    CU(c.cl_of_cam.alloc(Ncl)); CU(c.cl_ptr.alloc(ncl + 1)); CU(c.cl_cams.alloc(std::max<size_t>(cl_cams.size(), 1)));
+    CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1))); CU(c.mo_lc.alloc(mo_lc.size()));
+    CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(n * n)); CU(c.rc.alloc(n)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
+    int lw1 = 0, lw2 = 0;
+    if (cusolverDnDpotrf_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, &lw1) != CUSOLVER_STATUS_SUCCESS ||
+        cusolverDnDpotri_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, &lw2) != CUSOLVER_STATUS_SUCCESS)
+        return fail_with(e, VMM_BA_ERR_CUDA, "cusolver buffer size query failed");
+    c.lwork = std::max(lw1, lw2);
+    CU(c.work.alloc(std::max(c.lwork, 1)));
+    auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
+    CU(up(c.cl_of_cam.p, cl_of.data(), sizeof(int) * Ncl));
+    CU(up(c.cl_ptr.p, cl_ptr.data(), sizeof(int) * (ncl + 1)));
+    CU(up(c.cl_cams.p, cl_cams.data(), sizeof(int) * cl_cams.size()));
+    CU(up(c.mcl_ptr.p, mcl_ptr.data(), sizeof(int) * (Nm + 1)));
+    CU(up(c.mcl.p, mcl.data(), sizeof(int) * mcl.size()));
+    CU(up(c.mo_lc.p, mo_lc.data(), mocam.size()));
+    CU(up(c.xbar.p, xbar.data(), sizeof(double) * 3 * ncl));
+    CU(cudaStreamSynchronize(e->stream));
+    c.available = true;
+    return VMM_BA_OK;
+}
+
 int ensure_rj_buffers(vmm_ba_engine* e) {
     const size_t nobs = (size_t)4 * e->Ntol;
     if (e->res_dev.n != 2 * nobs || !e->res_dev.p) {
@@ -689,7 +848,8 @@ void vmm_ba_options_init(vmm_ba_options* o) {
     o->max_lm_diagonal = 1e32;
     o->max_num_consecutive_invalid_steps = 5;
     o->jacobi_scaling = 1;
-    o->preconditioner = VMM_BA_PRECOND_JACOBI;   // measured: as few PCG iterations as SCHUR_JACOBI on C2/C3, no extra pass over E
+    o->preconditioner = VMM_BA_PRECOND_TWO_LEVEL;   // block-Jacobi + rigid-motion coarse space over camera clusters (falls back to
+                                                    // block-Jacobi when the problem has fewer than two clusters or is sharded)
     o->pcg_tolerance = 1e-2;
     o->pcg_max_iterations = 500;
     o->pcg_min_iterations = 1;
@@ -733,6 +893,10 @@ static int create_common(int device, vmm_ba_engine** out) {
     e = new vmm_ba_engine();
     e->device = device;
     e->sp_grid = prop.multiProcessorCount;   // persistent kernel: one CTA per SM
+    if (cusolverDnCreate(&e->cusolver) != CUSOLVER_STATUS_SUCCESS) {
+        delete e;
+        return fail_with(nullptr, VMM_BA_ERR_CUDA, "cusolverDnCreate failed");
+    }
     if ((err = cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
         delete e;
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(err));
@@ -791,6 +955,7 @@ int vmm_ba_destroy(vmm_ba_handle e) {
     cudaSetDevice(e->device);
     cudaDeviceSynchronize();
     if (e->comm) nccl_api().CommDestroy(e->comm);
+    if (e->cusolver) cusolverDnDestroy(e->cusolver);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
     for (auto& p : e->prof_pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& ev : e->prof_free) cudaEventDestroy(ev);
@@ -943,6 +1108,8 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     {
         // segment lists (active markers only: the constant origin tag and unobserved tags have no columns)
         int rc = build_segments(e, h_mptr, h_mtile, h_tact);
+        if (rc) return rc;
+        rc = build_clusters(e, cam_q, cam_t, h_cact, h_mptr, h_mocam, h_tact);
         if (rc) return rc;
     }
     e->cur = 0;
@@ -1138,6 +1305,12 @@ int vmm_ba_schur_multiply(vmm_ba_handle e, int loss_kind, double loss_scale, dou
     }
 #endif
     if (e->profiling) profile_resolve(e);
+    return VMM_BA_OK;
+}
+
+int vmm_ba_set_coarse_cluster_size(vmm_ba_handle e, int cameras_per_cluster) {
+    if (!e || cameras_per_cluster < 1) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "cameras_per_cluster must be positive");
+    e->coarse_cams_per_cluster = cameras_per_cluster;
     return VMM_BA_OK;
 }
 

@@ -326,15 +326,15 @@ k_sum_squares(int n, const double* __restrict__ v, double* __restrict__ acc, con
 // (pbp lives at the tail of the marker-space vector w so that one all-reduce carries both).
 enum { SC_RZ = 0, SC_WZ = 2, SC_RZ0 = 4, SC_DONE = 5, SC_ITERS = 6, SC_REL2 = 7, SC_N = 8 };
 
-// r = b (already in r), x = 0, z = Minv r, p = z, q = (B + lam) p, rz[0] = r.z, pBp[0] = p.q
+// r = b (already in r): x = 0, p = 0, z = Minv r, rz[0] = rz0 = r.z.  The first direction (p = z [+ coarse
+// part], q = (B + lam) p, pBp[0]) is set by k_pcg_direction(s = 1) right after.
 __global__ void __launch_bounds__(kThreads)
-k_pcg_init(int nc, const double* __restrict__ Minv, const double* __restrict__ B, const double* __restrict__ lam,
-           const double* __restrict__ r, double* __restrict__ x, double* __restrict__ z, double* __restrict__ p,
-           double* __restrict__ q, double* __restrict__ sc, double* __restrict__ pbp) {
+k_pcg_init(int nc, const double* __restrict__ Minv, const double* __restrict__ r, double* __restrict__ x,
+           double* __restrict__ z, double* __restrict__ p, double* __restrict__ sc) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    double rz = 0.0, pq = 0.0;
+    double rz = 0.0;
     if (i < nc) {
-        double rv[6], zv[6];
+        double rv[6];
 #pragma unroll
         for (int a = 0; a < 6; ++a) rv[a] = r[(size_t)i * 6 + a];
         const double* Mi = Minv + (size_t)i * 36;
@@ -343,25 +343,14 @@ k_pcg_init(int nc, const double* __restrict__ Minv, const double* __restrict__ B
             double s = 0.0;
 #pragma unroll
             for (int b = 0; b < 6; ++b) s += Mi[a * 6 + b] * rv[b];
-            zv[a] = s;
             rz += s * rv[a];
-        }
-        const double* Bi = B + (size_t)i * 36;
-#pragma unroll
-        for (int a = 0; a < 6; ++a) {
-            double s = lam[(size_t)i * 6 + a] * zv[a];
-#pragma unroll
-            for (int b = 0; b < 6; ++b) s += Bi[a * 6 + b] * zv[b];
-            q[(size_t)i * 6 + a] = s;
-            pq += s * zv[a];
             x[(size_t)i * 6 + a] = 0.0;
-            z[(size_t)i * 6 + a] = zv[a];
-            p[(size_t)i * 6 + a] = zv[a];
+            p[(size_t)i * 6 + a] = 0.0;
+            z[(size_t)i * 6 + a] = s;
         }
     }
     const double s1 = block_sum(rz);
-    const double s2 = block_sum(pq);
-    if (threadIdx.x == 0) { atomicAdd(sc + 0, s1); atomicAdd(pbp + 0, s2); atomicAdd(sc + 4, s1); }
+    if (threadIdx.x == 0) { atomicAdd(sc + 0, s1); atomicAdd(sc + 4, s1); }
 }
 
 // alpha = rz[s] / (pbp[s] - wz[s]); x += alpha p; r -= alpha q; z = Minv r; rz[o] += r.z
@@ -399,10 +388,21 @@ k_pcg_update(int nc, int s, const double* __restrict__ Minv, const double* __res
 }
 
 // beta = rz[o] / rz[s]; p = z + beta p; q = (B + lam) p; pBp[o] += p.q
+// With the two-level preconditioner z holds only the block-Jacobi part; the coarse part P yc is added
+// here on the fly (cl_of_cam != nullptr; cameras outside every cluster have cl_of_cam < 0).
+struct CoarseView {
+    const int* cl_of_cam;
+    const double* xbar;
+    const double* camP;
+    const double* yc;
+};
+__device__ __forceinline__ void coarse_add(const CoarseView& cv, int i, double (&v)[6]);   // ba_coarse.cuh
+
 __global__ void __launch_bounds__(kThreads)
 k_pcg_direction(int nc, int s, const double* __restrict__ B, const double* __restrict__ lam,
                 const double* __restrict__ z, double* __restrict__ p, double* __restrict__ q,
-                double* __restrict__ sc, double* __restrict__ pbp, int iters_done, int min_iters, double tol2) {
+                double* __restrict__ sc, double* __restrict__ pbp, int iters_done, int min_iters, double tol2,
+                CoarseView cv) {
     if (sc[SC_DONE] != 0.0) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int o = s ^ 1;
@@ -422,9 +422,12 @@ k_pcg_direction(int nc, int s, const double* __restrict__ B, const double* __res
     if (i < nc) {
         double pv[6];
 #pragma unroll
+        for (int a = 0; a < 6; ++a) pv[a] = z[(size_t)i * 6 + a];
+        if (cv.cl_of_cam) coarse_add(cv, i, pv);
+#pragma unroll
         for (int a = 0; a < 6; ++a) {
             const size_t e = (size_t)i * 6 + a;
-            pv[a] = z[e] + beta * p[e];
+            pv[a] += beta * p[e];
             p[e] = pv[a];
         }
         const double* Bi = B + (size_t)i * 36;

@@ -17,7 +17,7 @@ from . import _build
 
 LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY = 0, 1, 2
 CONVERGENCE, NO_CONVERGENCE, FAILURE = 0, 1, 2
-PRECOND_JACOBI, PRECOND_SCHUR_JACOBI = 0, 1
+PRECOND_JACOBI, PRECOND_SCHUR_JACOBI, PRECOND_TWO_LEVEL = 0, 1, 2
 
 # every symbol include/vmm_ba.h declares
 ABI_SYMBOLS = [
@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "vmm_ba_create_distributed", "vmm_ba_nccl_unique_id", "vmm_ba_destroy", "vmm_ba_last_error",
     "vmm_ba_set_stream", "vmm_ba_set_intrinsics", "vmm_ba_set_problem", "vmm_ba_set_poses",
     "vmm_ba_get_poses", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
-    "vmm_ba_reprojection_error_sums", "vmm_ba_schur_multiply", "vmm_ba_shard_info", "vmm_ba_partition_cameras",
+    "vmm_ba_reprojection_error_sums", "vmm_ba_schur_multiply", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras",
     "vmm_ba_kernel_launches", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
     "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
 ]
@@ -125,6 +125,7 @@ def load_library():
     lib.vmm_ba_evaluate.argtypes = [C.c_void_p, C.c_int, C.c_double, dp, dp, dp, dp]
     lib.vmm_ba_evaluate_device.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp]
     lib.vmm_ba_reprojection_error_sums.argtypes = [C.c_void_p, dp]
+    lib.vmm_ba_set_coarse_cluster_size.argtypes = [C.c_void_p, C.c_int]
     lib.vmm_ba_schur_multiply.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.vmm_ba_shard_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.vmm_ba_partition_cameras.argtypes = [C.c_int64, C.c_int64, ip, C.c_int, C.POINTER(C.c_int64)]
@@ -290,6 +291,10 @@ class BundleAdjuster:
         y = np.zeros_like(x)
         self._check(self._lib.vmm_ba_schur_multiply(self._h, loss_kind, loss_scale, radius, path, _dp(x), _dp(y)))
         return y
+
+    def set_coarse_cluster_size(self, cameras_per_cluster: int):
+        """Target cameras per cluster of the two-level preconditioner (before set_scene)."""
+        self._check(self._lib.vmm_ba_set_coarse_cluster_size(self._h, int(cameras_per_cluster)))
 
     def shard_info(self):
         a, b, n = C.c_int64(0), C.c_int64(0), C.c_int64(0)
