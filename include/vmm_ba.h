@@ -86,6 +86,11 @@ typedef struct {
     double pcg_parity_tolerance;          /* default 1e-13 */
     int pcg_parity_max_iterations;        /* default 20000 */
     int verbose;                          /* 1: one line per LM iteration on stderr */
+    int coarse_refresh_iterations;        /* TWO_LEVEL: the inverse coarse matrix of an earlier LM iteration is kept
+                                             while the last PCG solve took at most this many iterations more than the
+                                             first solve after the last refresh (a stale preconditioner changes the
+                                             iteration count, not the solution); 0 = refresh every LM iteration.
+                                             default 32 (about the set-up's cost in PCG iterations) */
 } vmm_ba_options;
 
 /* replaces: ceres::Solver::Summary (the reference only prints termination_type / FullReport) */

@@ -10,6 +10,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -19,6 +20,7 @@
 #include "ba_kernels.cuh"
 #include "ba_schur.cuh"
 #include "ba_coarse.cuh"
+#include "ba_stage.cuh"
 #include "nccl_dyn.h"
 #include <cusolverDn.h>
 
@@ -31,17 +33,22 @@ thread_local std::string g_create_error;
 template <typename T>
 struct DevBuf {
     T* p = nullptr;
-    size_t n = 0;
+    size_t n = 0, cap = 0;
+    // a buffer that is already large enough is kept (set_problem is called once per solve by the facade:
+    // cudaFree / cudaMalloc of a few GB per call would cost more than the uploads)
     cudaError_t alloc(size_t count) {
+        if (p && count <= cap) { n = count; return cudaSuccess; }
         release();
-        n = count;
         if (count == 0) return cudaSuccess;
-        return cudaMalloc(&p, count * sizeof(T));
+        cudaError_t err = cudaMalloc(&p, count * sizeof(T));
+        if (err == cudaSuccess) { n = count; cap = count; }
+        return err;
     }
     void release() {
         if (p) cudaFree(p);
         p = nullptr;
         n = 0;
+        cap = 0;
     }
     ~DevBuf() { release(); }
     DevBuf() = default;
@@ -69,8 +76,13 @@ struct vmm_ba_engine {
     int64_t Nc = 0, Nm = 0, Nto = 0, fixed_tag = -1;
     // local shard (camera range, tag observations in camera-sorted order)
     int64_t cam0 = 0, cam1 = 0, Ncl = 0, to0 = 0, Ntol = 0;
-    std::vector<int64_t> perm_c;      // sorted position -> caller's tag-observation index (global)
-    bool perm_identity = true;
+    // staging (ba_stage.cuh): the caller's arrays as uploaded, sort scratch, and the local permutation
+    // perm_dev[s] = caller's tag-observation index of camera-order position s (host mirror fetched on demand)
+    DevBuf<int> raw_cam, raw_tag, perm_all, perm_dev, mperm, sort_keys, sort_keys2, sort_iota;
+    DevBuf<double2> raw_uv;
+    DevBuf<unsigned char> sort_tmp;
+    std::vector<int> perm_c;
+    bool perm_c_valid = false;
     int64_t n_active_cams_local = 0;
 
     // observations: camera order (uv AoS, ocam, otag) and marker order (uvm corner planes, mo_cam, CSR mptr)
@@ -223,6 +235,17 @@ int fail_with(vmm_ba_engine* e, int code, const char* fmt, ...) {
         ++e->launches;                                                     \
     } while (0)
 #define LAUNCH(kernel, grid, block, ...) LAUNCH_NAMED(#kernel, kernel, grid, block, 0, __VA_ARGS__)
+// A library call on the engine's stream (cuSOLVER), timed like a kernel under its own name.
+#define LIBCALL_NAMED(name, ok_expr, what)                                 \
+    do {                                                                   \
+        static const int _kid = register_kernel(name);                     \
+        cudaEvent_t _eb = nullptr;                                         \
+        if (e->profiling) _eb = profile_begin(e);                          \
+        const bool _ok = (ok_expr);                                        \
+        if (_eb) profile_end(e, _kid, _eb);                                \
+        ++e->launches;                                                     \
+        if (!_ok) return fail_with(e, VMM_BA_ERR_CUDA, what " failed");    \
+    } while (0)
 
 int nccl_check(vmm_ba_engine* e, int rc, const char* what) {
     if (rc == 0) return VMM_BA_OK;
@@ -377,14 +400,13 @@ int coarse_setup(vmm_ba_engine* e, int slot) {
         LAUNCH(k_coarse_offdiag, (int)e->Nm, kCoarseThreads, e->mptr.p, e->tag_active.p, e->mtile.p, e->mo_cam.p, c.mo_lc.p, c.mcl_ptr.p,
                c.mcl.p, c.cl_of_cam.p, c.xbar.p, e->camP[slot].p, e->Es.p, c.nC, c.Ac.p);
     if (cusolverDnSetStream(e->cusolver, e->stream) != CUSOLVER_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cusolverDnSetStream failed");
-    if (cusolverDnDpotrf(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) != CUSOLVER_STATUS_SUCCESS)
-        return fail_with(e, VMM_BA_ERR_CUDA, "cusolverDnDpotrf failed");
+    LIBCALL_NAMED("cusolverDnDpotrf", cusolverDnDpotrf(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) == CUSOLVER_STATUS_SUCCESS,
+                  "cusolverDnDpotrf");
     int h_info[2] = { 0, 0 };
     CU(cudaMemcpyAsync(&h_info[0], c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    if (cusolverDnDpotri(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) != CUSOLVER_STATUS_SUCCESS)
-        return fail_with(e, VMM_BA_ERR_CUDA, "cusolverDnDpotri failed");
+    LIBCALL_NAMED("cusolverDnDpotri", cusolverDnDpotri(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) == CUSOLVER_STATUS_SUCCESS,
+                  "cusolverDnDpotri");
     CU(cudaMemcpyAsync(&h_info[1], c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    e->launches += 2;
     LAUNCH(k_symmetrize, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Ac.p);
     CU(cudaStreamSynchronize(e->stream));
     if (e->profiling) profile_resolve(e);
@@ -503,6 +525,9 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
     int iteration = 0;
     int termination = VMM_BA_NO_CONVERGENCE;
     const char* msg = "";
+    e->coarse.active = false;   // every solve starts with a fresh coarse matrix
+    bool coarse_fresh_known = false, coarse_refreshed = false;
+    int pcg_fresh = 0, pcg_last = 0;
     if (!std::isfinite(x_cost)) {
         termination = VMM_BA_FAILURE;
         msg = "Initial cost is not finite.";
@@ -539,8 +564,15 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
             }
         }
         if (opt->preconditioner == VMM_BA_PRECOND_TWO_LEVEL) {
-            rc = coarse_setup(e, e->cur);
-            if (rc) return rc;
+            // the coarse inverse is refreshed when the last solve showed it ageing (more than
+            // coarse_refresh_iterations above the first solve after the last refresh) and after a failed factorisation
+            const bool stale = !coarse_fresh_known || pcg_last > pcg_fresh + opt->coarse_refresh_iterations;
+            if (!e->coarse.active || opt->coarse_refresh_iterations <= 0 || stale) {
+                rc = coarse_setup(e, e->cur);
+                if (rc) return rc;
+                coarse_fresh_known = false;
+                coarse_refreshed = true;
+            }
         } else {
             e->coarse.active = false;
         }
@@ -554,6 +586,8 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         rc = pcg_solve(e, tol, std::max(1, max_it), std::max(1, opt->pcg_min_iterations), &pr);
         if (rc) return rc;
         sum->pcg_iterations += pr.iterations;
+        pcg_last = pr.iterations;
+        if (coarse_refreshed) { pcg_fresh = pr.iterations; coarse_fresh_known = true; coarse_refreshed = false; }
         // back-substitution: dm = -Cinv (gm + E^T dc) = -Linv^T (zm + Es^T dc)
         rc = schur_gather(e, e->px.p, e->w.p, nullptr);
         if (rc) return rc;
@@ -806,6 +840,16 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     return VMM_BA_OK;
 }
 
+// host mirror of perm_dev (camera-order position -> caller's tag-observation index), fetched when a
+// per-observation result has to go back in the caller's order
+int ensure_host_perm(vmm_ba_engine* e) {
+    if (e->perm_c_valid) return VMM_BA_OK;
+    e->perm_c.resize(e->Ntol);
+    if (e->Ntol > 0) CU(cudaMemcpy(e->perm_c.data(), e->perm_dev.p, sizeof(int) * e->Ntol, cudaMemcpyDeviceToHost));
+    e->perm_c_valid = true;
+    return VMM_BA_OK;
+}
+
 int ensure_rj_buffers(vmm_ba_engine* e) {
     const size_t nobs = (size_t)4 * e->Ntol;
     if (e->res_dev.n != 2 * nobs || !e->res_dev.p) {
@@ -857,6 +901,7 @@ void vmm_ba_options_init(vmm_ba_options* o) {
     o->pcg_parity_tolerance = 1e-13;
     o->pcg_parity_max_iterations = 20000;
     o->verbose = 0;
+    o->coarse_refresh_iterations = 32;
 }
 
 int vmm_ba_abi_version(void) { return VMM_BA_ABI_VERSION; }
@@ -1004,6 +1049,14 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "problem too large for 32-bit block indices");
     CU(cudaSetDevice(e->device));
     e->have_problem = false;
+    const bool timing = std::getenv("VMM_BA_TIMING") != nullptr;
+    auto t_phase = std::chrono::steady_clock::now();
+    auto phase = [&](const char* what) {
+        if (!timing) return;
+        cudaStreamSynchronize(e->stream);
+        fprintf(stderr, "[vmm_ba] set_problem %-28s %8.2f ms\n", what, elapsed_s(t_phase) * 1e3);
+        t_phase = std::chrono::steady_clock::now();
+    };
     std::vector<int64_t> cam_count(Nc, 0), tag_count(Nm, 0);
     bool sorted = true;
     for (int64_t k = 0; k < Nto; ++k) {
@@ -1014,17 +1067,9 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         if (k > 0 && to_cam[k - 1] > c) sorted = false;
     }
     e->Nc = Nc; e->Nm = Nm; e->Nto = Nto; e->fixed_tag = fixed_tag;
-    // stable counting sort by camera
     std::vector<int64_t> cam_ptr(Nc + 1, 0);
     for (int64_t i = 0; i < Nc; ++i) cam_ptr[i + 1] = cam_ptr[i] + cam_count[i];
-    e->perm_c.resize(Nto);
-    e->perm_identity = sorted;
-    if (sorted) {
-        for (int64_t k = 0; k < Nto; ++k) e->perm_c[k] = k;
-    } else {
-        std::vector<int64_t> fill(cam_ptr.begin(), cam_ptr.end() - 1);
-        for (int64_t k = 0; k < Nto; ++k) e->perm_c[fill[to_cam[k]]++] = k;
-    }
+    phase("validate + count");
     // shard
     std::vector<int64_t> begin;
     partition_cameras(Nc, cam_count, e->world, begin);
@@ -1033,39 +1078,63 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     e->to0 = cam_ptr[e->cam0];
     e->Ntol = cam_ptr[e->cam1] - e->to0;
     const int64_t Ncl = e->Ncl, Ntol = e->Ntol;
-
-    // host staging of the local shard: camera order ...
-    std::vector<double2> h_uv((size_t)4 * Ntol);
-    std::vector<int> h_ocam(Ntol), h_otag(Ntol), h_mocam(Ntol), h_mptr(Nm + 1, 0);
-    for (int64_t s = 0; s < Ntol; ++s) {
-        const int64_t k = e->perm_c[e->to0 + s];
-        h_ocam[s] = (int)(to_cam[k] - e->cam0);
-        h_otag[s] = to_tag[k];
-        for (int c = 0; c < 4; ++c) h_uv[4 * s + c] = make_double2(to_uv[8 * k + 2 * c], to_uv[8 * k + 2 * c + 1]);
-    }
-    // ... and marker order (stable counting sort by marker; corners as four planes of stride uv_stride)
-    const size_t uv_stride = ((size_t)std::max<int64_t>(Ntol, 1) + 31) / 32 * 32;
-    std::vector<double2> h_uvm(4 * uv_stride, make_double2(0.0, 0.0));
-    {
-        for (int64_t s = 0; s < Ntol; ++s) h_mptr[h_otag[s] + 1]++;
+    // tag observations per marker on this shard (CSR of the marker order)
+    std::vector<int> h_mptr(Nm + 1, 0);
+    if (e->world == 1) {
+        for (int64_t j = 0; j < Nm; ++j) h_mptr[j + 1] = h_mptr[j] + (int)tag_count[j];
+    } else {
+        for (int64_t k = 0; k < Nto; ++k)
+            if (to_cam[k] >= e->cam0 && to_cam[k] < e->cam1) h_mptr[to_tag[k] + 1]++;
         for (int64_t j = 0; j < Nm; ++j) h_mptr[j + 1] += h_mptr[j];
-        std::vector<int> fill(h_mptr.begin(), h_mptr.end() - 1);
-        for (int64_t s = 0; s < Ntol; ++s) {
-            const int pos = fill[h_otag[s]]++;
-            h_mocam[pos] = h_ocam[s];
-            for (int c = 0; c < 4; ++c) h_uvm[c * uv_stride + pos] = h_uv[4 * s + c];
+    }
+
+    // the caller's arrays go to the device as they are; both orders are built there (ba_stage.cuh)
+    const size_t ncl1 = (size_t)std::max<int64_t>(Ncl, 1), nto1 = (size_t)std::max<int64_t>(Ntol, 1), ntoa1 = (size_t)std::max<int64_t>(Nto, 1);
+    const size_t uv_stride = (nto1 + 31) / 32 * 32;
+    CU(e->raw_cam.alloc(ntoa1)); CU(e->raw_tag.alloc(ntoa1)); CU(e->raw_uv.alloc(4 * ntoa1));
+    CU(e->perm_all.alloc(ntoa1)); CU(e->sort_keys.alloc(ntoa1)); CU(e->sort_iota.alloc(ntoa1));
+    CU(e->perm_dev.alloc(nto1)); CU(e->mperm.alloc(nto1)); CU(e->sort_keys2.alloc(nto1));
+    CU(e->uv.alloc(4 * nto1));
+    CU(e->ocam.alloc(nto1)); CU(e->otag.alloc(nto1)); CU(e->mo_cam.alloc(nto1)); CU(e->mptr.alloc(Nm + 1));
+    CU(e->uvm.alloc(4 * uv_stride));
+    e->uv_stride = uv_stride;
+    e->perm_c_valid = false;
+    std::vector<int> h_mocam(Ntol);
+    if (Nto > 0) {
+        CU(cudaMemcpyAsync(e->raw_cam.p, to_cam, sizeof(int) * Nto, cudaMemcpyHostToDevice, e->stream));
+        CU(cudaMemcpyAsync(e->raw_tag.p, to_tag, sizeof(int) * Nto, cudaMemcpyHostToDevice, e->stream));
+        CU(cudaMemcpyAsync(e->raw_uv.p, to_uv, sizeof(double) * 8 * Nto, cudaMemcpyHostToDevice, e->stream));
+        phase("upload of the caller's arrays");
+        auto tmp_alloc = [&](size_t bytes) -> void* {
+            if (e->sort_tmp.alloc(std::max<size_t>(bytes, 1)) != cudaSuccess) return nullptr;
+            return e->sort_tmp.p;
+        };
+        LAUNCH(k_iota, nblocks(Nto, kThreads), kThreads, Nto, e->sort_iota.p);
+        const int* perm_local = e->sort_iota.p + e->to0;   // sorted input: the identity
+        if (!sorted) {
+            CU(stable_sort_pairs(e->raw_cam.p, e->sort_keys.p, e->sort_iota.p, e->perm_all.p, Nto, key_bits(Nc), e->stream, tmp_alloc));
+            ++e->launches;
+            perm_local = e->perm_all.p + e->to0;
         }
+        if (Ntol > 0) {
+            CU(cudaMemcpyAsync(e->perm_dev.p, perm_local, sizeof(int) * Ntol, cudaMemcpyDeviceToDevice, e->stream));
+            LAUNCH(k_stage_camera_order, nblocks(4 * Ntol, kThreads), kThreads, Ntol, e->perm_dev.p, e->raw_cam.p, e->raw_tag.p, e->raw_uv.p,
+                   (int)e->cam0, e->ocam.p, e->otag.p, e->uv.p);
+            CU(stable_sort_pairs(e->otag.p, e->sort_keys2.p, e->sort_iota.p, e->mperm.p, Ntol, key_bits(Nm), e->stream, tmp_alloc));
+            ++e->launches;
+            CU(cudaMemsetAsync(e->uvm.p, 0, sizeof(double2) * 4 * uv_stride, e->stream));
+            LAUNCH(k_stage_marker_order, nblocks(4 * Ntol, kThreads), kThreads, Ntol, e->mperm.p, e->ocam.p, e->uv.p, uv_stride, e->mo_cam.p,
+                   e->uvm.p);
+            CU(cudaMemcpyAsync(h_mocam.data(), e->mo_cam.p, sizeof(int) * Ntol, cudaMemcpyDeviceToHost, e->stream));
+        }
+        CU(cudaStreamSynchronize(e->stream));
+        phase("device sort + both orders");
     }
     std::vector<unsigned char> h_cact(std::max<int64_t>(Ncl, 1), 0), h_tact(Nm, 0);
     e->n_active_cams_local = 0;
     for (int64_t i = 0; i < Ncl; ++i) { h_cact[i] = cam_count[e->cam0 + i] > 0; e->n_active_cams_local += h_cact[i]; }
     for (int64_t j = 0; j < Nm; ++j) h_tact[j] = (tag_count[j] > 0) && (j != fixed_tag);
 
-    const size_t ncl1 = (size_t)std::max<int64_t>(Ncl, 1), nto1 = (size_t)std::max<int64_t>(Ntol, 1);
-    CU(e->uv.alloc(4 * nto1));
-    CU(e->ocam.alloc(nto1)); CU(e->otag.alloc(nto1)); CU(e->mo_cam.alloc(nto1)); CU(e->mptr.alloc(Nm + 1));
-    CU(e->uvm.alloc(4 * uv_stride));
-    e->uv_stride = uv_stride;
     // E stream: every marker's observation count padded to a multiple of 8 (tile), tiles contiguous per marker
     std::vector<int> h_mtile(Nm + 1, 0);
     for (int64_t j = 0; j < Nm; ++j) h_mtile[j + 1] = h_mtile[j] + (h_mptr[j + 1] - h_mptr[j] + kTileObs - 1) / kTileObs;
@@ -1094,23 +1163,22 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(e->sums_dev.alloc(nto1));
     e->res_dev.release(); e->jac_dev.release(); e->rj_partials.release();
 
+    phase("device allocation");
     auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
-    CU(up(e->uv.p, h_uv.data(), sizeof(double2) * 4 * Ntol));
-    CU(up(e->ocam.p, h_ocam.data(), sizeof(int) * Ntol));
-    CU(up(e->otag.p, h_otag.data(), sizeof(int) * Ntol));
-    CU(up(e->mo_cam.p, h_mocam.data(), sizeof(int) * Ntol));
     CU(up(e->mptr.p, h_mptr.data(), sizeof(int) * (Nm + 1)));
-    CU(up(e->uvm.p, h_uvm.data(), sizeof(double2) * 4 * uv_stride));
     CU(up(e->cam_active.p, h_cact.data(), Ncl));
     CU(up(e->tag_active.p, h_tact.data(), Nm));
     CU(up(e->tag_wh.p, tag_wh, sizeof(double) * 2 * Nm));
     CU(up(e->mtile.p, h_mtile.data(), sizeof(int) * (Nm + 1)));
+    phase("uploads");
     {
         // segment lists (active markers only: the constant origin tag and unobserved tags have no columns)
         int rc = build_segments(e, h_mptr, h_mtile, h_tact);
         if (rc) return rc;
+        phase("segment lists");
         rc = build_clusters(e, cam_q, cam_t, h_cact, h_mptr, h_mocam, h_tact);
         if (rc) return rc;
+        phase("camera clusters");
     }
     e->cur = 0;
     CU(up(e->cam_q[0].p, cam_q + 4 * e->cam0, sizeof(double) * 4 * Ncl));
@@ -1202,8 +1270,10 @@ int vmm_ba_evaluate(vmm_ba_handle e, int loss_kind, double loss_scale, double* c
         if (residuals) { hr.resize(2 * nobs); CU(cudaMemcpy(hr.data(), e->res_dev.p, sizeof(double) * 2 * nobs, cudaMemcpyDeviceToHost)); }
         if (jacobians) { hj.resize(24 * nobs); CU(cudaMemcpy(hj.data(), e->jac_dev.p, sizeof(double) * 24 * nobs, cudaMemcpyDeviceToHost)); }
         // component-major device layout -> caller's order, row-major per corner
+        rc = ensure_host_perm(e);
+        if (rc) return rc;
         for (int64_t s = 0; s < e->Ntol; ++s) {
-            const int64_t k = e->perm_c[e->to0 + s];
+            const int64_t k = e->perm_c[s];
             for (int c = 0; c < 4; ++c) {
                 const int64_t src = 4 * s + c, dst = 4 * k + c;
                 if (residuals) { residuals[2 * dst] = hr[src]; residuals[2 * dst + 1] = hr[nobs + src]; }
@@ -1249,7 +1319,9 @@ int vmm_ba_reprojection_error_sums(vmm_ba_handle e, double* out) {
         std::vector<double> h(e->Ntol);
         CU(cudaMemcpyAsync(h.data(), e->sums_dev.p, sizeof(double) * e->Ntol, cudaMemcpyDeviceToHost, e->stream));
         CU(cudaStreamSynchronize(e->stream));
-        for (int64_t i = 0; i < e->Ntol; ++i) out[e->perm_c[e->to0 + i]] = h[i];
+        int rc = ensure_host_perm(e);
+        if (rc) return rc;
+        for (int64_t i = 0; i < e->Ntol; ++i) out[e->perm_c[i]] = h[i];
     }
     return VMM_BA_OK;
 }

@@ -55,6 +55,7 @@ class Options(C.Structure):
         ("pcg_parity_tolerance", C.c_double),
         ("pcg_parity_max_iterations", C.c_int),
         ("verbose", C.c_int),
+        ("coarse_refresh_iterations", C.c_int),
     ]
 
 
