@@ -1,9 +1,12 @@
-"""Print the headline and the per-kernel table of a bench.py JSON line."""
+"""Print the headline numbers and the per-kernel table of a bench.py JSON line (file may hold other lines)."""
 import json, sys
-d = json.load(open(sys.argv[1]))
-print("value", round(d["value"], 3), d["unit"], "ms/step", round(d["ms_per_step"], 3), "e2e", d.get("e2e") and round(d["e2e"]["value"], 3))
-print("roofline", d["roofline"])
-print("rj", d["rj"]["roofline"]["frac"], d["rj"]["ms_per_pass"])
-for k, v in list(d["kernels"].items())[:10]:
-    print(f"  {k:34s} n={v['launches']:5d} avg={v['ms_avg']:.4f} ms share={v['share']:.3f} frac_hbm={v.get('frac_hbm', 0):.3f}")
-print(d["solve"])
+for l in open(sys.argv[1]):
+    l = l.strip()
+    if not l.startswith("{"):
+        continue
+    d = json.loads(l)
+    print({k: d.get(k) for k in ("value", "ms_per_step", "n_gpus", "gpu_launches")}, "e2e", (d.get("e2e") or {}).get("value"))
+    print("roofline", d.get("roofline"))
+    for k, v in sorted(d.get("kernels", {}).items(), key=lambda kv: -kv[1]["ms_total"])[:int(sys.argv[2]) if len(sys.argv) > 2 else 16]:
+        print(f"{k:36s} n={v['launches']:5d} avg={v['ms_avg']:.4f} share={v['share']:.3f}")
+    print(d.get("solve"))

@@ -36,7 +36,7 @@ def main():
             row = {"cams_per_cluster": cs, "set_problem_s": round(t_set, 3), "solve_s": round(t_solve, 4), "lm": s.num_iterations,
                    "pcg": s.pcg_iterations, "final_cost": s.final_cost,
                    "t_linear_solver_s": round(s.time_linear_solver_s, 4)}
-            for k in ("k_coarse_offdiag", "k_coarse_diag", "cusolverDnDpotrf", "cusolverDnDpotri", "k_schur_product<SP_FULL>", "k_coarse_apply"):
+            for k in ("k_coarse_w", "k_coarse_outer", "k_coarse_diag", "cusolverDnDpotrf", "cusolverDnDpotri", "k_schur_product<SP_FULL>", "k_coarse_apply"):
                 if k in prof:
                     row[k + "_ms_avg"] = round(prof[k][1] / max(prof[k][0], 1), 4)
             print(json.dumps(row), flush=True)

@@ -119,60 +119,99 @@ k_coarse_diag(const int* __restrict__ cl_ptr, const int* __restrict__ cl_cams, c
     }
 }
 
-// A_c -= W^T W with W = Es^T P: per marker j the blocks W_{j,c} = sum_{k in j, cam(k) in c} Es_k^T P_cam(k)
-// are accumulated in shared memory (the clusters a marker touches are few: mcl_ptr/mcl list them,
-// mo_lc[k] is the position of observation k's cluster in that list), then every pair of touched
-// clusters receives -W_a^T W_b.  One CTA per marker.
+// A_c -= W^T W with W = Es^T P, in two kernels so that a sharded engine can sum the per-rank parts of W
+// (ncclAllReduce) in between:
+//   k_coarse_w      W_{j,c} = sum_{k in j, cam(k) in c} Es_k^T P_cam(k)   over this rank's observations,
+//                   written to Wbuf[(mcl_ptr[j] + position of c in marker j's cluster list) * 36 ..]
+//   k_coarse_outer  every pair (a, b) of clusters touched by marker j receives -W_a^T W_b
+// The clusters a marker touches are few (mcl_ptr / mcl list them — over ALL ranks' observations; mo_lc[k]
+// is the position of observation k's cluster in that list).  One CTA per marker.
 constexpr int kCoarseMaxTouched = 24;
+constexpr int kCwPad = 37;   // row pitch of the staged G blocks (odd: conflict-free column writes)
 __global__ void __launch_bounds__(kCoarseThreads)
-k_coarse_offdiag(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active, const int* __restrict__ mtile,
-                 const int* __restrict__ mo_cam, const unsigned char* __restrict__ mo_lc, const int* __restrict__ mcl_ptr,
-                 const int* __restrict__ mcl, const int* __restrict__ cl_of_cam, const double* __restrict__ xbar,
-                 const double* __restrict__ camP, const unsigned char* __restrict__ Es, int nC, double* __restrict__ Ac) {
+k_coarse_w(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active, const int* __restrict__ mtile,
+           const int* __restrict__ mo_cam, const unsigned char* __restrict__ mo_lc, const int* __restrict__ mcl_ptr,
+           const int* __restrict__ cl_of_cam, const double* __restrict__ xbar, const double* __restrict__ camP,
+           const unsigned char* __restrict__ Es, double* __restrict__ Wbuf) {
     const int j = blockIdx.x;
-    if (!tag_active[j]) return;
     const int tb = mcl_ptr[j], nt = mcl_ptr[j + 1] - tb;
-    __shared__ double s_w[kCoarseMaxTouched][36];
-    for (int i = threadIdx.x; i < nt * 36; i += kCoarseThreads) (&s_w[0][0])[i] = 0.0;
-    __syncthreads();
-    const int kb = mptr[j], n = mptr[j + 1] - kb, t0 = mtile[j];
-    for (int i = threadIdx.x; i < n; i += kCoarseThreads) {
-        const int cam = __ldg(mo_cam + kb + i);
-        const int lc = mo_lc[kb + i];
-        const int c = __ldg(cl_of_cam + cam);
-        const double xb[3] = { xbar[3 * c], xbar[3 * c + 1], xbar[3 * c + 2] };
-        double P[36], E[36];
-        coarse_basis(camP + (size_t)cam * CAM_PREP, xb, P);
+    if (nt == 0) return;
+    __shared__ double s_g[kCoarseThreads][kCwPad];
+    __shared__ double s_w[kCoarseMaxTouched * 36];
+    __shared__ unsigned char s_lc[kCoarseThreads];
+    for (int i = threadIdx.x; i < nt * 36; i += kCoarseThreads) s_w[i] = 0.0;
+    const int kb = mptr[j], n = tag_active[j] ? mptr[j + 1] - kb : 0, t0 = mtile[j];
+    for (int base = 0; base < n; base += kCoarseThreads) {
+        const int i = base + threadIdx.x;
+        __syncthreads();
+        if (i < n) {
+            const int cam = __ldg(mo_cam + kb + i);
+            const int c = __ldg(cl_of_cam + cam);
+            s_lc[threadIdx.x] = mo_lc[kb + i];
+            const double xb[3] = { xbar[3 * c], xbar[3 * c + 1], xbar[3 * c + 2] };
+            double P[36], E[36];
+            coarse_basis(camP + (size_t)cam * CAM_PREP, xb, P);
 #pragma unroll
-        for (int p = 0; p < 18; ++p) {
-            const double2 v = __ldcs(e_entry(Es, t0, i, p));
-            E[2 * p] = v.x; E[2 * p + 1] = v.y;
-        }
-        // G = Es^T P  (marker dof x coarse dof)
-#pragma unroll
-        for (int m = 0; m < 6; ++m)
-#pragma unroll
-            for (int col = 0; col < 6; ++col) {
-                double s = 0.0;
-#pragma unroll
-                for (int a = 0; a < 6; ++a) s += E[a * 6 + m] * P[a * 6 + col];
-                atomicAdd(&s_w[lc][m * 6 + col], s);
+            for (int p = 0; p < 18; ++p) {
+                const double2 v = __ldcs(e_entry(Es, t0, i, p));
+                E[2 * p] = v.x; E[2 * p + 1] = v.y;
             }
+            // G = Es^T P  (marker dof x coarse dof)
+#pragma unroll
+            for (int m = 0; m < 6; ++m)
+#pragma unroll
+                for (int col = 0; col < 6; ++col) {
+                    double g = 0.0;
+#pragma unroll
+                    for (int a = 0; a < 6; ++a) g += E[a * 6 + m] * P[a * 6 + col];
+                    s_g[threadIdx.x][m * 6 + col] = g;
+                }
+        } else {
+            s_lc[threadIdx.x] = 255;
+        }
+        __syncthreads();
+        // thread (cluster slot t, entry) owns s_w[t*36 + entry]: no atomics
+        const int cnt = min(kCoarseThreads, n - base);
+        for (int id = threadIdx.x; id < nt * 36; id += kCoarseThreads) {
+            const int t = id / 36, en = id % 36;
+            double acc = 0.0;
+            for (int q = 0; q < cnt; ++q)
+                if (s_lc[q] == t) acc += s_g[q][en];
+            s_w[id] += acc;
+        }
     }
     __syncthreads();
-    // pairs of touched clusters: A_c[6a.., 6b..] -= W_a^T W_b
+    for (int id = threadIdx.x; id < nt * 36; id += kCoarseThreads) Wbuf[(size_t)tb * 36 + id] = s_w[id];
+}
+
+// markers j with j % stride == first are handled by this rank (stride = world size)
+__global__ void __launch_bounds__(kCoarseThreads)
+k_coarse_outer(int nm, int first, int stride, const unsigned char* __restrict__ tag_active, const int* __restrict__ mcl_ptr,
+               const int* __restrict__ mcl, const double* __restrict__ Wbuf, int nC, double* __restrict__ Ac) {
+    const int j = first + blockIdx.x * stride;
+    if (j >= nm || !tag_active[j]) return;
+    const int tb = mcl_ptr[j], nt = mcl_ptr[j + 1] - tb;
+    __shared__ double s_w[kCoarseMaxTouched * 36];
+    for (int i = threadIdx.x; i < nt * 36; i += kCoarseThreads) s_w[i] = Wbuf[(size_t)tb * 36 + i];
+    __syncthreads();
     for (int t = threadIdx.x; t < nt * nt * 36; t += kCoarseThreads) {
-        const int pair = t / 36, e = t % 36;
+        const int pair = t / 36, en = t % 36;
         const int ia = pair / nt, ib = pair % nt;
-        const int r = e / 6, col = e % 6;
+        const int r = en / 6, col = en % 6;
         double s = 0.0;
 #pragma unroll
-        for (int m = 0; m < 6; ++m) s += s_w[ia][m * 6 + r] * s_w[ib][m * 6 + col];
+        for (int m = 0; m < 6; ++m) s += s_w[ia * 36 + m * 6 + r] * s_w[ib * 36 + m * 6 + col];
         atomicAdd(Ac + (size_t)(6 * mcl[tb + ia] + r) * nC + 6 * mcl[tb + ib] + col, -s);
     }
 }
 
-// potri leaves the inverse in one triangle: mirror it (column-major lower == row-major upper).
+__global__ void k_identity(int n, double* __restrict__ A) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)n * n) return;
+    A[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
+}
+
+// syrk leaves the inverse in one triangle: mirror it (column-major lower == row-major upper).
 __global__ void k_symmetrize(int n, double* __restrict__ A) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (int64_t)n * n) return;
@@ -239,6 +278,34 @@ k_coarse_apply(int n, const double* __restrict__ Ainv, const double* __restrict_
         for (int w = 0; w < 8; ++w) d += s_d[w];
         atomicAdd(dot_acc, d);
         if (dot_acc2) atomicAdd(dot_acc2, d);
+    }
+}
+
+// Sharded engines: the r.z partials travel in the tail of the rc all-reduce (pack before, unpack after),
+// and the coarse part of r.z is summed in a fixed order so that every rank takes the same stopping decision.
+__global__ void k_pack2(const double* __restrict__ a, const double* __restrict__ b, double* __restrict__ tail,
+                        const double* __restrict__ done) {
+    if (done && *done != 0.0) return;
+    if (threadIdx.x == 0) tail[0] = *a;
+    if (threadIdx.x == 1) tail[1] = b ? *b : 0.0;
+}
+__global__ void __launch_bounds__(256)
+k_coarse_dot(int n, const double* __restrict__ rc, const double* __restrict__ yc, const double* __restrict__ tail,
+             double* __restrict__ acc, double* __restrict__ acc2, const double* __restrict__ done) {
+    if (done && *done != 0.0) return;
+    double s = 0.0;
+    for (int k = threadIdx.x; k < n; k += 256) s += rc[k] * yc[k];
+    s = warp_sum(s);
+    __shared__ double s_p[8];
+    if ((threadIdx.x & 31) == 0) s_p[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double d = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) d += s_p[w];
+        // tail[0] (and tail[1]): the block-Jacobi part of r.z, complete after the all-reduce
+        *acc = tail[0] + d;
+        if (acc2) *acc2 = tail[1] + d;
     }
 }
 

@@ -22,6 +22,7 @@
 #include "ba_coarse.cuh"
 #include "ba_stage.cuh"
 #include "nccl_dyn.h"
+#include <cublas_v2.h>
 #include <cusolverDn.h>
 
 using namespace vmm;
@@ -83,6 +84,14 @@ struct vmm_ba_engine {
     DevBuf<unsigned char> sort_tmp;
     std::vector<int> perm_c;
     bool perm_c_valid = false;
+    // sharded engines renumber the cameras in a spatially coherent (k-d leaf) order before cutting them into
+    // per-rank ranges, so that most markers are seen from one rank only: cam_order[internal] = caller's index
+    // (empty = identity).  Everything below the ABI works on internal indices.
+    std::vector<int> cam_order;
+    // markers whose observations are spread over several ranks (or too many for one SP_FULL segment) go
+    // through gather / all-reduce / scatter on a compact vector of n_bnd x 6 (+4 scalars in its tail)
+    int64_t n_bnd = 0;
+    DevBuf<double> wb;
     int64_t n_active_cams_local = 0;
 
     // observations: camera order (uv AoS, ocam, otag) and marker order (uvm corner planes, mo_cam, CSR mptr)
@@ -100,16 +109,19 @@ struct vmm_ba_engine {
     };
     SegList seg_full, seg_big, seg_all;
     int sp_grid = 1;
-    // coarse level of the two-level preconditioner (ba_coarse.cuh); single-GPU handles only
+    // coarse level of the two-level preconditioner (ba_coarse.cuh)
     struct Coarse {
         bool available = false;   // clusters exist for this problem
         bool active = false;      // A_c^-1 is valid for the current LM iteration
         int ncl = 0, nC = 0, lwork = 0;
         DevBuf<int> cl_of_cam, cl_ptr, cl_cams, mcl_ptr, mcl, info;
         DevBuf<unsigned char> mo_lc;
-        DevBuf<double> xbar, Ac, rc, yc, work;
+        DevBuf<double> Linv;      // inverse Cholesky factor of A_c (scratch of the inversion)
+        DevBuf<double> xbar, Ac, rc /* nC + 2: r.z partials ride along in its tail when sharded */, yc, work, Wbuf;
+        size_t n_w = 0;           // (marker, touched cluster) pairs: Wbuf holds 36 doubles for each
     } coarse;
     cusolverDnHandle_t cusolver = nullptr;
+    cublasHandle_t cublas = nullptr;
     int coarse_cams_per_cluster = 192;
     DevBuf<unsigned char> cam_active, tag_active;
     // poses: current and candidate (pointer-swapped on acceptance)
@@ -380,11 +392,25 @@ int factor_and_scale(vmm_ba_engine* e) {
     return VMM_BA_OK;
 }
 
-// yc = A_c^-1 P^T r (r in e->pr); acc (+ acc2) += (P^T r) . yc, the coarse part of r.z
-void coarse_correction(vmm_ba_engine* e, double* acc, double* acc2, const double* done) {
+// yc = A_c^-1 P^T r (r in e->pr); acc (+ acc2) += (P^T r) . yc, the coarse part of r.z.
+// Sharded: every rank restricts its own cameras, the parts of rc are summed over ranks — with the local
+// r.z partials acc / acc2 riding in the tail of the same all-reduce, so that they come back complete —
+// and every rank applies the (replicated) inverse to the complete rc.
+int coarse_correction(vmm_ba_engine* e, double* acc, double* acc2, const double* done, bool partial_in_tail = false) {
     auto& c = e->coarse;
     LAUNCH(k_coarse_restrict, c.ncl, kCoarseThreads, c.cl_ptr.p, c.cl_cams.p, c.xbar.p, e->camP[e->cur].p, e->pr.p, c.rc.p, done);
+    if (e->world > 1) {
+        double* tail = c.rc.p + c.nC;
+        // partial_in_tail: k_pcg_update has already left this rank's r.z partial in tail[0]
+        if (!partial_in_tail) LAUNCH(k_pack2, 1, 32, acc, acc2, tail, done);
+        int rc = allreduce(e, c.rc.p, (size_t)c.nC + (partial_in_tail ? 1 : 2), NCCL_SUM);
+        if (rc) return rc;
+        LAUNCH(k_coarse_apply, (c.nC + 7) / 8, 256, c.nC, c.Ac.p, c.rc.p, c.yc.p, (double*)nullptr, (double*)nullptr, done);
+        LAUNCH(k_coarse_dot, 1, 256, c.nC, c.rc.p, c.yc.p, tail, acc, acc2, done);
+        return VMM_BA_OK;
+    }
     LAUNCH(k_coarse_apply, (c.nC + 7) / 8, 256, c.nC, c.Ac.p, c.rc.p, c.yc.p, acc, acc2, done);
+    return VMM_BA_OK;
 }
 
 // A_c = P^T S P at the current linearisation and damping, then its inverse (dense, cuSOLVER potrf + potri:
@@ -392,25 +418,43 @@ void coarse_correction(vmm_ba_engine* e, double* acc, double* acc2, const double
 int coarse_setup(vmm_ba_engine* e, int slot) {
     auto& c = e->coarse;
     c.active = false;
-    if (!c.available || e->world != 1) return VMM_BA_OK;
+    if (!c.available) return VMM_BA_OK;
     const size_t n = (size_t)c.nC;
     CU(cudaMemsetAsync(c.Ac.p, 0, sizeof(double) * n * n, e->stream));
     LAUNCH(k_coarse_diag, c.ncl, kCoarseThreads, c.cl_ptr.p, c.cl_cams.p, c.xbar.p, e->camP[slot].p, e->B.p, e->lam_c.p, c.nC, c.Ac.p);
-    if (e->Ntol > 0)
-        LAUNCH(k_coarse_offdiag, (int)e->Nm, kCoarseThreads, e->mptr.p, e->tag_active.p, e->mtile.p, e->mo_cam.p, c.mo_lc.p, c.mcl_ptr.p,
-               c.mcl.p, c.cl_of_cam.p, c.xbar.p, e->camP[slot].p, e->Es.p, c.nC, c.Ac.p);
+    if (c.n_w > 0) {
+        if (e->world > 1) CU(cudaMemsetAsync(c.Wbuf.p, 0, sizeof(double) * 36 * c.n_w, e->stream));   // markers without local observations
+        LAUNCH(k_coarse_w, (int)e->Nm, kCoarseThreads, e->mptr.p, e->tag_active.p, e->mtile.p, e->mo_cam.p, c.mo_lc.p, c.mcl_ptr.p,
+               c.cl_of_cam.p, c.xbar.p, e->camP[slot].p, e->Es.p, c.Wbuf.p);
+        int rc = allreduce(e, c.Wbuf.p, 36 * c.n_w, NCCL_SUM);
+        if (rc) return rc;
+        // the outer products are split over ranks by marker; the parts of A_c (diagonal blocks included) are summed below
+        const int mine = (int)((e->Nm - e->rank + e->world - 1) / e->world);
+        if (mine > 0)
+            LAUNCH(k_coarse_outer, mine, kCoarseThreads, (int)e->Nm, e->rank, e->world, e->tag_active.p, c.mcl_ptr.p, c.mcl.p, c.Wbuf.p, c.nC, c.Ac.p);
+    }
+    {
+        int rc = allreduce(e, c.Ac.p, n * n, NCCL_SUM);
+        if (rc) return rc;
+    }
     if (cusolverDnSetStream(e->cusolver, e->stream) != CUSOLVER_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cusolverDnSetStream failed");
     LIBCALL_NAMED("cusolverDnDpotrf", cusolverDnDpotrf(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) == CUSOLVER_STATUS_SUCCESS,
                   "cusolverDnDpotrf");
     int h_info[2] = { 0, 0 };
     CU(cudaMemcpyAsync(&h_info[0], c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    LIBCALL_NAMED("cusolverDnDpotri", cusolverDnDpotri(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) == CUSOLVER_STATUS_SUCCESS,
-                  "cusolverDnDpotri");
-    CU(cudaMemcpyAsync(&h_info[1], c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    // A_c^-1 = L^-T L^-1: X = L^-1 by a triangular solve against the identity, then X^T X (two plain cuBLAS level-3
+    // calls, ~1 ms together at n = 3000; cusolverDnDpotri needs 7.8 ms for the same result)
+    if (cublasSetStream(e->cublas, e->stream) != CUBLAS_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cublasSetStream failed");
+    LAUNCH(k_identity, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Linv.p);
+    const double one = 1.0, zero = 0.0;
+    LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, c.nC, c.nC, &one,
+                                             c.Ac.p, c.nC, c.Linv.p, c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
+    LIBCALL_NAMED("cublasDsyrk", cublasDsyrk(e->cublas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, c.nC, c.nC, &one, c.Linv.p, c.nC, &zero, c.Ac.p,
+                                             c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDsyrk");
     LAUNCH(k_symmetrize, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Ac.p);
     CU(cudaStreamSynchronize(e->stream));
     if (e->profiling) profile_resolve(e);
-    c.active = (h_info[0] == 0 && h_info[1] == 0);   // not positive definite: this iteration runs block-Jacobi only
+    c.active = (h_info[0] == 0);   // not positive definite: this iteration runs block-Jacobi only
     return VMM_BA_OK;
 }
 
@@ -425,19 +469,30 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
     const int gb = nblocks(std::max<int64_t>(nc, 1), kThreads);
     const int check_every = 8;
     double* done = e->sc.p + SC_DONE;
+    // p.(B+lam)p and w.w pairs: one GPU keeps them in the tail of w and in sc; a sharded engine in the tail of the
+    // boundary vector wb (pbp0, pbp1, ww0, ww1), which its all-reduce carries
+    double* pbp = e->world == 1 ? e->pbp() : e->wb.p + 6 * e->n_bnd;
+    const double* wz = e->world == 1 ? e->sc.p + SC_WZ : pbp + 2;
+    // where k_pcg_update leaves r.z of the next iteration: sc[SC_RZ + o], or — sharded two-level — the tail of the
+    // restricted residual, whose all-reduce completes it (k_coarse_dot then writes sc[SC_RZ + o])
+    const bool rz_in_tail = e->world > 1 && e->coarse.active;
+    double* rz_next = rz_in_tail ? e->coarse.rc.p + e->coarse.nC : e->sc.p + SC_RZ;
+    const int rz_stride = rz_in_tail ? 0 : 1;
     CU(cudaMemsetAsync(e->sc.p, 0, sizeof(double) * SC_N, e->stream));
-    CU(cudaMemsetAsync(e->pbp(), 0, sizeof(double) * 2, e->stream));
+    CU(cudaMemsetAsync(pbp, 0, sizeof(double) * (e->world == 1 ? 2 : 4), e->stream));
     const bool two_level = e->coarse.active;
     CoarseView cv{ nullptr, nullptr, nullptr, nullptr };
     if (two_level) cv = CoarseView{ e->coarse.cl_of_cam.p, e->coarse.xbar.p, e->camP[e->cur].p, e->coarse.yc.p };
     LAUNCH(k_pcg_init, gb, kThreads, nc, e->Minv.p, e->pr.p, e->px.p, e->pz.p, e->pp.p, e->sc.p);
-    if (two_level) coarse_correction(e, e->sc.p + SC_RZ, e->sc.p + SC_RZ0, nullptr);
-    if (e->world > 1) {
+    if (two_level) {   // sums the local partials of rz0 (sc[SC_RZ], sc[SC_RZ0]) over ranks on the way
+        int rc = coarse_correction(e, e->sc.p + SC_RZ, e->sc.p + SC_RZ0, nullptr);
+        if (rc) return rc;
+    } else if (e->world > 1) {
         int rc = allreduce(e, e->sc.p, 5, NCCL_SUM);   // rz0 (sc[0], sc[4]) are local partials
         if (rc) return rc;
     }
     // first direction: p = z (+ P yc), q = (B + lam) p, pBp[0]
-    LAUNCH(k_pcg_direction, gb, kThreads, nc, 1, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, e->pbp(), 0, 1, tol * tol, cv);
+    LAUNCH(k_pcg_direction, gb, kThreads, nc, 1, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, pbp, 0, 1, tol * tol, cv);
     out->iterations = 0;
     out->ok = true;
     out->rel = 1.0;
@@ -448,21 +503,31 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
             int rc = schur_offdiag(e, e->pp.p, e->pq.p, e->sc.p + SC_WZ + s, done, e->sc.p + SC_RZ + o, e->sc.p + SC_WZ + o, e->pbp() + o);
             if (rc) return rc;
         } else {
-            // w = Es^T p per rank, summed over ranks together with the local p.(B+lam)p partials in its tail
-            int rc = schur_gather(e, e->pp.p, e->w.p, done, e->sc.p + SC_RZ + o, e->sc.p + SC_WZ + o, e->pbp() + o);
+            // markers seen from this rank only: one pass over their blocks, as on one GPU.  The others: w = Es^T p per
+            // rank into the compact boundary vector, summed over ranks together with the local p.(B+lam)p and w.w
+            // partials in its tail, then scattered back.  rz[o], ww[o], pbp[o] (next iteration's sums) are cleared first.
+            double* ww = pbp + 2;
+            LAUNCH(k_zero_boundary, nblocks(6 * e->n_bnd + 3, kThreads), kThreads, (int)(6 * e->n_bnd), e->wb.p, rz_next + o * rz_stride, ww + o, pbp + o,
+                   (const double*)done);
+            if (e->seg_full.count > 0)
+                schur_launch<SP_FULL>(e, e->seg_full, e->pp.p, nullptr, -1.0, e->pq.p, ww + s, done, nullptr, nullptr, nullptr);
+            if (e->seg_big.count > 0)
+                schur_launch<SP_GATHER>(e, e->seg_big, e->pp.p, e->wb.p, 1.0, nullptr, nullptr, done, nullptr, nullptr, nullptr);
+            int rc = allreduce(e, e->wb.p, 6 * (size_t)e->n_bnd + 4, NCCL_SUM);
             if (rc) return rc;
-            rc = allreduce(e, e->w.p, 6 * (size_t)nm + 2, NCCL_SUM);
-            if (rc) return rc;
-            LAUNCH(k_sum_squares, nblocks(6 * nm, kThreads), kThreads, 6 * nm, e->w.p, e->sc.p + SC_WZ + s, (const double*)done);
-            schur_scatter(e, e->w.p, -1.0, e->pq.p, done);
+            if (e->n_bnd > 0) LAUNCH(k_sum_squares, nblocks(6 * e->n_bnd, kThreads), kThreads, (int)(6 * e->n_bnd), e->wb.p, ww + s, (const double*)done);
+            if (e->seg_big.count > 0)
+                schur_launch<SP_SCATTER>(e, e->seg_big, nullptr, e->wb.p, -1.0, e->pq.p, nullptr, done, nullptr, nullptr, nullptr);
         }
-        LAUNCH(k_pcg_update, gb, kThreads, nc, s, e->Minv.p, e->pp.p, e->pq.p, e->px.p, e->pr.p, e->pz.p, e->sc.p, e->pbp());
-        if (e->world > 1) {
+        LAUNCH(k_pcg_update, gb, kThreads, nc, s, e->Minv.p, e->pp.p, e->pq.p, e->px.p, e->pr.p, e->pz.p, e->sc.p, pbp, wz, rz_next + o * rz_stride);
+        if (two_level) {
+            int rc = coarse_correction(e, e->sc.p + SC_RZ + o, nullptr, done, e->world > 1);
+            if (rc) return rc;
+        } else if (e->world > 1) {
             int rc = allreduce(e, e->sc.p + SC_RZ + o, 1, NCCL_SUM);
             if (rc) return rc;
         }
-        if (two_level) coarse_correction(e, e->sc.p + SC_RZ + o, nullptr, done);
-        LAUNCH(k_pcg_direction, gb, kThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, e->pbp(), it + 1,
+        LAUNCH(k_pcg_direction, gb, kThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, pbp, it + 1,
                min_it, tol2, cv);
         out->iterations = it + 1;
         if ((it + 1) % check_every == 0 || it + 1 == max_it) {
@@ -723,16 +788,25 @@ int upload_seglist(vmm_ba_engine* e, vmm_ba_engine::SegList& L, std::vector<Host
     return VMM_BA_OK;
 }
 
-int build_segments(vmm_ba_engine* e, const std::vector<int>& mptr, const std::vector<int>& mtile, const std::vector<unsigned char>& active) {
+int build_segments(vmm_ba_engine* e, const std::vector<int>& mptr, const std::vector<int>& mtile, const std::vector<unsigned char>& active,
+                   const std::vector<int>& bnd_id) {
+    // one GPU:  full = whole markers (one pass), big = sub-segments of the markers too long for that, all = every marker as sub-segments
+    // sharded:  full = markers seen from this rank only, big = sub-segments of the others with .marker = their compact
+    //           (boundary) number, all = every marker as sub-segments with .marker = j (right-hand side, back-substitution)
     std::vector<HostSeg> full, big, all;
+    const bool sharded = e->world > 1;
     for (int64_t j = 0; j < e->Nm; ++j) {
         const int n = mptr[j + 1] - mptr[j];
         if (!active[j] || n == 0) continue;
-        if (n <= kSegMaxObs) full.push_back(HostSeg{ SpSeg{ (int)j, 0, n, mptr[j] }, mtile[j] });
+        const bool whole = sharded ? bnd_id[j] < 0 : n <= kSegMaxObs;
+        if (whole) full.push_back(HostSeg{ SpSeg{ (int)j, 0, n, mptr[j] }, mtile[j] });
         for (int o = 0; o < n; o += kSegRegObs) {
-            const HostSeg d{ SpSeg{ (int)j, 0, std::min(kSegRegObs, n - o), mptr[j] + o }, mtile[j] + o / kTileObs };
+            HostSeg d{ SpSeg{ (int)j, 0, std::min(kSegRegObs, n - o), mptr[j] + o }, mtile[j] + o / kTileObs };
             all.push_back(d);
-            if (n > kSegMaxObs) big.push_back(d);
+            if (!whole) {
+                if (sharded) d.d.marker = bnd_id[j];
+                big.push_back(d);
+            }
         }
     }
     int rc = upload_seglist(e, e->seg_full, full);
@@ -741,91 +815,134 @@ int build_segments(vmm_ba_engine* e, const std::vector<int>& mptr, const std::ve
     return rc;
 }
 
-// Camera clusters of the coarse space: k-d median splits of the (active) camera centres C = -R^T t at the
-// initial poses, the clusters every marker touches and, per marker-order observation, the position of its
-// camera's cluster in that marker's list.  Host side, once per problem.
-int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, const std::vector<unsigned char>& cam_active,
-                   const std::vector<int>& mptr, const std::vector<int>& mocam, const std::vector<unsigned char>& tag_active) {
-    auto& c = e->coarse;
-    c.available = false;
-    c.active = false;
-    const int64_t Ncl = e->Ncl, Nm = e->Nm;
-    if (e->world != 1 || Ncl == 0) return VMM_BA_OK;
-    std::vector<int> act;
-    for (int64_t i = 0; i < Ncl; ++i) if (cam_active[i]) act.push_back((int)i);
-    const int kMaxClusters = 768;
-    int target = std::max(8, e->coarse_cams_per_cluster);
-    target = std::max<int>(target, (int)((act.size() + kMaxClusters - 1) / kMaxClusters) * 2);   // the k-d leaves hold target/2 .. target cameras
-    if ((int64_t)act.size() < 2 * (int64_t)target) return VMM_BA_OK;   // one cluster = the gauge mode of a single block: nothing to gain
-    std::vector<double> ctr(3 * Ncl, 0.0);
-    for (int i : act) {
-        const double* q = cam_q + 4 * (e->cam0 + i);
-        const double* t = cam_t + 3 * (e->cam0 + i);
+// Camera centres C = -R^T t of the listed cameras (3 doubles per camera of the problem, zeros elsewhere).
+void camera_centres(const double* cam_q, const double* cam_t, const std::vector<int>& cams, int64_t Nc, std::vector<double>& ctr) {
+    ctr.assign(3 * (size_t)Nc, 0.0);
+    for (int i : cams) {
+        const double* q = cam_q + 4 * (size_t)i;
+        const double* t = cam_t + 3 * (size_t)i;
         double R[9];
         quat_to_rot(q, R);
-        for (int a = 0; a < 3; ++a) ctr[3 * i + a] = -(R[a] * t[0] + R[3 + a] * t[1] + R[6 + a] * t[2]);
+        for (int a = 0; a < 3; ++a) ctr[3 * (size_t)i + a] = -(R[a] * t[0] + R[3 + a] * t[1] + R[6 + a] * t[2]);
     }
-    // iterative k-d splitting of index ranges of `act`
-    std::vector<std::pair<int, int>> stack{ { 0, (int)act.size() } }, leaves;
+}
+
+// k-d median splits of `act` (reordered in place) along the widest axis until a leaf holds at most `target`
+// cameras; the leaves come back as index ranges of `act` in depth-first (spatially coherent) order.
+// Ties are broken by camera index: every rank of a sharded engine must arrive at the same split.
+void kd_leaves(std::vector<int>& act, const std::vector<double>& ctr, int target, std::vector<std::pair<int, int>>& leaves) {
+    leaves.clear();
+    std::vector<std::pair<int, int>> stack{ { 0, (int)act.size() } };
     while (!stack.empty()) {
         auto [lo, hi] = stack.back();
         stack.pop_back();
         if (hi - lo <= target) { leaves.push_back({ lo, hi }); continue; }
         double mn[3] = { 1e300, 1e300, 1e300 }, mx[3] = { -1e300, -1e300, -1e300 };
         for (int k = lo; k < hi; ++k)
-            for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], ctr[3 * act[k] + a]); mx[a] = std::max(mx[a], ctr[3 * act[k] + a]); }
+            for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], ctr[3 * (size_t)act[k] + a]); mx[a] = std::max(mx[a], ctr[3 * (size_t)act[k] + a]); }
         int ax = 0;
         for (int a = 1; a < 3; ++a) if (mx[a] - mn[a] > mx[ax] - mn[ax]) ax = a;
         const int mid = lo + (hi - lo) / 2;
-        std::nth_element(act.begin() + lo, act.begin() + mid, act.begin() + hi, [&](int a, int b) { return ctr[3 * a + ax] < ctr[3 * b + ax]; });
+        std::nth_element(act.begin() + lo, act.begin() + mid, act.begin() + hi, [&](int a, int b) {
+            const double va = ctr[3 * (size_t)a + ax], vb = ctr[3 * (size_t)b + ax];
+            return va < vb || (va == vb && a < b);
+        });
         stack.push_back({ lo, mid });
         stack.push_back({ mid, hi });
     }
+    std::sort(leaves.begin(), leaves.end());
+}
+
+int coarse_leaf_target(const vmm_ba_engine* e, size_t n_active) {
+    const int kMaxClusters = 768;
+    int target = std::max(8, e->coarse_cams_per_cluster);
+    return std::max<int>(target, (int)((n_active + kMaxClusters - 1) / kMaxClusters) * 2);   // the k-d leaves hold target/2 .. target cameras
+}
+
+// Camera clusters of the coarse space: k-d median splits of the (active) camera centres C = -R^T t at the
+// initial poses — over ALL cameras, identically on every rank of a sharded engine — the clusters every
+// marker touches (over all ranks' observations) and, per local marker-order observation, the position of
+// its camera's cluster in that marker's list.  Host side, once per problem.
+int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, const std::vector<int64_t>& cam_count, int64_t Nto,
+                   const int32_t* to_cam, const int32_t* to_tag, const std::vector<int>& mptr, const std::vector<int>& mocam,
+                   const std::vector<unsigned char>& tag_active) {
+    auto& c = e->coarse;
+    c.available = false;
+    c.active = false;
+    const int64_t Nc = e->Nc, Ncl = e->Ncl, Nm = e->Nm;
+    if (Nc == 0) return VMM_BA_OK;
+    std::vector<int> act;
+    for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
+    const int target = coarse_leaf_target(e, act.size());
+    if ((int64_t)act.size() < 2 * (int64_t)target) return VMM_BA_OK;   // one cluster = the gauge mode of a single block: nothing to gain
+    std::vector<double> ctr;
+    camera_centres(cam_q, cam_t, act, Nc, ctr);
+    std::vector<std::pair<int, int>> leaves;
+    kd_leaves(act, ctr, target, leaves);
     const int ncl = (int)leaves.size();
     if (ncl < 2) return VMM_BA_OK;
-    std::vector<int> cl_of(Ncl, -1), cl_ptr(ncl + 1, 0), cl_cams(act.size());
+    std::vector<int> cl_of_g(Nc, -1), cl_of(std::max<int64_t>(Ncl, 1), -1), cl_ptr(ncl + 1, 0), cl_cams;
     std::vector<double> xbar(3 * (size_t)ncl, 0.0);
-    std::sort(leaves.begin(), leaves.end());
+    cl_cams.reserve(Ncl);
     for (int cidx = 0; cidx < ncl; ++cidx) {
         const auto [lo, hi] = leaves[cidx];
-        cl_ptr[cidx] = lo;
+        cl_ptr[cidx] = (int)cl_cams.size();
         for (int k = lo; k < hi; ++k) {
-            cl_of[act[k]] = cidx;
-            cl_cams[k] = act[k];
-            for (int a = 0; a < 3; ++a) xbar[3 * cidx + a] += ctr[3 * act[k] + a] / (hi - lo);
+            const int g = act[k];
+            cl_of_g[g] = cidx;
+            for (int a = 0; a < 3; ++a) xbar[3 * (size_t)cidx + a] += ctr[3 * (size_t)g + a] / (hi - lo);
+        }
+        // this rank's cameras of the cluster, ascending (fixed summation order)
+        const size_t first = cl_cams.size();
+        for (int k = lo; k < hi; ++k)
+            if (act[k] >= e->cam0 && act[k] < e->cam1) cl_cams.push_back((int)(act[k] - e->cam0));
+        std::sort(cl_cams.begin() + first, cl_cams.end());
+        for (size_t q = first; q < cl_cams.size(); ++q) cl_of[cl_cams[q]] = cidx;
+    }
+    cl_ptr[ncl] = (int)cl_cams.size();
+    // clusters touched per marker (all observations of the problem, caller's order)
+    std::vector<int> lst((size_t)Nm * kCoarseMaxTouched), cnt(Nm, 0);
+    for (int64_t k = 0; k < Nto; ++k) {
+        const int j = to_tag[k];
+        if (!tag_active[j]) continue;
+        const int cc = cl_of_g[to_cam[k]];
+        int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
+        int pos = 0;
+        while (pos < cnt[j] && l[pos] != cc) ++pos;
+        if (pos == cnt[j]) {
+            if (cnt[j] >= kCoarseMaxTouched) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
+            l[cnt[j]++] = cc;
         }
     }
-    cl_ptr[ncl] = (int)act.size();
-    // clusters touched per marker, local position per marker-order observation
     std::vector<int> mcl_ptr(Nm + 1, 0), mcl;
+    for (int64_t j = 0; j < Nm; ++j) {
+        mcl.insert(mcl.end(), lst.begin() + (size_t)j * kCoarseMaxTouched, lst.begin() + (size_t)j * kCoarseMaxTouched + cnt[j]);
+        mcl_ptr[j + 1] = (int)mcl.size();
+    }
     std::vector<unsigned char> mo_lc(std::max<size_t>(mocam.size(), 1), 0);
     for (int64_t j = 0; j < Nm; ++j) {
-        const size_t base = mcl.size();
-        if (tag_active[j]) {
-            for (int k = mptr[j]; k < mptr[j + 1]; ++k) {
-                const int cc = cl_of[mocam[k]];
-                size_t pos = base;
-                while (pos < mcl.size() && mcl[pos] != cc) ++pos;
-                if (pos == mcl.size()) {
-                    if ((int)(mcl.size() - base) >= kCoarseMaxTouched) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
-                    mcl.push_back(cc);
-                }
-                mo_lc[k] = (unsigned char)(pos - base);
-            }
+        if (!tag_active[j]) continue;
+        const int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
+        for (int k = mptr[j]; k < mptr[j + 1]; ++k) {
+            const int cc = cl_of[mocam[k]];
+            int pos = 0;
+            while (l[pos] != cc) ++pos;
+            mo_lc[k] = (unsigned char)pos;
         }
-        mcl_ptr[j + 1] = (int)mcl.size();
     }
     c.ncl = ncl;
     c.nC = 6 * ncl;
+    c.n_w = mcl.size();
     const size_t n = (size_t)c.nC;
-    CU(c.cl_of_cam.alloc(Ncl)); CU(c.cl_ptr.alloc(ncl + 1)); CU(c.cl_cams.alloc(std::max<size_t>(cl_cams.size(), 1)));
+    CU(c.cl_of_cam.alloc(std::max<int64_t>(Ncl, 1))); CU(c.cl_ptr.alloc(ncl + 1)); CU(c.cl_cams.alloc(std::max<size_t>(cl_cams.size(), 1)));
     CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1))); CU(c.mo_lc.alloc(mo_lc.size()));
-    CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(n * n)); CU(c.rc.alloc(n)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
-    int lw1 = 0, lw2 = 0;
-    if (cusolverDnDpotrf_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, &lw1) != CUSOLVER_STATUS_SUCCESS ||
-        cusolverDnDpotri_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, &lw2) != CUSOLVER_STATUS_SUCCESS)
+    CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(n * n)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
+    CU(c.Wbuf.alloc(std::max<size_t>(36 * c.n_w, 1)));
+    CU(c.Linv.alloc(n * n));
+    int lw1 = 0;
+    if (cusolverDnDpotrf_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, &lw1) != CUSOLVER_STATUS_SUCCESS)
         return fail_with(e, VMM_BA_ERR_CUDA, "cusolver buffer size query failed");
-    c.lwork = std::max(lw1, lw2);
+    c.lwork = lw1;
     CU(c.work.alloc(std::max(c.lwork, 1)));
     auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
     CU(up(c.cl_of_cam.p, cl_of.data(), sizeof(int) * Ncl));
@@ -942,6 +1059,10 @@ static int create_common(int device, vmm_ba_engine** out) {
         delete e;
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "cusolverDnCreate failed");
     }
+    if (cublasCreate(&e->cublas) != CUBLAS_STATUS_SUCCESS) {
+        delete e;
+        return fail_with(nullptr, VMM_BA_ERR_CUDA, "cublasCreate failed");
+    }
     if ((err = cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
         delete e;
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(err));
@@ -1001,6 +1122,7 @@ int vmm_ba_destroy(vmm_ba_handle e) {
     cudaDeviceSynchronize();
     if (e->comm) nccl_api().CommDestroy(e->comm);
     if (e->cusolver) cusolverDnDestroy(e->cusolver);
+    if (e->cublas) cublasDestroy(e->cublas);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
     for (auto& p : e->prof_pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& ev : e->prof_free) cudaEventDestroy(ev);
@@ -1067,6 +1189,42 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         if (k > 0 && to_cam[k - 1] > c) sorted = false;
     }
     e->Nc = Nc; e->Nm = Nm; e->Nto = Nto; e->fixed_tag = fixed_tag;
+    // sharded: spatial renumbering of the cameras (see cam_order); the permuted copies shadow the caller's arrays
+    std::vector<double> cam_q_p, cam_t_p;
+    std::vector<int32_t> to_cam_p;
+    e->cam_order.clear();
+    if (e->world > 1 && Nc > 0) {
+        std::vector<int> act, order;
+        for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
+        std::vector<double> ctr;
+        camera_centres(cam_q, cam_t, act, Nc, ctr);
+        std::vector<std::pair<int, int>> leaves;
+        kd_leaves(act, ctr, std::max(8, coarse_leaf_target(e, act.size())), leaves);
+        order.reserve(Nc);
+        for (const auto& lf : leaves) {
+            const size_t first = order.size();
+            order.insert(order.end(), act.begin() + lf.first, act.begin() + lf.second);
+            std::sort(order.begin() + first, order.end());
+        }
+        for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] == 0) order.push_back((int)i);
+        std::vector<int> pos(Nc);
+        for (int64_t i = 0; i < Nc; ++i) pos[order[i]] = (int)i;
+        cam_q_p.resize(4 * (size_t)Nc); cam_t_p.resize(3 * (size_t)Nc);
+        std::vector<int64_t> cc(Nc);
+        for (int64_t i = 0; i < Nc; ++i) {
+            const int src = order[i];
+            for (int a = 0; a < 4; ++a) cam_q_p[4 * i + a] = cam_q[4 * (size_t)src + a];
+            for (int a = 0; a < 3; ++a) cam_t_p[3 * i + a] = cam_t[3 * (size_t)src + a];
+            cc[i] = cam_count[src];
+        }
+        cam_count.swap(cc);
+        to_cam_p.resize(Nto);
+        for (int64_t k = 0; k < Nto; ++k) to_cam_p[k] = pos[to_cam[k]];
+        cam_q = cam_q_p.data(); cam_t = cam_t_p.data(); to_cam = to_cam_p.data();
+        sorted = false;
+        e->cam_order.swap(order);
+        phase("spatial camera order");
+    }
     std::vector<int64_t> cam_ptr(Nc + 1, 0);
     for (int64_t i = 0; i < Nc; ++i) cam_ptr[i + 1] = cam_ptr[i] + cam_count[i];
     phase("validate + count");
@@ -1086,6 +1244,22 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         for (int64_t k = 0; k < Nto; ++k)
             if (to_cam[k] >= e->cam0 && to_cam[k] < e->cam1) h_mptr[to_tag[k] + 1]++;
         for (int64_t j = 0; j < Nm; ++j) h_mptr[j + 1] += h_mptr[j];
+    }
+    // compact numbering of the markers that need the gather / all-reduce / scatter path (same on every rank)
+    std::vector<int> bnd_id(Nm, -1);
+    e->n_bnd = 0;
+    if (e->world > 1) {
+        std::vector<int> cam_rank(std::max<int64_t>(Nc, 1), 0), first(Nm, -1);
+        std::vector<unsigned char> multi(Nm, 0);
+        for (int r = 0; r < e->world; ++r)
+            for (int64_t i = begin[r]; i < begin[r + 1]; ++i) cam_rank[i] = r;
+        for (int64_t k = 0; k < Nto; ++k) {
+            const int j = to_tag[k], r = cam_rank[to_cam[k]];
+            if (first[j] < 0) first[j] = r; else if (first[j] != r) multi[j] = 1;
+        }
+        for (int64_t j = 0; j < Nm; ++j)
+            if (tag_count[j] > 0 && (multi[j] || tag_count[j] > kSegMaxObs)) bnd_id[j] = (int)e->n_bnd++;
+        CU(e->wb.alloc(6 * (size_t)e->n_bnd + 4));
     }
 
     // the caller's arrays go to the device as they are; both orders are built there (ba_stage.cuh)
@@ -1173,10 +1347,10 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     phase("uploads");
     {
         // segment lists (active markers only: the constant origin tag and unobserved tags have no columns)
-        int rc = build_segments(e, h_mptr, h_mtile, h_tact);
+        int rc = build_segments(e, h_mptr, h_mtile, h_tact, bnd_id);
         if (rc) return rc;
         phase("segment lists");
-        rc = build_clusters(e, cam_q, cam_t, h_cact, h_mptr, h_mocam, h_tact);
+        rc = build_clusters(e, cam_q, cam_t, cam_count, Nto, to_cam, to_tag, h_mptr, h_mocam, h_tact);
         if (rc) return rc;
         phase("camera clusters");
     }
@@ -1196,6 +1370,16 @@ int vmm_ba_set_poses(vmm_ba_handle e, const double* cam_q, const double* cam_t, 
     if ((e->Nc > 0 && (!cam_q || !cam_t)) || !tag_q || !tag_t) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null array");
     CU(cudaSetDevice(e->device));
     const int s = e->cur;
+    std::vector<double> qp, tp;
+    if (!e->cam_order.empty()) {   // caller's camera order -> internal order (this rank's range only)
+        qp.resize(4 * (size_t)e->Ncl); tp.resize(3 * (size_t)e->Ncl);
+        for (int64_t i = 0; i < e->Ncl; ++i) {
+            const size_t src = (size_t)e->cam_order[e->cam0 + i];
+            for (int a = 0; a < 4; ++a) qp[4 * i + a] = cam_q[4 * src + a];
+            for (int a = 0; a < 3; ++a) tp[3 * i + a] = cam_t[3 * src + a];
+        }
+        cam_q = qp.data() - 4 * e->cam0; cam_t = tp.data() - 3 * e->cam0;
+    }
     if (e->Ncl > 0) {
         CU(cudaMemcpyAsync(e->cam_q[s].p, cam_q + 4 * e->cam0, sizeof(double) * 4 * e->Ncl, cudaMemcpyHostToDevice, e->stream));
         CU(cudaMemcpyAsync(e->cam_t[s].p, cam_t + 3 * e->cam0, sizeof(double) * 3 * e->Ncl, cudaMemcpyHostToDevice, e->stream));
@@ -1220,8 +1404,16 @@ static int gather_cameras(vmm_ba_engine* e, const double* local_dev, int width, 
         CU(cudaMemcpyAsync(e->gather.p + (size_t)width * e->cam0, local_dev, sizeof(double) * width * e->Ncl, cudaMemcpyDeviceToDevice, e->stream));
     int rc = allreduce(e, e->gather.p, n, NCCL_SUM);
     if (rc) return rc;
-    CU(cudaMemcpyAsync(host_out, e->gather.p, sizeof(double) * n, cudaMemcpyDeviceToHost, e->stream));
+    if (e->cam_order.empty()) {
+        CU(cudaMemcpyAsync(host_out, e->gather.p, sizeof(double) * n, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        return VMM_BA_OK;
+    }
+    std::vector<double> tmp(n);   // internal camera order -> caller's
+    CU(cudaMemcpyAsync(tmp.data(), e->gather.p, sizeof(double) * n, cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
+    for (int64_t i = 0; i < e->Nc; ++i)
+        for (int a = 0; a < width; ++a) host_out[(size_t)width * e->cam_order[i] + a] = tmp[(size_t)width * i + a];
     return VMM_BA_OK;
 }
 

@@ -319,6 +319,18 @@ k_sum_squares(int n, const double* __restrict__ v, double* __restrict__ acc, con
     if (threadIdx.x == 0) atomicAdd(acc, s);
 }
 
+// sharded engines, start of a PCG iteration: clears the boundary vector and the three accumulators of the
+// next iteration (one GPU does the latter inside the product kernel)
+__global__ void k_zero_boundary(int n, double* __restrict__ wb, double* __restrict__ a, double* __restrict__ b,
+                                double* __restrict__ c, const double* __restrict__ done) {
+    if (done && *done != 0.0) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) wb[i] = 0.0;
+    else if (i == n) *a = 0.0;
+    else if (i == n + 1) *b = 0.0;
+    else if (i == n + 2) *c = 0.0;
+}
+
 // PCG scalars, device resident. Slot parity s = iteration & 1.
 //   sc[0+s] rz = r.M^-1 r   sc[2+s] wz = w.w (w = Es^T p)   sc[4] rz0      pbp[s] = p.(B+lam)p
 //   sc[5] done flag (set on device when rz <= tol^2 rz0; every later PCG launch is then a no-op)
@@ -357,11 +369,12 @@ k_pcg_init(int nc, const double* __restrict__ Minv, const double* __restrict__ r
 __global__ void __launch_bounds__(kThreads)
 k_pcg_update(int nc, int s, const double* __restrict__ Minv, const double* __restrict__ p,
              const double* __restrict__ q, double* __restrict__ x, double* __restrict__ r, double* __restrict__ z,
-             double* __restrict__ sc, const double* __restrict__ pbp) {
+             double* __restrict__ sc, const double* __restrict__ pbp, const double* __restrict__ wz,
+             double* __restrict__ rz_out) {
     if (sc[SC_DONE] != 0.0) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int o = s ^ 1;
-    const double denom = pbp[s] - sc[2 + s];
+    const double denom = pbp[s] - wz[s];
     const double alpha = (sc[0 + s] != 0.0) ? sc[0 + s] / denom : 0.0;
     double rz = 0.0;
     if (i < nc) {
@@ -384,7 +397,7 @@ k_pcg_update(int nc, int s, const double* __restrict__ Minv, const double* __res
         }
     }
     const double s1 = block_sum(rz);
-    if (threadIdx.x == 0) atomicAdd(sc + 0 + o, s1);
+    if (threadIdx.x == 0) atomicAdd(rz_out, s1);
 }
 
 // beta = rz[o] / rz[s]; p = z + beta p; q = (B + lam) p; pBp[o] += p.q
