@@ -90,7 +90,7 @@ typedef struct {
                                              while the last PCG solve took at most this many iterations more than the
                                              first solve after the last refresh (a stale preconditioner changes the
                                              iteration count, not the solution); 0 = refresh every LM iteration.
-                                             default 32 (about the set-up's cost in PCG iterations) */
+                                             default 8 (the set-up costs about 17 PCG iterations at C3) */
 } vmm_ba_options;
 
 /* replaces: ceres::Solver::Summary (the reference only prints termination_type / FullReport) */
@@ -208,13 +208,25 @@ int vmm_ba_set_coarse_cluster_size(vmm_ba_handle h, int cameras_per_cluster);
  * sharded form).  The parity tests check both against the product formed from the oracle's Jacobian. */
 int vmm_ba_schur_multiply(vmm_ba_handle h, int loss_kind, double loss_scale, double radius, int path, const double* x, double* y);
 
-/* Camera range [begin,end) and tag-observation count owned by this engine. */
+/* Camera range [begin,end) — positions in the engine's internal camera sequence, which is the caller's on one GPU
+ * and the spatial order of vmm_ba_shard_plan on a distributed engine — and tag-observation count owned by this engine. */
 int vmm_ba_shard_info(vmm_ba_handle h, int64_t* cam_begin, int64_t* cam_end, int64_t* num_local_tag_obs);
 
-/* Host-side partition used by distributed engines: cameras split into `world_size` contiguous
- * ranges balanced by tag-observation count.  cam_begin has world_size+1 entries.  Needs no GPU. */
+/* The cut used by distributed engines on a camera sequence: `world_size` contiguous ranges balanced by
+ * tag-observation count.  cam_begin has world_size+1 entries.  Needs no GPU.  (A distributed engine applies it to
+ * its spatially renumbered camera sequence, see vmm_ba_shard_plan.) */
 int vmm_ba_partition_cameras(int64_t num_cameras, int64_t num_tag_obs, const int32_t* to_cam, int world_size,
                              int64_t* cam_begin);
+
+/* The sharding plan a distributed engine of `world_size` ranks applies to this problem (needs no GPU): cameras are
+ * renumbered in a spatially coherent order (k-d leaves of the camera centres, `cameras_per_cluster` per leaf, 0 = the
+ * default) and that sequence is cut into `world_size` ranges balanced by tag-observation count, so that most markers
+ * are seen from one rank only.  cam_rank_out[i] = owner of the caller's camera i; marker_boundary_out[j] = -1 when all
+ * blocks of marker j live on one rank (handled there in one pass), else its position in the compact boundary vector
+ * that is all-reduced once per PCG iteration.  Either output may be NULL. */
+int vmm_ba_shard_plan(int64_t num_cameras, const double* cam_q, const double* cam_t, int64_t num_markers, int64_t num_tag_obs,
+                      const int32_t* to_cam, const int32_t* to_tag, int world_size, int cameras_per_cluster, int32_t* cam_rank_out,
+                      int32_t* marker_boundary_out);
 
 /* Number of kernel launches issued by this library on this handle since creation. */
 int64_t vmm_ba_kernel_launches(vmm_ba_handle h);

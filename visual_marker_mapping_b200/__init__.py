@@ -7,10 +7,10 @@ and csrc/host/ (C++ TagReconstructor facade); this package is the Python plumbin
 from . import synth  # noqa: F401
 from .engine import (  # noqa: F401
     BundleAdjuster, Options, Summary, VmmBaError, default_options, device_count, load_library,
-    partition_cameras, LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY, CONVERGENCE, NO_CONVERGENCE, FAILURE,
+    partition_cameras, shard_plan, LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY, CONVERGENCE, NO_CONVERGENCE, FAILURE,
 )
 
 __all__ = [
     "BundleAdjuster", "Options", "Summary", "VmmBaError", "default_options", "device_count",
-    "load_library", "partition_cameras", "synth",
+    "load_library", "partition_cameras", "shard_plan", "synth",
 ]

@@ -14,6 +14,7 @@
 #include <cstring>
 #include <limits>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/vmm_ba.h"
@@ -815,6 +816,21 @@ int build_segments(vmm_ba_engine* e, const std::vector<int>& mptr, const std::ve
     return rc;
 }
 
+// Host-side set-up loops (k-d splits, cluster lists) run on a few threads: chunk c of `chunks` gets fn(c, chunks).
+template <typename F>
+void parallel_chunks(int chunks, F&& fn) {
+    if (chunks <= 1) { fn(0, 1); return; }
+    std::vector<std::thread> th;
+    th.reserve(chunks - 1);
+    for (int c = 1; c < chunks; ++c) th.emplace_back([&fn, c, chunks] { fn(c, chunks); });
+    fn(0, chunks);
+    for (auto& t : th) t.join();
+}
+int host_threads() {
+    const unsigned hc = std::thread::hardware_concurrency();
+    return (int)std::max(1u, std::min(8u, hc ? hc : 1u));
+}
+
 // Camera centres C = -R^T t of the listed cameras (3 doubles per camera of the problem, zeros elsewhere).
 void camera_centres(const double* cam_q, const double* cam_t, const std::vector<int>& cams, int64_t Nc, std::vector<double>& ctr) {
     ctr.assign(3 * (size_t)Nc, 0.0);
@@ -830,9 +846,12 @@ void camera_centres(const double* cam_q, const double* cam_t, const std::vector<
 // k-d median splits of `act` (reordered in place) along the widest axis until a leaf holds at most `target`
 // cameras; the leaves come back as index ranges of `act` in depth-first (spatially coherent) order.
 // Ties are broken by camera index: every rank of a sharded engine must arrive at the same split.
-void kd_leaves(std::vector<int>& act, const std::vector<double>& ctr, int target, std::vector<std::pair<int, int>>& leaves) {
-    leaves.clear();
-    std::vector<std::pair<int, int>> stack{ { 0, (int)act.size() } };
+void kd_split_range(std::vector<int>& act, const std::vector<double>& ctr, int target, int lo0, int hi0, int spawn_depth,
+                    std::vector<std::pair<int, int>>& leaves) {
+    std::vector<std::pair<int, int>> stack{ { lo0, hi0 } };
+    std::vector<std::thread> th;
+    std::vector<std::vector<std::pair<int, int>>> sub;
+    sub.reserve(2);
     while (!stack.empty()) {
         auto [lo, hi] = stack.back();
         stack.pop_back();
@@ -847,16 +866,71 @@ void kd_leaves(std::vector<int>& act, const std::vector<double>& ctr, int target
             const double va = ctr[3 * (size_t)a + ax], vb = ctr[3 * (size_t)b + ax];
             return va < vb || (va == vb && a < b);
         });
-        stack.push_back({ lo, mid });
-        stack.push_back({ mid, hi });
+        if (spawn_depth > 0 && hi - lo > 4096) {
+            // the two halves are disjoint ranges of act: the upper one goes to its own thread
+            sub.emplace_back();
+            auto* out = &sub.back();
+            th.emplace_back([&act, &ctr, target, mid, hi = hi, spawn_depth, out] { kd_split_range(act, ctr, target, mid, hi, spawn_depth - 1, *out); });
+            kd_split_range(act, ctr, target, lo, mid, spawn_depth - 1, leaves);
+        } else {
+            stack.push_back({ lo, mid });
+            stack.push_back({ mid, hi });
+        }
     }
+    for (auto& t : th) t.join();
+    for (auto& v : sub) leaves.insert(leaves.end(), v.begin(), v.end());
+}
+void kd_leaves(std::vector<int>& act, const std::vector<double>& ctr, int target, std::vector<std::pair<int, int>>& leaves) {
+    leaves.clear();
+    kd_split_range(act, ctr, target, 0, (int)act.size(), host_threads() >= 8 ? 3 : host_threads() >= 4 ? 2 : host_threads() >= 2 ? 1 : 0, leaves);
     std::sort(leaves.begin(), leaves.end());
 }
 
-int coarse_leaf_target(const vmm_ba_engine* e, size_t n_active) {
+int coarse_leaf_target(int cams_per_cluster, size_t n_active) {
     const int kMaxClusters = 768;
-    int target = std::max(8, e->coarse_cams_per_cluster);
+    int target = std::max(8, cams_per_cluster);
     return std::max<int>(target, (int)((n_active + kMaxClusters - 1) / kMaxClusters) * 2);   // the k-d leaves hold target/2 .. target cameras
+}
+
+// Spatially coherent numbering of the cameras for sharded engines: the k-d leaves in depth-first order (each
+// leaf ascending), cameras without observations last.  order[internal] = caller's index.
+void spatial_camera_order(const double* cam_q, const double* cam_t, const std::vector<int64_t>& cam_count, int64_t Nc,
+                          int cams_per_cluster, std::vector<int>& order) {
+    std::vector<int> act;
+    for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
+    std::vector<double> ctr;
+    camera_centres(cam_q, cam_t, act, Nc, ctr);
+    std::vector<std::pair<int, int>> leaves;
+    kd_leaves(act, ctr, coarse_leaf_target(cams_per_cluster, act.size()), leaves);
+    order.clear();
+    order.reserve(Nc);
+    for (const auto& lf : leaves) {
+        const size_t first = order.size();
+        order.insert(order.end(), act.begin() + lf.first, act.begin() + lf.second);
+        std::sort(order.begin() + first, order.end());
+    }
+    for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] == 0) order.push_back((int)i);
+}
+
+// Markers that need the gather / all-reduce / scatter path of a sharded product — seen from more than one
+// rank, or with more observations than one SP_FULL segment holds — numbered compactly (the same on every
+// rank); -1 = the marker's blocks live on one rank and are handled there in one pass.  to_cam: internal indices.
+void classify_markers(const std::vector<int64_t>& begin, int world, int64_t Nc, int64_t Nm, int64_t Nto, const int32_t* to_cam,
+                      const int32_t* to_tag, const std::vector<int64_t>& tag_count, std::vector<int>& cam_rank,
+                      std::vector<int>& bnd_id, int64_t& n_bnd) {
+    cam_rank.assign(std::max<int64_t>(Nc, 1), 0);
+    std::vector<int> first(Nm, -1);
+    std::vector<unsigned char> multi(Nm, 0);
+    for (int r = 0; r < world; ++r)
+        for (int64_t i = begin[r]; i < begin[r + 1]; ++i) cam_rank[i] = r;
+    for (int64_t k = 0; k < Nto; ++k) {
+        const int j = to_tag[k], r = cam_rank[to_cam[k]];
+        if (first[j] < 0) first[j] = r; else if (first[j] != r) multi[j] = 1;
+    }
+    bnd_id.assign(Nm, -1);
+    n_bnd = 0;
+    for (int64_t j = 0; j < Nm; ++j)
+        if (tag_count[j] > 0 && (multi[j] || tag_count[j] > kSegMaxObs)) bnd_id[j] = (int)n_bnd++;
 }
 
 // Camera clusters of the coarse space: k-d median splits of the (active) camera centres C = -R^T t at the
@@ -873,7 +947,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     if (Nc == 0) return VMM_BA_OK;
     std::vector<int> act;
     for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
-    const int target = coarse_leaf_target(e, act.size());
+    const int target = coarse_leaf_target(e->coarse_cams_per_cluster, act.size());
     if ((int64_t)act.size() < 2 * (int64_t)target) return VMM_BA_OK;   // one cluster = the gauge mode of a single block: nothing to gain
     std::vector<double> ctr;
     camera_centres(cam_q, cam_t, act, Nc, ctr);
@@ -902,17 +976,28 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     cl_ptr[ncl] = (int)cl_cams.size();
     // clusters touched per marker (all observations of the problem, caller's order)
     std::vector<int> lst((size_t)Nm * kCoarseMaxTouched), cnt(Nm, 0);
-    for (int64_t k = 0; k < Nto; ++k) {
-        const int j = to_tag[k];
-        if (!tag_active[j]) continue;
-        const int cc = cl_of_g[to_cam[k]];
-        int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
-        int pos = 0;
-        while (pos < cnt[j] && l[pos] != cc) ++pos;
-        if (pos == cnt[j]) {
-            if (cnt[j] >= kCoarseMaxTouched) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
-            l[cnt[j]++] = cc;
-        }
+    {
+        // every thread scans all observations in the caller's order and keeps the markers of its own range:
+        // the list order (first seen) does not depend on the number of threads
+        const int T = host_threads();
+        std::vector<unsigned char> overflow(T, 0);
+        parallel_chunks(T, [&](int c, int chunks) {
+            const int64_t j0 = Nm * c / chunks, j1 = Nm * (c + 1) / chunks;
+            for (int64_t k = 0; k < Nto; ++k) {
+                const int j = to_tag[k];
+                if (j < j0 || j >= j1 || !tag_active[j]) continue;
+                const int cc = cl_of_g[to_cam[k]];
+                int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
+                int pos = 0;
+                while (pos < cnt[j] && l[pos] != cc) ++pos;
+                if (pos == cnt[j]) {
+                    if (cnt[j] >= kCoarseMaxTouched) { overflow[c] = 1; return; }
+                    l[cnt[j]++] = cc;
+                }
+            }
+        });
+        for (int c = 0; c < T; ++c)
+            if (overflow[c]) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
     }
     std::vector<int> mcl_ptr(Nm + 1, 0), mcl;
     for (int64_t j = 0; j < Nm; ++j) {
@@ -920,16 +1005,18 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
         mcl_ptr[j + 1] = (int)mcl.size();
     }
     std::vector<unsigned char> mo_lc(std::max<size_t>(mocam.size(), 1), 0);
-    for (int64_t j = 0; j < Nm; ++j) {
-        if (!tag_active[j]) continue;
-        const int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
-        for (int k = mptr[j]; k < mptr[j + 1]; ++k) {
-            const int cc = cl_of[mocam[k]];
-            int pos = 0;
-            while (l[pos] != cc) ++pos;
-            mo_lc[k] = (unsigned char)pos;
+    parallel_chunks(host_threads(), [&](int c, int chunks) {
+        for (int64_t j = Nm * c / chunks; j < Nm * (c + 1) / chunks; ++j) {
+            if (!tag_active[j]) continue;
+            const int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
+            for (int k = mptr[j]; k < mptr[j + 1]; ++k) {
+                const int cc = cl_of[mocam[k]];
+                int pos = 0;
+                while (l[pos] != cc) ++pos;
+                mo_lc[k] = (unsigned char)pos;
+            }
         }
-    }
+    });
     c.ncl = ncl;
     c.nC = 6 * ncl;
     c.n_w = mcl.size();
@@ -1018,7 +1105,7 @@ void vmm_ba_options_init(vmm_ba_options* o) {
     o->pcg_parity_tolerance = 1e-13;
     o->pcg_parity_max_iterations = 20000;
     o->verbose = 0;
-    o->coarse_refresh_iterations = 32;
+    o->coarse_refresh_iterations = 8;
 }
 
 int vmm_ba_abi_version(void) { return VMM_BA_ABI_VERSION; }
@@ -1159,6 +1246,33 @@ int vmm_ba_partition_cameras(int64_t num_cameras, int64_t num_tag_obs, const int
     return VMM_BA_OK;
 }
 
+int vmm_ba_shard_plan(int64_t Nc, const double* cam_q, const double* cam_t, int64_t Nm, int64_t Nto, const int32_t* to_cam,
+                      const int32_t* to_tag, int world_size, int cameras_per_cluster, int32_t* cam_rank_out, int32_t* marker_boundary_out) {
+    if (Nc < 0 || Nm < 1 || Nto < 0 || world_size < 1 || (Nc > 0 && (!cam_q || !cam_t)) || (Nto > 0 && (!to_cam || !to_tag)))
+        return VMM_BA_ERR_INVALID_ARGUMENT;
+    std::vector<int64_t> cam_count(Nc, 0), tag_count(Nm, 0);
+    for (int64_t k = 0; k < Nto; ++k) {
+        if (to_cam[k] < 0 || to_cam[k] >= Nc || to_tag[k] < 0 || to_tag[k] >= Nm) return VMM_BA_ERR_INVALID_ARGUMENT;
+        cam_count[to_cam[k]]++;
+        tag_count[to_tag[k]]++;
+    }
+    std::vector<int> order(Nc), pos(Nc);
+    if (world_size > 1 && Nc > 0) spatial_camera_order(cam_q, cam_t, cam_count, Nc, cameras_per_cluster > 0 ? cameras_per_cluster : 192, order);
+    else for (int64_t i = 0; i < Nc; ++i) order[i] = (int)i;
+    std::vector<int64_t> cc(Nc), begin;
+    for (int64_t i = 0; i < Nc; ++i) { pos[order[i]] = (int)i; cc[i] = cam_count[order[i]]; }
+    partition_cameras(Nc, cc, world_size, begin);
+    std::vector<int32_t> to_cam_p(Nto);
+    for (int64_t k = 0; k < Nto; ++k) to_cam_p[k] = pos[to_cam[k]];
+    std::vector<int> cam_rank, bnd_id;
+    int64_t n_bnd = 0;
+    classify_markers(begin, world_size, Nc, Nm, Nto, to_cam_p.data(), to_tag, tag_count, cam_rank, bnd_id, n_bnd);
+    if (world_size == 1) bnd_id.assign(Nm, -1);
+    if (cam_rank_out) for (int64_t i = 0; i < Nc; ++i) cam_rank_out[order[i]] = cam_rank[i];
+    if (marker_boundary_out) for (int64_t j = 0; j < Nm; ++j) marker_boundary_out[j] = bnd_id[j];
+    return VMM_BA_OK;
+}
+
 int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const double* cam_t, int64_t Nm, const double* tag_q,
                        const double* tag_t, const double* tag_wh, int64_t fixed_tag, int64_t Nto, const int32_t* to_cam,
                        const int32_t* to_tag, const double* to_uv) {
@@ -1194,19 +1308,8 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     std::vector<int32_t> to_cam_p;
     e->cam_order.clear();
     if (e->world > 1 && Nc > 0) {
-        std::vector<int> act, order;
-        for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
-        std::vector<double> ctr;
-        camera_centres(cam_q, cam_t, act, Nc, ctr);
-        std::vector<std::pair<int, int>> leaves;
-        kd_leaves(act, ctr, std::max(8, coarse_leaf_target(e, act.size())), leaves);
-        order.reserve(Nc);
-        for (const auto& lf : leaves) {
-            const size_t first = order.size();
-            order.insert(order.end(), act.begin() + lf.first, act.begin() + lf.second);
-            std::sort(order.begin() + first, order.end());
-        }
-        for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] == 0) order.push_back((int)i);
+        std::vector<int> order;
+        spatial_camera_order(cam_q, cam_t, cam_count, Nc, e->coarse_cams_per_cluster, order);
         std::vector<int> pos(Nc);
         for (int64_t i = 0; i < Nc; ++i) pos[order[i]] = (int)i;
         cam_q_p.resize(4 * (size_t)Nc); cam_t_p.resize(3 * (size_t)Nc);
@@ -1249,16 +1352,8 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     std::vector<int> bnd_id(Nm, -1);
     e->n_bnd = 0;
     if (e->world > 1) {
-        std::vector<int> cam_rank(std::max<int64_t>(Nc, 1), 0), first(Nm, -1);
-        std::vector<unsigned char> multi(Nm, 0);
-        for (int r = 0; r < e->world; ++r)
-            for (int64_t i = begin[r]; i < begin[r + 1]; ++i) cam_rank[i] = r;
-        for (int64_t k = 0; k < Nto; ++k) {
-            const int j = to_tag[k], r = cam_rank[to_cam[k]];
-            if (first[j] < 0) first[j] = r; else if (first[j] != r) multi[j] = 1;
-        }
-        for (int64_t j = 0; j < Nm; ++j)
-            if (tag_count[j] > 0 && (multi[j] || tag_count[j] > kSegMaxObs)) bnd_id[j] = (int)e->n_bnd++;
+        std::vector<int> cam_rank;
+        classify_markers(begin, e->world, Nc, Nm, Nto, to_cam, to_tag, tag_count, cam_rank, bnd_id, e->n_bnd);
         CU(e->wb.alloc(6 * (size_t)e->n_bnd + 4));
     }
 

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "vmm_ba_create_distributed", "vmm_ba_nccl_unique_id", "vmm_ba_destroy", "vmm_ba_last_error",
     "vmm_ba_set_stream", "vmm_ba_set_intrinsics", "vmm_ba_set_problem", "vmm_ba_set_poses",
     "vmm_ba_get_poses", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
-    "vmm_ba_reprojection_error_sums", "vmm_ba_schur_multiply", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras",
+    "vmm_ba_reprojection_error_sums", "vmm_ba_schur_multiply", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
     "vmm_ba_kernel_launches", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
     "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
 ]
@@ -130,6 +130,8 @@ def load_library():
     lib.vmm_ba_schur_multiply.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.vmm_ba_shard_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.vmm_ba_partition_cameras.argtypes = [C.c_int64, C.c_int64, ip, C.c_int, C.POINTER(C.c_int64)]
+    lib.vmm_ba_shard_plan.argtypes = [C.c_int64, dp, dp, C.c_int64, C.c_int64, ip, ip, C.c_int, C.c_int, ip, ip]
+    lib.vmm_ba_shard_plan.restype = C.c_int
     lib.vmm_ba_measure_fp64_peak.argtypes = [C.c_void_p, dp]
     lib.vmm_ba_measure_copy_bandwidth.argtypes = [C.c_void_p, C.c_size_t, dp]
     lib.vmm_ba_nccl_unique_id.argtypes = [C.c_void_p, C.c_size_t]
@@ -165,6 +167,23 @@ def partition_cameras(num_cameras: int, to_cam: np.ndarray, world_size: int) -> 
     if rc != 0:
         raise VmmBaError(f"vmm_ba_partition_cameras failed with status {rc}")
     return out
+
+
+def shard_plan(cam_q, cam_t, num_markers: int, to_cam, to_tag, world_size: int, cameras_per_cluster: int = 0):
+    """The sharding plan of a distributed engine (no GPU needed): (owner rank per camera, per marker -1 when all its
+    blocks live on one rank else its position in the all-reduced boundary vector)."""
+    cam_q, cam_t = _f64(cam_q), _f64(cam_t)
+    to_cam = np.ascontiguousarray(to_cam, dtype=np.int32)
+    to_tag = np.ascontiguousarray(to_tag, dtype=np.int32)
+    cam_rank = np.zeros(cam_q.shape[0], dtype=np.int32)
+    boundary = np.zeros(num_markers, dtype=np.int32)
+    ip = C.POINTER(C.c_int32)
+    rc = load_library().vmm_ba_shard_plan(cam_q.shape[0], _dp(cam_q), _dp(cam_t), num_markers, to_cam.shape[0], to_cam.ctypes.data_as(ip),
+                                          to_tag.ctypes.data_as(ip), world_size, cameras_per_cluster, cam_rank.ctypes.data_as(ip),
+                                          boundary.ctypes.data_as(ip))
+    if rc != 0:
+        raise VmmBaError(f"vmm_ba_shard_plan failed with status {rc}")
+    return cam_rank, boundary
 
 
 def nccl_unique_id() -> bytes:
