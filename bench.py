@@ -46,6 +46,15 @@ KERNEL_BYTES_PER_TAG_OBS = {
 }
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures of this
+# workload on one GPU (profiles/r01_ncu_solver.md, profiles/r01_ncu_rj.md); None for other workloads / shard sizes
+NCU_TRAFFIC_BYTES_C3 = {
+    "k_schur_product<SP_FULL>": 1.222487e9 + 0.009618e9,
+    "k_residual_jacobian": 0.299655e9 + 3.268961e9,
+    "k_coarse_w": 1.202321e9 + 0.011970e9,
+}
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -315,7 +324,9 @@ def run_b200(args):
     ntol_max = float(ntol_t.item())
     rj_gbs = 4 * ntol_max * RJ_BYTES_PER_CORNER / (ms_rj * 1e-3) / 1e9
     rj = {"value": scene.n_corners / (ms_rj * 1e-3), "unit": "corner evaluations/s", "ms_per_pass": ms_rj,
-          "roofline": {"bound": "hbm", "achieved": rj_gbs, "peak": peak, "unit": "GB/s", "frac": rj_gbs / peak, "traffic": None,
+          "roofline": {"bound": "hbm", "achieved": rj_gbs, "peak": peak, "unit": "GB/s", "frac": rj_gbs / peak,
+                       "traffic": NCU_TRAFFIC_BYTES_C3["k_residual_jacobian"] if (args.workload == "c3" and world == 1) else None,
+                       "algorithmic_bytes": 4 * ntol_max * RJ_BYTES_PER_CORNER,
                        "kernel": "k_residual_jacobian", "bytes_per_corner": RJ_BYTES_PER_CORNER, "peak_source": peak_src}}
 
     if rank == 0:
@@ -330,7 +341,9 @@ def run_b200(args):
             kernels[name] = ent
         if top and top[0] in KERNEL_BYTES_PER_TAG_OBS:
             k = kernels[top[0]]
-            roofline = {"bound": "hbm", "achieved": k["gbs"], "peak": peak, "unit": "GB/s", "frac": k["frac_hbm"], "traffic": None,
+            roofline = {"bound": "hbm", "achieved": k["gbs"], "peak": peak, "unit": "GB/s", "frac": k["frac_hbm"],
+                        "traffic": NCU_TRAFFIC_BYTES_C3.get(top[0]) if (args.workload == "c3" and world == 1) else None,
+                        "algorithmic_bytes": KERNEL_BYTES_PER_TAG_OBS[top[0]] * ntol,
                         "kernel": top[0], "bytes_per_tag_obs": KERNEL_BYTES_PER_TAG_OBS[top[0]], "peak_source": peak_src,
                         "share_of_step": k["share"]}
         cpu = None

@@ -267,7 +267,13 @@ int nccl_check(vmm_ba_engine* e, int rc, const char* what) {
 
 int allreduce(vmm_ba_engine* e, double* dev, size_t n, int op) {
     if (e->world == 1 || n == 0) return VMM_BA_OK;
-    return nccl_check(e, nccl_api().AllReduce(dev, dev, n, NCCL_FLOAT64, op, e->comm, e->stream), "ncclAllReduce");
+    // timed like a kernel, in two size classes (latency-bound vectors of the PCG loop / the bulk sums of a linearisation)
+    static const int kid_small = register_kernel("ncclAllReduce(<=256KB)"), kid_large = register_kernel("ncclAllReduce(>256KB)");
+    cudaEvent_t eb = nullptr;
+    if (e->profiling) eb = profile_begin(e);
+    const int rc = nccl_api().AllReduce(dev, dev, n, NCCL_FLOAT64, op, e->comm, e->stream);
+    if (eb) profile_end(e, n * sizeof(double) <= (256u << 10) ? kid_small : kid_large, eb);
+    return nccl_check(e, rc, "ncclAllReduce");
 }
 
 // Contiguous camera ranges balanced by tag-observation count.
