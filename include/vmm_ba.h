@@ -193,6 +193,14 @@ int vmm_ba_evaluate_device(vmm_ba_handle h, int loss_kind, double loss_scale, in
  * Euclidean reprojection error of tag observation k at the current poses (caller's order). */
 int vmm_ba_reprojection_error_sums(vmm_ba_handle h, double* per_tag_obs_sum);
 
+/* replaces: the ceres::Covariance block of doBundleAdjustment   src/TagReconstructor.cpp:744-783
+ * cov[9*j .. 9*j+8] = the 3x3 block (row-major) of (J^T J)^-1 that belongs to the translation of marker j at the
+ * current poses, under the given loss (the reference calls it after the final solve, which runs without a loss);
+ * zeros for the constant origin tag (as ceres::Covariance returns for constant blocks) and for unobserved markers.
+ * Dense in the markers (cameras are eliminated first): limited to 4096 markers, single-GPU engines.
+ * VMM_BA_ERR_NUMERIC when the normal equations are rank deficient (Ceres: Compute() returns false). */
+int vmm_ba_marker_translation_covariance(vmm_ba_handle h, int loss_kind, double loss_scale, double* cov);
+
 /* Target number of cameras per cluster of the two-level preconditioner's coarse space (default 192; the
  * coarse matrix is 6 x clusters squared and dense, the library caps it at 768 clusters).  Takes effect at
  * the next vmm_ba_set_problem. */

@@ -187,3 +187,43 @@ def solve(s, options: Optional[Options] = None, **kw) -> SolveResult:
     )
     assert rc == 0
     return SolveResult(cam_q, cam_t, tag_q, tag_t, summ, trace[: summ.num_iterations])
+
+
+def marker_translation_covariance(s, loss_kind=LOSS_NONE, loss_scale=1.0) -> np.ndarray:
+    """3x3 blocks of (J^T J)^-1 for every marker's translation, as ceres::Covariance delivers them at
+    src/TagReconstructor.cpp:744-783: the FULL tangent-space normal matrix (cameras and markers, 6 dofs per pose,
+    loss-corrected Jacobians) is formed densely and inverted; the constant origin tag has no columns and gets a zero
+    block, like every constant parameter block in Ceres.  Dense — small scenes only.  numpy restatement, no
+    elimination trick: an independent check of the engine's Schur-reduced computation."""
+    ev = evaluate(s, loss_kind, loss_scale, residuals=False, jac_local=True, gradient=False)
+    Nc, Nm = s.n_cameras, s.n_markers
+    J = ev.jac_local.reshape(-1, 4, 2, 12)                       # per tag observation: 4 corners x 2 rows x 12 columns
+    n = 6 * (Nc + Nm)
+    H = np.zeros((n, n))
+    cam = np.asarray(s.to_cam, dtype=np.int64)
+    tag = np.asarray(s.to_tag, dtype=np.int64)
+    for k in range(J.shape[0]):
+        Jk = J[k].reshape(8, 12)
+        cols = np.concatenate([6 * cam[k] + np.arange(6), 6 * (Nc + tag[k]) + np.arange(6)])
+        H[np.ix_(cols, cols)] += Jk.T @ Jk
+    free = np.ones(n, dtype=bool)
+    observed_m = np.zeros(Nm, dtype=bool)
+    observed_m[tag] = True
+    observed_c = np.zeros(Nc, dtype=bool)
+    observed_c[cam] = True
+    for j in range(Nm):
+        if j == s.fixed_tag or not observed_m[j]:
+            free[6 * (Nc + j):6 * (Nc + j) + 6] = False
+    for i in range(Nc):
+        if not observed_c[i]:
+            free[6 * i:6 * i + 6] = False
+    idx = np.flatnonzero(free)
+    Hinv = np.linalg.inv(H[np.ix_(idx, idx)])
+    pos = -np.ones(n, dtype=np.int64)
+    pos[idx] = np.arange(idx.size)
+    cov = np.zeros((Nm, 3, 3))
+    for j in range(Nm):
+        p = pos[6 * (Nc + j):6 * (Nc + j) + 3]
+        if (p >= 0).all():
+            cov[j] = Hinv[np.ix_(p, p)]
+    return cov

@@ -260,3 +260,45 @@ def test_schur_product_matches_reference(oracle, name, path):
             y = ba.schur_multiply(x, loss, a, radius=1e4, path=path)
             ref = _reference_schur_product(s, oracle, x, loss, a, 1e4)
             assert np.abs(y - ref).max() <= 1e-10 * np.abs(ref).max(), (name, path, loss)
+
+
+# ---- marker-translation covariance (src/TagReconstructor.cpp:744-783) ----------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("loss_kind,loss_scale", [(pkg.LOSS_NONE, 1.0), (pkg.LOSS_HUBER, 1.0)])
+def test_marker_translation_covariance_matches_dense_inverse(oracle, loss_kind, loss_scale):
+    """Engine: cameras eliminated, dense marker system, Gram matrices of L^-1.  Oracle: the full tangent-space
+    normal matrix inverted densely.  Relative 1e-8 on every 3x3 block (the two routes differ in conditioning)."""
+    s = synth.make_scene(n_markers=40, n_cameras=90, markers_per_camera=8, seed=21, outlier_frac=0.1)
+    ref = oracle.marker_translation_covariance(s, loss_kind, loss_scale)
+    with pkg.BundleAdjuster(0) as ba:
+        ba.set_scene(s)
+        cov = ba.marker_translation_covariance(loss_kind, loss_scale)
+    assert cov.shape == ref.shape
+    assert not cov[s.fixed_tag].any()                         # constant origin tag: zero block, as in Ceres
+    scale = np.abs(ref).reshape(len(ref), -1).max(1)
+    ok = scale > 0
+    observed = np.bincount(s.to_tag, minlength=s.n_markers) > 0
+    observed[s.fixed_tag] = False
+    assert np.array_equal(ok, observed)                       # unobserved markers: zero blocks on both sides
+    err = np.abs(cov - ref).reshape(len(ref), -1).max(1)
+    assert (err[ok] <= 1e-8 * scale[ok]).all(), (err[ok] / scale[ok]).max()
+    assert np.allclose(cov, np.transpose(cov, (0, 2, 1)))
+
+
+@pytest.mark.gpu
+def test_marker_translation_covariance_c1_and_limits(oracle):
+    s = synth.make_config("c1")
+    with pkg.BundleAdjuster(0) as ba:
+        ba.set_scene(s)
+        ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_NONE, parity_mode=1)
+        cq, ct, tq, tt = ba.get_poses()
+        cov = ba.marker_translation_covariance()
+    s.cam_q, s.cam_t, s.tag_q, s.tag_t = cq, ct, tq, tt
+    ref = oracle.marker_translation_covariance(s)
+    assert np.abs(cov - ref).max() <= 1e-8 * np.abs(ref).max()
+    # dense in the markers: refused beyond the documented limit instead of allocating (6 Nm)^2 doubles
+    big = synth.make_scene(n_markers=4200, n_cameras=20, markers_per_camera=10, seed=3)
+    with pkg.BundleAdjuster(0) as ba:
+        ba.set_scene(big)
+        with pytest.raises(pkg.VmmBaError, match="limited to 4096 markers"):
+            ba.marker_translation_covariance()

@@ -129,6 +129,8 @@ def oracle_closing_sequence(oracle, s):
                      tag_wh=s.tag_wh[keep_tag], fixed_tag=int(tmap[s.fixed_tag]), to_cam=cmap[s1.to_cam[ko]].astype(np.int32),
                      to_tag=tmap[s1.to_tag[ko]].astype(np.int32), to_uv=s1.to_uv[ko])
     o2 = oracle.solve(s2, max_num_iterations=1500)
+    s2.cam_q, s2.cam_t, s2.tag_q, s2.tag_t = o2.cam_q, o2.cam_t, o2.tag_q, o2.tag_t
+    o2.final_scene = s2
     return np.nonzero(keep_tag)[0], np.nonzero(keep_cam)[0], o2
 
 
@@ -149,6 +151,18 @@ def test_cli_closing_sequence_matches_oracle(host, oracle, tmp_path):
     for i, c in enumerate(keep_cam):
         assert np.abs(cams[int(c) + 7]["t"] - o2.cam_t[i]).max() < 1e-6
         assert synth.quat_angle(cams[int(c) + 7]["q"], o2.cam_q[i]) < 1e-6
+    # the covariance print-out of the final solve (src/TagReconstructor.cpp:744-783) against the oracle's dense (J^T J)^-1
+    cov = oracle.marker_translation_covariance(o2.final_scene)
+    std = np.sqrt(np.diagonal(cov, axis1=1, axis2=2))
+    lines = {int(l.split()[3].rstrip(":")): l for l in r.stdout.splitlines() if l.startswith("StdDev of tag ")}
+    assert sorted(lines) == [int(t) + 20 for t in keep_tag]
+    for j, t in enumerate(keep_tag):
+        f = lines[int(t) + 20].split()
+        got = np.array([float(f[4]), float(f[5]), float(f[6])])
+        assert np.abs(got - std[j]).max() <= 1e-4 * std.max() + 1e-12, (t, got, std[j])     # 6 printed digits
+        assert abs(float(f[-1]) - np.sqrt(np.linalg.norm(std[j]))) <= 1e-4 * np.sqrt(np.linalg.norm(std[j])) + 1e-12
+    rms = [float(l.split("=")[1]) for l in r.stdout.splitlines() if l.startswith("Marker Position RMS")]
+    assert len(rms) == 1 and abs(rms[0] - np.linalg.norm(np.sqrt(np.diagonal(cov, axis1=1, axis2=2).mean(0)))) <= 1e-4 * rms[0]
     # reconstruction.json carries the derived world corners and the camera model as the reference writes them
     root = json.loads((tmp_path / "reconstruction.json").read_text())
     assert list(root) == ["reconstructed_tags", "reconstructed_marker_corners", "reconstructed_cameras", "camera_model"]

@@ -211,6 +211,13 @@ __global__ void k_identity(int n, double* __restrict__ A) {
     A[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
 }
 
+// columns [c0, c0 + nb) of the n x n identity, column-major (columns past n: zero padding)
+__global__ void k_identity_columns(int n, int c0, int nb, double* __restrict__ A) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)n * nb) return;
+    A[idx] = (idx % n == c0 + idx / n) ? 1.0 : 0.0;
+}
+
 // syrk leaves the inverse in one triangle: mirror it (column-major lower == row-major upper).
 __global__ void k_symmetrize(int n, double* __restrict__ A) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

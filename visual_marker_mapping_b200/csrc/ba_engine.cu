@@ -22,6 +22,7 @@
 #include "ba_schur.cuh"
 #include "ba_coarse.cuh"
 #include "ba_stage.cuh"
+#include "ba_cov.cuh"
 #include "nccl_dyn.h"
 #include <cublas_v2.h>
 #include <cusolverDn.h>
@@ -81,6 +82,8 @@ struct vmm_ba_engine {
     // staging (ba_stage.cuh): the caller's arrays as uploaded, sort scratch, and the local permutation
     // perm_dev[s] = caller's tag-observation index of camera-order position s (host mirror fetched on demand)
     DevBuf<int> raw_cam, raw_tag, perm_all, perm_dev, mperm, sort_keys, sort_keys2, sort_iota;
+    DevBuf<int> cpos, cam_ptr_dev;    // marker-order position per camera-order observation; CSR of the camera order
+    DevBuf<double> covR, covX, cov_out;
     DevBuf<double2> raw_uv;
     DevBuf<unsigned char> sort_tmp;
     std::vector<int> perm_c;
@@ -452,12 +455,31 @@ int coarse_setup(vmm_ba_engine* e, int slot) {
     // A_c^-1 = L^-T L^-1: X = L^-1 by a triangular solve against the identity, then X^T X (two plain cuBLAS level-3
     // calls, ~1 ms together at n = 3000; cusolverDnDpotri needs 7.8 ms for the same result)
     if (cublasSetStream(e->cublas, e->stream) != CUBLAS_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cublasSetStream failed");
-    LAUNCH(k_identity, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Linv.p);
     const double one = 1.0, zero = 0.0;
-    LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, c.nC, c.nC, &one,
-                                             c.Ac.p, c.nC, c.Linv.p, c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
-    LIBCALL_NAMED("cublasDsyrk", cublasDsyrk(e->cublas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, c.nC, c.nC, &one, c.Linv.p, c.nC, &zero, c.Ac.p,
-                                             c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDsyrk");
+    if (e->world == 1) {
+        LAUNCH(k_identity, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Linv.p);
+        LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, c.nC, c.nC, &one,
+                                                 c.Ac.p, c.nC, c.Linv.p, c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
+        LIBCALL_NAMED("cublasDsyrk", cublasDsyrk(e->cublas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, c.nC, c.nC, &one, c.Linv.p, c.nC, &zero, c.Ac.p,
+                                                 c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDsyrk");
+    } else {
+        // sharded: the factor is replicated, the inverse is not formed redundantly — every rank solves
+        // L L^T X = I for its block of columns (two triangular solves on n / world right-hand sides) and the
+        // blocks are all-gathered (column-major: a block of columns is contiguous)
+        const int nb = (c.nC + e->world - 1) / e->world;          // columns per rank (the last block is padded)
+        double* mine = c.Linv.p + (size_t)e->rank * nb * n;
+        LAUNCH(k_identity_columns, nblocks((int64_t)n * nb, kThreads), kThreads, c.nC, e->rank * nb, nb, mine);
+        LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, c.nC, nb, &one,
+                                                 c.Ac.p, c.nC, mine, c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
+        LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, CUBLAS_DIAG_NON_UNIT, c.nC, nb, &one,
+                                                 c.Ac.p, c.nC, mine, c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
+        static const int kid_ag = register_kernel("ncclAllGather");
+        cudaEvent_t eb = e->profiling ? profile_begin(e) : nullptr;
+        const int nrc = nccl_api().AllGather(mine, c.Linv.p, (size_t)nb * n, NCCL_FLOAT64, e->comm, e->stream);
+        if (eb) profile_end(e, kid_ag, eb);
+        if (nrc) return nccl_check(e, nrc, "ncclAllGather");
+        CU(cudaMemcpyAsync(c.Ac.p, c.Linv.p, sizeof(double) * n * n, cudaMemcpyDeviceToDevice, e->stream));
+    }
     LAUNCH(k_symmetrize, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Ac.p);
     CU(cudaStreamSynchronize(e->stream));
     if (e->profiling) profile_resolve(e);
@@ -1031,7 +1053,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1))); CU(c.mo_lc.alloc(mo_lc.size()));
     CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(n * n)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
     CU(c.Wbuf.alloc(std::max<size_t>(36 * c.n_w, 1)));
-    CU(c.Linv.alloc(n * n));
+    CU(c.Linv.alloc(n * (size_t)((c.nC + e->world - 1) / e->world) * e->world));   // whole column blocks per rank
     int lw1 = 0;
     if (cusolverDnDpotrf_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, &lw1) != CUSOLVER_STATUS_SUCCESS)
         return fail_with(e, VMM_BA_ERR_CUDA, "cusolver buffer size query failed");
@@ -1369,6 +1391,13 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(e->raw_cam.alloc(ntoa1)); CU(e->raw_tag.alloc(ntoa1)); CU(e->raw_uv.alloc(4 * ntoa1));
     CU(e->perm_all.alloc(ntoa1)); CU(e->sort_keys.alloc(ntoa1)); CU(e->sort_iota.alloc(ntoa1));
     CU(e->perm_dev.alloc(nto1)); CU(e->mperm.alloc(nto1)); CU(e->sort_keys2.alloc(nto1));
+    CU(e->cpos.alloc(nto1)); CU(e->cam_ptr_dev.alloc(ncl1 + 1));
+    {
+        std::vector<int> h_cptr(Ncl + 1);
+        for (int64_t i = 0; i <= Ncl; ++i) h_cptr[i] = (int)(cam_ptr[e->cam0 + i] - e->to0);
+        CU(cudaMemcpyAsync(e->cam_ptr_dev.p, h_cptr.data(), sizeof(int) * (Ncl + 1), cudaMemcpyHostToDevice, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+    }
     CU(e->uv.alloc(4 * nto1));
     CU(e->ocam.alloc(nto1)); CU(e->otag.alloc(nto1)); CU(e->mo_cam.alloc(nto1)); CU(e->mptr.alloc(Nm + 1));
     CU(e->uvm.alloc(4 * uv_stride));
@@ -1399,7 +1428,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
             ++e->launches;
             CU(cudaMemsetAsync(e->uvm.p, 0, sizeof(double2) * 4 * uv_stride, e->stream));
             LAUNCH(k_stage_marker_order, nblocks(4 * Ntol, kThreads), kThreads, Ntol, e->mperm.p, e->ocam.p, e->uv.p, uv_stride, e->mo_cam.p,
-                   e->uvm.p);
+                   e->uvm.p, e->cpos.p);
             CU(cudaMemcpyAsync(h_mocam.data(), e->mo_cam.p, sizeof(int) * Ntol, cudaMemcpyDeviceToHost, e->stream));
         }
         CU(cudaStreamSynchronize(e->stream));
@@ -1616,6 +1645,55 @@ int vmm_ba_reprojection_error_sums(vmm_ba_handle e, double* out) {
         if (rc) return rc;
         for (int64_t i = 0; i < e->Ntol; ++i) out[e->perm_c[i]] = h[i];
     }
+    return VMM_BA_OK;
+}
+
+int vmm_ba_marker_translation_covariance(vmm_ba_handle e, int loss_kind, double loss_scale, double* cov) {
+    if (!e || !cov) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null argument");
+    if (!e->have_problem || !e->have_intrinsics) return fail_with(e, VMM_BA_ERR_STATE, "set_intrinsics and set_problem must be called first");
+    if (e->world != 1) return fail_with(e, VMM_BA_ERR_STATE, "vmm_ba_marker_translation_covariance needs a single-GPU engine");
+    if (loss_kind < 0 || loss_kind > 2 || !(loss_scale > 0)) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "bad loss");
+    const int64_t kMaxMarkers = 4096;   // dense marker-reduced system: (6 Nm)^2 doubles, twice
+    if (e->Nm > kMaxMarkers) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "covariance is limited to %lld markers (dense reduced system)", (long long)kMaxMarkers);
+    CU(cudaSetDevice(e->device));
+    const int nm = (int)e->Nm, nc = (int)e->Ncl, n = 6 * nm;
+    prepare_poses(e, e->cur);
+    int rc = linearize(e, e->cur, loss_kind, loss_scale);
+    if (rc) return rc;
+    CU(e->covR.alloc((size_t)n * n)); CU(e->covX.alloc((size_t)n * n)); CU(e->cov_out.alloc((size_t)9 * nm));
+    CU(cudaMemsetAsync(e->covR.p, 0, sizeof(double) * n * n, e->stream));
+    CU(cudaMemsetAsync(e->fail.p, 0, sizeof(int), e->stream));
+    if (nc > 0) {
+        LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->B.p, (const double*)nullptr, e->cam_active.p, e->Minv.p, e->fail.p);
+        if (e->Ntol > 0)
+            LAUNCH(k_cov_eliminate_cameras, nc, 128, e->cam_ptr_dev.p, e->otag.p, e->cpos.p, e->mptr.p, e->mtile.p, e->tag_active.p, e->Minv.p,
+                   e->Et.p, n, e->covR.p);
+    }
+    LAUNCH(k_cov_add_marker_blocks, nblocks((int64_t)nm * 36, kThreads), kThreads, nm, e->C.p, e->tag_active.p, n, e->covR.p);
+    int lwork = 0;
+    if (cusolverDnSetStream(e->cusolver, e->stream) != CUSOLVER_STATUS_SUCCESS || cublasSetStream(e->cublas, e->stream) != CUBLAS_STATUS_SUCCESS ||
+        cusolverDnDpotrf_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, n, e->covR.p, n, &lwork) != CUSOLVER_STATUS_SUCCESS)
+        return fail_with(e, VMM_BA_ERR_CUDA, "cusolver set-up failed");
+    DevBuf<double> work;
+    DevBuf<int> info;
+    CU(work.alloc(std::max(lwork, 1))); CU(info.alloc(1));
+    LIBCALL_NAMED("cusolverDnDpotrf", cusolverDnDpotrf(e->cusolver, CUBLAS_FILL_MODE_LOWER, n, e->covR.p, n, work.p, lwork, info.p) == CUSOLVER_STATUS_SUCCESS,
+                  "cusolverDnDpotrf");
+    int h_info = 0, h_fail = 0;
+    CU(cudaMemcpyAsync(&h_info, info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(&h_fail, e->fail.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    if (h_info != 0 || h_fail != 0)   // Ceres: "Jacobian is rank deficient" (a camera or marker block without enough observations)
+        return fail_with(e, VMM_BA_ERR_NUMERIC, "the normal equations are rank deficient (potrf info %d): no covariance", h_info);
+    LAUNCH(k_identity, nblocks((int64_t)n * n, kThreads), kThreads, n, e->covX.p);
+    const double one = 1.0;
+    LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, n, n, &one, e->covR.p, n,
+                                             e->covX.p, n) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
+    LAUNCH(k_cov_translation_blocks, nm, 256, n, e->covX.p, e->tag_active.p, e->cov_out.p);
+    CU(cudaMemcpyAsync(cov, e->cov_out.p, sizeof(double) * 9 * nm, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    if (e->profiling) profile_resolve(e);
+    e->covR.release(); e->covX.release();   // up to 2 x 4.8 GB: not kept
     return VMM_BA_OK;
 }
 

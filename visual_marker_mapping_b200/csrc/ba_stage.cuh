@@ -36,14 +36,17 @@ __global__ void k_stage_camera_order(int64_t ntol, const int* __restrict__ perm,
 // marker order: position pos -> camera-order position s = mperm[pos]; corners go to four planes of stride `stride`
 __global__ void k_stage_marker_order(int64_t ntol, const int* __restrict__ mperm, const int* __restrict__ ocam,
                                      const double2* __restrict__ uv, size_t stride, int* __restrict__ mo_cam,
-                                     double2* __restrict__ uvm) {
+                                     double2* __restrict__ uvm, int* __restrict__ cpos) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= 4 * ntol) return;
     const int64_t pos = idx % ntol;
     const int c = (int)(idx / ntol);
     const int64_t s = mperm[pos];
     uvm[(size_t)c * stride + pos] = uv[4 * s + c];
-    if (c == 0) mo_cam[pos] = ocam[s];
+    if (c == 0) {
+        mo_cam[pos] = ocam[s];
+        cpos[s] = (int)pos;   // camera-order position -> marker-order position (the E block of that observation)
+    }
 }
 
 inline int key_bits(int64_t n) {

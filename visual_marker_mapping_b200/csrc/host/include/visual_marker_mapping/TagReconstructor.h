@@ -8,6 +8,7 @@
 #include "visual_marker_mapping/Camera.h"
 #include "visual_marker_mapping/CameraModel.h"
 #include "visual_marker_mapping/DetectionResults.h"
+#include <array>
 #include <cstddef>
 #include <map>
 #include <string>
@@ -82,6 +83,10 @@ public:
     void setParityMode(bool on);     // true: PCG to 1e-13 so that iterates track an exact-solve (Ceres) trajectory
     void setQuiet(bool on);
     const BundleAdjustmentReport& lastReport() const { return report_; }
+    // what the reference only prints (src/TagReconstructor.cpp:744-783): 3x3 translation covariance per tag id
+    // (row-major) and the "Marker Position RMS" of the last doBundleAdjustment(..., printSummary = true)
+    const std::map<int, std::array<double, 9>>& tagTranslationCovariances() const { return tagCovariances_; }
+    double markerPositionRms() const { return markerPositionRms_; }
 
 protected:
     struct Flat;
@@ -99,6 +104,8 @@ protected:
     int device_ = 0;
     bool parity_ = false, quiet_ = false, haveInitial_ = false;
     BundleAdjustmentReport report_;
+    std::map<int, std::array<double, 9>> tagCovariances_;
+    double markerPositionRms_ = 0.0;
 };
 }
 #endif

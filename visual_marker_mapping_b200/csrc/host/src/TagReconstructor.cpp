@@ -184,8 +184,30 @@ void TagReconstructor::doBundleAdjustment(int maxNumIterations, size_t /*ceresTh
                   << " (successful " << s.num_successful_steps << ", unsuccessful " << s.num_unsuccessful_steps << "), PCG iterations "
                   << s.pcg_iterations << "\n  time total " << s.time_total_s << " s (linearize " << s.time_linearize_s << ", linear solver "
                   << s.time_linear_solver_s << ", cost evaluation " << s.time_cost_eval_s << ")\n  termination: " << s.message << std::endl;
-        // the reference additionally prints ceres::Covariance standard deviations of the tag translations
-        // (:744-783); that read-out is not built
+    }
+    // :744-783 — standard deviations of the tag translations from the covariance blocks, same lines as the reference
+    // ("StdDevNorm" is the square root of the norm of the standard deviations, :772-773, reproduced as it is)
+    if (printSummary) {
+        std::vector<double> cov(9 * f.tagIds.size(), 0.0);
+        const int rc = vmm_ba_marker_translation_covariance(engine_, opt.loss_kind, opt.loss_scale, cov.data());
+        if (rc != VMM_BA_OK) {
+            if (!quiet_) std::cout << "Covariance not available: " << vmm_ba_last_error(engine_) << std::endl;
+            return;
+        }
+        tagCovariances_.clear();
+        double avg[3] = { 0.0, 0.0, 0.0 };
+        for (size_t j = 0; j < f.tagIds.size(); ++j) {
+            const double* c = cov.data() + 9 * j;
+            tagCovariances_[f.tagIds[j]] = { c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7], c[8] };
+            const double sx = std::sqrt(c[0]), sy = std::sqrt(c[4]), sz = std::sqrt(c[8]);
+            if (!quiet_)
+                std::cout << "StdDev of tag " << f.tagIds[j] << ": " << sx << " " << sy << " " << sz
+                          << " | StdDevNorm: " << std::sqrt(std::sqrt(sx * sx + sy * sy + sz * sz)) << std::endl;
+            avg[0] += c[0]; avg[1] += c[4]; avg[2] += c[8];
+        }
+        for (double& a : avg) a /= (double)f.tagIds.size();
+        markerPositionRms_ = std::sqrt(avg[0] + avg[1] + avg[2]);   // norm of the per-axis RMS standard deviations, :777-781
+        if (!quiet_) std::cout << "Marker Position RMS = " << markerPositionRms_ << std::endl;
     }
 }
 

@@ -21,6 +21,7 @@ struct NcclApi {
     int (*CommInitRank)(nccl_comm_t*, int, nccl_unique_id, int) = nullptr;
     int (*CommDestroy)(nccl_comm_t) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, nccl_comm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
     int (*GetVersion)(int*) = nullptr;
     bool ok = false;
@@ -38,9 +39,10 @@ struct NcclApi {
         CommInitRank = (decltype(CommInitRank))dlsym(handle, "ncclCommInitRank");
         CommDestroy = (decltype(CommDestroy))dlsym(handle, "ncclCommDestroy");
         AllReduce = (decltype(AllReduce))dlsym(handle, "ncclAllReduce");
+        AllGather = (decltype(AllGather))dlsym(handle, "ncclAllGather");
         GetErrorString = (decltype(GetErrorString))dlsym(handle, "ncclGetErrorString");
         GetVersion = (decltype(GetVersion))dlsym(handle, "ncclGetVersion");
-        if (!GetUniqueId || !CommInitRank || !CommDestroy || !AllReduce || !GetErrorString) {
+        if (!GetUniqueId || !CommInitRank || !CommDestroy || !AllReduce || !AllGather || !GetErrorString) {
             error = "libnccl is missing required symbols";
             return false;
         }

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "vmm_ba_create_distributed", "vmm_ba_nccl_unique_id", "vmm_ba_destroy", "vmm_ba_last_error",
     "vmm_ba_set_stream", "vmm_ba_set_intrinsics", "vmm_ba_set_problem", "vmm_ba_set_poses",
     "vmm_ba_get_poses", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
-    "vmm_ba_reprojection_error_sums", "vmm_ba_schur_multiply", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
+    "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_schur_multiply", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
     "vmm_ba_kernel_launches", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
     "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
 ]
@@ -126,6 +126,7 @@ def load_library():
     lib.vmm_ba_evaluate.argtypes = [C.c_void_p, C.c_int, C.c_double, dp, dp, dp, dp]
     lib.vmm_ba_evaluate_device.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp]
     lib.vmm_ba_reprojection_error_sums.argtypes = [C.c_void_p, dp]
+    lib.vmm_ba_marker_translation_covariance.argtypes = [C.c_void_p, C.c_int, C.c_double, dp]
     lib.vmm_ba_set_coarse_cluster_size.argtypes = [C.c_void_p, C.c_int]
     lib.vmm_ba_schur_multiply.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.vmm_ba_shard_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -302,6 +303,12 @@ class BundleAdjuster:
     def reprojection_error_sums(self) -> np.ndarray:
         out = np.zeros(self.n_tag_obs)
         self._check(self._lib.vmm_ba_reprojection_error_sums(self._h, _dp(out)))
+        return out
+
+    def marker_translation_covariance(self, loss_kind=LOSS_NONE, loss_scale=1.0) -> np.ndarray:
+        """3x3 blocks of (J^T J)^-1 of every marker's translation at the current poses: [n_markers, 3, 3]."""
+        out = np.zeros((self.n_markers, 3, 3))
+        self._check(self._lib.vmm_ba_marker_translation_covariance(self._h, int(loss_kind), float(loss_scale), _dp(out)))
         return out
 
     def schur_multiply(self, x, loss_kind=LOSS_NONE, loss_scale=1.0, radius=1e4, path=0) -> np.ndarray:

@@ -21,7 +21,7 @@ from typing import Optional
 
 import numpy as np
 
-GENERATOR_VERSION = "vmm-synth-3"
+GENERATOR_VERSION = "vmm-synth-4"
 
 # README.md:132-145 — fx, fy, cx, cy, k1, k2, p1, p2, k3
 README_INTRINSICS = np.array(
@@ -229,6 +229,7 @@ def make_scene(
     rot_sigma_deg: float = 1.0,
     trans_sigma: float = 0.03,
     outlier_frac: float = 0.0,
+    relabel: str = "visible",
     height_range=(2.5, 3.5),
     max_tilt_deg: float = 12.0,
     marker_tilt_deg: float = 20.0,
@@ -371,9 +372,24 @@ def make_scene(
         # half: common shift U(-40,40) px + N(0,5^2) per corner
         sh = rng.uniform(-40, 40, (shift_sel.size, 1, 2)) + rng.normal(0, 5.0, (shift_sel.size, 4, 2))
         to_uv[shift_sel] += sh.reshape(-1, 8)
-        # half: relabelled to a random other marker id
-        new_ids = rng.integers(1, n_markers, relabel_sel.size).astype(np.int32)
-        new_ids = np.where(new_ids == to_tag[relabel_sel], (new_ids % (n_markers - 1)) + 1, new_ids).astype(np.int32)
+        # half: re-labelled to another marker id.  "visible" (default): the id of another marker seen in the same
+        # image — a decoding mix-up between detections, residuals of hundreds to thousands of pixels.  "any": a
+        # random id of the whole map; on a site-sized sheet that marker is usually hundreds of metres away, its
+        # projection (no Z check in the functor, TagReconstructionCostFunction.h:125-126) runs through the r^6
+        # distortion term and the cost starts at 1e50: a stress case no loss function rescues, kept for tests.
+        if relabel == "visible":
+            order = np.argsort(to_cam, kind="stable")
+            counts = np.bincount(to_cam, minlength=n_cameras)
+            starts = np.concatenate([[0], np.cumsum(counts)[:-1]])
+            c = to_cam[relabel_sel]
+            r = rng.integers(0, np.maximum(counts[c], 1))
+            cand = order[starts[c] + r]
+            same = to_tag[cand] == to_tag[relabel_sel]
+            cand = np.where(same, order[starts[c] + (r + 1) % np.maximum(counts[c], 1)], cand)
+            new_ids = to_tag[cand].astype(np.int32)     # gathered from the unmodified labels
+        else:
+            new_ids = rng.integers(1, n_markers, relabel_sel.size).astype(np.int32)
+            new_ids = np.where(new_ids == to_tag[relabel_sel], (new_ids % (n_markers - 1)) + 1, new_ids).astype(np.int32)
         to_tag[relabel_sel] = new_ids
     if float32_round:
         to_uv = to_uv.astype(np.float32).astype(np.float64)
@@ -455,6 +471,24 @@ def make_config(name: str, **overrides) -> Scene:
         kw = dict(CONFIGS[name])
     kw.update(overrides)
     return make_scene(**kw)
+
+
+def tile_scene(scene: Scene, copies: int) -> Scene:
+    """`copies` disjoint replicas of a scene in one problem (camera / marker indices offset per replica, poses and
+    observations repeated): evaluation-only workloads beyond what the generator produces in reasonable time (C5)."""
+    if copies <= 1:
+        return scene
+    nc, nm = scene.n_cameras, scene.n_markers
+    off_c = np.repeat(np.arange(copies, dtype=np.int64) * nc, scene.n_tag_obs)
+    off_m = np.repeat(np.arange(copies, dtype=np.int64) * nm, scene.n_tag_obs)
+    return Scene(
+        intr=scene.intr, cam_q=np.tile(scene.cam_q, (copies, 1)), cam_t=np.tile(scene.cam_t, (copies, 1)),
+        tag_q=np.tile(scene.tag_q, (copies, 1)), tag_t=np.tile(scene.tag_t, (copies, 1)), tag_wh=np.tile(scene.tag_wh, (copies, 1)),
+        fixed_tag=scene.fixed_tag,
+        to_cam=(np.tile(scene.to_cam.astype(np.int64), copies) + off_c).astype(np.int32),
+        to_tag=(np.tile(scene.to_tag.astype(np.int64), copies) + off_m).astype(np.int32),
+        to_uv=np.tile(scene.to_uv, (copies,) + (1,) * (scene.to_uv.ndim - 1)),
+        meta=dict(scene.meta, tiled=copies))
 
 
 def make_rj_sweep_scene(n_corners: int, seed: int = 0x564D4D05) -> Scene:
