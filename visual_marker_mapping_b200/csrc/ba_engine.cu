@@ -23,6 +23,7 @@
 #include "ba_coarse.cuh"
 #include "ba_stage.cuh"
 #include "ba_cov.cuh"
+#include "ba_peer.cuh"
 #include "nccl_dyn.h"
 #include <cublas_v2.h>
 #include <cusolverDn.h>
@@ -69,6 +70,11 @@ struct vmm_ba_engine {
     cudaStream_t own_stream = nullptr;
     int rank = 0, world = 1;
     nccl_comm_t comm = nullptr;
+    // one-shot all-reduce over peer memory (ba_peer.cuh); NCCL carries what does not fit or when IPC is unavailable
+    bool peer_ok = false;
+    PeerView peer{};
+    uint4* peer_own = nullptr;
+    uint32_t peer_seq = 0;
     std::string last_error;
     int64_t launches = 0;
 
@@ -274,6 +280,15 @@ int allreduce(vmm_ba_engine* e, double* dev, size_t n, int op) {
     static const int kid_small = register_kernel("ncclAllReduce(<=256KB)"), kid_large = register_kernel("ncclAllReduce(>256KB)");
     cudaEvent_t eb = nullptr;
     if (e->profiling) eb = profile_begin(e);
+    if (e->peer_ok && op == NCCL_SUM && n <= kPeerCapDoubles) {
+        static const int kid_peer = register_kernel("k_peer_allreduce");
+        if (++e->peer_seq == 0) e->peer_seq = 2;   // 32-bit wrap: 0 is the "never written" value, parity continues
+        const int grid = (int)std::min<size_t>(kPeerMaxBlocks, (n + kPeerThreads - 1) / kPeerThreads);
+        k_peer_allreduce<<<grid, kPeerThreads, 0, e->stream>>>(e->peer, (int)n, dev, e->peer_seq);
+        ++e->launches;
+        if (eb) profile_end(e, kid_peer, eb);
+        return VMM_BA_OK;
+    }
     const int rc = nccl_api().AllReduce(dev, dev, n, NCCL_FLOAT64, op, e->comm, e->stream);
     if (eb) profile_end(e, n * sizeof(double) <= (256u << 10) ? kid_small : kid_large, eb);
     return nccl_check(e, rc, "ncclAllReduce");
@@ -1103,6 +1118,64 @@ int launch_rj(vmm_ba_engine* e, int loss_kind, double loss_a, bool with_cost) {
 
 }  // namespace
 
+namespace {
+// Exchange buffers of the one-shot all-reduce: allocate, export, all-gather the IPC handles through NCCL, map the
+// peers'.  Every rank reaches the same verdict (the per-rank status is summed), so either all ranks use the peer
+// path or none does.  VMM_BA_NO_PEER=1 keeps everything on NCCL.
+void peer_setup(vmm_ba_engine* e) {
+    e->peer_ok = false;
+    if (e->world > kPeerMaxWorld) return;
+    const bool disabled = std::getenv("VMM_BA_NO_PEER") != nullptr;
+    const size_t bytes = peer_buffer_bytes(e->world);
+    int ok = !disabled;
+    if (ok && cudaMalloc(&e->peer_own, bytes) != cudaSuccess) { e->peer_own = nullptr; ok = 0; cudaGetLastError(); }
+    if (e->peer_own) { cudaMemset(e->peer_own, 0, bytes); cudaDeviceSynchronize(); }   // flags are zero before any peer can map the buffer
+    cudaIpcMemHandle_t mine{};
+    if (ok && cudaIpcGetMemHandle(&mine, e->peer_own) != cudaSuccess) { ok = 0; cudaGetLastError(); }
+    // all-gather of (handle, status): 64 + 8 bytes per rank, as doubles
+    constexpr int kWords = (int)(sizeof(cudaIpcMemHandle_t) / sizeof(double)) + 1;
+    double h_send[kWords];
+    std::memcpy(h_send, &mine, sizeof(mine));
+    h_send[kWords - 1] = ok ? 1.0 : 0.0;
+    double* d_all = nullptr;
+    if (cudaMalloc(&d_all, sizeof(double) * kWords * e->world) != cudaSuccess) { cudaGetLastError(); return; }
+    std::vector<double> h_all((size_t)kWords * e->world, 0.0);
+    cudaMemcpyAsync(d_all + (size_t)kWords * e->rank, h_send, sizeof(h_send), cudaMemcpyHostToDevice, e->stream);
+    const int nrc = nccl_api().AllGather(d_all + (size_t)kWords * e->rank, d_all, kWords, NCCL_FLOAT64, e->comm, e->stream);
+    cudaMemcpyAsync(h_all.data(), d_all, sizeof(double) * kWords * e->world, cudaMemcpyDeviceToHost, e->stream);
+    cudaStreamSynchronize(e->stream);
+    cudaFree(d_all);
+    if (nrc) return;
+    int all_ok = 1;
+    for (int r = 0; r < e->world; ++r) all_ok &= (h_all[(size_t)kWords * r + kWords - 1] == 1.0);
+    // second round: did every rank manage to map every peer?
+    int mapped = all_ok;
+    if (all_ok) {
+        for (int r = 0; r < e->world && mapped; ++r) {
+            if (r == e->rank) { e->peer.buf[r] = e->peer_own; continue; }
+            cudaIpcMemHandle_t h;
+            std::memcpy(&h, &h_all[(size_t)kWords * r], sizeof(h));
+            void* p = nullptr;
+            if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); mapped = 0; break; }
+            e->peer.buf[r] = static_cast<uint4*>(p);
+        }
+    }
+    double* d_flag = nullptr;
+    if (cudaMalloc(&d_flag, sizeof(double)) != cudaSuccess) { cudaGetLastError(); return; }
+    const double mine_ok = mapped ? 0.0 : 1.0;   // number of ranks that failed
+    double total = 1.0;
+    cudaMemcpyAsync(d_flag, &mine_ok, sizeof(double), cudaMemcpyHostToDevice, e->stream);
+    const int arc = nccl_api().AllReduce(d_flag, d_flag, 1, NCCL_FLOAT64, NCCL_SUM, e->comm, e->stream);
+    cudaMemcpyAsync(&total, d_flag, sizeof(double), cudaMemcpyDeviceToHost, e->stream);
+    cudaStreamSynchronize(e->stream);
+    cudaFree(d_flag);
+    e->peer.rank = e->rank;
+    e->peer.world = e->world;
+    e->peer_seq = 0;
+    e->peer_ok = (arc == 0 && total == 0.0);
+}
+}  // namespace
+
 // =====================================================================================
 // C ABI
 // =====================================================================================
@@ -1227,6 +1300,7 @@ int vmm_ba_create_distributed(int device, int rank, int world_size, const void* 
             *out = nullptr;
             return fail_with(nullptr, VMM_BA_ERR_NCCL, "ncclCommInitRank: %s", m.c_str());
         }
+        peer_setup(e);   // optional: on failure the small all-reduces stay on NCCL
     }
     return VMM_BA_OK;
 }
@@ -1235,7 +1309,10 @@ int vmm_ba_destroy(vmm_ba_handle e) {
     if (!e) return VMM_BA_OK;
     cudaSetDevice(e->device);
     cudaDeviceSynchronize();
+    for (int r = 0; r < e->world && r < kPeerMaxWorld; ++r)
+        if (e->peer.buf[r] && e->peer.buf[r] != e->peer_own) cudaIpcCloseMemHandle(e->peer.buf[r]);
     if (e->comm) nccl_api().CommDestroy(e->comm);
+    if (e->peer_own) cudaFree(e->peer_own);
     if (e->cusolver) cusolverDnDestroy(e->cusolver);
     if (e->cublas) cublasDestroy(e->cublas);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
