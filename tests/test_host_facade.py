@@ -184,3 +184,44 @@ def test_facade_reprojection_statistics(host, oracle, tmp_path, scene_c1):
     per_img = np.bincount(scene_c1.to_cam, sums, scene_c1.n_cameras) / (4 * np.bincount(scene_c1.to_cam, minlength=scene_c1.n_cameras))
     for i in range(scene_c1.n_cameras):
         assert abs(float(got["per_img"][str(i)]) - per_img[i]) < 1e-9 * max(per_img[i], 1.0)
+
+
+# ---- incremental PnP initialisation (src/TagReconstructor.cpp:146-267) -----------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("wave", [False, True])
+def test_cli_reconstructs_from_detections_alone(host, oracle, tmp_path, scene_c1, wave):
+    """No initial poses: the tool initialises every camera (robust PnP on the corners of the tags reconstructed so far) and
+    every tag (PnP on its four corners), bundle-adjusts per added image (or per round with --wave) and runs the closing
+    sequence.  The result is the least-squares solution of the final problem — the same one the oracle reaches from the
+    synthetic initial guess — and close to ground truth."""
+    s = scene_c1
+    project_io.write_project(s, str(tmp_path), image_id_offset=3, tag_id_offset=0)
+    os.remove(tmp_path / "initial_reconstruction.json")
+    args = [CLI, "--project_path", str(tmp_path), "--parity", "--overwrite"] + (["--wave"] if wave else [])
+    r = subprocess.run(args, capture_output=True, text=True)
+    assert r.returncode == 0 and "Error" not in r.stderr, r.stderr
+    n_ba = r.stdout.count("Solution ")
+    assert ("Initialized camera with id" in r.stdout) and ("Initialized tag with id" in r.stdout)
+    if wave:
+        assert n_ba < 10                                  # a handful of rounds + the two closing solves
+    else:
+        assert n_ba == s.n_cameras + 2                    # one bundle adjustment per image, :243, plus :271,:277
+    tags, cams = project_io.read_reconstruction(str(tmp_path / "reconstruction.json"))
+    assert sorted(tags) == list(range(s.n_markers)) and sorted(cams) == [i + 3 for i in range(s.n_cameras)]
+    o = oracle.solve(s, max_num_iterations=1500)          # final solve of the reference sequence runs without a loss
+    for j in range(s.n_markers):
+        assert np.abs(tags[j]["t"] - o.tag_t[j]).max() < 2e-5
+        assert synth.quat_angle(tags[j]["q"], o.tag_q[j]) < 2e-5
+        assert np.abs(tags[j]["t"] - s.tag_t_gt[j]).max() < 5e-3
+    for i in range(s.n_cameras):
+        assert np.abs(cams[i + 3]["t"] - o.cam_t[i]).max() < 2e-5
+        assert synth.quat_angle(cams[i + 3]["q"], o.cam_q[i]) < 2e-5
+
+
+@pytest.mark.gpu
+def test_cli_origin_tag_errors(host, tmp_path, scene_c1):
+    project_io.write_project(scene_c1, str(tmp_path))
+    os.remove(tmp_path / "initial_reconstruction.json")
+    r = subprocess.run([CLI, "--project_path", str(tmp_path), "--start_tag_id", "99", "--overwrite"], capture_output=True, text=True)
+    assert r.returncode == 0                              # the reference's main swallows the exception, src/main_mapping.cpp:90-95
+    assert "Could not use tag with id 99 as origin tag, because it was not detected." in r.stderr

@@ -11,6 +11,7 @@
 #include <array>
 #include <cstddef>
 #include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -51,9 +52,8 @@ public:
     TagReconstructor& operator=(const TagReconstructor&) = delete;
 
     // Reference: incremental PnP initialisation + BA per camera, then BA / cull / BA
-    // (src/TagReconstructor.cpp:86-278).  This build runs the closing sequence (:271-277) on the poses
-    // given to setInitialReconstruction(); the PnP initialisation needs OpenCV and is not built
-    //  — without initial poses this throws std::runtime_error.
+    // (src/TagReconstructor.cpp:86-278), with the in-repo PnP of PnP.h in place of the OpenCV calls.
+    // When initial poses were given with setInitialReconstruction() only the closing sequence (:271-277) runs.
     void startReconstruction(size_t numThreads = 1);
 
     // initial camera / tag poses (e.g. parseReconstructions of an earlier run)
@@ -82,6 +82,9 @@ public:
     void setDevice(int cudaDevice);
     void setParityMode(bool on);     // true: PCG to 1e-13 so that iterates track an exact-solve (Ceres) trajectory
     void setQuiet(bool on);
+    // true: every image that already sees a reconstructed tag is initialised in the same round and the bundle
+    // adjustment runs once per round instead of once per image; false = the reference's schedule
+    void setWaveMode(bool on) { waveMode_ = on; }
     const BundleAdjustmentReport& lastReport() const { return report_; }
     // what the reference only prints (src/TagReconstructor.cpp:744-783): 3x3 translation covariance per tag id
     // (row-major) and the "Marker Position RMS" of the last doBundleAdjustment(..., printSummary = true)
@@ -93,6 +96,8 @@ protected:
     void flatten(Flat& f) const;
     void ensureEngine() const;
     std::vector<double> reprojectionErrorSums(const Flat& f) const;
+    bool computeRelativeCameraPoseFromImg(int imageId, Vector4d& q, Vector3d& t);   // TagReconstructor.h:134-136
+    void initialiseTagsSeenFrom(int imageId, const std::map<int, std::set<int> >& whichImagesObserveTag, const std::map<int, const Tag*>& tagById);
 
     int originTagId;
     DetectionResult detectionResults_;
@@ -102,7 +107,7 @@ protected:
 
     mutable vmm_ba_engine* engine_ = nullptr;
     int device_ = 0;
-    bool parity_ = false, quiet_ = false, haveInitial_ = false;
+    bool parity_ = false, quiet_ = false, haveInitial_ = false, waveMode_ = false;
     BundleAdjustmentReport report_;
     std::map<int, std::array<double, 9>> tagCovariances_;
     double markerPositionRms_ = 0.0;

@@ -2,12 +2,14 @@
 // std::map state -> dense SoA arrays -> C ABI (include/vmm_ba.h) -> poses written back into the map nodes.
 // What the reference delegates to ceres::Problem / ceres::Solve (:657-738) runs in libvmm_ba.so on the GPU.
 #include "visual_marker_mapping/TagReconstructor.h"
+#include "visual_marker_mapping/PnP.h"
 
 #include "../../../../include/vmm_ba.h"
 
 #include <algorithm>
 #include <cmath>
 #include <iostream>
+#include <set>
 #include <stdexcept>
 
 namespace visual_marker_mapping
@@ -300,17 +302,155 @@ void TagReconstructor::removeBadCameras(double threshold)
     }
 }
 
+bool TagReconstructor::computeRelativeCameraPoseFromImg(int imageId, Vector4d& q, Vector3d& t)
+{
+    // :280-312 — all corners of already reconstructed tags seen in this image against their current world positions
+    std::vector<Vector3d> markerCorners3D;
+    std::vector<Vector2d> observations2D;
+    for (const auto& tagObs : detectionResults_.tagObservations) {
+        if (tagObs.imageId != imageId) continue;
+        const auto tagIt = reconstructedTags.find(tagObs.tagId);
+        if (tagIt == reconstructedTags.end()) continue;
+        const std::vector<Vector3d> tagCorners = tagIt->second.computeMarkerCorners3D();
+        markerCorners3D.insert(markerCorners3D.begin(), tagCorners.begin(), tagCorners.end());
+        observations2D.insert(observations2D.begin(), tagObs.corners.begin(), tagObs.corners.end());
+    }
+    if (!quiet_) std::cout << "   Reconstructing camera pose from " << observations2D.size() << " 2d/3d correspondences" << std::endl;
+    if (observations2D.empty()) return false;
+    const PnPResult r = solvePnPRobust(markerCorners3D, observations2D, camModel);   // replaces solvePnPRansacEigen, :306
+    if (!r.ok) throw std::runtime_error("Camera pose of image " + std::to_string(imageId) + " could not be initialised (degenerate correspondences)");
+    q = rotationMatrixToQuaternion(r.R);
+    t = r.t;
+    return true;
+}
+
+void TagReconstructor::initialiseTagsSeenFrom(int imageId, const std::map<int, std::set<int> >& whichImagesObserveTag,
+                                              const std::map<int, const Tag*>& tagById)
+{
+    // :180-240 — tags seen in this image that are not reconstructed yet: T_world<-tag = T_cam<-world^-1 * T_cam<-tag
+    const Camera& cam = reconstructedCameras.at(imageId);
+    const Matrix3d Rc = quaternionToRotationMatrix(cam.q);
+    for (const auto& tagObs : detectionResults_.tagObservations) {
+        if (tagObs.imageId != imageId) continue;
+        if (reconstructedTags.count(tagObs.tagId)) continue;
+        const auto seen = whichImagesObserveTag.find(tagObs.tagId);
+        if (seen == whichImagesObserveTag.end() || seen->second.size() < 2) {
+            if (!quiet_) std::cout << "   Skipping reconstruction of tag " << tagObs.tagId << ": Only observed once!" << std::endl;
+            continue;
+        }
+        const auto tg = tagById.find(tagObs.tagId);
+        if (tg == tagById.end()) continue;   // the reference dereferences a null pointer here (tagById[...]->tagType, :211)
+        ReconstructedTag recTag;
+        recTag.id = tagObs.tagId;
+        recTag.tagType = tg->second->tagType;
+        recTag.tagWidth = tg->second->width;
+        recTag.tagHeight = tg->second->height;
+        const PnPResult r = solvePnP(recTag.computeLocalMarkerCorners3D(), tagObs.corners, camModel);   // replaces solvePnPEigen, :221
+        if (!r.ok) {
+            if (!quiet_) std::cout << "   Skipping reconstruction of tag " << tagObs.tagId << ": degenerate corner configuration" << std::endl;
+            continue;
+        }
+        // extrinsic^-1 * T: R_w = Rc^T R, t_w = Rc^T (t - tc)
+        Matrix3d Rw;
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) Rw.m[i * 3 + j] = Rc.m[i] * r.R.m[j] + Rc.m[3 + i] * r.R.m[3 + j] + Rc.m[6 + i] * r.R.m[6 + j];
+        const Vector3d d = r.t - cam.t;
+        recTag.q = rotationMatrixToQuaternion(Rw);
+        recTag.t = Vector3d(Rc.m[0] * d(0) + Rc.m[3] * d(1) + Rc.m[6] * d(2), Rc.m[1] * d(0) + Rc.m[4] * d(1) + Rc.m[7] * d(2),
+                            Rc.m[2] * d(0) + Rc.m[5] * d(1) + Rc.m[8] * d(2));
+        reconstructedTags.emplace(tagObs.tagId, recTag);
+        if (!quiet_) std::cout << "   Initialized tag with id " << tagObs.tagId << std::endl;
+    }
+}
+
 void TagReconstructor::startReconstruction(size_t numThreads)
 {
     if (originTagId == -1) originTagId = getLowestTag();   // :89-92
-    if (!haveInitial_)
-        throw std::runtime_error("startReconstruction: the incremental PnP initialisation (src/TagReconstructor.cpp:146-267) is not "
-                                 "part of this build; provide initial poses with setInitialReconstruction()");
-    if (reconstructedTags.find(originTagId) == reconstructedTags.end())
-        throw std::runtime_error("Origin tag " + std::to_string(originTagId) + " is not among the initial tags");
-    if (!quiet_) std::cout << "Start bundle adjustment with " << reconstructedCameras.size() << " cameras and " << reconstructedTags.size() << " tags" << std::endl;
-    // the closing sequence of the reference, :271-277
-    doBundleAdjustment(1500, numThreads, true, false);
+    if (haveInitial_) {
+        // initial poses were handed in (setInitialReconstruction): only the closing sequence of the reference, :271-277
+        if (reconstructedTags.find(originTagId) == reconstructedTags.end())
+            throw std::runtime_error("Origin tag " + std::to_string(originTagId) + " is not among the initial tags");
+        if (!quiet_) std::cout << "Start bundle adjustment with " << reconstructedCameras.size() << " cameras and " << reconstructedTags.size() << " tags" << std::endl;
+        doBundleAdjustment(1500, numThreads, true, false);
+        removeBadMarkers(2.0);
+        removeBadCameras(2.0);
+        doBundleAdjustment(1500, numThreads, false, true);
+        return;
+    }
+    // ---- the incremental initialisation of the reference, src/TagReconstructor.cpp:97-267 ----
+    std::map<int, std::set<int> > whichImagesObserveTag, tagsInImage;
+    for (const auto& tagObs : detectionResults_.tagObservations) {
+        whichImagesObserveTag[tagObs.tagId].insert(tagObs.imageId);
+        tagsInImage[tagObs.imageId].insert(tagObs.tagId);
+    }
+    std::map<int, std::string> imageFilenames;
+    for (const auto& img : detectionResults_.images) imageFilenames[img.imageId] = img.filename;
+    std::map<int, const Tag*> tagById;
+    for (const auto& tag : detectionResults_.tags) tagById[tag.tagId] = &tag;
+
+    // the image with the most tags among those that see the origin tag, :113-124
+    size_t maxObservations = 0;
+    int curImageId = -1;
+    for (int imageId : whichImagesObserveTag[originTagId])
+        if (tagsInImage[imageId].size() > maxObservations) { curImageId = imageId; maxObservations = tagsInImage[imageId].size(); }
+    if (tagById.find(originTagId) == tagById.end())
+        throw std::runtime_error("Could not use tag with id " + std::to_string(originTagId) + " as origin tag, because it was not detected.");
+    if (curImageId == -1)
+        throw std::runtime_error("Could not use tag with id " + std::to_string(originTagId) + " as origin tag, because no image observes it.");
+
+    reconstructedTags.clear();
+    reconstructedCameras.clear();
+    ReconstructedTag origin;   // :134-141
+    origin.id = originTagId;
+    origin.tagType = tagById[originTagId]->tagType;
+    origin.tagWidth = tagById[originTagId]->width;
+    origin.tagHeight = tagById[originTagId]->height;
+    reconstructedTags.emplace(originTagId, origin);
+
+    while (true) {
+        // one camera per round (:146-267); in wave mode every image that already sees a reconstructed tag joins the
+        // round, so that the number of bundle adjustments grows with the depth of the map, not with its images
+        std::vector<int> round{ curImageId };
+        if (waveMode_) {
+            round.clear();
+            for (const auto& img : detectionResults_.images) {
+                if (reconstructedCameras.count(img.imageId)) continue;
+                bool sees = false;
+                for (int tagId : tagsInImage[img.imageId]) sees = sees || reconstructedTags.count(tagId);
+                if (sees) round.push_back(img.imageId);
+            }
+        }
+        for (int imageId : round) {
+            if (!quiet_)
+                std::cout << "Reconstructing image " << reconstructedCameras.size() << "/" << detectionResults_.images.size() << " | "
+                          << imageFilenames[imageId] << " with id: " << imageId << std::endl;
+            Camera newCamera;
+            newCamera.cameraId = imageId;
+            if (!computeRelativeCameraPoseFromImg(imageId, newCamera.q, newCamera.t))
+                throw std::runtime_error("No reconstructed tags in image found. To reconstruct the image pose "
+                                         "already reconstructed markers are needed. This should NOT happen.");
+            if (!quiet_) std::cout << "   Initialized camera with id " << imageId << std::endl;
+            reconstructedCameras.emplace(imageId, newCamera);
+        }
+        for (int imageId : round) initialiseTagsSeenFrom(imageId, whichImagesObserveTag, tagById);
+
+        doBundleAdjustment(400, numThreads, true);   // :243
+        removeBadMarkers(2.0);                       // :246
+
+        // next image: the unreconstructed one with the most reconstructed tags, :248-263
+        int maxPairs = 0;
+        for (const auto& img : detectionResults_.images) {
+            if (reconstructedCameras.count(img.imageId)) continue;
+            int numCorrespondences = 0;
+            for (int tagId : tagsInImage[img.imageId])
+                if (reconstructedTags.count(tagId)) numCorrespondences++;
+            if (numCorrespondences > maxPairs) { maxPairs = numCorrespondences; curImageId = img.imageId; }
+        }
+        if (maxPairs == 0) break;
+        if (!quiet_) std::cout << "----------------------------------------------------------" << std::endl;
+    }
+    if (!quiet_) std::cout << "Starting final bundle adjustment" << std::endl;
+    doBundleAdjustment(1500, numThreads, true, false);   // :271-277
     removeBadMarkers(2.0);
     removeBadCameras(2.0);
     doBundleAdjustment(1500, numThreads, false, true);

@@ -1,13 +1,17 @@
 // vmm_host_test — test driver of the host facade (tests/test_host_facade.py).
 //   vmm_host_test roundtrip <project_dir> <out_dir>   re-writes the three project files through the C++ reader/writer (no GPU)
 //   vmm_host_test stats <project_dir>                 GPU: reprojection statistics at the initial poses, as JSON on stdout
+//   vmm_host_test pnp <cases.txt>                     PnP.h on text cases (no GPU): "case <n> <robust> fx fy cx cy k1 k2 p1 p2 k3" then
+//                                                     n lines "X Y Z u v"; prints "R(9 row-major) t(3) rms inliers" per case
 #include "PtreeJson.h"
 #include "visual_marker_mapping/CameraUtilities.h"
 #include "visual_marker_mapping/DetectionIO.h"
 #include "visual_marker_mapping/ReconstructionIO.h"
+#include "visual_marker_mapping/PnP.h"
 #include "visual_marker_mapping/TagReconstructor.h"
 
 #include <cstdio>
+#include <fstream>
 #include <iostream>
 #include <string>
 
@@ -30,6 +34,27 @@ int main(int argc, char** argv)
             exportReconstructions(out + "/initial_reconstruction.json", tags, cams, m);
             std::printf("images %zu tags %zu observations %zu rec_tags %zu rec_cams %zu fx %.17g\n", det.images.size(), det.tags.size(),
                 det.tagObservations.size(), tags.size(), cams.size(), m.fx);
+            return 0;
+        }
+        if (mode == "pnp") {
+            std::ifstream in(dir);
+            std::string word;
+            while (in >> word) {
+                if (word != "case") return 2;
+                int n = 0, robust = 0;
+                CameraModel m;
+                in >> n >> robust >> m.fx >> m.fy >> m.cx >> m.cy;
+                for (double& d : m.distortionCoefficients) in >> d;
+                std::vector<Vector3d> X(n);
+                std::vector<Vector2d> uv(n);
+                for (int i = 0; i < n; ++i) in >> X[i](0) >> X[i](1) >> X[i](2) >> uv[i](0) >> uv[i](1);
+                std::vector<unsigned char> inl(n, 1);
+                const PnPResult r = robust ? solvePnPRobust(X, uv, m, 8.0, &inl) : solvePnP(X, uv, m);
+                int cnt = 0;
+                for (unsigned char c : inl) cnt += c;
+                for (int k = 0; k < 9; ++k) std::printf("%.17g ", r.R.m[k]);
+                std::printf("%.17g %.17g %.17g %.17g %d %d\n", r.t(0), r.t(1), r.t(2), r.rmsError, cnt, r.ok ? 1 : 0);
+            }
             return 0;
         }
         if (mode == "stats") {

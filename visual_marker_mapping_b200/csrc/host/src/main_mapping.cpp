@@ -2,9 +2,10 @@
 //   --project_path <dir>   reads <dir>/camera_intrinsics.json and <dir>/marker_detections.json,
 //                          writes <dir>/reconstruction.json
 //   --start_tag_id <id>    origin tag (default: lowest id)
-// The PnP initialisation of the reference needs OpenCV and is not built; initial poses
-// are read from --initial_reconstruction (default <dir>/initial_reconstruction.json) and refined by the
-// closing sequence of startReconstruction: BA(Huber) -> cull 2 px -> BA (src/TagReconstructor.cpp:271-277).
+// Like the reference the tool starts from the detections alone: incremental PnP initialisation with a bundle
+// adjustment per added image (src/TagReconstructor.cpp:146-267; --wave: per round of images), then the closing
+// sequence BA(Huber) -> cull 2 px -> BA (:271-277).  Extension: when --initial_reconstruction is given (or
+// <dir>/initial_reconstruction.json exists) its poses are taken as the start and only the closing sequence runs.
 #include "visual_marker_mapping/CameraUtilities.h"
 #include "visual_marker_mapping/DetectionIO.h"
 #include "visual_marker_mapping/ReconstructionIO.h"
@@ -24,7 +25,7 @@ struct Params
 {
     std::string projectPath, initialReconstruction;
     int startTagId = -1, device = 0;
-    bool overwrite = false, parity = false, help = false;
+    bool overwrite = false, parity = false, help = false, wave = false;
 };
 
 Params loadParameters(int argc, char** argv)
@@ -45,6 +46,7 @@ Params loadParameters(int argc, char** argv)
         else if (a.compare(0, 8, "--device") == 0) p.device = std::atoi(value("--device").c_str());
         else if (a == "--overwrite") p.overwrite = true;
         else if (a == "--parity") p.parity = true;
+        else if (a == "--wave") p.wave = true;
         else throw std::runtime_error("unrecognised option '" + a + "'");
     }
     if (!p.help && p.projectPath.empty()) throw std::runtime_error("the option '--project_path' is required but missing");
@@ -60,7 +62,7 @@ int main(int argc, char** argv)
         const Params p = loadParameters(argc, argv);
         if (p.help) {
             std::cout << "Usage: visual_marker_mapping --project_path <dir> [--start_tag_id <id>]\n"
-                         "         [--initial_reconstruction <json>] [--device <cuda device>] [--overwrite] [--parity]\n";
+                         "         [--initial_reconstruction <json>] [--device <cuda device>] [--overwrite] [--parity] [--wave]\n";
             return 0;
         }
         const size_t numThreads = std::thread::hardware_concurrency() ? std::thread::hardware_concurrency() : 4;
@@ -78,13 +80,15 @@ int main(int argc, char** argv)
         std::map<int, Camera> cams;
         CameraModel ignored = camModel;
         const std::string init = p.initialReconstruction.empty() ? p.projectPath + "/initial_reconstruction.json" : p.initialReconstruction;
-        parseReconstructions(init, tags, cams, ignored);
+        const bool haveInit = !p.initialReconstruction.empty() || exists(init);
+        if (haveInit) parseReconstructions(init, tags, cams, ignored);
         TagReconstructor reconstructor(std::move(detections));
         reconstructor.setCameraModel(camModel);
         reconstructor.setOriginTagId(p.startTagId);
         reconstructor.setDevice(p.device);
         reconstructor.setParityMode(p.parity);
-        reconstructor.setInitialReconstruction(tags, cams);
+        reconstructor.setWaveMode(p.wave);
+        if (haveInit) reconstructor.setInitialReconstruction(tags, cams);
         reconstructor.startReconstruction(numThreads);
         exportReconstructions(out, reconstructor.getReconstructedTags(), reconstructor.getReconstructedCameras(), reconstructor.getCameraModel());
         std::cout << "Wrote " << out << std::endl;
