@@ -43,6 +43,8 @@ def c5(max_corners):
 def solve_line(ba, scene, tag, **kw):
     ba.set_poses(scene.cam_q, scene.cam_t, scene.tag_q, scene.tag_t)
     t0 = time.time()
+    if "PCGTOL" in os.environ:
+        kw = dict(kw, pcg_tolerance=float(os.environ["PCGTOL"]))
     s = ba.solve(max_num_iterations=100, **kw)
     dt = time.time() - t0
     cq, ct, tq, tt = ba.get_poses()

@@ -1199,7 +1199,7 @@ void vmm_ba_options_init(vmm_ba_options* o) {
     o->jacobi_scaling = 1;
     o->preconditioner = VMM_BA_PRECOND_TWO_LEVEL;   // block-Jacobi + rigid-motion coarse space over camera clusters (falls back to
                                                     // block-Jacobi when the problem has fewer than two clusters or is sharded)
-    o->pcg_tolerance = 1e-2;
+    o->pcg_tolerance = 5e-2;   // forcing term of the inexact Newton step (Ceres' own default for iterative solvers, eta, is 1e-1)
     o->pcg_max_iterations = 500;
     o->pcg_min_iterations = 1;
     o->parity_mode = 0;
