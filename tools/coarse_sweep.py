@@ -26,17 +26,17 @@ def main():
             ba.set_poses(scene.cam_q, scene.cam_t, scene.tag_q, scene.tag_t)
             t0 = time.time()
             s = ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, verbose=int(os.environ.get("VERBOSE", "0")),
-                         coarse_refresh_iterations=int(os.environ.get("REFRESH", "8")), pcg_tolerance=float(os.environ.get("PCGTOL", "1e-2")))
+                         coarse_refresh_iterations=int(os.environ.get("REFRESH", "8")), pcg_tolerance=float(os.environ.get("PCGTOL", "5e-2")))
             t_solve = time.time() - t0
             ba.set_poses(scene.cam_q, scene.cam_t, scene.tag_q, scene.tag_t)
             ba.profile_enable(True)
-            ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, coarse_refresh_iterations=int(os.environ.get("REFRESH", "8")), pcg_tolerance=float(os.environ.get("PCGTOL", "1e-2")))
+            ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, coarse_refresh_iterations=int(os.environ.get("REFRESH", "8")), pcg_tolerance=float(os.environ.get("PCGTOL", "5e-2")))
             prof = ba.profile()
             ba.profile_enable(False)
             row = {"cams_per_cluster": cs, "set_problem_s": round(t_set, 3), "solve_s": round(t_solve, 4), "lm": s.num_iterations,
                    "pcg": s.pcg_iterations, "final_cost": s.final_cost,
                    "t_linear_solver_s": round(s.time_linear_solver_s, 4)}
-            for k in ("k_coarse_w", "k_coarse_outer", "k_coarse_diag", "cusolverDnDpotrf", "cusolverDnDpotri", "k_schur_product<SP_FULL>", "k_coarse_apply"):
+            for k in ("k_coarse_w", "cublasDtrsm", "cublasDgemm", "cublasDsyrk", "cusolverDnDpotrf", "k_schur_product<SP_FULL>", "k_coarse_apply"):
                 if k in prof:
                     row[k + "_ms_avg"] = round(prof[k][1] / max(prof[k][0], 1), 4)
             print(json.dumps(row), flush=True)

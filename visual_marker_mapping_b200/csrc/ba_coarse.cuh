@@ -211,11 +211,12 @@ __global__ void k_identity(int n, double* __restrict__ A) {
     A[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
 }
 
-// columns [c0, c0 + nb) of the n x n identity, column-major (columns past n: zero padding)
-__global__ void k_identity_columns(int n, int c0, int nb, double* __restrict__ A) {
+// m x m identity into a block of a column-major matrix with leading dimension ld
+__global__ void k_identity_block(int m, int ld, double* __restrict__ A) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (int64_t)n * nb) return;
-    A[idx] = (idx % n == c0 + idx / n) ? 1.0 : 0.0;
+    if (idx >= (int64_t)m * m) return;
+    const int r = (int)(idx % m), c = (int)(idx / m);
+    A[(size_t)c * ld + r] = (r == c) ? 1.0 : 0.0;
 }
 
 // syrk leaves the inverse in one triangle: mirror it (column-major lower == row-major upper).

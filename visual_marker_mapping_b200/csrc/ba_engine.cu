@@ -126,7 +126,7 @@ struct vmm_ba_engine {
         int ncl = 0, nC = 0, lwork = 0;
         DevBuf<int> cl_of_cam, cl_ptr, cl_cams, mcl_ptr, mcl, info;
         DevBuf<unsigned char> mo_lc;
-        DevBuf<double> Linv;      // inverse Cholesky factor of A_c (scratch of the inversion)
+        DevBuf<double> Linv, tmp; // inverse Cholesky factor of A_c and the GEMM scratch of its blocked inversion
         DevBuf<double> xbar, Ac, rc /* nC + 2: r.z partials ride along in its tail when sharded */, yc, work, Wbuf;
         size_t n_w = 0;           // (marker, touched cluster) pairs: Wbuf holds 36 doubles for each
     } coarse;
@@ -438,6 +438,35 @@ int coarse_correction(vmm_ba_engine* e, double* acc, double* acc2, const double*
     return VMM_BA_OK;
 }
 
+// X[off.., off..] = inverse of the lower-triangular block L[off.., off..] of order m (column-major, leading dimension n;
+// X zero outside its lower triangle on entry).  tmp: m/2 x m/2 doubles at least.
+int invert_lower_triangular(vmm_ba_engine* e, const double* L, double* X, double* tmp, int n, int off, int m) {
+    const double one = 1.0, zero = 0.0, minus = -1.0;
+    const double* Ld = L + (size_t)off * n + off;
+    double* Xd = X + (size_t)off * n + off;
+    static const int leaf = std::getenv("VMM_BA_INV_LEAF") ? std::max(64, std::atoi(std::getenv("VMM_BA_INV_LEAF"))) : 256;
+    if (m <= leaf) {
+        LAUNCH(k_identity_block, nblocks((int64_t)m * m, kThreads), kThreads, m, n, Xd);
+        LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, m, m, &one, Ld, n, Xd,
+                                                 n) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
+        return VMM_BA_OK;
+    }
+    const int m1 = ((m / 2 + 63) / 64) * 64, m2 = m - m1;
+    int rc = invert_lower_triangular(e, L, X, tmp, n, off, m1);
+    if (!rc) rc = invert_lower_triangular(e, L, X, tmp, n, off + m1, m2);
+    if (rc) return rc;
+    // T = L21 X11 (m2 x m1), X21 = -X22 T
+    const double* L21 = Ld + m1;
+    const double* X11 = Xd;
+    const double* X22 = Xd + (size_t)m1 * n + m1;
+    double* X21 = Xd + m1;
+    LIBCALL_NAMED("cublasDgemm", cublasDgemm(e->cublas, CUBLAS_OP_N, CUBLAS_OP_N, m2, m1, m1, &one, L21, n, X11, n, &zero, tmp, m2) == CUBLAS_STATUS_SUCCESS,
+                  "cublasDgemm");
+    LIBCALL_NAMED("cublasDgemm", cublasDgemm(e->cublas, CUBLAS_OP_N, CUBLAS_OP_N, m2, m1, m2, &minus, X22, n, tmp, m2, &zero, X21, n) == CUBLAS_STATUS_SUCCESS,
+                  "cublasDgemm");
+    return VMM_BA_OK;
+}
+
 // A_c = P^T S P at the current linearisation and damping, then its inverse (dense, cuSOLVER potrf + potri:
 // a plain library factorisation of a few-thousand-square matrix, once per LM iteration).
 int coarse_setup(vmm_ba_engine* e, int slot) {
@@ -467,34 +496,20 @@ int coarse_setup(vmm_ba_engine* e, int slot) {
                   "cusolverDnDpotrf");
     int h_info[2] = { 0, 0 };
     CU(cudaMemcpyAsync(&h_info[0], c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    // A_c^-1 = L^-T L^-1: X = L^-1 by a triangular solve against the identity, then X^T X (two plain cuBLAS level-3
-    // calls, ~1 ms together at n = 3000; cusolverDnDpotri needs 7.8 ms for the same result)
+    // A_c^-1 = L^-T L^-1.  X = L^-1 by recursive blocking, so that the n^3/3 flops run as fp64 tensor-core GEMMs
+    // (cuBLAS) instead of one triangular solve against a dense identity: for L = [L11 0; L21 L22],
+    // X = [X11 0; -X22 L21 X11, X22]; diagonal blocks of <= 256 rows by cublasDtrsm.  Then X^T X (cublasDsyrk).
+    // 0.9 + 0.9 ms at n = 3126, where trsm + syrk took 2.6 + 0.9 and cusolverDnDpotri 7.8.  Replicated on every rank
+    // of a sharded engine (cheaper than solving by column blocks and all-gathering).
     if (cublasSetStream(e->cublas, e->stream) != CUBLAS_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cublasSetStream failed");
     const double one = 1.0, zero = 0.0;
-    if (e->world == 1) {
-        LAUNCH(k_identity, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Linv.p);
-        LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, c.nC, c.nC, &one,
-                                                 c.Ac.p, c.nC, c.Linv.p, c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
-        LIBCALL_NAMED("cublasDsyrk", cublasDsyrk(e->cublas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, c.nC, c.nC, &one, c.Linv.p, c.nC, &zero, c.Ac.p,
-                                                 c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDsyrk");
-    } else {
-        // sharded: the factor is replicated, the inverse is not formed redundantly — every rank solves
-        // L L^T X = I for its block of columns (two triangular solves on n / world right-hand sides) and the
-        // blocks are all-gathered (column-major: a block of columns is contiguous)
-        const int nb = (c.nC + e->world - 1) / e->world;          // columns per rank (the last block is padded)
-        double* mine = c.Linv.p + (size_t)e->rank * nb * n;
-        LAUNCH(k_identity_columns, nblocks((int64_t)n * nb, kThreads), kThreads, c.nC, e->rank * nb, nb, mine);
-        LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, c.nC, nb, &one,
-                                                 c.Ac.p, c.nC, mine, c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
-        LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, CUBLAS_DIAG_NON_UNIT, c.nC, nb, &one,
-                                                 c.Ac.p, c.nC, mine, c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
-        static const int kid_ag = register_kernel("ncclAllGather");
-        cudaEvent_t eb = e->profiling ? profile_begin(e) : nullptr;
-        const int nrc = nccl_api().AllGather(mine, c.Linv.p, (size_t)nb * n, NCCL_FLOAT64, e->comm, e->stream);
-        if (eb) profile_end(e, kid_ag, eb);
-        if (nrc) return nccl_check(e, nrc, "ncclAllGather");
-        CU(cudaMemcpyAsync(c.Ac.p, c.Linv.p, sizeof(double) * n * n, cudaMemcpyDeviceToDevice, e->stream));
+    CU(cudaMemsetAsync(c.Linv.p, 0, sizeof(double) * n * n, e->stream));
+    {
+        int rc = invert_lower_triangular(e, c.Ac.p, c.Linv.p, c.tmp.p, c.nC, 0, c.nC);
+        if (rc) return rc;
     }
+    LIBCALL_NAMED("cublasDsyrk", cublasDsyrk(e->cublas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, c.nC, c.nC, &one, c.Linv.p, c.nC, &zero, c.Ac.p,
+                                             c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDsyrk");
     LAUNCH(k_symmetrize, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Ac.p);
     CU(cudaStreamSynchronize(e->stream));
     if (e->profiling) profile_resolve(e);
@@ -1068,7 +1083,8 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1))); CU(c.mo_lc.alloc(mo_lc.size()));
     CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(n * n)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
     CU(c.Wbuf.alloc(std::max<size_t>(36 * c.n_w, 1)));
-    CU(c.Linv.alloc(n * (size_t)((c.nC + e->world - 1) / e->world) * e->world));   // whole column blocks per rank
+    CU(c.Linv.alloc(n * n));
+    CU(c.tmp.alloc(std::max<size_t>((n / 2 + 64) * (n / 2 + 64), 1)));
     int lw1 = 0;
     if (cusolverDnDpotrf_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, &lw1) != CUSOLVER_STATUS_SUCCESS)
         return fail_with(e, VMM_BA_ERR_CUDA, "cusolver buffer size query failed");
