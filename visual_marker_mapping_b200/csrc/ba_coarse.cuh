@@ -184,6 +184,44 @@ k_coarse_w(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_a
     for (int id = threadIdx.x; id < nt * 36; id += kCoarseThreads) Wbuf[(size_t)tb * 36 + id] = s_w[id];
 }
 
+// Set-up (one GPU): the distinct clusters every marker touches, in order of first appearance in the marker order,
+// and per observation the position of its cluster in that list.  One warp per marker.
+__global__ void __launch_bounds__(128)
+k_marker_cluster_lists(int nm, const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active,
+                       const int* __restrict__ mo_cam, const int* __restrict__ cl_of_cam, int* __restrict__ lists,
+                       int* __restrict__ counts, unsigned char* __restrict__ mo_lc, int* __restrict__ overflow) {
+    const int j = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (j >= nm) return;
+    __shared__ int s_list[4][kCoarseMaxTouched];
+    int* list = s_list[threadIdx.x >> 5];
+    int cnt = 0;
+    if (tag_active[j]) {
+        const int kb = mptr[j], ke = mptr[j + 1];
+        for (int base = kb; base < ke; base += 32) {
+            const int k = base + lane;
+            const bool valid = k < ke;
+            const int cc = valid ? __ldg(cl_of_cam + __ldg(mo_cam + k)) : -1;
+            int pos = -1;
+            for (int t = 0; t < cnt; ++t) if (list[t] == cc) pos = t;
+            unsigned pending = __ballot_sync(0xffffffffu, valid && pos < 0);
+            while (pending) {
+                const int leader = __ffs(pending) - 1;
+                const int v = __shfl_sync(0xffffffffu, cc, leader);
+                if (cnt < kCoarseMaxTouched) { if (lane == 0) list[cnt] = v; }
+                else if (lane == 0) *overflow = 1;
+                if (valid && pos < 0 && cc == v) pos = min(cnt, kCoarseMaxTouched - 1);
+                cnt = min(cnt + 1, kCoarseMaxTouched);
+                pending &= ~__ballot_sync(0xffffffffu, cc == v);
+                __syncwarp();
+            }
+            if (valid) mo_lc[k] = (unsigned char)pos;
+        }
+    }
+    __syncwarp();
+    if (lane == 0) counts[j] = cnt;
+    for (int t = lane; t < cnt; t += 32) lists[(size_t)j * kCoarseMaxTouched + t] = list[t];
+}
+
 // markers j with j % stride == first are handled by this rank (stride = world size)
 __global__ void __launch_bounds__(kCoarseThreads)
 k_coarse_outer(int nm, int first, int stride, const unsigned char* __restrict__ tag_active, const int* __restrict__ mcl_ptr,

@@ -124,7 +124,7 @@ struct vmm_ba_engine {
         bool available = false;   // clusters exist for this problem
         bool active = false;      // A_c^-1 is valid for the current LM iteration
         int ncl = 0, nC = 0, lwork = 0;
-        DevBuf<int> cl_of_cam, cl_ptr, cl_cams, mcl_ptr, mcl, info;
+        DevBuf<int> cl_of_cam, cl_ptr, cl_cams, mcl_ptr, mcl, info, d_lists, d_cnt, d_over;
         DevBuf<unsigned char> mo_lc;
         DevBuf<double> Linv, tmp; // inverse Cholesky factor of A_c and the GEMM scratch of its blocked inversion
         DevBuf<double> xbar, Ac, rc /* nC + 2: r.z partials ride along in its tail when sharded */, yc, work, Wbuf;
@@ -1032,11 +1032,28 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
         for (size_t q = first; q < cl_cams.size(); ++q) cl_of[cl_cams[q]] = cidx;
     }
     cl_ptr[ncl] = (int)cl_cams.size();
-    // clusters touched per marker (all observations of the problem, caller's order)
     std::vector<int> lst((size_t)Nm * kCoarseMaxTouched), cnt(Nm, 0);
-    {
-        // every thread scans all observations in the caller's order and keeps the markers of its own range:
-        // the list order (first seen) does not depend on the number of threads
+    std::vector<unsigned char> mo_lc;
+    CU(c.cl_of_cam.alloc(std::max<int64_t>(Ncl, 1)));
+    CU(c.mo_lc.alloc(std::max<size_t>((size_t)e->Ntol, 1)));
+    CU(cudaMemcpyAsync(c.cl_of_cam.p, cl_of.data(), sizeof(int) * Ncl, cudaMemcpyHostToDevice, e->stream));
+    if (e->world == 1) {
+        // one GPU: the marker-order arrays are on the device already — lists and positions are built there
+        auto& d_lists = c.d_lists; auto& d_cnt = c.d_cnt; auto& d_over = c.d_over;   // kept across set_problem calls
+        CU(d_lists.alloc((size_t)Nm * kCoarseMaxTouched)); CU(d_cnt.alloc(Nm)); CU(d_over.alloc(1));
+        CU(cudaMemsetAsync(d_over.p, 0, sizeof(int), e->stream));
+        LAUNCH(k_marker_cluster_lists, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, e->tag_active.p, e->mo_cam.p, c.cl_of_cam.p, d_lists.p, d_cnt.p,
+               c.mo_lc.p, d_over.p);
+        int h_over = 0;
+        CU(cudaMemcpyAsync(lst.data(), d_lists.p, sizeof(int) * lst.size(), cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaMemcpyAsync(cnt.data(), d_cnt.p, sizeof(int) * Nm, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaMemcpyAsync(&h_over, d_over.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        if (h_over) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
+    } else {
+        // sharded: clusters touched per marker over ALL observations of the problem (caller's order), the same on every rank.
+        // Every thread scans all observations and keeps the markers of its own range: the list order (first seen)
+        // does not depend on the number of threads.
         const int T = host_threads();
         std::vector<unsigned char> overflow(T, 0);
         parallel_chunks(T, [&](int c, int chunks) {
@@ -1056,31 +1073,32 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
         });
         for (int c = 0; c < T; ++c)
             if (overflow[c]) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
+        mo_lc.assign(std::max<size_t>(mocam.size(), 1), 0);
+        parallel_chunks(host_threads(), [&](int c, int chunks) {
+            for (int64_t j = Nm * c / chunks; j < Nm * (c + 1) / chunks; ++j) {
+                if (!tag_active[j]) continue;
+                const int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
+                for (int k = mptr[j]; k < mptr[j + 1]; ++k) {
+                    const int cc = cl_of[mocam[k]];
+                    int pos = 0;
+                    while (l[pos] != cc) ++pos;
+                    mo_lc[k] = (unsigned char)pos;
+                }
+            }
+        });
+        CU(cudaMemcpyAsync(c.mo_lc.p, mo_lc.data(), mocam.size(), cudaMemcpyHostToDevice, e->stream));
     }
     std::vector<int> mcl_ptr(Nm + 1, 0), mcl;
     for (int64_t j = 0; j < Nm; ++j) {
         mcl.insert(mcl.end(), lst.begin() + (size_t)j * kCoarseMaxTouched, lst.begin() + (size_t)j * kCoarseMaxTouched + cnt[j]);
         mcl_ptr[j + 1] = (int)mcl.size();
     }
-    std::vector<unsigned char> mo_lc(std::max<size_t>(mocam.size(), 1), 0);
-    parallel_chunks(host_threads(), [&](int c, int chunks) {
-        for (int64_t j = Nm * c / chunks; j < Nm * (c + 1) / chunks; ++j) {
-            if (!tag_active[j]) continue;
-            const int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
-            for (int k = mptr[j]; k < mptr[j + 1]; ++k) {
-                const int cc = cl_of[mocam[k]];
-                int pos = 0;
-                while (l[pos] != cc) ++pos;
-                mo_lc[k] = (unsigned char)pos;
-            }
-        }
-    });
     c.ncl = ncl;
     c.nC = 6 * ncl;
     c.n_w = mcl.size();
     const size_t n = (size_t)c.nC;
-    CU(c.cl_of_cam.alloc(std::max<int64_t>(Ncl, 1))); CU(c.cl_ptr.alloc(ncl + 1)); CU(c.cl_cams.alloc(std::max<size_t>(cl_cams.size(), 1)));
-    CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1))); CU(c.mo_lc.alloc(mo_lc.size()));
+    CU(c.cl_ptr.alloc(ncl + 1)); CU(c.cl_cams.alloc(std::max<size_t>(cl_cams.size(), 1)));
+    CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1)));
     CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(n * n)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
     CU(c.Wbuf.alloc(std::max<size_t>(36 * c.n_w, 1)));
     CU(c.Linv.alloc(n * n));
@@ -1091,12 +1109,10 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     c.lwork = lw1;
     CU(c.work.alloc(std::max(c.lwork, 1)));
     auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
-    CU(up(c.cl_of_cam.p, cl_of.data(), sizeof(int) * Ncl));
     CU(up(c.cl_ptr.p, cl_ptr.data(), sizeof(int) * (ncl + 1)));
     CU(up(c.cl_cams.p, cl_cams.data(), sizeof(int) * cl_cams.size()));
     CU(up(c.mcl_ptr.p, mcl_ptr.data(), sizeof(int) * (Nm + 1)));
     CU(up(c.mcl.p, mcl.data(), sizeof(int) * mcl.size()));
-    CU(up(c.mo_lc.p, mo_lc.data(), mocam.size()));
     CU(up(c.xbar.p, xbar.data(), sizeof(double) * 3 * ncl));
     CU(cudaStreamSynchronize(e->stream));
     c.available = true;
@@ -1496,7 +1512,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(e->uvm.alloc(4 * uv_stride));
     e->uv_stride = uv_stride;
     e->perm_c_valid = false;
-    std::vector<int> h_mocam(Ntol);
+    std::vector<int> h_mocam(e->world > 1 ? Ntol : 0);
     if (Nto > 0) {
         CU(cudaMemcpyAsync(e->raw_cam.p, to_cam, sizeof(int) * Nto, cudaMemcpyHostToDevice, e->stream));
         CU(cudaMemcpyAsync(e->raw_tag.p, to_tag, sizeof(int) * Nto, cudaMemcpyHostToDevice, e->stream));
@@ -1522,7 +1538,8 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
             CU(cudaMemsetAsync(e->uvm.p, 0, sizeof(double2) * 4 * uv_stride, e->stream));
             LAUNCH(k_stage_marker_order, nblocks(4 * Ntol, kThreads), kThreads, Ntol, e->mperm.p, e->ocam.p, e->uv.p, uv_stride, e->mo_cam.p,
                    e->uvm.p, e->cpos.p);
-            CU(cudaMemcpyAsync(h_mocam.data(), e->mo_cam.p, sizeof(int) * Ntol, cudaMemcpyDeviceToHost, e->stream));
+            if (e->world > 1)   // the host-side cluster lists of a sharded engine need it
+                CU(cudaMemcpyAsync(h_mocam.data(), e->mo_cam.p, sizeof(int) * Ntol, cudaMemcpyDeviceToHost, e->stream));
         }
         CU(cudaStreamSynchronize(e->stream));
         phase("device sort + both orders");
