@@ -953,7 +953,7 @@ int coarse_leaf_target(int cams_per_cluster, size_t n_active) {
 // Spatially coherent numbering of the cameras for sharded engines: the k-d leaves in depth-first order (each
 // leaf ascending), cameras without observations last.  order[internal] = caller's index.
 void spatial_camera_order(const double* cam_q, const double* cam_t, const std::vector<int64_t>& cam_count, int64_t Nc,
-                          int cams_per_cluster, std::vector<int>& order) {
+                          int cams_per_cluster, std::vector<int>& order, std::vector<std::pair<int, int>>* leaves_out = nullptr) {
     std::vector<int> act;
     for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
     std::vector<double> ctr;
@@ -968,6 +968,7 @@ void spatial_camera_order(const double* cam_q, const double* cam_t, const std::v
         std::sort(order.begin() + first, order.end());
     }
     for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] == 0) order.push_back((int)i);
+    if (leaves_out) *leaves_out = leaves;   // in the new numbering leaf l is the index range [first, second) itself
 }
 
 // Markers that need the gather / all-reduce / scatter path of a sharded product — seen from more than one
@@ -997,7 +998,7 @@ void classify_markers(const std::vector<int64_t>& begin, int world, int64_t Nc, 
 // its camera's cluster in that marker's list.  Host side, once per problem.
 int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, const std::vector<int64_t>& cam_count, int64_t Nto,
                    const int32_t* to_cam, const int32_t* to_tag, const std::vector<int>& mptr, const std::vector<int>& mocam,
-                   const std::vector<unsigned char>& tag_active) {
+                   const std::vector<unsigned char>& tag_active, const std::vector<std::pair<int, int>>* spatial_leaves) {
     auto& c = e->coarse;
     c.available = false;
     c.active = false;
@@ -1010,7 +1011,8 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     std::vector<double> ctr;
     camera_centres(cam_q, cam_t, act, Nc, ctr);
     std::vector<std::pair<int, int>> leaves;
-    kd_leaves(act, ctr, target, leaves);
+    if (spatial_leaves) leaves = *spatial_leaves;   // sharded: the cameras are already numbered leaf by leaf (act[k] == k)
+    else kd_leaves(act, ctr, target, leaves);
     const int ncl = (int)leaves.size();
     if (ncl < 2) return VMM_BA_OK;
     std::vector<int> cl_of_g(Nc, -1), cl_of(std::max<int64_t>(Ncl, 1), -1), cl_ptr(ncl + 1, 0), cl_cams;
@@ -1443,10 +1445,11 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     // sharded: spatial renumbering of the cameras (see cam_order); the permuted copies shadow the caller's arrays
     std::vector<double> cam_q_p, cam_t_p;
     std::vector<int32_t> to_cam_p;
+    std::vector<std::pair<int, int>> spatial_leaves;
     e->cam_order.clear();
     if (e->world > 1 && Nc > 0) {
         std::vector<int> order;
-        spatial_camera_order(cam_q, cam_t, cam_count, Nc, e->coarse_cams_per_cluster, order);
+        spatial_camera_order(cam_q, cam_t, cam_count, Nc, e->coarse_cams_per_cluster, order, &spatial_leaves);
         std::vector<int> pos(Nc);
         for (int64_t i = 0; i < Nc; ++i) pos[order[i]] = (int)i;
         cam_q_p.resize(4 * (size_t)Nc); cam_t_p.resize(3 * (size_t)Nc);
@@ -1459,7 +1462,9 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         }
         cam_count.swap(cc);
         to_cam_p.resize(Nto);
-        for (int64_t k = 0; k < Nto; ++k) to_cam_p[k] = pos[to_cam[k]];
+        parallel_chunks(host_threads(), [&](int c, int chunks) {
+            for (int64_t k = Nto * c / chunks; k < Nto * (c + 1) / chunks; ++k) to_cam_p[k] = pos[to_cam[k]];
+        });
         cam_q = cam_q_p.data(); cam_t = cam_t_p.data(); to_cam = to_cam_p.data();
         sorted = false;
         e->cam_order.swap(order);
@@ -1590,7 +1595,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         int rc = build_segments(e, h_mptr, h_mtile, h_tact, bnd_id);
         if (rc) return rc;
         phase("segment lists");
-        rc = build_clusters(e, cam_q, cam_t, cam_count, Nto, to_cam, to_tag, h_mptr, h_mocam, h_tact);
+        rc = build_clusters(e, cam_q, cam_t, cam_count, Nto, to_cam, to_tag, h_mptr, h_mocam, h_tact, e->cam_order.empty() ? nullptr : &spatial_leaves);
         if (rc) return rc;
         phase("camera clusters");
     }
