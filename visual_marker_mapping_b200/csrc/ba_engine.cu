@@ -1447,7 +1447,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     std::vector<int32_t> to_cam_p;
     std::vector<std::pair<int, int>> spatial_leaves;
     e->cam_order.clear();
-    if (e->world > 1 && Nc > 0) {
+    if (e->world > 1 && Nc > 0) {   // (on one GPU the renumbering was measured neutral for the solve: 0.0898 vs 0.0905 s at C3)
         std::vector<int> order;
         spatial_camera_order(cam_q, cam_t, cam_count, Nc, e->coarse_cams_per_cluster, order, &spatial_leaves);
         std::vector<int> pos(Nc);
