@@ -222,6 +222,15 @@ k_marker_cluster_lists(int nm, const int* __restrict__ mptr, const unsigned char
     for (int t = lane; t < cnt; t += 32) lists[(size_t)j * kCoarseMaxTouched + t] = list[t];
 }
 
+// Sharded set-up: positions in this rank's local cluster list -> positions in the merged (all ranks) list.
+// map[j * kCoarseMaxTouched + local position] = merged position.  One warp per marker.
+__global__ void __launch_bounds__(128)
+k_remap_cluster_positions(int nm, const int* __restrict__ mptr, const unsigned char* __restrict__ map, unsigned char* __restrict__ mo_lc) {
+    const int j = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (j >= nm) return;
+    for (int k = mptr[j] + lane; k < mptr[j + 1]; k += 32) mo_lc[k] = map[(size_t)j * kCoarseMaxTouched + mo_lc[k]];
+}
+
 // markers j with j % stride == first are handled by this rank (stride = world size)
 __global__ void __launch_bounds__(kCoarseThreads)
 k_coarse_outer(int nm, int first, int stride, const unsigned char* __restrict__ tag_active, const int* __restrict__ mcl_ptr,

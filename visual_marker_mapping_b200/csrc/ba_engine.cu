@@ -125,7 +125,7 @@ struct vmm_ba_engine {
         bool active = false;      // A_c^-1 is valid for the current LM iteration
         int ncl = 0, nC = 0, lwork = 0;
         DevBuf<int> cl_of_cam, cl_ptr, cl_cams, mcl_ptr, mcl, info, d_lists, d_cnt, d_over;
-        DevBuf<unsigned char> mo_lc;
+        DevBuf<unsigned char> mo_lc, d_map;
         DevBuf<double> Linv, tmp; // inverse Cholesky factor of A_c and the GEMM scratch of its blocked inversion
         DevBuf<double> xbar, Ac, rc /* nC + 2: r.z partials ride along in its tail when sharded */, yc, work, Wbuf;
         size_t n_w = 0;           // (marker, touched cluster) pairs: Wbuf holds 36 doubles for each
@@ -884,9 +884,10 @@ void parallel_chunks(int chunks, F&& fn) {
     fn(0, chunks);
     for (auto& t : th) t.join();
 }
+int g_processes_per_node = 1;   // ranks sharing this host's cores (set by vmm_ba_create_distributed)
 int host_threads() {
     const unsigned hc = std::thread::hardware_concurrency();
-    return (int)std::max(1u, std::min(8u, hc ? hc : 1u));
+    return (int)std::max(1u, std::min(8u, (hc ? hc : 1u) / (unsigned)std::max(1, g_processes_per_node)));
 }
 
 // Camera centres C = -R^T t of the listed cameras (3 doubles per camera of the problem, zeros elsewhere).
@@ -976,16 +977,24 @@ void spatial_camera_order(const double* cam_q, const double* cam_t, const std::v
 // rank); -1 = the marker's blocks live on one rank and are handled there in one pass.  to_cam: internal indices.
 void classify_markers(const std::vector<int64_t>& begin, int world, int64_t Nc, int64_t Nm, int64_t Nto, const int32_t* to_cam,
                       const int32_t* to_tag, const std::vector<int64_t>& tag_count, std::vector<int>& cam_rank,
-                      std::vector<int>& bnd_id, int64_t& n_bnd) {
+                      std::vector<int>& bnd_id, int64_t& n_bnd, int count_rank = -1, std::vector<int>* local_count = nullptr) {
     cam_rank.assign(std::max<int64_t>(Nc, 1), 0);
     std::vector<int> first(Nm, -1);
     std::vector<unsigned char> multi(Nm, 0);
+    if (local_count) local_count->assign(Nm, 0);
     for (int r = 0; r < world; ++r)
         for (int64_t i = begin[r]; i < begin[r + 1]; ++i) cam_rank[i] = r;
-    for (int64_t k = 0; k < Nto; ++k) {
-        const int j = to_tag[k], r = cam_rank[to_cam[k]];
-        if (first[j] < 0) first[j] = r; else if (first[j] != r) multi[j] = 1;
-    }
+    // every thread scans all observations and keeps the markers of its own range (no shared writes)
+    parallel_chunks(host_threads(), [&](int c, int chunks) {
+        const int64_t j0 = Nm * c / chunks, j1 = Nm * (c + 1) / chunks;
+        for (int64_t k = 0; k < Nto; ++k) {
+            const int j = to_tag[k];
+            if (j < j0 || j >= j1) continue;
+            const int r = cam_rank[to_cam[k]];
+            if (first[j] < 0) first[j] = r; else if (first[j] != r) multi[j] = 1;
+            if (local_count && r == count_rank) (*local_count)[j]++;
+        }
+    });
     bnd_id.assign(Nm, -1);
     n_bnd = 0;
     for (int64_t j = 0; j < Nm; ++j)
@@ -1053,42 +1062,47 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
         CU(cudaStreamSynchronize(e->stream));
         if (h_over) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
     } else {
-        // sharded: clusters touched per marker over ALL observations of the problem (caller's order), the same on every rank.
-        // Every thread scans all observations and keeps the markers of its own range: the list order (first seen)
-        // does not depend on the number of threads.
-        const int T = host_threads();
-        std::vector<unsigned char> overflow(T, 0);
-        parallel_chunks(T, [&](int c, int chunks) {
-            const int64_t j0 = Nm * c / chunks, j1 = Nm * (c + 1) / chunks;
-            for (int64_t k = 0; k < Nto; ++k) {
-                const int j = to_tag[k];
-                if (j < j0 || j >= j1 || !tag_active[j]) continue;
-                const int cc = cl_of_g[to_cam[k]];
-                int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
-                int pos = 0;
-                while (pos < cnt[j] && l[pos] != cc) ++pos;
-                if (pos == cnt[j]) {
-                    if (cnt[j] >= kCoarseMaxTouched) { overflow[c] = 1; return; }
-                    l[cnt[j]++] = cc;
-                }
-            }
-        });
-        for (int c = 0; c < T; ++c)
-            if (overflow[c]) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
-        mo_lc.assign(std::max<size_t>(mocam.size(), 1), 0);
-        parallel_chunks(host_threads(), [&](int c, int chunks) {
-            for (int64_t j = Nm * c / chunks; j < Nm * (c + 1) / chunks; ++j) {
-                if (!tag_active[j]) continue;
-                const int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
-                for (int k = mptr[j]; k < mptr[j + 1]; ++k) {
-                    const int cc = cl_of[mocam[k]];
+        // sharded: every rank lists the clusters its own observations touch (same kernel), the lists are all-gathered and
+        // merged in rank order — the same merged list on every rank — and the local positions are renumbered on the device
+        const int W = e->world;
+        const size_t per = (size_t)Nm * kCoarseMaxTouched + Nm + 1;   // lists | counts | overflow flag
+        CU(c.d_lists.alloc(per * W));
+        int* mine = c.d_lists.p + per * e->rank;
+        CU(cudaMemsetAsync(mine + per - 1, 0, sizeof(int), e->stream));
+        LAUNCH(k_marker_cluster_lists, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, e->tag_active.p, e->mo_cam.p, c.cl_of_cam.p, mine,
+               mine + (size_t)Nm * kCoarseMaxTouched, c.mo_lc.p, mine + per - 1);
+        {
+            const int nrc = nccl_api().AllGather(mine, c.d_lists.p, per, NCCL_INT32, e->comm, e->stream);
+            if (nrc) return nccl_check(e, nrc, "ncclAllGather");
+        }
+        std::vector<int> all(per * W);
+        CU(cudaMemcpyAsync(all.data(), c.d_lists.p, sizeof(int) * per * W, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        std::vector<unsigned char> map((size_t)Nm * kCoarseMaxTouched, 0);
+        bool overflow = false;
+        for (int r = 0; r < W; ++r) overflow = overflow || all[per * r + per - 1] != 0;
+        for (int64_t j = 0; j < Nm && !overflow; ++j) {
+            int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
+            for (int r = 0; r < W && !overflow; ++r) {
+                const int* lr = all.data() + per * r + (size_t)j * kCoarseMaxTouched;
+                const int nr = all[per * r + (size_t)Nm * kCoarseMaxTouched + j];
+                for (int t = 0; t < nr; ++t) {
                     int pos = 0;
-                    while (l[pos] != cc) ++pos;
-                    mo_lc[k] = (unsigned char)pos;
+                    while (pos < cnt[j] && l[pos] != lr[t]) ++pos;
+                    if (pos == cnt[j]) {
+                        if (cnt[j] >= kCoarseMaxTouched) { overflow = true; break; }
+                        l[cnt[j]++] = lr[t];
+                    }
+                    if (r == e->rank) map[(size_t)j * kCoarseMaxTouched + t] = (unsigned char)pos;
                 }
             }
-        });
-        CU(cudaMemcpyAsync(c.mo_lc.p, mo_lc.data(), mocam.size(), cudaMemcpyHostToDevice, e->stream));
+        }
+        if (overflow) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off (the same verdict on every rank)
+        DevBuf<unsigned char>& d_map = c.d_map;
+        CU(d_map.alloc(map.size()));
+        CU(cudaMemcpyAsync(d_map.p, map.data(), map.size(), cudaMemcpyHostToDevice, e->stream));
+        LAUNCH(k_remap_cluster_positions, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, d_map.p, c.mo_lc.p);
+        CU(cudaStreamSynchronize(e->stream));   // map goes out of scope
     }
     std::vector<int> mcl_ptr(Nm + 1, 0), mcl;
     for (int64_t j = 0; j < Nm; ++j) {
@@ -1323,6 +1337,7 @@ int vmm_ba_create_distributed(int device, int rank, int world_size, const void* 
     vmm_ba_engine* e = *out;
     e->rank = rank;
     e->world = world_size;
+    g_processes_per_node = std::max(g_processes_per_node, world_size);
     if (world_size > 1) {
         if (!nccl_api().load()) { std::string m = nccl_api().error; vmm_ba_destroy(e); *out = nullptr; return fail_with(nullptr, VMM_BA_ERR_NCCL, "%s", m.c_str()); }
         nccl_unique_id id;
@@ -1483,19 +1498,15 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     const int64_t Ncl = e->Ncl, Ntol = e->Ntol;
     // tag observations per marker on this shard (CSR of the marker order)
     std::vector<int> h_mptr(Nm + 1, 0);
-    if (e->world == 1) {
-        for (int64_t j = 0; j < Nm; ++j) h_mptr[j + 1] = h_mptr[j] + (int)tag_count[j];
-    } else {
-        for (int64_t k = 0; k < Nto; ++k)
-            if (to_cam[k] >= e->cam0 && to_cam[k] < e->cam1) h_mptr[to_tag[k] + 1]++;
-        for (int64_t j = 0; j < Nm; ++j) h_mptr[j + 1] += h_mptr[j];
-    }
     // compact numbering of the markers that need the gather / all-reduce / scatter path (same on every rank)
     std::vector<int> bnd_id(Nm, -1);
     e->n_bnd = 0;
-    if (e->world > 1) {
-        std::vector<int> cam_rank;
-        classify_markers(begin, e->world, Nc, Nm, Nto, to_cam, to_tag, tag_count, cam_rank, bnd_id, e->n_bnd);
+    if (e->world == 1) {
+        for (int64_t j = 0; j < Nm; ++j) h_mptr[j + 1] = h_mptr[j] + (int)tag_count[j];
+    } else {
+        std::vector<int> cam_rank, local_count;
+        classify_markers(begin, e->world, Nc, Nm, Nto, to_cam, to_tag, tag_count, cam_rank, bnd_id, e->n_bnd, e->rank, &local_count);
+        for (int64_t j = 0; j < Nm; ++j) h_mptr[j + 1] = h_mptr[j] + local_count[j];
         CU(e->wb.alloc(6 * (size_t)e->n_bnd + 4));
     }
 
@@ -1517,7 +1528,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(e->uvm.alloc(4 * uv_stride));
     e->uv_stride = uv_stride;
     e->perm_c_valid = false;
-    std::vector<int> h_mocam(e->world > 1 ? Ntol : 0);
+    std::vector<int> h_mocam;   // (the cluster lists are built from the device copy)
     if (Nto > 0) {
         CU(cudaMemcpyAsync(e->raw_cam.p, to_cam, sizeof(int) * Nto, cudaMemcpyHostToDevice, e->stream));
         CU(cudaMemcpyAsync(e->raw_tag.p, to_tag, sizeof(int) * Nto, cudaMemcpyHostToDevice, e->stream));
@@ -1543,8 +1554,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
             CU(cudaMemsetAsync(e->uvm.p, 0, sizeof(double2) * 4 * uv_stride, e->stream));
             LAUNCH(k_stage_marker_order, nblocks(4 * Ntol, kThreads), kThreads, Ntol, e->mperm.p, e->ocam.p, e->uv.p, uv_stride, e->mo_cam.p,
                    e->uvm.p, e->cpos.p);
-            if (e->world > 1)   // the host-side cluster lists of a sharded engine need it
-                CU(cudaMemcpyAsync(h_mocam.data(), e->mo_cam.p, sizeof(int) * Ntol, cudaMemcpyDeviceToHost, e->stream));
+
         }
         CU(cudaStreamSynchronize(e->stream));
         phase("device sort + both orders");

@@ -12,7 +12,7 @@ namespace vmm {
 typedef struct ncclComm* nccl_comm_t;
 typedef struct { char internal[128]; } nccl_unique_id;
 // values of ncclDataType_t / ncclRedOp_t (stable across NCCL 2.x)
-enum { NCCL_FLOAT64 = 8 };
+enum { NCCL_INT32 = 2, NCCL_FLOAT64 = 8 };
 enum { NCCL_SUM = 0, NCCL_MAX = 2 };
 
 struct NcclApi {
