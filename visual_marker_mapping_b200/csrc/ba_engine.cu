@@ -1449,12 +1449,30 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     };
     std::vector<int64_t> cam_count(Nc, 0), tag_count(Nm, 0);
     bool sorted = true;
-    for (int64_t k = 0; k < Nto; ++k) {
-        const int32_t c = to_cam[k], m = to_tag[k];
-        if (c < 0 || c >= Nc || m < 0 || m >= Nm) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "tag observation %lld has an index out of range", (long long)k);
-        cam_count[c]++;
-        tag_count[m]++;
-        if (k > 0 && to_cam[k - 1] > c) sorted = false;
+    {
+        // validation and per-camera / per-marker counts: chunks of the observation list with thread-private histograms
+        const int T = Nto >= (1 << 18) ? host_threads() : 1;
+        std::vector<std::vector<int>> hc(T), ht(T);
+        std::vector<int64_t> bad(T, -1);
+        std::vector<unsigned char> unsorted(T, 0);
+        parallel_chunks(T, [&](int c, int chunks) {
+            hc[c].assign(Nc, 0);
+            ht[c].assign(Nm, 0);
+            const int64_t k0 = Nto * c / chunks, k1 = Nto * (c + 1) / chunks;
+            for (int64_t k = k0; k < k1; ++k) {
+                const int32_t cam = to_cam[k], m = to_tag[k];
+                if (cam < 0 || cam >= Nc || m < 0 || m >= Nm) { bad[c] = k; return; }
+                hc[c][cam]++;
+                ht[c][m]++;
+                if (k > 0 && to_cam[k - 1] > cam) unsorted[c] = 1;
+            }
+        });
+        for (int c = 0; c < T; ++c) {
+            if (bad[c] >= 0) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "tag observation %lld has an index out of range", (long long)bad[c]);
+            if (unsorted[c]) sorted = false;
+            for (int64_t i = 0; i < Nc; ++i) cam_count[i] += hc[c][i];
+            for (int64_t j = 0; j < Nm; ++j) tag_count[j] += ht[c][j];
+        }
     }
     e->Nc = Nc; e->Nm = Nm; e->Nto = Nto; e->fixed_tag = fixed_tag;
     // sharded: spatial renumbering of the cameras (see cam_order); the permuted copies shadow the caller's arrays
