@@ -122,3 +122,65 @@ def test_reprojection_error_sums_follow_cameramodel_quirk(oracle):
         yd = y * rad + 2 * p2 * xd * y + p1 * (r2 + 2 * y * y)      # quirk: distorted x
         ref += np.hypot(fx * xd + cx - s.to_uv[:, 2 * c], fy * yd + cy - s.to_uv[:, 2 * c + 1])
     assert np.abs(sums - ref).max() < 1e-9
+
+
+# ---- covariance restatement (src/TagReconstructor.cpp:744-783) and scene tiling ---------------------------
+def test_oracle_covariance_equals_schur_form_and_scales_with_noise(oracle):
+    """The oracle inverts the full tangent-space normal matrix; the engine eliminates the cameras first.  Both are the
+    same blocks of the same inverse: check the identity in numpy, independent of any GPU code."""
+    from visual_marker_mapping_b200 import synth
+
+    s = synth.make_scene(n_markers=10, n_cameras=24, markers_per_camera=6, seed=5)
+    cov = oracle.marker_translation_covariance(s)
+    assert cov.shape == (s.n_markers, 3, 3) and not cov[s.fixed_tag].any()
+    ev = oracle.evaluate(s, oracle.LOSS_NONE, 1.0, residuals=False, gradient=False)
+    J = ev.jac_local.reshape(-1, 8, 12)
+    Nc, Nm = s.n_cameras, s.n_markers
+    B = np.zeros((Nc, 6, 6)); C = np.zeros((Nm, 6, 6))
+    np.add.at(B, s.to_cam, np.einsum("kra,krb->kab", J[:, :, :6], J[:, :, :6]))
+    np.add.at(C, s.to_tag, np.einsum("kra,krb->kab", J[:, :, 6:], J[:, :, 6:]))
+    E = np.einsum("kra,krb->kab", J[:, :, :6], J[:, :, 6:])
+    R = np.zeros((6 * Nm, 6 * Nm))
+    for j in range(Nm):
+        R[6 * j:6 * j + 6, 6 * j:6 * j + 6] = C[j]
+    Binv = np.linalg.inv(B)
+    for i in range(Nc):
+        obs = np.nonzero(s.to_cam == i)[0]
+        for a in obs:
+            for b in obs:
+                ja, jb = s.to_tag[a], s.to_tag[b]
+                R[6 * ja:6 * ja + 6, 6 * jb:6 * jb + 6] -= E[a].T @ Binv[i] @ E[b]
+    keep = np.ones(6 * Nm, dtype=bool)
+    keep[6 * s.fixed_tag:6 * s.fixed_tag + 6] = False
+    Rinv = np.linalg.inv(R[np.ix_(keep, keep)])
+    idx = -np.ones(6 * Nm, dtype=int)
+    idx[keep] = np.arange(keep.sum())
+    for j in range(Nm):
+        if j == s.fixed_tag:
+            continue
+        p = idx[6 * j:6 * j + 3]
+        blk = Rinv[np.ix_(p, p)]
+        assert np.abs(blk - cov[j]).max() <= 1e-9 * np.abs(cov[j]).max()
+        assert np.all(np.linalg.eigvalsh(cov[j]) > 0)
+    # markers far from the fixed origin tag are less certain than its neighbours
+    d = np.linalg.norm(s.tag_t_gt - s.tag_t_gt[s.fixed_tag], axis=1)
+    tr = np.trace(cov, axis1=1, axis2=2)
+    far, near = np.argsort(d)[-3:], np.argsort(d)[1:4]
+    assert tr[far].mean() > tr[near].mean()
+
+
+def test_tile_scene_replicas_are_disjoint_and_evaluate_alike(oracle):
+    from visual_marker_mapping_b200 import synth
+
+    s = synth.make_scene(n_markers=8, n_cameras=10, markers_per_camera=5, seed=2)
+    t = synth.tile_scene(s, 3)
+    assert (t.n_cameras, t.n_markers, t.n_tag_obs) == (3 * s.n_cameras, 3 * s.n_markers, 3 * s.n_tag_obs)
+    assert t.to_cam.dtype == np.int32 and t.to_cam.max() == t.n_cameras - 1 and t.to_tag.max() == t.n_markers - 1
+    # replica r only refers to its own cameras and markers
+    for r in range(3):
+        sl = slice(r * s.n_tag_obs, (r + 1) * s.n_tag_obs)
+        assert np.array_equal(t.to_cam[sl], s.to_cam + r * s.n_cameras) and np.array_equal(t.to_tag[sl], s.to_tag + r * s.n_markers)
+    e1 = oracle.evaluate(s, oracle.LOSS_HUBER, 1.0, gradient=False)
+    e3 = oracle.evaluate(t, oracle.LOSS_HUBER, 1.0, gradient=False)
+    assert abs(e3.cost - 3 * e1.cost) <= 1e-12 * e3.cost
+    assert np.array_equal(e3.residuals[:e1.residuals.shape[0]], e1.residuals)
