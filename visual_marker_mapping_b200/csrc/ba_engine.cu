@@ -408,12 +408,19 @@ int schur_offdiag(vmm_ba_engine* e, const double* v, double* out, double* dot_ac
     return VMM_BA_OK;
 }
 
-// (C + L_m)^-1 = Linv^T Linv per marker, then Es = E Linv^T: once per damping value.
-int factor_and_scale(vmm_ba_engine* e) {
+// (C + L_m)^-1 = Linv^T Linv per marker, then Es = E Linv^T: once per damping value.  with_rhs: also the right-hand
+// side of the reduced system, r = -gc + E Cinv gm = -gc + Es (Linv gm), formed while the blocks are written; zm = Linv gm
+// is kept for the back-substitution.
+int factor_and_scale(vmm_ba_engine* e, bool with_rhs = false) {
     const int nm = (int)e->Nm;
     LAUNCH(k_factor_markers, nblocks(nm, 128), 128, nm, e->C.p, e->lam_m.p, e->tag_active.p, e->Linv.p, e->fail.p);
+    if (with_rhs) {
+        LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 0, (const double*)e->gm(), (const double*)nullptr, 1.0, e->zm.p);
+        if (e->Ncl > 0) LAUNCH(k_negate, nblocks(std::max<int64_t>(6 * e->Ncl, 1), kThreads), kThreads, (int)(6 * e->Ncl), e->gc.p, e->pr.p);
+    }
     if (e->Ntol > 0)
-        LAUNCH(k_scale_e, nm, kScaleThreads, e->mptr.p, e->tag_active.p, e->mtile.p, e->Linv.p, e->Et.p, e->Es.p);
+        LAUNCH(k_scale_e, nm, kScaleThreads, e->mptr.p, e->tag_active.p, e->mtile.p, e->Linv.p, e->Et.p, e->Es.p, e->mo_cam.p,
+               (const double*)e->zm.p, with_rhs ? e->pr.p : (double*)nullptr);
     return VMM_BA_OK;
 }
 
@@ -674,7 +681,7 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         reuse_diagonal = false;
         if (nc > 0) LAUNCH(k_lambda, gc_b, kThreads, 6 * nc, e->lmd_c.p, e->scale_c.p, radius, e->lam_c.p);
         LAUNCH(k_lambda, gm_b, kThreads, 6 * nm, e->lmd_m.p, e->scale_m.p, radius, e->lam_m.p);
-        rc = factor_and_scale(e);
+        rc = factor_and_scale(e, true);   // leaves the right-hand side in e->pr
         if (rc) return rc;
         if (nc > 0) {
             if (opt->preconditioner == VMM_BA_PRECOND_SCHUR_JACOBI) {
@@ -700,10 +707,6 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         } else {
             e->coarse.active = false;
         }
-        // rhs: r = -gc + E Cinv gm = -gc + Es (Linv gm); zm = Linv gm is kept for the back-substitution
-        LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 0, (const double*)e->gm(), (const double*)nullptr, 1.0, e->zm.p);
-        if (nc > 0) LAUNCH(k_negate, gc_b, kThreads, 6 * nc, e->gc.p, e->pr.p);
-        schur_scatter(e, e->zm.p, 1.0, e->pr.p, nullptr);
         PcgResult pr{};
         const double tol = opt->parity_mode ? opt->pcg_parity_tolerance : opt->pcg_tolerance;
         const int max_it = opt->parity_mode ? opt->pcg_parity_max_iterations : opt->pcg_max_iterations;

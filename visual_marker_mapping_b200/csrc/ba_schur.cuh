@@ -167,15 +167,20 @@ k_linearize_markers(Intrinsics in, const int* __restrict__ mptr, const unsigned 
 // tag observation; reads and writes whole tiles.  Algorithmic bytes per tag observation: 2 x 288.
 // ------------------------------------------------------------------------------------------
 constexpr int kScaleThreads = 128;
+// rhs != nullptr: the right-hand side of the reduced system rides along, rhs[cam(k)] += Es_k zm_j (zm = Linv g_m),
+// which saves the separate scatter pass over the freshly written blocks.
 __global__ void __launch_bounds__(kScaleThreads)
 k_scale_e(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_active, const int* __restrict__ mtile,
-          const double* __restrict__ Linv, const unsigned char* __restrict__ Et, unsigned char* __restrict__ Es) {
+          const double* __restrict__ Linv, const unsigned char* __restrict__ Et, unsigned char* __restrict__ Es,
+          const int* __restrict__ mo_cam, const double* __restrict__ zm, double* __restrict__ rhs) {
     const int j = blockIdx.x;
     if (!tag_active[j]) return;
     __shared__ double s_l[36];
+    __shared__ double s_z[6];
     if (threadIdx.x < 36) s_l[threadIdx.x] = Linv[(size_t)j * 36 + threadIdx.x];
+    if (rhs && threadIdx.x >= 64 && threadIdx.x < 70) s_z[threadIdx.x - 64] = zm[(size_t)j * 6 + threadIdx.x - 64];
     __syncthreads();
-    const int n = mptr[j + 1] - mptr[j], t0 = mtile[j];
+    const int kb = mptr[j], n = mptr[j + 1] - kb, t0 = mtile[j];
     for (int i = threadIdx.x; i < n; i += kScaleThreads) {
         double E[36];
 #pragma unroll
@@ -183,6 +188,7 @@ k_scale_e(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_ac
             const double2 v = __ldcs(e_entry(Et, t0, i, p));
             E[2 * p] = v.x; E[2 * p + 1] = v.y;
         }
+        double* out = rhs ? rhs + (size_t)__ldg(mo_cam + kb + i) * 6 : nullptr;
 #pragma unroll
         for (int a = 0; a < 6; ++a) {
             double o[6];
@@ -195,6 +201,12 @@ k_scale_e(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_ac
             }
 #pragma unroll
             for (int h = 0; h < 3; ++h) *e_entry(Es, t0, i, 3 * a + h) = make_double2(o[2 * h], o[2 * h + 1]);
+            if (out) {
+                double r = 0.0;
+#pragma unroll
+                for (int c = 0; c < 6; ++c) r += o[c] * s_z[c];
+                atomicAdd(out + a, r);
+            }
         }
     }
 }
