@@ -225,3 +225,29 @@ def test_cli_origin_tag_errors(host, tmp_path, scene_c1):
     r = subprocess.run([CLI, "--project_path", str(tmp_path), "--start_tag_id", "99", "--overwrite"], capture_output=True, text=True)
     assert r.returncode == 0                              # the reference's main swallows the exception, src/main_mapping.cpp:90-95
     assert "Could not use tag with id 99 as origin tag, because it was not detected." in r.stderr
+
+
+def test_move_tag_into_origin_matches_reference_formulas(host, tmp_path, scene_c1):
+    """src/TagReconstructor.cpp:314-338: q = quat(tag)^-1, every pose becomes (q * pose.q, R(q) (pose.t - tag.t))."""
+    s = scene_c1
+    project_io.write_project(s, str(tmp_path))
+    out = tmp_path / "moved.json"
+    r = subprocess.run([DRIVER, "moveorigin", str(tmp_path), "3", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    tags, cams = project_io.read_reconstruction(str(out))
+
+    def qmul(a, b):
+        return np.array([a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3], a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2],
+                         a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1], a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0]])
+
+    q3 = s.tag_q[3] / np.dot(s.tag_q[3], s.tag_q[3]) * np.array([1, -1, -1, -1])
+    R = synth.quat_to_rot(q3[None] / np.linalg.norm(q3))[0] if abs(np.linalg.norm(q3) - 1) > 1e-9 else synth.quat_to_rot(q3[None])[0]
+    assert np.abs(tags[3]["t"]).max() < 1e-12 and synth.quat_angle(tags[3]["q"], np.array([1.0, 0, 0, 0])) < 1e-9
+    for j in range(s.n_markers):
+        assert np.abs(tags[j]["q"] - qmul(q3, s.tag_q[j])).max() < 1e-9
+        assert np.abs(tags[j]["t"] - R @ (s.tag_t[j] - s.tag_t[3])).max() < 1e-9
+    for i in range(s.n_cameras):
+        assert np.abs(cams[i]["q"] - qmul(q3, s.cam_q[i])).max() < 1e-9
+        assert np.abs(cams[i]["t"] - R @ (s.cam_t[i] - s.tag_t[3])).max() < 1e-9
+    bad = subprocess.run([DRIVER, "moveorigin", str(tmp_path), "77", str(out)], capture_output=True, text=True)
+    assert bad.returncode == 1 and "Tag with id 77 is not reconstructed." in bad.stderr

@@ -63,6 +63,10 @@ public:
     const std::map<int, double> computeReprojectionErrorPerTag(double& avg) const;
     const std::vector<Vector2d> computeReprojectionErrorPerCorner() const;
 
+    // TagReconstructor.h:110 / src/TagReconstructor.cpp:314-338: re-express every pose relative to tag `tagId`
+    // (the reference's formulas, applied to tags and cameras alike, reproduced as they are)
+    void moveTagIntoOrigin(int tagId);
+
     int getLowestTag() const;
     const std::map<int, ReconstructedTag> getReconstructedTags() const;
     const std::map<int, Camera> getReconstructedCameras() const;

@@ -61,6 +61,31 @@ void TagReconstructor::setDevice(int cudaDevice)
 void TagReconstructor::setParityMode(bool on) { parity_ = on; }
 void TagReconstructor::setQuiet(bool on) { quiet_ = on; }
 
+void TagReconstructor::moveTagIntoOrigin(int tagId)
+{
+    if (!reconstructedTags.count(tagId)) throw std::runtime_error("Tag with id " + std::to_string(tagId) + " is not reconstructed.");
+    if (!quiet_) std::cout << "Transforming tag with id " << tagId << " into origin." << std::endl;
+    // q = quat(tag)^-1 (Eigen's inverse: conjugate / squared norm), t = tag.t, :321-322
+    const Vector4d qt = reconstructedTags[tagId].q;
+    const double n2 = qt(0) * qt(0) + qt(1) * qt(1) + qt(2) * qt(2) + qt(3) * qt(3);
+    const Vector4d q(qt(0) / n2, -qt(1) / n2, -qt(2) / n2, -qt(3) / n2);
+    const Vector3d t = reconstructedTags[tagId].t;
+    const Matrix3d R = quaternionToRotationMatrix(q);
+    auto mul = [](const Vector4d& a, const Vector4d& b) {   // Hamilton product, (w,x,y,z)
+        return Vector4d(a(0) * b(0) - a(1) * b(1) - a(2) * b(2) - a(3) * b(3), a(0) * b(1) + a(1) * b(0) + a(2) * b(3) - a(3) * b(2),
+                        a(0) * b(2) - a(1) * b(3) + a(2) * b(0) + a(3) * b(1), a(0) * b(3) + a(1) * b(2) - a(2) * b(1) + a(3) * b(0));
+    };
+    for (auto& tag : reconstructedTags) {   // :324-328
+        tag.second.q = mul(q, tag.second.q);
+        tag.second.t = R * (tag.second.t - t);
+    }
+    for (auto& cam : reconstructedCameras) {   // :330-335 (the same two lines, although a camera pose maps world -> camera)
+        cam.second.q = mul(q, cam.second.q);
+        cam.second.t = R * (cam.second.t - t);
+    }
+    if (!quiet_) std::cout << "Finished transforming Tags" << std::endl;
+}
+
 int TagReconstructor::getLowestTag() const
 {
     if (detectionResults_.tags.empty()) throw std::runtime_error("No tags in the detection result");   // reference: UB

@@ -11,6 +11,7 @@
 #include "visual_marker_mapping/TagReconstructor.h"
 
 #include <cstdio>
+#include <cstdlib>
 #include <fstream>
 #include <iostream>
 #include <string>
@@ -55,6 +56,21 @@ int main(int argc, char** argv)
                 for (int k = 0; k < 9; ++k) std::printf("%.17g ", r.R.m[k]);
                 std::printf("%.17g %.17g %.17g %.17g %d %d\n", r.t(0), r.t(1), r.t(2), r.rmsError, cnt, r.ok ? 1 : 0);
             }
+            return 0;
+        }
+        if (mode == "moveorigin") {   // vmm_host_test moveorigin <project_dir> <tag id> <out.json>: no GPU
+            if (argc < 5) return 2;
+            DetectionResult det = readDetectionResult(dir + "/marker_detections.json");
+            std::map<int, ReconstructedTag> tags;
+            std::map<int, Camera> cams;
+            CameraModel m = readCameraModel(dir + "/camera_intrinsics.json");
+            parseReconstructions(dir + "/initial_reconstruction.json", tags, cams, m);
+            TagReconstructor rec(std::move(det));
+            rec.setCameraModel(m);
+            rec.setQuiet(true);
+            rec.setInitialReconstruction(tags, cams);
+            rec.moveTagIntoOrigin(std::atoi(argv[3]));
+            exportReconstructions(argv[4], rec.getReconstructedTags(), rec.getReconstructedCameras(), rec.getCameraModel());
             return 0;
         }
         if (mode == "stats") {
