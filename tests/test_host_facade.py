@@ -97,6 +97,53 @@ def test_reader_error_messages(host, tmp_path, scene_c1):
     assert r.returncode == 1 and "Not enough many parameters in vector. Expected 5, got 4!" in r.stderr
 
 
+def test_streamed_io_is_bounded_in_memory(host, tmp_path):
+    """site-sized files go through the chunked section reader and the streaming writer.  400 k tag
+    observations (a 237 MB marker_detections.json) are written, read back and compared; the process may grow by
+    the DetectionResult itself (~50 MB) but never by a whole-file tree (several times the file size)."""
+    r = subprocess.run([DRIVER, "bigio", str(tmp_path), "400000"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    f = dict(zip(r.stdout.split()[0::2], map(int, r.stdout.split()[1::2])))
+    assert f["observations"] == 400000 and f["mismatches"] == 0
+    assert f["file_bytes"] > 200e6
+    assert (f["maxrss_kb"] - f["base_rss_kb"]) * 1024 < 0.35 * f["file_bytes"]
+    text = (tmp_path / "marker_detections.json").read_text()
+    assert text.startswith('{\n    "images": [\n        {\n            "filename": "images\\/img_0.jpg",\n            "id": "0"\n        },')
+    assert text.endswith('                ]\n            ]\n        }\n    ]\n}\n')
+
+
+def test_streamed_reader_edge_cases(host, tmp_path, scene_c1):
+    """Section reader: key order free, unknown sections and members skipped, object-valued sections iterate their
+    members (ptree makes no array/object distinction), missing sections and syntax errors reported."""
+    src, dst = tmp_path / "src", tmp_path / "dst"
+    dst.mkdir()
+    project_io.write_project(scene_c1, str(src))
+    good = (src / "marker_detections.json").read_text()
+    det = json.loads(good)
+    shuffled = {"comment": {"deep": [[1, {"x": []}], "y"]}, "tag_observations": det["tag_observations"],
+                "tags": {f"t{i}": dict(t, extra=[1, 2]) for i, t in enumerate(det["tags"])}, "version": 3, "images": det["images"]}
+    (src / "marker_detections.json").write_text(json.dumps(shuffled, indent=1))
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert (dst / "marker_detections.json").read_text() == good
+    del det["tags"]
+    (src / "marker_detections.json").write_text(json.dumps(det))
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 1 and "No such node (tags)" in r.stderr
+    (src / "marker_detections.json").write_text(good[: len(good) // 2])
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 1 and "marker_detections.json(" in r.stderr
+    (src / "marker_detections.json").write_text(good.rstrip() + " x")
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 1 and "garbage after data" in r.stderr
+    (src / "marker_detections.json").write_text(good)
+    rec = json.loads((src / "initial_reconstruction.json").read_text())
+    del rec["reconstructed_cameras"]
+    (src / "initial_reconstruction.json").write_text(json.dumps(rec))
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 1 and "No such node (reconstructed_cameras)" in r.stderr
+
+
 def test_cli_without_device_reports_and_returns_zero(host, tmp_path, scene_c1, have_gpu):
     """No CPU fallback; like the reference's main the exception is printed and the exit code stays 0."""
     if have_gpu:

@@ -6,6 +6,7 @@
 #include <cstring>
 #include <fstream>
 #include <sstream>
+#include <vector>
 
 namespace vmm_json
 {
@@ -37,41 +38,67 @@ int Node::value_int() const
 
 namespace
 {
+// Input: a whole string, or a file read in 1 MiB chunks (nothing but the current chunk is kept).
+struct Input
+{
+    const char* cur = nullptr;
+    const char* lim = nullptr;
+    std::FILE* file = nullptr;
+    std::vector<char> chunk;
+    size_t line = 1;
+
+    bool fill()
+    {
+        if (!file) return false;
+        if (chunk.empty()) chunk.resize((size_t)1 << 20);
+        const size_t n = std::fread(chunk.data(), 1, chunk.size(), file);
+        cur = chunk.data();
+        lim = cur + n;
+        return n > 0;
+    }
+    bool eof() { return cur == lim && !fill(); }
+    char peek() { return *cur; }   // only after !eof()
+    char get()
+    {
+        const char c = *cur++;
+        if (c == '\n') ++line;
+        return c;
+    }
+};
+
 struct Parser
 {
-    const std::string& s;
+    Input& in;
     const std::string& what;
-    size_t p = 0;
 
-    [[noreturn]] void fail(const std::string& msg) const
-    {
-        size_t line = 1;
-        for (size_t i = 0; i < p && i < s.size(); ++i)
-            if (s[i] == '\n') ++line;
-        throw std::runtime_error(what + "(" + std::to_string(line) + "): " + msg);
-    }
+    [[noreturn]] void fail(const std::string& msg) const { throw std::runtime_error(what + "(" + std::to_string(in.line) + "): " + msg); }
     void ws()
     {
-        while (p < s.size() && (s[p] == ' ' || s[p] == '\t' || s[p] == '\n' || s[p] == '\r')) ++p;
+        while (!in.eof()) {
+            const char c = in.peek();
+            if (c != ' ' && c != '\t' && c != '\n' && c != '\r') break;
+            in.get();
+        }
     }
+    bool next_is(char c) { return !in.eof() && in.peek() == c; }
     static void utf8(std::string& out, unsigned cp)
     {
         if (cp < 0x80) out += (char)cp;
         else if (cp < 0x800) { out += (char)(0xC0 | (cp >> 6)); out += (char)(0x80 | (cp & 0x3F)); }
         else { out += (char)(0xE0 | (cp >> 12)); out += (char)(0x80 | ((cp >> 6) & 0x3F)); out += (char)(0x80 | (cp & 0x3F)); }
     }
-    std::string string()
+    void string(std::string& out)
     {
-        if (s[p] != '"') fail("expected string");
-        ++p;
-        std::string out;
+        if (!next_is('"')) fail("expected string");
+        in.get();
+        out.clear();
         while (true) {
-            if (p >= s.size()) fail("unterminated string");
-            const char c = s[p++];
+            if (in.eof()) fail("unterminated string");
+            const char c = in.get();
             if (c == '"') break;
             if (c != '\\') { out += c; continue; }
-            if (p >= s.size()) fail("unterminated escape");
-            const char e = s[p++];
+            if (in.eof()) fail("unterminated escape");
+            const char e = in.get();
             switch (e) {
             case '"': out += '"'; break;
             case '\\': out += '\\'; break;
@@ -82,62 +109,118 @@ struct Parser
             case 'r': out += '\r'; break;
             case 't': out += '\t'; break;
             case 'u': {
-                if (p + 4 > s.size()) fail("bad \\u escape");
-                utf8(out, (unsigned)std::strtoul(s.substr(p, 4).c_str(), nullptr, 16));
-                p += 4;
+                char hex[5] = { 0, 0, 0, 0, 0 };
+                for (int i = 0; i < 4; ++i) {
+                    if (in.eof()) fail("bad \\u escape");
+                    hex[i] = in.get();
+                }
+                utf8(out, (unsigned)std::strtoul(hex, nullptr, 16));
                 break;
             }
             default: fail("invalid escape sequence");
             }
         }
-        return out;
     }
-    Node value()
+    // bare literal: number, true, false, null — kept as text, like read_json does
+    void literal(std::string& out)
+    {
+        out.clear();
+        while (!in.eof()) {
+            const char c = in.peek();
+            if (c == ',' || c == '}' || c == ']' || c == ' ' || c == '\n' || c == '\r' || c == '\t') break;
+            out += in.get();
+        }
+        if (out.empty()) fail("expected value");
+    }
+    // Children of the container that starts at the cursor ('{' or '['); each (key, child) goes to `sink`.
+    template <class Sink> void container(const Sink& sink)
+    {
+        const bool object = in.get() == '{';
+        const char close = object ? '}' : ']';
+        ws();
+        if (next_is(close)) { in.get(); return; }
+        std::string key;
+        while (true) {
+            if (object) {
+                ws();
+                string(key);
+                ws();
+                if (!next_is(':')) fail("expected ':'");
+                in.get();
+            }
+            Node child;
+            value(child);
+            sink(key, child);
+            ws();
+            if (next_is(',')) { in.get(); continue; }
+            if (next_is(close)) { in.get(); break; }
+            fail(object ? "expected ',' or '}'" : "expected ',' or ']'");
+        }
+    }
+    void value(Node& n)
     {
         ws();
-        if (p >= s.size()) fail("unexpected end of input");
-        Node n;
-        const char c = s[p];
-        if (c == '{') {
-            ++p;
-            ws();
-            if (p < s.size() && s[p] == '}') { ++p; return n; }
-            while (true) {
-                ws();
-                std::string key = string();
-                ws();
-                if (p >= s.size() || s[p] != ':') fail("expected ':'");
-                ++p;
-                Node child = value();
-                n.children.emplace_back(std::move(key), std::move(child));
-                ws();
-                if (p < s.size() && s[p] == ',') { ++p; continue; }
-                if (p < s.size() && s[p] == '}') { ++p; break; }
-                fail("expected ',' or '}'");
-            }
-        } else if (c == '[') {
-            ++p;
-            ws();
-            if (p < s.size() && s[p] == ']') { ++p; return n; }
-            while (true) {
-                Node child = value();
-                n.children.emplace_back(std::string(), std::move(child));
-                ws();
-                if (p < s.size() && s[p] == ',') { ++p; continue; }
-                if (p < s.size() && s[p] == ']') { ++p; break; }
-                fail("expected ',' or ']'");
-            }
-        } else if (c == '"') {
-            n.data = string();
-        } else {
-            // bare literal: number, true, false, null — kept as text, like read_json does
-            const size_t b = p;
-            while (p < s.size() && s[p] != ',' && s[p] != '}' && s[p] != ']' && s[p] != ' ' && s[p] != '\n' && s[p] != '\r' && s[p] != '\t') ++p;
-            if (p == b) fail("expected value");
-            n.data = s.substr(b, p - b);
-        }
-        return n;
+        if (in.eof()) fail("unexpected end of input");
+        const char c = in.peek();
+        if (c == '{' || c == '[')
+            container([&n](std::string& key, Node& child) { n.children.emplace_back(std::move(key), std::move(child)); key.clear(); });
+        else if (c == '"') string(n.data);
+        else literal(n.data);
     }
+    void finish()
+    {
+        ws();
+        if (!in.eof()) fail("garbage after data");
+    }
+    // root object → sections → elements (see read_json_sections in the header)
+    std::vector<std::string> sections(const ElementFn& element)
+    {
+        std::vector<std::string> seen;
+        ws();
+        if (in.eof()) fail("unexpected end of input");
+        if (in.peek() != '{') {   // not an object: nothing to hand out; parsed (and dropped) for its syntax errors only
+            Node n;
+            value(n);
+            finish();
+            return seen;
+        }
+        in.get();
+        ws();
+        if (next_is('}')) { in.get(); finish(); return seen; }
+        std::string section;
+        while (true) {
+            ws();
+            string(section);
+            ws();
+            if (!next_is(':')) fail("expected ':'");
+            in.get();
+            ws();
+            if (in.eof()) fail("unexpected end of input");
+            seen.push_back(section);
+            const char c = in.peek();
+            if (c == '{' || c == '[') container([&](std::string& key, Node& child) { element(section, key, child); });
+            else {
+                Node leaf;
+                value(leaf);
+            }
+            ws();
+            if (next_is(',')) { in.get(); continue; }
+            if (next_is('}')) { in.get(); break; }
+            fail("expected ',' or '}'");
+        }
+        finish();
+        return seen;
+    }
+};
+
+struct FileInput : Input
+{
+    explicit FileInput(const std::string& filename)
+    {
+        file = std::fopen(filename.c_str(), "rb");
+        if (!file) throw std::runtime_error(filename + ": cannot open file");
+    }
+    ~FileInput() { std::fclose(file); }
 };
 
 std::string escape(const std::string& in)
@@ -197,20 +280,40 @@ void write_node(std::string& out, const Node& n, int indent)
 
 Node parse_json(const std::string& text, const std::string& what)
 {
-    Parser ps{ text, what };
-    Node n = ps.value();
-    ps.ws();
-    if (ps.p != text.size()) ps.fail("garbage after data");
+    Input in;
+    in.cur = text.data();
+    in.lim = text.data() + text.size();
+    Parser ps{ in, what };
+    Node n;
+    ps.value(n);
+    ps.finish();
     return n;
 }
 
 Node read_json(const std::string& filename)
 {
-    std::ifstream in(filename.c_str(), std::ios::binary);
-    if (!in) throw std::runtime_error(filename + ": cannot open file");
-    std::stringstream ss;
-    ss << in.rdbuf();
-    return parse_json(ss.str(), filename);
+    FileInput in(filename);
+    Parser ps{ in, filename };
+    Node n;
+    ps.value(n);
+    ps.finish();
+    return n;
+}
+
+std::vector<std::string> parse_json_sections(const std::string& text, const ElementFn& element, const std::string& what)
+{
+    Input in;
+    in.cur = text.data();
+    in.lim = text.data() + text.size();
+    Parser ps{ in, what };
+    return ps.sections(element);
+}
+
+std::vector<std::string> read_json_sections(const std::string& filename, const ElementFn& element)
+{
+    FileInput in(filename);
+    Parser ps{ in, filename };
+    return ps.sections(element);
 }
 
 std::string to_json(const Node& root)
@@ -228,5 +331,90 @@ void write_json(const std::string& filename, const Node& root)
     const std::string text = to_json(root);
     out.write(text.data(), (std::streamsize)text.size());
     if (!out) throw std::runtime_error(filename + ": write error");
+}
+
+Writer::Writer(const std::string& filename) : filename_(filename), file_(std::fopen(filename.c_str(), "wb"))
+{
+    if (!file_) throw std::runtime_error(filename + ": cannot open file");
+    stack_.push_back(Frame{ false, 0 });
+}
+
+Writer::~Writer()
+{
+    if (file_) std::fclose(file_);
+}
+
+void Writer::flush()
+{
+    if (!buf_.empty() && std::fwrite(buf_.data(), 1, buf_.size(), file_) != buf_.size()) throw std::runtime_error(filename_ + ": write error");
+    buf_.clear();
+}
+
+// Everything a child prints before its own value: the parent's bracket (first child), the separator, the
+// indentation and, inside an object, the key.
+void Writer::child_prefix(const std::string& key)
+{
+    Frame& parent = stack_.back();
+    if (parent.count++ == 0) buf_ += parent.is_array ? '[' : '{';
+    else buf_ += ',';
+    buf_ += '\n';
+    buf_.append((size_t)4 * stack_.size(), ' ');
+    if (!parent.is_array) {
+        buf_ += '"';
+        buf_ += escape(key);
+        buf_ += "\": ";
+    }
+    if (buf_.size() > ((size_t)1 << 20)) flush();
+}
+
+void Writer::begin(const std::string& key, bool is_array)
+{
+    child_prefix(key);
+    stack_.push_back(Frame{ is_array, 0 });
+}
+
+void Writer::end()
+{
+    if (stack_.size() < 2) throw std::logic_error("vmm_json::Writer::end without begin");
+    const Frame f = stack_.back();
+    stack_.pop_back();
+    if (f.count == 0) { buf_ += "\"\""; return; }
+    buf_ += '\n';
+    buf_.append((size_t)4 * stack_.size(), ' ');
+    buf_ += f.is_array ? ']' : '}';
+}
+
+void Writer::leaf(const std::string& key, const std::string& value)
+{
+    child_prefix(key);
+    buf_ += '"';
+    buf_ += escape(value);
+    buf_ += '"';
+}
+
+void Writer::leaf(const std::string& key, double value)
+{
+    child_prefix(key);
+    char text[64];
+    const int n = std::snprintf(text, sizeof(text), "\"%.17g\"", value);
+    buf_.append(text, (size_t)n);
+}
+
+void Writer::node(const std::string& key, const Node& subtree)
+{
+    child_prefix(key);
+    write_node(buf_, subtree, (int)stack_.size());
+}
+
+void Writer::close()
+{
+    if (stack_.size() != 1) throw std::logic_error("vmm_json::Writer::close with open containers");
+    if (stack_.back().count == 0) buf_ += '{';
+    buf_ += "\n}\n";
+    flush();
+    const bool bad = std::fflush(file_) != 0 || std::ferror(file_);
+    const bool bad_close = std::fclose(file_) != 0;
+    file_ = nullptr;
+    if (bad || bad_close) throw std::runtime_error(filename_ + ": write error");
 }
 }

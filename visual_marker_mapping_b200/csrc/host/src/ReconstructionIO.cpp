@@ -10,11 +10,11 @@ namespace visual_marker_mapping
 {
 namespace
 {
-template <int N> vmm_json::Node vectorNode(const VectorNd<N>& v)
+template <int N> void writeVector(vmm_json::Writer& w, const char* key, const VectorNd<N>& v)
 {
-    vmm_json::Node n;
-    for (int i = 0; i < N; ++i) n.push_back(vmm_json::Node::leaf(v(i)));
-    return n;
+    w.begin_array(key);
+    for (int i = 0; i < N; ++i) w.value(v(i));
+    w.end();
 }
 template <int N> VectorNd<N> nodeVector(const vmm_json::Node& n)
 {
@@ -32,67 +32,77 @@ template <int N> VectorNd<N> nodeVector(const vmm_json::Node& n)
 void exportReconstructions(const std::string& outputPath, const std::map<int, ReconstructedTag>& reconstructedTags,
     const std::map<int, Camera>& reconstructedCameras, const CameraModel& camModel)
 {
-    using vmm_json::Node;
-    Node root, tags, corners, cams;
+    vmm_json::Writer w(outputPath);   // streamed: 120 k poses + 80 k corners at site size
+    w.begin_array("reconstructed_tags");
     for (const auto& it : reconstructedTags) {
         const ReconstructedTag& tag = it.second;
-        Node n;
-        n.put("id", tag.id);
-        n.put("type", tag.tagType);
-        n.put("width", tag.tagWidth);
-        n.put("height", tag.tagHeight);
-        n.add_child("rotation", vectorNode(tag.q));
-        n.add_child("translation", vectorNode(tag.t));
-        tags.push_back(n);
+        w.begin_object();
+        w.leaf("id", tag.id);
+        w.leaf("type", tag.tagType);
+        w.leaf("width", tag.tagWidth);
+        w.leaf("height", tag.tagHeight);
+        writeVector(w, "rotation", tag.q);
+        writeVector(w, "translation", tag.t);
+        w.end();
     }
-    root.add_child("reconstructed_tags", tags);
+    w.end();
+    w.begin_array("reconstructed_marker_corners");
     for (const auto& it : reconstructedTags) {
         const std::vector<Vector3d> c = it.second.computeMarkerCorners3D();
         for (int i = 0; i < 4; ++i) {
-            Node n;
-            n.put("marker_id", it.second.id);
-            n.put("corner_index", i);
-            n.add_child("coords", vectorNode(c[i]));
-            corners.push_back(n);
+            w.begin_object();
+            w.leaf("marker_id", it.second.id);
+            w.leaf("corner_index", i);
+            writeVector(w, "coords", c[i]);
+            w.end();
         }
     }
-    root.add_child("reconstructed_marker_corners", corners);
+    w.end();
+    w.begin_array("reconstructed_cameras");
     for (const auto& it : reconstructedCameras) {
-        Node n;
-        n.put("id", it.second.cameraId);
-        n.add_child("rotation", vectorNode(it.second.q));
-        n.add_child("translation", vectorNode(it.second.t));
-        cams.push_back(n);
+        w.begin_object();
+        w.leaf("id", it.second.cameraId);
+        writeVector(w, "rotation", it.second.q);
+        writeVector(w, "translation", it.second.t);
+        w.end();
     }
-    root.add_child("reconstructed_cameras", cams);
-    root.add_child("camera_model", cameraModelToJson(camModel));
-    vmm_json::write_json(outputPath, root);
+    w.end();
+    w.node("camera_model", cameraModelToJson(camModel));
+    w.close();
 }
 
 void parseReconstructions(const std::string& inputPath, std::map<int, ReconstructedTag>& reconstructedTags,
     std::map<int, Camera>& reconstructedCameras, CameraModel& camModel)
 {
-    const vmm_json::Node root = vmm_json::read_json(inputPath);
     reconstructedTags.clear();
     reconstructedCameras.clear();
-    for (const auto& it : root.get_child("reconstructed_tags").children) {
-        const vmm_json::Node& n = it.second;
-        ReconstructedTag tag;
-        tag.id = n.get_int("id");
-        tag.q = nodeVector<4>(n.get_child("rotation"));
-        tag.t = nodeVector<3>(n.get_child("translation"));
-        tag.tagWidth = n.get_double("width");
-        tag.tagHeight = n.get_double("height");
-        tag.tagType = n.get_string("type");
-        reconstructedTags[tag.id] = tag;
+    vmm_json::Node model;
+    const std::vector<std::string> seen = vmm_json::read_json_sections(inputPath, [&](const std::string& section, const std::string& key, vmm_json::Node& n) {
+        if (section == "reconstructed_tags") {
+            ReconstructedTag tag;
+            tag.id = n.get_int("id");
+            tag.q = nodeVector<4>(n.get_child("rotation"));
+            tag.t = nodeVector<3>(n.get_child("translation"));
+            tag.tagWidth = n.get_double("width");
+            tag.tagHeight = n.get_double("height");
+            tag.tagType = n.get_string("type");
+            reconstructedTags[tag.id] = tag;
+        } else if (section == "reconstructed_cameras") {
+            Camera cam;
+            cam.cameraId = n.get_int("id");
+            cam.q = nodeVector<4>(n.get_child("rotation"));
+            cam.t = nodeVector<3>(n.get_child("translation"));
+            reconstructedCameras[cam.cameraId] = cam;
+        } else if (section == "camera_model") {
+            model.add_child(key, std::move(n));
+        }
+    });
+    for (const char* key : { "reconstructed_tags", "reconstructed_cameras" }) {
+        bool found = false;
+        for (const std::string& s : seen) found = found || s == key;
+        if (!found) throw std::runtime_error(std::string("No such node (") + key + ")");
     }
-    for (const auto& it : root.get_child("reconstructed_cameras").children) {
-        Camera cam;
-        cam.cameraId = it.second.get_int("id");
-        cam.q = nodeVector<4>(it.second.get_child("rotation"));
-        cam.t = nodeVector<3>(it.second.get_child("translation"));
-        reconstructedCameras[cam.cameraId] = cam;
-    }
-    if (const vmm_json::Node* m = root.find("camera_model")) camModel = cameraModelFromJson(*m);
+    for (const std::string& s : seen)
+        if (s == "camera_model") { camModel = cameraModelFromJson(model); break; }
 }
 }

@@ -1,6 +1,7 @@
 // vmm_host_test — test driver of the host facade (tests/test_host_facade.py).
 //   vmm_host_test roundtrip <project_dir> <out_dir>   re-writes the three project files through the C++ reader/writer (no GPU)
 //   vmm_host_test stats <project_dir>                 GPU: reprojection statistics at the initial poses, as JSON on stdout
+//   vmm_host_test bigio <out_dir> <n>                  streamed write + read-back of n synthetic tag observations; prints the peak RSS (no GPU)
 //   vmm_host_test pnp <cases.txt>                     PnP.h on text cases (no GPU): "case <n> <robust> fx fy cx cy k1 k2 p1 p2 k3" then
 //                                                     n lines "X Y Z u v"; prints "R(9 row-major) t(3) rms inliers" per case
 #include "PtreeJson.h"
@@ -10,11 +11,13 @@
 #include "visual_marker_mapping/PnP.h"
 #include "visual_marker_mapping/TagReconstructor.h"
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
 #include <iostream>
 #include <string>
+#include <sys/resource.h>
 
 using namespace visual_marker_mapping;
 
@@ -36,6 +39,40 @@ int main(int argc, char** argv)
             std::printf("images %zu tags %zu observations %zu rec_tags %zu rec_cams %zu fx %.17g\n", det.images.size(), det.tags.size(),
                 det.tagObservations.size(), tags.size(), cams.size(), m.fx);
             return 0;
+        }
+        if (mode == "bigio") {   // vmm_host_test bigio <out_dir> <n tag observations>: streamed write + read of a large marker_detections.json (no GPU)
+            if (argc < 4) return 2;
+            const size_t n = (size_t)std::atoll(argv[3]), nImg = n / 40 + 1, nTag = n / 200 + 1;
+            const std::string file = dir + "/marker_detections.json";
+            struct rusage ru0;
+            getrusage(RUSAGE_SELF, &ru0);   // the CUDA runtime the library links is resident before any I/O
+            const auto coord = [](size_t i, int k) { return (double)(float)(3000.0 + 2500.0 * std::sin(0.001 * (double)i + k)); };
+            {
+                DetectionResult det;
+                for (size_t i = 0; i < nImg; ++i) det.images.push_back(TagImg{ (int)i, dir + "/images/img_" + std::to_string(i) + ".jpg" });
+                for (size_t i = 0; i < nTag; ++i) det.tags.push_back(Tag{ (int)i, "apriltag_36h11", 0.1285, 0.1295 });
+                det.tagObservations.resize(n);
+                for (size_t i = 0; i < n; ++i) {
+                    TagObservation& o = det.tagObservations[i];
+                    o.imageId = (int)(i / 40);
+                    o.tagId = (int)(i % nTag);
+                    for (int c = 0; c < 4; ++c) o.corners.push_back(Vector2d(coord(i, 2 * c), coord(i, 2 * c + 1)));
+                }
+                writeDetectionResult(det, file);
+            }
+            const DetectionResult back = readDetectionResult(file);
+            size_t bad = (back.images.size() != nImg) + (back.tags.size() != nTag) + (back.tagObservations.size() != n);
+            for (size_t i = 0; i < back.tagObservations.size() && !bad; ++i) {
+                const TagObservation& o = back.tagObservations[i];
+                bad += o.imageId != (int)(i / 40) || o.tagId != (int)(i % nTag) || o.corners.size() != 4;
+                for (int c = 0; c < 4 && !bad; ++c) bad += o.corners[c].x() != coord(i, 2 * c) || o.corners[c].y() != coord(i, 2 * c + 1);
+            }
+            if (back.images.size() == nImg && nImg) bad += back.images[nImg - 1].filename != "images/img_" + std::to_string(nImg - 1) + ".jpg";
+            struct rusage ru;
+            getrusage(RUSAGE_SELF, &ru);
+            std::ifstream in(file, std::ios::binary | std::ios::ate);
+            std::printf("observations %zu mismatches %zu file_bytes %lld base_rss_kb %ld maxrss_kb %ld\n", n, bad, (long long)in.tellg(), ru0.ru_maxrss, ru.ru_maxrss);
+            return bad ? 1 : 0;
         }
         if (mode == "pnp") {
             std::ifstream in(dir);
