@@ -949,9 +949,12 @@ void kd_leaves(std::vector<int>& act, const std::vector<double>& ctr, int target
 }
 
 int coarse_leaf_target(int cams_per_cluster, size_t n_active) {
-    const int kMaxClusters = 768;
-    int target = std::max(8, cams_per_cluster);
-    return std::max<int>(target, (int)((n_active + kMaxClusters - 1) / kMaxClusters) * 2);   // the k-d leaves hold target/2 .. target cameras
+    // 6·clusters is the order of the dense coarse matrix: its factorisation and inversion grow with the cube.  C3 on
+    // one B200 (gpurun sweeps, profiles/r01_configs.md): 512 clusters 88.6 ms per solve / 125 PCG iterations,
+    // 256 clusters 81.0 / 140, 128 clusters 85.6 / 160, 64 clusters 105.9 / 222.
+    const int kMaxClusters = 256;   // a power of two: after 8 median splits no leaf exceeds ceil(n / 256)
+    const int target = std::max(8, cams_per_cluster);
+    return std::max<int>(target, (int)((n_active + kMaxClusters - 1) / kMaxClusters));   // the k-d leaves hold target/2 .. target cameras
 }
 
 // Spatially coherent numbering of the cameras for sharded engines: the k-d leaves in depth-first order (each
