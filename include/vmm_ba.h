@@ -203,7 +203,7 @@ int vmm_ba_reprojection_error_sums(vmm_ba_handle h, double* per_tag_obs_sum);
 int vmm_ba_marker_translation_covariance(vmm_ba_handle h, int loss_kind, double loss_scale, double* cov);
 
 /* Target number of cameras per cluster of the two-level preconditioner's coarse space (default 192; the
- * coarse matrix is 6 x clusters squared and dense, the library caps it at 768 clusters).  Takes effect at
+ * coarse matrix is 6 x clusters squared and dense, the library caps it at 256 clusters).  Takes effect at
  * the next vmm_ba_set_problem. */
 int vmm_ba_set_coarse_cluster_size(vmm_ba_handle h, int cameras_per_cluster);
 

@@ -26,11 +26,11 @@ def main():
             ba.set_poses(scene.cam_q, scene.cam_t, scene.tag_q, scene.tag_t)
             t0 = time.time()
             s = ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, verbose=int(os.environ.get("VERBOSE", "0")),
-                         coarse_refresh_iterations=int(os.environ.get("REFRESH", "8")), pcg_tolerance=float(os.environ.get("PCGTOL", "5e-2")))
+                         coarse_refresh_iterations=int(os.environ.get("REFRESH", "8")), pcg_tolerance=float(os.environ.get("PCGTOL", "5e-2")), preconditioner=int(os.environ.get("PRECOND", "2")))
             t_solve = time.time() - t0
             ba.set_poses(scene.cam_q, scene.cam_t, scene.tag_q, scene.tag_t)
             ba.profile_enable(True)
-            ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, coarse_refresh_iterations=int(os.environ.get("REFRESH", "8")), pcg_tolerance=float(os.environ.get("PCGTOL", "5e-2")))
+            ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, coarse_refresh_iterations=int(os.environ.get("REFRESH", "8")), pcg_tolerance=float(os.environ.get("PCGTOL", "5e-2")), preconditioner=int(os.environ.get("PRECOND", "2")))
             prof = ba.profile()
             ba.profile_enable(False)
             row = {"cams_per_cluster": cs, "set_problem_s": round(t_set, 3), "solve_s": round(t_solve, 4), "lm": s.num_iterations,
