@@ -68,6 +68,21 @@ __device__ __forceinline__ void coarse_add(const CoarseView& cv, int i, double (
     for (int a = 0; a < 6; ++a) v[a] += o[a];
 }
 
+// row a of P_i yc[cluster(i)] (k_pcg_direction, one thread per block row): the same arithmetic as coarse_prolong
+__device__ __forceinline__ double coarse_row(const CoarseView& cv, int i, int a) {
+    const int c = cv.cl_of_cam[i];
+    if (c < 0) return 0.0;
+    const double* __restrict__ y = cv.yc + (size_t)c * 6;
+    const double* __restrict__ xb = cv.xbar + 3 * (size_t)c;
+    const int k = a < 3 ? a : a - 3;
+    const double* __restrict__ R = cv.camP + (size_t)i * CAM_PREP + 3 * k;
+    if (a >= 3) return -0.5 * (R[0] * y[3] + R[1] * y[4] + R[2] * y[5]);
+    const double ux = y[0] + (xb[1] * y[5] - xb[2] * y[4]);
+    const double uy = y[1] + (xb[2] * y[3] - xb[0] * y[5]);
+    const double uz = y[2] + (xb[0] * y[4] - xb[1] * y[3]);
+    return -(R[0] * ux + R[1] * uy + R[2] * uz);
+}
+
 constexpr int kCoarseThreads = 128;
 
 // A_c[c,c] += sum_{i in c} P_i^T (B_i + diag(lam_i)) P_i.  One CTA per cluster.

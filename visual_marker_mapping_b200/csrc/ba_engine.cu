@@ -533,6 +533,8 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
     const int nc = (int)e->Ncl;
     const int nm = (int)e->Nm;
     const int gb = nblocks(std::max<int64_t>(nc, 1), kThreads);
+    const int gb6 = nblocks(6 * std::max<int64_t>(nc, 1), kPcgThreads);   // update / direction: six threads per camera
+    static const bool narrow = std::getenv("VMM_BA_PCG_NARROW") != nullptr;   // A/B: the one-thread-per-camera kernels
     const int check_every = 8;
     double* done = e->sc.p + SC_DONE;
     // p.(B+lam)p and w.w pairs: one GPU keeps them in the tail of w and in sc; a sharded engine in the tail of the
@@ -558,7 +560,8 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
         if (rc) return rc;
     }
     // first direction: p = z (+ P yc), q = (B + lam) p, pBp[0]
-    LAUNCH(k_pcg_direction, gb, kThreads, nc, 1, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, pbp, 0, 1, tol * tol, cv);
+    if (narrow) LAUNCH(k_pcg_direction_1, gb, kThreads, nc, 1, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, pbp, 0, 1, tol * tol, cv);
+    else LAUNCH(k_pcg_direction, gb6, kPcgThreads, nc, 1, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, pbp, 0, 1, tol * tol, cv);
     out->iterations = 0;
     out->ok = true;
     out->rel = 1.0;
@@ -585,7 +588,8 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
             if (e->seg_big.count > 0)
                 schur_launch<SP_SCATTER>(e, e->seg_big, nullptr, e->wb.p, -1.0, e->pq.p, nullptr, done, nullptr, nullptr, nullptr);
         }
-        LAUNCH(k_pcg_update, gb, kThreads, nc, s, e->Minv.p, e->pp.p, e->pq.p, e->px.p, e->pr.p, e->pz.p, e->sc.p, pbp, wz, rz_next + o * rz_stride);
+        if (narrow) LAUNCH(k_pcg_update_1, gb, kThreads, nc, s, e->Minv.p, e->pp.p, e->pq.p, e->px.p, e->pr.p, e->pz.p, e->sc.p, pbp, wz, rz_next + o * rz_stride);
+        else LAUNCH(k_pcg_update, gb6, kPcgThreads, nc, s, e->Minv.p, e->pp.p, e->pq.p, e->px.p, e->pr.p, e->pz.p, e->sc.p, pbp, wz, rz_next + o * rz_stride);
         if (two_level) {
             int rc = coarse_correction(e, e->sc.p + SC_RZ + o, nullptr, done, e->world > 1);
             if (rc) return rc;
@@ -593,8 +597,8 @@ int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* o
             int rc = allreduce(e, e->sc.p + SC_RZ + o, 1, NCCL_SUM);
             if (rc) return rc;
         }
-        LAUNCH(k_pcg_direction, gb, kThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, pbp, it + 1,
-               min_it, tol2, cv);
+        if (narrow) LAUNCH(k_pcg_direction_1, gb, kThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, pbp, it + 1, min_it, tol2, cv);
+        else LAUNCH(k_pcg_direction, gb6, kPcgThreads, nc, s, e->B.p, e->lam_c.p, e->pz.p, e->pp.p, e->pq.p, e->sc.p, pbp, it + 1, min_it, tol2, cv);
         out->iterations = it + 1;
         if ((it + 1) % check_every == 0 || it + 1 == max_it) {
             CU(cudaMemcpyAsync(e->h_st + ST_SC, e->sc.p, sizeof(double) * SC_N, cudaMemcpyDeviceToHost, e->stream));
@@ -1011,23 +1015,48 @@ void classify_markers(const std::vector<int64_t>& begin, int world, int64_t Nc, 
 // initial poses — over ALL cameras, identically on every rank of a sharded engine — the clusters every
 // marker touches (over all ranks' observations) and, per local marker-order observation, the position of
 // its camera's cluster in that marker's list.  Host side, once per problem.
+// The k-d part of build_clusters, computed ahead on its own thread by vmm_ba_set_problem (one GPU) while the main
+// thread enqueues the uploads and the device sorts and builds the segment lists.
+struct ClusterSplits {
+    std::vector<int> act;
+    std::vector<double> ctr;
+    std::vector<std::pair<int, int>> leaves;
+    bool valid = false;
+};
+void cluster_splits(const double* cam_q, const double* cam_t, const std::vector<int64_t>& cam_count, int64_t Nc, int cams_per_cluster,
+                    ClusterSplits& out) {
+    for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) out.act.push_back((int)i);
+    const int target = coarse_leaf_target(cams_per_cluster, out.act.size());
+    if ((int64_t)out.act.size() >= 2 * (int64_t)target) {
+        camera_centres(cam_q, cam_t, out.act, Nc, out.ctr);
+        kd_leaves(out.act, out.ctr, target, out.leaves);
+    }
+    out.valid = true;
+}
+
 int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, const std::vector<int64_t>& cam_count, int64_t Nto,
                    const int32_t* to_cam, const int32_t* to_tag, const std::vector<int>& mptr, const std::vector<int>& mocam,
-                   const std::vector<unsigned char>& tag_active, const std::vector<std::pair<int, int>>* spatial_leaves) {
+                   const std::vector<unsigned char>& tag_active, const std::vector<std::pair<int, int>>* spatial_leaves,
+                   ClusterSplits* ahead = nullptr) {
     auto& c = e->coarse;
     c.available = false;
     c.active = false;
     const int64_t Nc = e->Nc, Ncl = e->Ncl, Nm = e->Nm;
     if (Nc == 0) return VMM_BA_OK;
     std::vector<int> act;
-    for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
+    std::vector<double> ctr;
+    std::vector<std::pair<int, int>> leaves;
+    const bool have_ahead = ahead && ahead->valid && !spatial_leaves;
+    if (have_ahead) act.swap(ahead->act);
+    else for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
     const int target = coarse_leaf_target(e->coarse_cams_per_cluster, act.size());
     if ((int64_t)act.size() < 2 * (int64_t)target) return VMM_BA_OK;   // one cluster = the gauge mode of a single block: nothing to gain
-    std::vector<double> ctr;
-    camera_centres(cam_q, cam_t, act, Nc, ctr);
-    std::vector<std::pair<int, int>> leaves;
-    if (spatial_leaves) leaves = *spatial_leaves;   // sharded: the cameras are already numbered leaf by leaf (act[k] == k)
-    else kd_leaves(act, ctr, target, leaves);
+    if (have_ahead) { ctr.swap(ahead->ctr); leaves.swap(ahead->leaves); }
+    else {
+        camera_centres(cam_q, cam_t, act, Nc, ctr);
+        if (spatial_leaves) leaves = *spatial_leaves;   // sharded: the cameras are already numbered leaf by leaf (act[k] == k)
+        else kd_leaves(act, ctr, target, leaves);
+    }
     const int ncl = (int)leaves.size();
     if (ncl < 2) return VMM_BA_OK;
     std::vector<int> cl_of_g(Nc, -1), cl_of(std::max<int64_t>(Ncl, 1), -1), cl_ptr(ncl + 1, 0), cl_cams;
@@ -1512,6 +1541,18 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     std::vector<int64_t> cam_ptr(Nc + 1, 0);
     for (int64_t i = 0; i < Nc; ++i) cam_ptr[i + 1] = cam_ptr[i] + cam_count[i];
     phase("validate + count");
+    // one GPU: the k-d splits of the camera clusters run beside the uploads, the device sorts and the segment lists
+    // (VMM_BA_KD_SERIAL=1: inside build_clusters as before, for A/B timing)
+    ClusterSplits splits_ahead;
+    std::thread splits_thread;
+    struct Joiner {
+        std::thread& t;
+        ~Joiner() { if (t.joinable()) t.join(); }
+    } splits_joiner{ splits_thread };
+    if (e->world == 1 && Nc > 0 && !std::getenv("VMM_BA_KD_SERIAL")) {
+        const int cpc = e->coarse_cams_per_cluster;
+        splits_thread = std::thread([&splits_ahead, &cam_count, cam_q, cam_t, Nc, cpc] { cluster_splits(cam_q, cam_t, cam_count, Nc, cpc, splits_ahead); });
+    }
     // shard
     std::vector<int64_t> begin;
     partition_cameras(Nc, cam_count, e->world, begin);
@@ -1629,7 +1670,9 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         int rc = build_segments(e, h_mptr, h_mtile, h_tact, bnd_id);
         if (rc) return rc;
         phase("segment lists");
-        rc = build_clusters(e, cam_q, cam_t, cam_count, Nto, to_cam, to_tag, h_mptr, h_mocam, h_tact, e->cam_order.empty() ? nullptr : &spatial_leaves);
+        if (splits_thread.joinable()) splits_thread.join();
+        rc = build_clusters(e, cam_q, cam_t, cam_count, Nto, to_cam, to_tag, h_mptr, h_mocam, h_tact, e->cam_order.empty() ? nullptr : &spatial_leaves,
+                            &splits_ahead);
         if (rc) return rc;
         phase("camera clusters");
     }

@@ -365,9 +365,111 @@ k_pcg_init(int nc, const double* __restrict__ Minv, const double* __restrict__ r
     if (threadIdx.x == 0) { atomicAdd(sc + 0, s1); atomicAdd(sc + 4, s1); }
 }
 
+// The two per-iteration vector kernels run SIX threads per camera, thread = 6 * camera + block row: every vector
+// access is one coalesced double per thread, a block row of Minv / B is 48 contiguous bytes per thread (three
+// 16-byte loads, contiguous across the warp), and the camera's 6-vector is exchanged through shared memory.  One
+// thread per camera (100 k threads at C3, a third of the SM thread slots, 288-byte strides) ran at 20 us per launch.
+constexpr int kPcgThreads = 192;   // 32 cameras x 6 rows
+
+__device__ __forceinline__ double row_dot6(const double* __restrict__ row, const double* v) {
+    const double2* r2 = reinterpret_cast<const double2*>(row);
+    const double2 a = r2[0], b = r2[1], c = r2[2];
+    double t = a.x * v[0];
+    t += a.y * v[1];
+    t += b.x * v[2];
+    t += b.y * v[3];
+    t += c.x * v[4];
+    t += c.y * v[5];
+    return t;
+}
+
+// alpha = rz[s] / (pbp[s] - wz[s]); x += alpha p; r -= alpha q; z = Minv r; rz[o] += r.z
+__global__ void __launch_bounds__(kPcgThreads)
+k_pcg_update(int nc, int s, const double* __restrict__ Minv, const double* __restrict__ p,
+             const double* __restrict__ q, double* __restrict__ x, double* __restrict__ r, double* __restrict__ z,
+             double* __restrict__ sc, const double* __restrict__ pbp, const double* __restrict__ wz,
+             double* __restrict__ rz_out) {
+    if (sc[SC_DONE] != 0.0) return;
+    __shared__ double s_v[kPcgThreads];
+    const int t = blockIdx.x * kPcgThreads + threadIdx.x;
+    const bool live = t < 6 * nc;
+    const double denom = pbp[s] - wz[s];
+    const double alpha = (sc[0 + s] != 0.0) ? sc[0 + s] / denom : 0.0;
+    double rv = 0.0;
+    if (live) {
+        x[t] += alpha * p[t];
+        rv = r[t] - alpha * q[t];
+        r[t] = rv;
+    }
+    s_v[threadIdx.x] = rv;
+    __syncthreads();
+    double rz = 0.0;
+    if (live) {
+        const double zt = row_dot6(Minv + (size_t)t * 6, s_v + (threadIdx.x / 6) * 6);
+        z[t] = zt;
+        rz = zt * rv;
+    }
+    const double s1 = block_sum(rz);
+    if (threadIdx.x == 0) atomicAdd(rz_out, s1);
+}
+
+// beta = rz[o] / rz[s]; p = z + beta p; q = (B + lam) p; pBp[o] += p.q
+// With the two-level preconditioner z holds only the block-Jacobi part; the coarse part P yc is added
+// here on the fly (cl_of_cam != nullptr; cameras outside every cluster have cl_of_cam < 0).
+struct CoarseView {
+    const int* cl_of_cam;
+    const double* xbar;
+    const double* camP;
+    const double* yc;
+};
+__device__ __forceinline__ void coarse_add(const CoarseView& cv, int i, double (&v)[6]);   // ba_coarse.cuh
+__device__ __forceinline__ double coarse_row(const CoarseView& cv, int i, int a);           // ba_coarse.cuh: row a of P_i yc
+
+__global__ void __launch_bounds__(kPcgThreads)
+k_pcg_direction(int nc, int s, const double* __restrict__ B, const double* __restrict__ lam,
+                const double* __restrict__ z, double* __restrict__ p, double* __restrict__ q,
+                double* __restrict__ sc, double* __restrict__ pbp, int iters_done, int min_iters, double tol2,
+                CoarseView cv) {
+    if (sc[SC_DONE] != 0.0) return;
+    __shared__ double s_v[kPcgThreads];
+    const int t = blockIdx.x * kPcgThreads + threadIdx.x;
+    const bool live = t < 6 * nc;
+    const int o = s ^ 1;
+    // device-side stopping test: every block evaluates the same predicate on the same (complete) sums
+    const double rz_new = sc[0 + o], rz0 = sc[SC_RZ0];
+    const bool stop = (iters_done >= min_iters) && (rz_new <= tol2 * rz0);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        sc[SC_REL2] = (rz0 > 0.0) ? rz_new / rz0 : 0.0;
+        if (stop) sc[SC_ITERS] = (double)iters_done;
+    }
+    if (stop) {   // blocks that start after the flag is up leave at the top: same effect
+        if (blockIdx.x == 0 && threadIdx.x == 0) sc[SC_DONE] = 1.0;
+        return;
+    }
+    const double beta = (sc[0 + s] != 0.0) ? rz_new / sc[0 + s] : 0.0;
+    double pv = 0.0;
+    if (live) {
+        pv = z[t];
+        if (cv.cl_of_cam) pv += coarse_row(cv, t / 6, threadIdx.x % 6);   // kPcgThreads is a multiple of 6
+        pv += beta * p[t];
+        p[t] = pv;
+    }
+    s_v[threadIdx.x] = pv;
+    __syncthreads();
+    double pq = 0.0;
+    if (live) {
+        const double qt = lam[t] * pv + row_dot6(B + (size_t)t * 6, s_v + (threadIdx.x / 6) * 6);
+        q[t] = qt;
+        pq = qt * pv;
+    }
+    const double s1 = block_sum(pq);
+    if (threadIdx.x == 0) atomicAdd(pbp + o, s1);
+}
+
+// One thread per camera: the variant the six-thread kernels replaced, kept for A/B runs (VMM_BA_PCG_NARROW=1).
 // alpha = rz[s] / (pbp[s] - wz[s]); x += alpha p; r -= alpha q; z = Minv r; rz[o] += r.z
 __global__ void __launch_bounds__(kThreads)
-k_pcg_update(int nc, int s, const double* __restrict__ Minv, const double* __restrict__ p,
+k_pcg_update_1(int nc, int s, const double* __restrict__ Minv, const double* __restrict__ p,
              const double* __restrict__ q, double* __restrict__ x, double* __restrict__ r, double* __restrict__ z,
              double* __restrict__ sc, const double* __restrict__ pbp, const double* __restrict__ wz,
              double* __restrict__ rz_out) {
@@ -403,16 +505,8 @@ k_pcg_update(int nc, int s, const double* __restrict__ Minv, const double* __res
 // beta = rz[o] / rz[s]; p = z + beta p; q = (B + lam) p; pBp[o] += p.q
 // With the two-level preconditioner z holds only the block-Jacobi part; the coarse part P yc is added
 // here on the fly (cl_of_cam != nullptr; cameras outside every cluster have cl_of_cam < 0).
-struct CoarseView {
-    const int* cl_of_cam;
-    const double* xbar;
-    const double* camP;
-    const double* yc;
-};
-__device__ __forceinline__ void coarse_add(const CoarseView& cv, int i, double (&v)[6]);   // ba_coarse.cuh
-
 __global__ void __launch_bounds__(kThreads)
-k_pcg_direction(int nc, int s, const double* __restrict__ B, const double* __restrict__ lam,
+k_pcg_direction_1(int nc, int s, const double* __restrict__ B, const double* __restrict__ lam,
                 const double* __restrict__ z, double* __restrict__ p, double* __restrict__ q,
                 double* __restrict__ sc, double* __restrict__ pbp, int iters_done, int min_iters, double tol2,
                 CoarseView cv) {
