@@ -144,6 +144,52 @@ def test_streamed_reader_edge_cases(host, tmp_path, scene_c1):
     assert r.returncode == 1 and "No such node (reconstructed_cameras)" in r.stderr
 
 
+def _ptree_leaves(node):
+    """What boost::property_tree keeps of a JSON document: every leaf as text."""
+    if isinstance(node, dict):
+        return {k: _ptree_leaves(v) for k, v in node.items()}
+    if isinstance(node, list):
+        return [_ptree_leaves(v) for v in node]
+    if isinstance(node, str):
+        return node
+    return json.dumps(node)   # true / false / null / numbers: the literal's text
+
+
+def test_tree_and_streamed_json_paths_agree(host, tmp_path):
+    """Property test of the two JSON paths of the host library on random documents: read_json + write_json (tree) and
+    read_json_sections + Writer (streamed) must print the same bytes, and those are the boost write_json dialect as
+    project_io.dumps_ptree states it (quoted leaves, "" for empty containers, escaped '/')."""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    text = st.text(alphabet=st.characters(min_codepoint=32, max_codepoint=126), max_size=12)
+    leaf = st.one_of(text, st.integers(-10**9, 10**9), st.booleans(), st.none(),
+                     st.floats(allow_nan=False, allow_infinity=False, width=64))
+    keys = st.text(alphabet=st.characters(min_codepoint=33, max_codepoint=126), min_size=1, max_size=8)
+    value = st.recursive(leaf, lambda c: st.one_of(st.lists(c, max_size=4), st.dictionaries(keys, c, max_size=4)), max_leaves=20)
+    container = st.one_of(st.lists(value, max_size=5), st.dictionaries(keys, value, max_size=5))
+    docs = st.dictionaries(keys, container, max_size=5)
+    src, tree, stream = tmp_path / "in.json", tmp_path / "tree.json", tmp_path / "stream.json"
+
+    @settings(max_examples=60, deadline=None, suppress_health_check=list(HealthCheck))
+    @given(docs, st.sampled_from([None, 1, 4]), st.booleans())
+    def check(doc, indent, ascii_only):
+        src.write_text(json.dumps(doc, indent=indent, ensure_ascii=ascii_only))
+        r = subprocess.run([DRIVER, "json", str(src), str(tree), str(stream)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        assert tree.read_bytes() == stream.read_bytes()
+        assert tree.read_text() == project_io.dumps_ptree(_ptree_leaves(doc))
+
+    check()
+    # control characters and non-ASCII text: both paths escape / pass them through alike
+    src.write_text(json.dumps({"a": ["tab\there", "nl\n", "\u00e9\u4e2d", "q\"b\\/"], "b": {"k\u0001": ["\u001f"]}, "c": [], "d": {}}))
+    r = subprocess.run([DRIVER, "json", str(src), str(tree), str(stream)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert tree.read_bytes() == stream.read_bytes()
+    out = tree.read_text()
+    assert '"tab\\there"' in out and '"\\u001F"' in out and '"q\\"b\\\\\\/"' in out and "\u00e9\u4e2d" in out
+    assert out.endswith('    "c": "",\n    "d": ""\n}\n')
+
+
 def test_cli_without_device_reports_and_returns_zero(host, tmp_path, scene_c1, have_gpu):
     """No CPU fallback; like the reference's main the exception is printed and the exit code stays 0."""
     if have_gpu:

@@ -18,6 +18,7 @@
 #include <iostream>
 #include <string>
 #include <sys/resource.h>
+#include <vector>
 
 using namespace visual_marker_mapping;
 
@@ -38,6 +39,31 @@ int main(int argc, char** argv)
             exportReconstructions(out + "/initial_reconstruction.json", tags, cams, m);
             std::printf("images %zu tags %zu observations %zu rec_tags %zu rec_cams %zu fx %.17g\n", det.images.size(), det.tags.size(),
                 det.tagObservations.size(), tags.size(), cams.size(), m.fx);
+            return 0;
+        }
+        if (mode == "json") {   // vmm_host_test json <in.json> <tree_out.json> <stream_out.json>: the same document through both paths (no GPU)
+            if (argc < 5) return 2;
+            vmm_json::write_json(argv[3], vmm_json::read_json(dir));
+            vmm_json::Writer w(argv[4]);
+            // sections arrive in file order; a section without children is only known from the returned list
+            struct Pending { std::string section, key; vmm_json::Node node; };
+            std::vector<Pending> all;
+            const std::vector<std::string> seen = vmm_json::read_json_sections(dir, [&](const std::string& section, const std::string& key, vmm_json::Node& n) {
+                all.push_back(Pending{ section, key, std::move(n) });
+            });
+            size_t k = 0;
+            for (const std::string& section : seen) {
+                // the elements of this occurrence of the section: the run of `all` that starts at k with this name
+                size_t e = k;
+                while (e < all.size() && all[e].section == section) ++e;
+                bool is_array = true;
+                for (size_t i = k; i < e; ++i) is_array = is_array && all[i].key.empty();
+                if (is_array) w.begin_array(section); else w.begin_object(section);
+                for (size_t i = k; i < e; ++i) w.node(all[i].key, all[i].node);
+                w.end();
+                k = e;
+            }
+            w.close();
             return 0;
         }
         if (mode == "bigio") {   // vmm_host_test bigio <out_dir> <n tag observations>: streamed write + read of a large marker_detections.json (no GPU)
