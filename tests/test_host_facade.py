@@ -190,6 +190,17 @@ def test_tree_and_streamed_json_paths_agree(host, tmp_path):
     assert out.endswith('    "c": "",\n    "d": ""\n}\n')
 
 
+@pytest.mark.parametrize("shape", [(40, 12, 475), (2000, 500, 200000)])
+def test_flatten_matches_map_restatement(host, shape):
+    """TagReconstructor::flatProblem (the arrays doBundleAdjustment hands to vmm_ba_set_problem: id tables + a threaded
+    two-pass fill) against the observation-by-observation std::map restatement of src/TagReconstructor.cpp:663-724, with
+    sparse ids (table and binary-search look-ups), unreconstructed images / tags, and a second call on the reused buffers."""
+    r = subprocess.run([DRIVER, "flatten", *map(str, shape)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    f = r.stdout.split()
+    assert f[0] == "kept" and int(f[1]) > 0.7 * shape[2] and int(f[3]) == shape[2] and f[4:6] == ["mismatches", "0"]
+
+
 def test_cli_without_device_reports_and_returns_zero(host, tmp_path, scene_c1, have_gpu):
     """No CPU fallback; like the reference's main the exception is printed and the exit code stays 0."""
     if have_gpu:

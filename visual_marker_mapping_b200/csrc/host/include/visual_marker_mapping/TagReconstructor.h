@@ -10,6 +10,7 @@
 #include "visual_marker_mapping/DetectionResults.h"
 #include <array>
 #include <cstddef>
+#include <cstdint>
 #include <map>
 #include <set>
 #include <string>
@@ -95,8 +96,25 @@ public:
     const std::map<int, std::array<double, 9>>& tagTranslationCovariances() const { return tagCovariances_; }
     double markerPositionRms() const { return markerPositionRms_; }
 
+    // the problem as doBundleAdjustment hands it to vmm_ba_set_problem (src/TagReconstructor.cpp:663-724 flattened):
+    // dense 0-based positions in std::map order, ids stay on the host side.  No GPU needed.
+    struct FlatProblem
+    {
+        std::vector<int> camIds, tagIds;                  // dense index -> id (ascending, std::map order)
+        std::vector<double> camQ, camT, tagQ, tagT, tagWH;
+        std::vector<int32_t> toCam, toTag;
+        std::vector<double> toUV;
+        std::vector<size_t> toSource;                     // index into the detection result's tagObservations
+        long long fixedTag = -1;
+    };
+    const FlatProblem& flatProblem() const   // valid until the next call that flattens (this one, doBundleAdjustment, the statistics)
+    {
+        flatten(flat_);
+        return flat_;
+    }
+
 protected:
-    struct Flat;
+    typedef FlatProblem Flat;
     void flatten(Flat& f) const;
     void ensureEngine() const;
     std::vector<double> reprojectionErrorSums(const Flat& f) const;
@@ -110,6 +128,8 @@ protected:
     CameraModel camModel;
 
     mutable vmm_ba_engine* engine_ = nullptr;
+    mutable Flat flat_;                                           // reused by every doBundleAdjustment / statistics call
+    mutable std::vector<int32_t> flatScratchCam_, flatScratchTag_;
     int device_ = 0;
     bool parity_ = false, quiet_ = false, haveInitial_ = false, waveMode_ = false;
     BundleAdjustmentReport report_;

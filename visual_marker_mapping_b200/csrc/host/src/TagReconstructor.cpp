@@ -8,9 +8,11 @@
 
 #include <algorithm>
 #include <cmath>
+#include <functional>
 #include <iostream>
 #include <set>
 #include <stdexcept>
+#include <thread>
 
 namespace visual_marker_mapping
 {
@@ -33,16 +35,6 @@ std::vector<Vector3d> ReconstructedTag::computeMarkerCorners3D() const
 }
 
 // dense view of the current maps (the problem assembly of src/TagReconstructor.cpp:663-724)
-struct TagReconstructor::Flat
-{
-    std::vector<int> camIds, tagIds;                  // dense index -> id (ascending, std::map order)
-    std::vector<double> camQ, camT, tagQ, tagT, tagWH;
-    std::vector<int32_t> toCam, toTag;
-    std::vector<double> toUV;
-    std::vector<size_t> toSource;                     // index into detectionResults_.tagObservations
-    long long fixedTag = -1;
-};
-
 TagReconstructor::TagReconstructor(DetectionResult detection_result)
     : originTagId(-1), detectionResults_(std::move(detection_result))
 {
@@ -115,36 +107,115 @@ void TagReconstructor::ensureEngine() const
     engine_ = h;
 }
 
+namespace
+{
+// id -> dense position for the ascending ids of a std::map: a direct table when the id range is compact (the usual
+// 0..N-1 numbering of images and tags), else a binary search.  A site-sized problem looks up 8 M ids per flatten;
+// std::map::find made that 2-6 s, longer than the bundle adjustment itself.
+class IdIndex
+{
+public:
+    explicit IdIndex(const std::vector<int>& ascendingIds) : ids_(ascendingIds)
+    {
+        if (ids_.empty()) return;
+        lo_ = ids_.front();
+        const long long range = (long long)ids_.back() - lo_ + 1;
+        if (range <= 8 * (long long)ids_.size() + 1024) {
+            table_.assign((size_t)range, -1);
+            for (size_t i = 0; i < ids_.size(); ++i) table_[(size_t)(ids_[i] - lo_)] = (int)i;
+        }
+    }
+    int find(int id) const   // -1: not reconstructed
+    {
+        if (!table_.empty()) {
+            const long long o = (long long)id - lo_;
+            return (o < 0 || o >= (long long)table_.size()) ? -1 : table_[(size_t)o];
+        }
+        const auto it = std::lower_bound(ids_.begin(), ids_.end(), id);
+        return (it == ids_.end() || *it != id) ? -1 : (int)(it - ids_.begin());
+    }
+
+private:
+    const std::vector<int>& ids_;
+    std::vector<int> table_;
+    int lo_ = 0;
+};
+}
+
 void TagReconstructor::flatten(Flat& f) const
 {
-    std::map<int, int> camIndex, tagIndex;
+    // f may be the buffer of an earlier call (the class keeps one): the pose arrays are rebuilt, the per-observation
+    // arrays only resized — no zero fill and no page faults for the 250 MB of a site-sized problem
+    f.camIds.clear(); f.camQ.clear(); f.camT.clear();
+    f.tagIds.clear(); f.tagQ.clear(); f.tagT.clear(); f.tagWH.clear();
+    f.fixedTag = -1;
+    f.camIds.reserve(reconstructedCameras.size());
+    f.camQ.reserve(4 * reconstructedCameras.size());
+    f.camT.reserve(3 * reconstructedCameras.size());
     for (const auto& it : reconstructedCameras) {
-        camIndex[it.first] = (int)f.camIds.size();
         f.camIds.push_back(it.first);
         for (int k = 0; k < 4; ++k) f.camQ.push_back(it.second.q(k));
         for (int k = 0; k < 3; ++k) f.camT.push_back(it.second.t(k));
     }
+    f.tagIds.reserve(reconstructedTags.size());
     for (const auto& it : reconstructedTags) {
         if (it.first == originTagId) f.fixedTag = (long long)f.tagIds.size();   // SetParameterBlockConstant, :669-673
-        tagIndex[it.first] = (int)f.tagIds.size();
         f.tagIds.push_back(it.first);
         for (int k = 0; k < 4; ++k) f.tagQ.push_back(it.second.q(k));
         for (int k = 0; k < 3; ++k) f.tagT.push_back(it.second.t(k));
         f.tagWH.push_back(it.second.tagWidth);    // corners come from the RECONSTRUCTED tag's size (:713)
         f.tagWH.push_back(it.second.tagHeight);
     }
+    const IdIndex camIndex(f.camIds), tagIndex(f.tagIds);
+    // the tag observations whose image and tag are both reconstructed (:699-724), in their order: chunks of the list
+    // are classified and counted by one thread each, then written at their prefix offsets
     const auto& obs = detectionResults_.tagObservations;
-    for (size_t k = 0; k < obs.size(); ++k) {
-        const auto c = camIndex.find(obs[k].imageId);
-        if (c == camIndex.end()) continue;
-        const auto t = tagIndex.find(obs[k].tagId);
-        if (t == tagIndex.end()) continue;
-        if (obs[k].corners.size() != 4) throw std::runtime_error("Unexpected number of values");
-        f.toCam.push_back(c->second);
-        f.toTag.push_back(t->second);
-        for (int i = 0; i < 4; ++i) { f.toUV.push_back(obs[k].corners[i].x()); f.toUV.push_back(obs[k].corners[i].y()); }
-        f.toSource.push_back(k);
-    }
+    const size_t n = obs.size();
+    const unsigned hw = std::thread::hardware_concurrency();
+    const size_t T = n >= ((size_t)1 << 16) ? std::max<size_t>(1, std::min<size_t>(hw ? hw : 1, 16)) : 1;
+    std::vector<size_t> kept(T + 1, 0), badAt(T, n);
+    std::vector<int32_t>& cam = flatScratchCam_;
+    std::vector<int32_t>& tag = flatScratchTag_;
+    if (cam.size() < n) { cam.resize(n); tag.resize(n); }
+    const auto chunk = [&](size_t c) { return std::make_pair(n * c / T, n * (c + 1) / T); };
+    const auto run = [&](const std::function<void(size_t)>& body) {
+        if (T == 1) { body(0); return; }
+        std::vector<std::thread> th;
+        for (size_t c = 0; c < T; ++c) th.emplace_back(body, c);
+        for (auto& t : th) t.join();
+    };
+    run([&](size_t c) {
+        size_t cnt = 0;
+        for (size_t k = chunk(c).first; k < chunk(c).second; ++k) {
+            const int ci = camIndex.find(obs[k].imageId);
+            const int ti = ci < 0 ? -1 : tagIndex.find(obs[k].tagId);
+            cam[k] = ti < 0 ? -1 : ci;
+            tag[k] = ti;
+            if (ti < 0) continue;
+            if (obs[k].corners.size() != 4 && badAt[c] == n) badAt[c] = k;
+            ++cnt;
+        }
+        kept[c + 1] = cnt;
+    });
+    for (size_t c = 0; c < T; ++c)
+        if (badAt[c] != n) throw std::runtime_error("Unexpected number of values");
+    for (size_t c = 0; c < T; ++c) kept[c + 1] += kept[c];
+    const size_t m = kept[T];
+    f.toCam.resize(m);
+    f.toTag.resize(m);
+    f.toUV.resize(8 * m);
+    f.toSource.resize(m);
+    run([&](size_t c) {
+        size_t o = kept[c];
+        for (size_t k = chunk(c).first; k < chunk(c).second; ++k) {
+            if (cam[k] < 0) continue;
+            f.toCam[o] = cam[k];
+            f.toTag[o] = tag[k];
+            for (int i = 0; i < 4; ++i) { f.toUV[8 * o + 2 * i] = obs[k].corners[i].x(); f.toUV[8 * o + 2 * i + 1] = obs[k].corners[i].y(); }
+            f.toSource[o] = k;
+            ++o;
+        }
+    });
 }
 
 static void check(vmm_ba_engine* e, int rc, const char* what)
@@ -165,7 +236,7 @@ static void upload(vmm_ba_engine* e, const CameraModel& m, const std::vector<dou
 void TagReconstructor::doBundleAdjustment(int maxNumIterations, size_t /*ceresThreads*/, bool robustify, bool printSummary)
 {
     if (reconstructedTags.empty()) throw std::runtime_error("doBundleAdjustment: no reconstructed tags");
-    Flat f;
+    Flat& f = flat_;
     flatten(f);
     ensureEngine();
     upload(engine_, camModel, f.camQ, f.camT, f.tagQ, f.tagT, f.tagWH, f.fixedTag, f.toCam, f.toTag, f.toUV);
@@ -248,44 +319,54 @@ std::vector<double> TagReconstructor::reprojectionErrorSums(const Flat& f) const
     return sums;
 }
 
+namespace
+{
+// Per-block sums of the per-observation error sums, accumulated in observation order (the order the reference's
+// std::map accumulators see, so the doubles are the same) in dense arrays instead of 4 M map look-ups.
+void accumulateByBlock(const std::vector<int32_t>& block, const std::vector<double>& sums, size_t numBlocks, std::vector<double>& err,
+    std::vector<long long>& num)
+{
+    err.assign(numBlocks, 0.0);
+    num.assign(numBlocks, 0);
+    for (size_t k = 0; k < sums.size(); ++k) {
+        num[(size_t)block[k]] += 4;
+        err[(size_t)block[k]] += sums[k];
+    }
+}
+}
+
 const std::map<int, double> TagReconstructor::computeReprojectionErrorPerImg() const
 {
-    Flat f;
+    Flat& f = flat_;
     flatten(f);
     const std::vector<double> sums = reprojectionErrorSums(f);
+    std::vector<double> e;
+    std::vector<long long> n;
+    accumulateByBlock(f.toCam, sums, f.camIds.size(), e, n);
     std::map<int, double> err;
-    std::map<int, int> num;
-    for (size_t k = 0; k < sums.size(); ++k) {
-        const int id = f.camIds[f.toCam[k]];
-        num[id] += 4;
-        err[id] += sums[k];
-    }
-    for (auto& e : err) e.second /= num[e.first];
-    for (const auto& cam : reconstructedCameras)     // cameras without observations: -1 (:379-383)
-        if (err.count(cam.first) == 0) err[cam.first] = -1.0;
+    for (size_t i = 0; i < f.camIds.size(); ++i)     // cameras without observations: -1 (:379-383)
+        err.emplace_hint(err.end(), f.camIds[i], n[i] ? e[i] / (double)n[i] : -1.0);
     return err;
 }
 
 const std::map<int, double> TagReconstructor::computeReprojectionErrorPerTag(double& avg) const
 {
-    Flat f;
+    Flat& f = flat_;
     flatten(f);
     const std::vector<double> sums = reprojectionErrorSums(f);
+    std::vector<double> e;
+    std::vector<long long> n;
+    accumulateByBlock(f.toTag, sums, f.tagIds.size(), e, n);
     std::map<int, double> err;
-    std::map<int, int> num;
-    for (size_t k = 0; k < sums.size(); ++k) {
-        const int id = f.tagIds[f.toTag[k]];
-        num[id] += 4;
-        err[id] += sums[k];
-    }
     avg = 0;
-    int total = 0;
-    for (auto& e : err) {       // avg = sum of the per-tag sums / total corner count (:416-426)
-        avg += e.second;
-        e.second /= num[e.first];
-        total += num[e.first];
+    long long total = 0;
+    for (size_t j = 0; j < f.tagIds.size(); ++j) {   // avg = sum of the per-tag sums / total corner count (:416-426)
+        if (!n[j]) continue;                         // a tag without observations has no entry
+        avg += e[j];
+        total += n[j];
+        err.emplace_hint(err.end(), f.tagIds[j], e[j] / (double)n[j]);
     }
-    if (total) avg /= total;
+    if (total) avg /= (double)total;
     return err;
 }
 

@@ -11,11 +11,14 @@
 #include "visual_marker_mapping/PnP.h"
 #include "visual_marker_mapping/TagReconstructor.h"
 
+#include <chrono>
 #include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
 #include <iostream>
+#include <map>
 #include <string>
 #include <sys/resource.h>
 #include <vector>
@@ -40,6 +43,81 @@ int main(int argc, char** argv)
             std::printf("images %zu tags %zu observations %zu rec_tags %zu rec_cams %zu fx %.17g\n", det.images.size(), det.tags.size(),
                 det.tagObservations.size(), tags.size(), cams.size(), m.fx);
             return 0;
+        }
+        if (mode == "flatten") {   // vmm_host_test flatten <n_cam> <n_tag> <n_obs>: TagReconstructor::flatProblem against a plain restatement (no GPU)
+            if (argc < 5) return 2;
+            const int nCam = std::atoi(argv[2]), nTag = std::atoi(argv[3]);
+            const size_t nObs = (size_t)std::atoll(argv[4]);
+            DetectionResult det;
+            std::map<int, ReconstructedTag> tags;
+            std::map<int, Camera> cams;
+            // sparse, unordered ids; every 7th image and every 11th tag are not reconstructed (their observations are skipped)
+            for (int i = 0; i < nCam; ++i) {
+                const int id = 3 * i + 5;
+                det.images.push_back(TagImg{ id, "img" });
+                if (i % 7 == 3) continue;
+                Camera c;
+                c.cameraId = id;
+                c.t = Vector3d(i, 0.5 * i, 1.0);
+                cams[id] = c;
+            }
+            for (int j = 0; j < nTag; ++j) {
+                const int id = (j % 2 ? 1000000 : 0) + 2 * j;
+                det.tags.push_back(Tag{ id, "apriltag_36h11", 0.1285, 0.1295 });
+                if (j % 11 == 4) continue;
+                ReconstructedTag t;
+                t.id = id;
+                t.tagType = "apriltag_36h11";
+                t.tagWidth = 0.1 + 1e-4 * j;
+                t.tagHeight = 0.2;
+                t.t = Vector3d(0.0, j, -1.0);
+                tags[id] = t;
+            }
+            det.tagObservations.resize(nObs);
+            uint64_t state = 88172645463325252ull;
+            const auto rnd = [&state]() { state ^= state << 13; state ^= state >> 7; state ^= state << 17; return state; };
+            for (size_t k = 0; k < nObs; ++k) {
+                TagObservation& o = det.tagObservations[k];
+                o.imageId = 3 * (int)(rnd() % (uint64_t)nCam) + 5;
+                const int j = (int)(rnd() % (uint64_t)nTag);
+                o.tagId = (j % 2 ? 1000000 : 0) + 2 * j;
+                for (int c = 0; c < 4; ++c) o.corners.push_back(Vector2d((double)(rnd() % 6000), (double)(rnd() % 4000)));
+            }
+            const std::vector<TagObservation> obs = det.tagObservations;
+            TagReconstructor rec(std::move(det));
+            rec.setQuiet(true);
+            rec.setInitialReconstruction(tags, cams);
+            rec.setOriginTagId(tags.begin()->first);
+            const auto t0 = std::chrono::steady_clock::now();
+            rec.flatProblem();
+            const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+            const auto t2 = std::chrono::steady_clock::now();
+            const TagReconstructor::FlatProblem& f = rec.flatProblem();   // second call: buffers reused
+            const double ms2 = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t2).count();
+            // plain restatement: std::map lookups, observation by observation
+            const auto t1 = std::chrono::steady_clock::now();
+            std::map<int, int> camIndex, tagIndex;
+            for (const auto& c : cams) { const int n = (int)camIndex.size(); camIndex[c.first] = n; }
+            for (const auto& t : tags) { const int n = (int)tagIndex.size(); tagIndex[t.first] = n; }
+            size_t bad = (f.camIds.size() != cams.size()) + (f.tagIds.size() != tags.size()) + (f.fixedTag != 0), n = 0;
+            for (size_t k = 0; k < obs.size(); ++k) {
+                const auto c = camIndex.find(obs[k].imageId);
+                const auto t = tagIndex.find(obs[k].tagId);
+                if (c == camIndex.end() || t == tagIndex.end()) continue;
+                if (n < f.toCam.size()) {
+                    bad += f.toCam[n] != c->second || f.toTag[n] != t->second || f.toSource[n] != k;
+                    for (int i = 0; i < 4; ++i) bad += f.toUV[8 * n + 2 * i] != obs[k].corners[i].x() || f.toUV[8 * n + 2 * i + 1] != obs[k].corners[i].y();
+                }
+                ++n;
+            }
+            const double ms_ref = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
+            bad += n != f.toCam.size() || f.toTag.size() != n || f.toUV.size() != 8 * n || f.toSource.size() != n;
+            size_t j = 0;
+            for (const auto& t : tags) { bad += f.tagIds[j] != t.first || f.tagWH[2 * j] != t.second.tagWidth || f.tagT[3 * j + 1] != t.second.t(1); ++j; }
+            j = 0;
+            for (const auto& c : cams) { bad += f.camIds[j] != c.first || f.camT[3 * j] != c.second.t(0) || f.camQ[4 * j] != c.second.q(0); ++j; }
+            std::printf("kept %zu of %zu mismatches %zu flatten_ms %.2f again_ms %.2f map_restatement_ms %.2f\n", n, obs.size(), bad, ms, ms2, ms_ref);
+            return bad ? 1 : 0;
         }
         if (mode == "json") {   // vmm_host_test json <in.json> <tree_out.json> <stream_out.json>: the same document through both paths (no GPU)
             if (argc < 5) return 2;
