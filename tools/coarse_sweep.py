@@ -2,7 +2,9 @@
 
 usage: python tools/coarse_sweep.py [workload] [cams_per_cluster ...]
 Prints, per cluster size: solve time, LM / PCG iterations, and the per-LM-iteration time of the set-up
-pieces (k_coarse_offdiag, cusolverDnDpotrf, cusolverDnDpotri) from the per-kernel CUDA-event profile.
+pieces (k_coarse_w, cusolverDnDpotrf, cuBLAS trsm / gemm / syrk) from the per-kernel CUDA-event profile.
+The k-d leaves halve, so the cluster count moves in powers of two (C3: 192..390 -> 256 clusters, the library's cap;
+512 -> 256, 1024 -> 128, ...).  Environment: REFRESH (coarse_refresh_iterations), PCGTOL, PRECOND, VERBOSE.
 """
 import os, sys, time, json
 
@@ -13,7 +15,7 @@ from visual_marker_mapping_b200 import synth
 
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "c3"
-    sizes = [int(a) for a in sys.argv[2:]] or [96, 192, 384, 768]
+    sizes = [int(a) for a in sys.argv[2:]] or [192, 512, 1024, 2048]
     scene = synth.make_config(name)
     out = []
     with pkg.BundleAdjuster(device=0) as ba:

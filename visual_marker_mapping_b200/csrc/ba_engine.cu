@@ -474,8 +474,8 @@ int invert_lower_triangular(vmm_ba_engine* e, const double* L, double* X, double
     return VMM_BA_OK;
 }
 
-// A_c = P^T S P at the current linearisation and damping, then its inverse (dense, cuSOLVER potrf + potri:
-// a plain library factorisation of a few-thousand-square matrix, once per LM iteration).
+// A_c = P^T S P at the current linearisation and damping, then its inverse (dense: cuSOLVER potrf, blocked triangular
+// inversion with cuBLAS, syrk — plain library calls on a matrix of at most 1536 rows, when the kept inverse has aged).
 int coarse_setup(vmm_ba_engine* e, int slot) {
     auto& c = e->coarse;
     c.active = false;
@@ -506,7 +506,8 @@ int coarse_setup(vmm_ba_engine* e, int slot) {
     // A_c^-1 = L^-T L^-1.  X = L^-1 by recursive blocking, so that the n^3/3 flops run as fp64 tensor-core GEMMs
     // (cuBLAS) instead of one triangular solve against a dense identity: for L = [L11 0; L21 L22],
     // X = [X11 0; -X22 L21 X11, X22]; diagonal blocks of <= 256 rows by cublasDtrsm.  Then X^T X (cublasDsyrk).
-    // 0.9 + 0.9 ms at n = 3126, where trsm + syrk took 2.6 + 0.9 and cusolverDnDpotri 7.8.  Replicated on every rank
+    // 0.9 + 0.9 ms at n = 3126 (521 clusters, before the cap at 256), where trsm + syrk took 2.6 + 0.9 and
+    // cusolverDnDpotri 7.8; 0.95 + 0.15 ms at n = 1536.  Replicated on every rank
     // of a sharded engine (cheaper than solving by column blocks and all-gathering).
     if (cublasSetStream(e->cublas, e->stream) != CUBLAS_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cublasSetStream failed");
     const double one = 1.0, zero = 0.0;
