@@ -201,6 +201,69 @@ def test_flatten_matches_map_restatement(host, shape):
     assert f[0] == "kept" and int(f[1]) > 0.7 * shape[2] and int(f[3]) == shape[2] and f[4:6] == ["mismatches", "0"]
 
 
+@pytest.fixture(scope="module")
+def abi_double(host):
+    """Environment that puts tests/host_harness/libabi_test_double.so (identity solve + plain C++ reprojection sums; test
+    infrastructure, see its header) in front of libvmm_ba.so: the facade's host logic then runs without a GPU."""
+    d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "host_harness")
+    subprocess.run(["make", "-C", d, "-s"], check=True)
+    return dict(os.environ, LD_PRELOAD=os.path.join(d, "libabi_test_double.so"))
+
+
+def test_facade_statistics_host_logic(host, oracle, abi_double, tmp_path, scene_c1):
+    """flatten + per-image / per-tag aggregation of computeReprojectionErrorPerImg/PerTag (src/TagReconstructor.cpp:340-428)
+    with sparse ids, against numpy on the oracle's per-observation sums.  (The same check runs on the GPU in
+    test_facade_reprojection_statistics; here the sums come from the ABI test double.)"""
+    project_io.write_project(scene_c1, str(tmp_path), image_id_offset=11, tag_id_offset=300)
+    r = subprocess.run([DRIVER, "stats", str(tmp_path)], capture_output=True, text=True, env=abi_double)
+    assert r.returncode == 0, r.stderr
+    got = json.loads(r.stdout)
+    s = scene_c1
+    sums = oracle.reprojection_error_sums(s)
+    per_tag = np.bincount(s.to_tag, sums, s.n_markers) / (4 * np.bincount(s.to_tag, minlength=s.n_markers))
+    per_img = np.bincount(s.to_cam, sums, s.n_cameras) / (4 * np.bincount(s.to_cam, minlength=s.n_cameras))
+    assert sorted(map(int, got["per_tag"])) == [300 + j for j in range(s.n_markers)]
+    assert sorted(map(int, got["per_img"])) == [11 + i for i in range(s.n_cameras)]
+    for j in range(s.n_markers):
+        assert abs(float(got["per_tag"][str(300 + j)]) - per_tag[j]) < 1e-9 * max(per_tag[j], 1.0)
+    for i in range(s.n_cameras):
+        assert abs(float(got["per_img"][str(11 + i)]) - per_img[i]) < 1e-9 * max(per_img[i], 1.0)
+    assert abs(float(got["avg"]) - sums.sum() / (4 * s.n_tag_obs)) < 1e-9 * float(got["avg"])
+
+
+def test_cli_closing_sequence_host_logic(host, oracle, abi_double, tmp_path):
+    """The CLI's closing sequence BA -> removeBadMarkers(2) -> removeBadCameras(2) -> BA -> export
+    (src/TagReconstructor.cpp:271-277, :786-816) with the identity solve of the ABI test double, started at the ground
+    truth: which markers and cameras survive is host logic and must equal the numpy statement of the same rules —
+    the badly detected marker goes, the origin tag stays whatever its error, a camera left without observations goes."""
+    s = culled_scene()
+    s.cam_q, s.cam_t, s.tag_q, s.tag_t = s.cam_q_gt.copy(), s.cam_t_gt.copy(), s.tag_q_gt.copy(), s.tag_t_gt.copy()
+    lonely = 17                                   # camera 17 only sees marker 5: culled once the marker is gone (-1, :379-383, :809)
+    keep = (s.to_cam != lonely) | (s.to_tag == 5)
+    s.to_cam, s.to_tag, s.to_uv = s.to_cam[keep], s.to_tag[keep], s.to_uv[keep]
+    s.to_uv[s.to_tag == s.fixed_tag] += 6.0       # the origin tag is never removed (:794)
+    project_io.write_project(s, str(tmp_path), image_id_offset=7, tag_id_offset=20)
+    r = subprocess.run([CLI, "--project_path", str(tmp_path), "--start_tag_id", str(20 + s.fixed_tag), "--overwrite"], capture_output=True,
+                       text=True, env=abi_double)
+    assert r.returncode == 0 and "Error" not in r.stderr, r.stderr
+    sums = oracle.reprojection_error_sums(s)
+    tag_err = np.bincount(s.to_tag, sums, s.n_markers) / np.maximum(4 * np.bincount(s.to_tag, minlength=s.n_markers), 1)
+    keep_tag = ~((tag_err > 2.0) & (np.arange(s.n_markers) != s.fixed_tag))
+    ko = keep_tag[s.to_tag]
+    cam_n = np.bincount(s.to_cam[ko], minlength=s.n_cameras)
+    cam_err = np.where(cam_n > 0, np.bincount(s.to_cam[ko], sums[ko], s.n_cameras) / np.maximum(4 * cam_n, 1), -1.0)
+    keep_cam = ~((cam_err > 2.0) | (cam_err < 0))
+    assert not keep_tag[5] and keep_tag[s.fixed_tag] and tag_err[s.fixed_tag] > 2.0 and not keep_cam[lonely]
+    tags, cams = project_io.read_reconstruction(str(tmp_path / "reconstruction.json"))
+    assert sorted(tags) == [20 + int(j) for j in np.nonzero(keep_tag)[0]]
+    assert sorted(cams) == [7 + int(i) for i in np.nonzero(keep_cam)[0]]
+    assert "Removing bad marker with id 25" in r.stdout and f"Removing bad camera with id {7 + lonely}" in r.stdout
+    for j in np.nonzero(keep_tag)[0]:            # identity solve: the poses come back as they went in
+        assert np.array_equal(tags[20 + int(j)]["t"], s.tag_t[j]) and np.array_equal(tags[20 + int(j)]["q"], s.tag_q[j])
+    for i in np.nonzero(keep_cam)[0]:
+        assert np.array_equal(cams[7 + int(i)]["t"], s.cam_t[i])
+
+
 def test_cli_without_device_reports_and_returns_zero(host, tmp_path, scene_c1, have_gpu):
     """No CPU fallback; like the reference's main the exception is printed and the exit code stays 0."""
     if have_gpu:
