@@ -264,6 +264,34 @@ def test_cli_closing_sequence_host_logic(host, oracle, abi_double, tmp_path):
         assert np.array_equal(cams[7 + int(i)]["t"], s.cam_t[i])
 
 
+@pytest.mark.parametrize("wave", [False, True])
+def test_cli_incremental_schedule_host_logic(host, abi_double, tmp_path, scene_c1, wave):
+    """startReconstruction from the detections alone (src/TagReconstructor.cpp:146-267) with the identity solve of the ABI
+    test double: every image and every tag gets initialised by the in-repo PnP in the reference's order, one bundle
+    adjustment is requested per added image (per round with --wave) plus the two closing ones, and the un-refined PnP
+    poses are already close to ground truth (0.3 px corner noise).  The refined result is checked on the GPU
+    (test_cli_reconstructs_from_detections_alone)."""
+    s = scene_c1
+    project_io.write_project(s, str(tmp_path), image_id_offset=3, tag_id_offset=0)
+    os.remove(tmp_path / "initial_reconstruction.json")
+    r = subprocess.run([CLI, "--project_path", str(tmp_path), "--overwrite"] + (["--wave"] if wave else []), capture_output=True, text=True,
+                       env=abi_double)
+    assert r.returncode == 0 and "Error" not in r.stderr, r.stderr
+    n_ba = r.stdout.count("Solution ")
+    assert r.stdout.count("Initialized camera with id") == s.n_cameras
+    assert r.stdout.count("Initialized tag with id") == s.n_markers - 1      # the origin tag is set, not initialised
+    assert (n_ba < 10) if wave else (n_ba == s.n_cameras + 2)
+    tags, cams = project_io.read_reconstruction(str(tmp_path / "reconstruction.json"))
+    if not wave:   # (per round, poses that were never refined may miss the 2 px of the closing cull: survivors only)
+        assert sorted(tags) == list(range(s.n_markers)) and sorted(cams) == [i + 3 for i in range(s.n_cameras)]
+    assert set(tags) <= set(range(s.n_markers)) and set(cams) <= {i + 3 for i in range(s.n_cameras)} and len(cams) > 0
+    assert np.array_equal(tags[s.fixed_tag]["t"], np.zeros(3))
+    for j in tags:
+        assert np.abs(tags[j]["t"] - s.tag_t_gt[j]).max() < 0.05
+    for i in cams:
+        assert np.abs(cams[i]["t"] - s.cam_t_gt[i - 3]).max() < 0.05
+
+
 def test_cli_without_device_reports_and_returns_zero(host, tmp_path, scene_c1, have_gpu):
     """No CPU fallback; like the reference's main the exception is printed and the exit code stays 0."""
     if have_gpu:
