@@ -51,6 +51,39 @@ def test_roundtrip_is_byte_exact(host, tmp_path, scene_c1):
             assert abs(fx - fy) <= 4e-16 * max(abs(fx), 1.0)
 
 
+def test_number_text_roundtrip_extremes(host, tmp_path, scene_c1):
+    """Doubles go out as boost's setprecision(17) prints them (= C "%.17g", here through std::to_chars) and come back through
+    std::from_chars / strtod: denormals, the largest double, negative zero, integers beyond 2^53, exponent forms."""
+    src, dst = tmp_path / "src", tmp_path / "dst"
+    dst.mkdir()
+    project_io.write_project(scene_c1, str(src))
+    det = json.loads((src / "marker_detections.json").read_text())
+    vals = [5e-324, 2.2250738585072014e-308, 1.7976931348623157e308, -0.0, 0.1, 1.0 / 3.0, 123456789012345678.0, 1e22, 1e-7,
+            -4536.70849609375, 6.02214076e23, 2.0 ** 53 + 2, 1e15, 1e16, 1e17, 0.30000000000000004]
+    rng = np.random.default_rng(3)
+    vals += list(np.ldexp(rng.standard_normal(200), rng.integers(-1000, 1000, 200)))
+    k = 0
+    for o in det["tag_observations"]:
+        for c in o["observations"]:
+            for i in range(2):
+                c[i] = "%.17g" % vals[k % len(vals)]
+                k += 1
+    assert k >= len(vals)
+    text = project_io.dumps_ptree(det)
+    (src / "marker_detections.json").write_text(text)
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert (dst / "marker_detections.json").read_text() == text
+    # the same values as bare JSON numbers in Python's shortest form, '+' exponents and capital E included
+    for o in det["tag_observations"]:
+        for c in o["observations"]:
+            c[0], c[1] = float(c[0]), float(c[1])
+    (src / "marker_detections.json").write_text(json.dumps(det).replace("e+", "E+"))
+    r = subprocess.run([DRIVER, "roundtrip", str(src), str(dst)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert (dst / "marker_detections.json").read_text() == text
+
+
 def test_dialect_literals(tmp_path, scene_c1):
     """boost write_json: quoted leaves, 17 significant digits, 4-space indent, '/' escaped, empty array = \"\"."""
     project_io.write_project(scene_c1, str(tmp_path))

@@ -2,6 +2,7 @@
 #include "PtreeJson.h"
 
 #include <cerrno>
+#include <charconv>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
@@ -19,9 +20,16 @@ std::string Node::format_double(double v)
 
 double Node::value_double() const
 {
+    // std::from_chars reads what strtod reads for the decimal / exponent forms the files hold (correctly rounded), several
+    // times faster; anything it does not take whole (hex floats, "inf", a leading '+', locale forms) goes to strtod
+    const char* b = data.data();
+    const char* e = b + data.size();
+    double v = 0.0;
+    const std::from_chars_result r = std::from_chars(b, e, v, std::chars_format::general);
+    if (r.ec == std::errc() && r.ptr == e && b != e) return v;
     errno = 0;
     char* end = nullptr;
-    const double v = std::strtod(data.c_str(), &end);
+    v = std::strtod(data.c_str(), &end);
     while (end && *end == ' ') ++end;
     if (data.empty() || !end || *end != '\0') throw std::runtime_error("conversion of data to type \"double\" failed: \"" + data + "\"");
     return v;
@@ -75,9 +83,13 @@ struct Parser
     void ws()
     {
         while (!in.eof()) {
-            const char c = in.peek();
-            if (c != ' ' && c != '\t' && c != '\n' && c != '\r') break;
-            in.get();
+            const char* p = in.cur;
+            while (p != in.lim && (*p == ' ' || *p == '\t' || *p == '\r' || *p == '\n')) {
+                if (*p == '\n') ++in.line;
+                ++p;
+            }
+            in.cur = p;
+            if (p != in.lim) break;
         }
     }
     bool next_is(char c) { return !in.eof() && in.peek() == c; }
@@ -94,9 +106,18 @@ struct Parser
         out.clear();
         while (true) {
             if (in.eof()) fail("unterminated string");
+            {   // plain run up to the next quote / backslash inside the current chunk
+                const char* p = in.cur;
+                while (p != in.lim && *p != '"' && *p != '\\') {
+                    if (*p == '\n') ++in.line;
+                    ++p;
+                }
+                out.append(in.cur, (size_t)(p - in.cur));
+                in.cur = p;
+                if (p == in.lim) continue;
+            }
             const char c = in.get();
             if (c == '"') break;
-            if (c != '\\') { out += c; continue; }
             if (in.eof()) fail("unterminated escape");
             const char e = in.get();
             switch (e) {
@@ -126,9 +147,11 @@ struct Parser
     {
         out.clear();
         while (!in.eof()) {
-            const char c = in.peek();
-            if (c == ',' || c == '}' || c == ']' || c == ' ' || c == '\n' || c == '\r' || c == '\t') break;
-            out += in.get();
+            const char* p = in.cur;
+            while (p != in.lim && *p != ',' && *p != '}' && *p != ']' && *p != ' ' && *p != '\n' && *p != '\r' && *p != '\t') ++p;
+            out.append(in.cur, (size_t)(p - in.cur));
+            in.cur = p;
+            if (p != in.lim) break;
         }
         if (out.empty()) fail("expected value");
     }
@@ -163,7 +186,11 @@ struct Parser
         if (in.eof()) fail("unexpected end of input");
         const char c = in.peek();
         if (c == '{' || c == '[')
-            container([&n](std::string& key, Node& child) { n.children.emplace_back(std::move(key), std::move(child)); key.clear(); });
+            container([&n](std::string& key, Node& child) {
+                if (n.children.empty()) n.children.reserve(4);   // most containers of the project files hold 2-4 children
+                n.children.emplace_back(std::move(key), std::move(child));
+                key.clear();
+            });
         else if (c == '"') string(n.data);
         else literal(n.data);
     }
@@ -246,6 +273,15 @@ std::string escape(const std::string& in)
         }
     }
     return out;
+}
+
+void append_escaped(std::string& out, const std::string& in)   // no temporary when nothing needs escaping (keys, numbers)
+{
+    bool plain = true;
+    for (unsigned char c : in)
+        if (c < 0x20 || c == '"' || c == '\\' || c == '/') { plain = false; break; }
+    if (plain) out += in;
+    else out += escape(in);
 }
 
 void write_node(std::string& out, const Node& n, int indent)
@@ -361,7 +397,7 @@ void Writer::child_prefix(const std::string& key)
     buf_.append((size_t)4 * stack_.size(), ' ');
     if (!parent.is_array) {
         buf_ += '"';
-        buf_ += escape(key);
+        append_escaped(buf_, key);
         buf_ += "\": ";
     }
     if (buf_.size() > ((size_t)1 << 20)) flush();
@@ -388,16 +424,19 @@ void Writer::leaf(const std::string& key, const std::string& value)
 {
     child_prefix(key);
     buf_ += '"';
-    buf_ += escape(value);
+    append_escaped(buf_, value);
     buf_ += '"';
 }
 
 void Writer::leaf(const std::string& key, double value)
 {
     child_prefix(key);
+    // std::to_chars(general, 17) prints what "%.17g" prints (the C++ standard defines it through printf), several times faster
     char text[64];
-    const int n = std::snprintf(text, sizeof(text), "\"%.17g\"", value);
-    buf_.append(text, (size_t)n);
+    text[0] = '"';
+    const std::to_chars_result r = std::to_chars(text + 1, text + 60, value, std::chars_format::general, 17);
+    *r.ptr = '"';
+    buf_.append(text, (size_t)(r.ptr - text) + 1);
 }
 
 void Writer::node(const std::string& key, const Node& subtree)

@@ -150,6 +150,7 @@ int main(int argc, char** argv)
             const std::string file = dir + "/marker_detections.json";
             struct rusage ru0;
             getrusage(RUSAGE_SELF, &ru0);   // the CUDA runtime the library links is resident before any I/O
+            const auto tw0 = std::chrono::steady_clock::now();
             const auto coord = [](size_t i, int k) { return (double)(float)(3000.0 + 2500.0 * std::sin(0.001 * (double)i + k)); };
             {
                 DetectionResult det;
@@ -164,7 +165,9 @@ int main(int argc, char** argv)
                 }
                 writeDetectionResult(det, file);
             }
+            const auto tr0 = std::chrono::steady_clock::now();
             const DetectionResult back = readDetectionResult(file);
+            const auto tr1 = std::chrono::steady_clock::now();
             size_t bad = (back.images.size() != nImg) + (back.tags.size() != nTag) + (back.tagObservations.size() != n);
             for (size_t i = 0; i < back.tagObservations.size() && !bad; ++i) {
                 const TagObservation& o = back.tagObservations[i];
@@ -175,7 +178,9 @@ int main(int argc, char** argv)
             struct rusage ru;
             getrusage(RUSAGE_SELF, &ru);
             std::ifstream in(file, std::ios::binary | std::ios::ate);
-            std::printf("observations %zu mismatches %zu file_bytes %lld base_rss_kb %ld maxrss_kb %ld\n", n, bad, (long long)in.tellg(), ru0.ru_maxrss, ru.ru_maxrss);
+            std::printf("observations %zu mismatches %zu file_bytes %lld base_rss_kb %ld maxrss_kb %ld build_and_write_ms %lld read_ms %lld\n", n, bad, (long long)in.tellg(), ru0.ru_maxrss,
+                ru.ru_maxrss, (long long)std::chrono::duration_cast<std::chrono::milliseconds>(tr0 - tw0).count(),
+                (long long)std::chrono::duration_cast<std::chrono::milliseconds>(tr1 - tr0).count());
             return bad ? 1 : 0;
         }
         if (mode == "pnp") {
