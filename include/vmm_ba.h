@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define VMM_BA_ABI_VERSION 1
+#define VMM_BA_ABI_VERSION 2
 
 typedef struct vmm_ba_engine* vmm_ba_handle;
 
@@ -92,6 +92,12 @@ typedef struct {
                                              first solve after the last refresh (a stale preconditioner changes the
                                              iteration count, not the solution); 0 = refresh every LM iteration.
                                              default 8 (the set-up costs about 17 PCG iterations at C3) */
+    double pcg_confirm_tolerance;         /* the reference takes EXACT steps (sparse Cholesky), so its convergence tests
+                                             (function / parameter tolerance) judge exact steps.  When one of them fires on
+                                             an inexact step (pcg_tolerance above this value), the same damped system is
+                                             solved again to this tolerance and the test is repeated on that step: the
+                                             solve only stops where a (nearly) exact step would also have stopped it.
+                                             default 1e-4; 0 = off (stop on the inexact step).  Unused in parity mode. */
 } vmm_ba_options;
 
 /* replaces: ceres::Solver::Summary (the reference only prints termination_type / FullReport) */
@@ -104,7 +110,7 @@ typedef struct {
     int num_iterations;                   /* LM iterations performed, iteration 0 excluded */
     int64_t num_linearizations;           /* residual+Jacobian(+Schur blocks) passes */
     int64_t num_cost_evaluations;         /* residual-only passes */
-    int64_t pcg_iterations;               /* total over the solve */
+    int64_t pcg_iterations;               /* total over the solve (confirmation solves included) */
     int64_t kernel_launches;              /* launches of this library's kernels during the solve */
     double time_total_s;                  /* host wall clock of vmm_ba_solve */
     double time_linearize_s;              /* CUDA-event time on the engine's stream */
@@ -112,6 +118,8 @@ typedef struct {
     double time_cost_eval_s;
     double gradient_max_norm;
     double trust_region_radius;
+    int num_confirmations;                /* convergence tests repeated on a (nearly) exact step (pcg_confirm_tolerance) */
+    int reserved;
     char message[256];
 } vmm_ba_summary;
 
@@ -165,6 +173,14 @@ int vmm_ba_set_poses(vmm_ba_handle h, const double* cam_q, const double* cam_t, 
 /* replaces: the in-place write-back through the pointers handed to Ceres   src/TagReconstructor.cpp:665-666,692-693
  * Full-size outputs on every rank (a distributed engine gathers the camera shards). */
 int vmm_ba_get_poses(vmm_ba_handle h, double* cam_q, double* cam_t, double* tag_q, double* tag_t);
+
+/* The trust-region step of the LAST Levenberg-Marquardt iteration of the last vmm_ba_solve, in the solver's tangent
+ * coordinates (what Plus is applied with: translation increment, then the half-angle rotation increment of
+ * ceres::QuaternionParameterization, src/TagReconstructor.cpp:661): delta_cam [6 * num_cameras], delta_tag
+ * [6 * num_markers] (zeros for blocks without columns).  Whether that step was accepted does not matter.  For the
+ * parity tests: an independent check that (J^T J + D) delta = -g at full problem size.  Full-size outputs on every
+ * rank of a distributed engine. */
+int vmm_ba_get_step(vmm_ba_handle h, double* delta_cam, double* delta_tag);
 
 /* ---- the hot path -------------------------------------------------------------------------- */
 

@@ -35,7 +35,12 @@ class Options(C.Structure):
         ("max_lm_diagonal", C.c_double),
         ("max_num_consecutive_invalid_steps", C.c_int),
         ("jacobi_scaling", C.c_int),
+        ("linear_solver", C.c_int),          # 0 block-envelope Cholesky (RCM marker order), 1 dense (cross-check)
+        ("max_solver_time_s", C.c_double),   # Ceres' max_solver_time_in_seconds
     ]
+
+
+SOLVER_ENVELOPE, SOLVER_DENSE = 0, 1
 
 
 class Summary(C.Structure):
@@ -187,6 +192,51 @@ def solve(s, options: Optional[Options] = None, **kw) -> SolveResult:
     )
     assert rc == 0
     return SolveResult(cam_q, cam_t, tag_q, tag_t, summ, trace[: summ.num_iterations])
+
+
+def lm_step_residual(s, delta, radius=1e4, loss_kind=LOSS_NONE, loss_scale=1.0, jacobi_scaling=True,
+                     min_lm_diagonal=1e-6, max_lm_diagonal=1e32) -> dict:
+    """Matrix-free check of one LM step ``delta`` (tangent, [6Nc+6Nm], cameras first) computed elsewhere for the FIRST
+    iteration at the scene's poses: residual of the damped, Jacobi-scaled normal equations from the oracle's own
+    dual-number Jacobian (no factorisation; linear in the corner count, so it runs at C3/C4 scale)."""
+    intr, cam_q, cam_t, tag_q, tag_t, tag_wh, to_cam, to_tag, to_uv = _scene_args(s)
+    Nc, Nm, Nto = cam_q.shape[0], tag_q.shape[0], to_cam.shape[0]
+    d = _f64(delta).reshape(-1)
+    assert d.shape[0] == 6 * (Nc + Nm)
+    out = np.zeros(4)
+    rc = lib().vmo_lm_step_residual(
+        _p(intr), C.c_int64(Nc), _p(cam_q), _p(cam_t), C.c_int64(Nm), _p(tag_q), _p(tag_t), _p(tag_wh),
+        C.c_int64(s.fixed_tag), C.c_int64(Nto), _p(to_cam, C.c_int32), _p(to_tag, C.c_int32), _p(to_uv),
+        C.c_int(loss_kind), C.c_double(loss_scale), C.c_int(1 if jacobi_scaling else 0), C.c_double(min_lm_diagonal),
+        C.c_double(max_lm_diagonal), C.c_double(radius), _p(d), _p(out))
+    assert rc == 0
+    return {"residual_norm": out[0], "gradient_norm": out[1], "relative": out[0] / out[1] if out[1] > 0 else out[0],
+            "model_cost_change": out[2], "cost": out[3]}
+
+
+def marker_translation_covariance_sparse(s, markers, loss_kind=LOSS_NONE, loss_scale=1.0) -> np.ndarray:
+    """3x3 translation blocks of (J^T J)^-1 for the listed markers through the envelope factorisation of the
+    marker-reduced matrix (site scale; src/TagReconstructor.cpp:744-783).  [len(markers), 3, 3]."""
+    intr, cam_q, cam_t, tag_q, tag_t, tag_wh, to_cam, to_tag, to_uv = _scene_args(s)
+    Nc, Nm, Nto = cam_q.shape[0], tag_q.shape[0], to_cam.shape[0]
+    sel = np.ascontiguousarray(markers, dtype=np.int64)
+    out = np.zeros((sel.shape[0], 3, 3))
+    rc = lib().vmo_marker_translation_covariance_sparse(
+        _p(intr), C.c_int64(Nc), _p(cam_q), _p(cam_t), C.c_int64(Nm), _p(tag_q), _p(tag_t), _p(tag_wh),
+        C.c_int64(s.fixed_tag), C.c_int64(Nto), _p(to_cam, C.c_int32), _p(to_tag, C.c_int32), _p(to_uv),
+        C.c_int(loss_kind), C.c_double(loss_scale), C.c_int64(sel.shape[0]), _p(sel, C.c_int64), _p(out))
+    if rc != 0:
+        raise RuntimeError("the normal equations are rank deficient")
+    return out
+
+
+def sparse_structure(s) -> dict:
+    """Size of the envelope factor the sparse path would build for this scene (no numbers are computed)."""
+    to_cam, to_tag = _i32(s.to_cam), _i32(s.to_tag)
+    out = np.zeros(5)
+    lib().vmo_sparse_structure(C.c_int64(s.n_cameras), C.c_int64(s.n_markers), C.c_int64(s.fixed_tag), C.c_int64(to_cam.shape[0]),
+                               _p(to_cam, C.c_int32), _p(to_tag, C.c_int32), _p(out))
+    return {"free_markers": int(out[0]), "order": int(out[1]), "blocks": int(out[2]), "factor_bytes": out[3], "factor_flops": out[4]}
 
 
 def marker_translation_covariance(s, loss_kind=LOSS_NONE, loss_scale=1.0) -> np.ndarray:

@@ -314,6 +314,228 @@ bool spd_inverse6(const double* A, double* Ainv) {
     return true;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Sparse exact solve for site-scale problems: block-envelope ("skyline") Cholesky.
+//
+// What SPARSE_NORMAL_CHOLESKY gives the reference (src/TagReconstructor.cpp:725-738, Ceres default
+// linear solver) is an EXACT solve of the damped normal equations under a fill-reducing ordering.
+// Here: cameras are eliminated block-wise (exact), the free markers are renumbered by reverse
+// Cuthill-McKee on the co-observation graph (two markers are adjacent when one camera sees both),
+// and the marker-reduced matrix is stored and factored inside its row envelope — Cholesky fill
+// never leaves the envelope, so this is an exact factorisation with no dropped entries.  Blocks of
+// NB x NB doubles (16 markers), right-looking, OpenMP over the trailing update.  On a site whose
+// cameras see a ~18 m neighbourhood the envelope of C3 (120k columns) holds ~4 GB instead of the
+// 115 GB of the dense matrix; a scene where every camera sees every marker degenerates to dense.
+// ---------------------------------------------------------------------------------------------
+constexpr int kNB = 96;             // block order: 16 marker slots of 6
+constexpr int kSlotsPerBlock = kNB / 6;
+typedef double v4d __attribute__((vector_size(32), aligned(8)));
+
+// C (NB x NB, row-major) -= A (NB x NB, row-major) * Bt (NB x NB, row-major; Bt[k][j] = B[j][k])
+inline void block_gemm_sub(const double* __restrict__ A, const double* __restrict__ Bt, double* __restrict__ Cm) {
+    for (int i0 = 0; i0 < kNB; i0 += 4) {
+        for (int j0 = 0; j0 < kNB; j0 += 12) {
+            v4d c[4][3];
+            for (int r = 0; r < 4; ++r)
+                for (int q = 0; q < 3; ++q) c[r][q] = *(const v4d*)(Cm + (size_t)(i0 + r) * kNB + j0 + 4 * q);
+            for (int k = 0; k < kNB; ++k) {
+                const v4d b0 = *(const v4d*)(Bt + (size_t)k * kNB + j0), b1 = *(const v4d*)(Bt + (size_t)k * kNB + j0 + 4),
+                          b2 = *(const v4d*)(Bt + (size_t)k * kNB + j0 + 8);
+                for (int r = 0; r < 4; ++r) {
+                    const double av = A[(size_t)(i0 + r) * kNB + k];
+                    const v4d a = { av, av, av, av };
+                    c[r][0] -= a * b0; c[r][1] -= a * b1; c[r][2] -= a * b2;
+                }
+            }
+            for (int r = 0; r < 4; ++r)
+                for (int q = 0; q < 3; ++q) *(v4d*)(Cm + (size_t)(i0 + r) * kNB + j0 + 4 * q) = c[r][q];
+        }
+    }
+}
+
+struct EnvelopeCholesky {
+    int64_t n = 0, nb = 0;          // scalar order (padded to a multiple of kNB), block rows
+    std::vector<int64_t> lo;        // first block column of block row I (non-decreasing)
+    std::vector<size_t> off;        // block offset of row I: block (I, J) lives at (off[I] + J - lo[I]) * kNB * kNB
+    std::vector<double> a;
+
+    // slot_lo[s]: smallest marker slot that shares a camera with slot s (s itself when none)
+    void set_structure(int64_t nslots, const std::vector<int64_t>& slot_lo) {
+        nb = std::max<int64_t>(1, (nslots + kSlotsPerBlock - 1) / kSlotsPerBlock);
+        n = nb * kNB;
+        lo.assign(nb, 0);
+        for (int64_t I = 0; I < nb; ++I) {
+            int64_t m = I;
+            for (int64_t s = I * kSlotsPerBlock; s < std::min(nslots, (I + 1) * kSlotsPerBlock); ++s) m = std::min(m, slot_lo[s] / kSlotsPerBlock);
+            lo[I] = m;
+        }
+        for (int64_t I = nb - 2; I >= 0; --I) lo[I] = std::min(lo[I], lo[I + 1]);   // monotone: the rows coupled to a column are contiguous
+        off.assign(nb + 1, 0);
+        for (int64_t I = 0; I < nb; ++I) off[I + 1] = off[I] + (size_t)(I - lo[I] + 1);
+    }
+    size_t blocks() const { return off[nb]; }
+    void clear(int64_t nslots) {
+        a.assign(blocks() * (size_t)kNB * kNB, 0.0);
+        // padding rows beyond the last marker slot: identity, so that the padded matrix stays positive definite
+        for (int64_t i = 6 * nslots; i < n; ++i) *entry(i, i) = 1.0;
+    }
+    double* block(int64_t I, int64_t J) { return a.data() + (off[I] + (size_t)(J - lo[I])) * (size_t)kNB * kNB; }
+    const double* block(int64_t I, int64_t J) const { return a.data() + (off[I] + (size_t)(J - lo[I])) * (size_t)kNB * kNB; }
+    double* entry(int64_t i, int64_t j) { return block(i / kNB, j / kNB) + (size_t)(i % kNB) * kNB + (j % kNB); }   // i >= j, inside the envelope
+    bool inside(int64_t si, int64_t sj) const { return sj / kSlotsPerBlock >= lo[si / kSlotsPerBlock]; }
+
+    // in-place A = L L^T (lower); false when a pivot is not positive
+    bool factor() {
+        std::vector<double> panelT;   // transposed copies of the blocks L[I][K] of the current block column
+        for (int64_t K = 0; K < nb; ++K) {
+            double* D = block(K, K);
+            for (int j = 0; j < kNB; ++j) {
+                double d = D[(size_t)j * kNB + j];
+                for (int p = 0; p < j; ++p) d -= D[(size_t)j * kNB + p] * D[(size_t)j * kNB + p];
+                if (!(d > 0.0)) return false;
+                d = std::sqrt(d);
+                D[(size_t)j * kNB + j] = d;
+                for (int i = j + 1; i < kNB; ++i) {
+                    double s = D[(size_t)i * kNB + j];
+                    for (int p = 0; p < j; ++p) s -= D[(size_t)i * kNB + p] * D[(size_t)j * kNB + p];
+                    D[(size_t)i * kNB + j] = s / d;
+                }
+            }
+            int64_t hi = K;   // last block row whose envelope reaches column K
+            while (hi + 1 < nb && lo[hi + 1] <= K) ++hi;
+            const int64_t rows = hi - K;
+            if (rows == 0) continue;
+            panelT.resize((size_t)rows * kNB * kNB);
+            // L[I][K] = A[I][K] L[K][K]^-T, row by row
+#pragma omp parallel for schedule(static)
+            for (int64_t q = 0; q < rows * kNB; ++q) {
+                const int64_t I = K + 1 + q / kNB;
+                const int r = (int)(q % kNB);
+                double* x = block(I, K) + (size_t)r * kNB;
+                double* xt = panelT.data() + (size_t)(I - K - 1) * kNB * kNB;
+                for (int j = 0; j < kNB; ++j) {
+                    double s = x[j];
+                    const double* Lj = D + (size_t)j * kNB;
+                    for (int p = 0; p < j; ++p) s -= x[p] * Lj[p];
+                    x[j] = s / Lj[j];
+                    xt[(size_t)j * kNB + r] = x[j];
+                }
+            }
+            // trailing update: A[I][J] -= L[I][K] L[J][K]^T for K < J <= I <= hi (all inside the envelope: lo[I] <= K < J)
+            const int64_t pairs = rows * (rows + 1) / 2;
+#pragma omp parallel for schedule(dynamic, 4)
+            for (int64_t t = 0; t < pairs; ++t) {
+                // t -> (ri, rj) with rj <= ri, largest rows first
+                int64_t ri = (int64_t)((std::sqrt(8.0 * (double)t + 1.0) - 1.0) / 2.0);
+                while (ri * (ri + 1) / 2 > t) --ri;
+                while ((ri + 1) * (ri + 2) / 2 <= t) ++ri;
+                const int64_t rj = t - ri * (ri + 1) / 2;
+                const int64_t I = K + 1 + ri, J = K + 1 + rj;
+                block_gemm_sub(block(I, K), panelT.data() + (size_t)rj * kNB * kNB, block(I, J));
+            }
+        }
+        return true;
+    }
+    // b <- A^-1 b (b has n entries, padded)
+    void solve(double* b) const {
+        for (int64_t I = 0; I < nb; ++I) {          // L y = b
+            double* bi = b + I * kNB;
+            for (int64_t J = lo[I]; J < I; ++J) {
+                const double* L = block(I, J);
+                const double* bj = b + J * kNB;
+                for (int r = 0; r < kNB; ++r) {
+                    double s = 0.0;
+                    for (int c = 0; c < kNB; ++c) s += L[(size_t)r * kNB + c] * bj[c];
+                    bi[r] -= s;
+                }
+            }
+            const double* D = block(I, I);
+            for (int r = 0; r < kNB; ++r) {
+                double s = bi[r];
+                for (int c = 0; c < r; ++c) s -= D[(size_t)r * kNB + c] * bi[c];
+                bi[r] = s / D[(size_t)r * kNB + r];
+            }
+        }
+        for (int64_t I = nb - 1; I >= 0; --I) {     // L^T x = y
+            double* bi = b + I * kNB;
+            const double* D = block(I, I);
+            for (int r = kNB - 1; r >= 0; --r) {
+                double s = bi[r];
+                for (int c = r + 1; c < kNB; ++c) s -= D[(size_t)c * kNB + r] * bi[c];
+                bi[r] = s / D[(size_t)r * kNB + r];
+            }
+            for (int64_t J = lo[I]; J < I; ++J) {
+                const double* L = block(I, J);
+                double* bj = b + J * kNB;
+                for (int r = 0; r < kNB; ++r) {
+                    const double xr = bi[r];
+                    for (int c = 0; c < kNB; ++c) bj[c] -= L[(size_t)r * kNB + c] * xr;
+                }
+            }
+        }
+    }
+};
+
+// Reverse Cuthill-McKee numbering of the free markers on the co-observation graph.
+// cam_ptr/cam_slots: per camera the free-marker slots (original numbering 0..nfree) it observes.
+// Returns new_of_old[slot].
+void rcm_marker_order(int64_t nfree, int64_t Nc, const std::vector<int64_t>& cam_ptr, const std::vector<int64_t>& cam_slots,
+                      std::vector<int64_t>& new_of_old) {
+    std::vector<int64_t> mk_ptr(nfree + 1, 0), mk_cams(cam_slots.size());
+    for (int64_t v : cam_slots) mk_ptr[v + 1]++;
+    for (int64_t s = 0; s < nfree; ++s) mk_ptr[s + 1] += mk_ptr[s];
+    {
+        std::vector<int64_t> fill(mk_ptr.begin(), mk_ptr.end() - 1);
+        for (int64_t i = 0; i < Nc; ++i)
+            for (int64_t e = cam_ptr[i]; e < cam_ptr[i + 1]; ++e) mk_cams[fill[cam_slots[e]]++] = i;
+    }
+    std::vector<int64_t> degree(nfree, 0);   // co-observations counted with multiplicity: a cheap stand-in for the vertex degree
+    for (int64_t s = 0; s < nfree; ++s)
+        for (int64_t e = mk_ptr[s]; e < mk_ptr[s + 1]; ++e) degree[s] += cam_ptr[mk_cams[e] + 1] - cam_ptr[mk_cams[e]];
+    std::vector<char> seen_m(nfree, 0), seen_c(Nc, 0);
+    std::vector<int64_t> order;
+    order.reserve(nfree);
+    std::vector<int64_t> nbrs;
+    // breadth-first sweep from `start`, appending to `out`; neighbours of a vertex enter by increasing degree
+    auto bfs = [&](int64_t start, std::vector<int64_t>& out) {
+        const size_t first = out.size();
+        seen_m[start] = 1;
+        out.push_back(start);
+        for (size_t head = first; head < out.size(); ++head) {
+            const int64_t u = out[head];
+            nbrs.clear();
+            for (int64_t e = mk_ptr[u]; e < mk_ptr[u + 1]; ++e) {
+                const int64_t i = mk_cams[e];
+                if (seen_c[i]) continue;     // all markers of an expanded camera are already queued
+                seen_c[i] = 1;
+                for (int64_t f = cam_ptr[i]; f < cam_ptr[i + 1]; ++f) {
+                    const int64_t v = cam_slots[f];
+                    if (!seen_m[v]) { seen_m[v] = 1; nbrs.push_back(v); }
+                }
+            }
+            std::sort(nbrs.begin(), nbrs.end(), [&](int64_t x, int64_t y) { return degree[x] < degree[y] || (degree[x] == degree[y] && x < y); });
+            out.insert(out.end(), nbrs.begin(), nbrs.end());
+        }
+    };
+    for (int64_t s0 = 0; s0 < nfree; ++s0) {
+        if (seen_m[s0]) continue;
+        // pseudo-peripheral start vertex of this component: the last vertex of two successive sweeps
+        int64_t start = s0;
+        for (int sweep = 0; sweep < 2; ++sweep) {
+            std::vector<int64_t> probe;
+            bfs(start, probe);
+            start = probe.back();
+            for (int64_t v : probe) {
+                seen_m[v] = 0;
+                for (int64_t e = mk_ptr[v]; e < mk_ptr[v + 1]; ++e) seen_c[mk_cams[e]] = 0;
+            }
+        }
+        bfs(start, order);
+    }
+    new_of_old.assign(nfree, 0);
+    for (int64_t p = 0; p < nfree; ++p) new_of_old[order[p]] = nfree - 1 - p;   // reversed
+}
+
 struct Linearization {
     // per tag-observation 8x6 camera and marker Jacobians (local, corrected, UNSCALED) and residuals(8)
     std::vector<double> Jc, Jm, r;
@@ -382,6 +604,134 @@ void compute_gradient(const Problem& P, const std::vector<double>& Jc, const std
     }
 }
 
+// The marker-reduced system of one LM step in its sparse form (see EnvelopeCholesky): structure once per solve,
+// numbers once per step.  Everything is in Jacobi-scaled coordinates like the rest of vmo_solve.
+struct SparseReduced {
+    int64_t nfree = 0;
+    std::vector<int64_t> slot_new;         // per marker: row block (6 rows) in the reverse Cuthill-McKee order, -1 = not free
+    std::vector<int64_t> mk_ptr, mk_obs;   // marker -> its tag observations
+    EnvelopeCholesky chol;
+    std::vector<double> Ek, Wk;            // per tag observation: E_k = Jc_s^T Jm_s and W_k = (B_i + D^2)^-1 E_k
+
+    void setup(const Problem& P, const std::vector<char>& tag_active, const std::vector<int64_t>& cam_ptr,
+               const std::vector<int64_t>& cam_obs) {
+        const int64_t Nc = P.Nc, Nm = P.Nm, Nto = P.Nto;
+        std::vector<int64_t> slot0(Nm, -1);
+        nfree = 0;
+        for (int64_t j = 0; j < Nm; ++j) if (tag_active[j]) slot0[j] = nfree++;
+        std::vector<int64_t> cs_ptr(Nc + 1, 0), cs;
+        cs.reserve(Nto);
+        for (int64_t i = 0; i < Nc; ++i) {
+            for (int64_t e = cam_ptr[i]; e < cam_ptr[i + 1]; ++e) {
+                const int64_t s = slot0[P.to_tag[cam_obs[e]]];
+                if (s >= 0) cs.push_back(s);
+            }
+            cs_ptr[i + 1] = (int64_t)cs.size();
+        }
+        std::vector<int64_t> new_of_old;
+        rcm_marker_order(nfree, Nc, cs_ptr, cs, new_of_old);
+        slot_new.assign(Nm, -1);
+        for (int64_t j = 0; j < Nm; ++j) if (slot0[j] >= 0) slot_new[j] = new_of_old[slot0[j]];
+        std::vector<int64_t> slot_lo(nfree);
+        for (int64_t s = 0; s < nfree; ++s) slot_lo[s] = s;
+        for (int64_t i = 0; i < Nc; ++i) {
+            int64_t m = nfree;
+            for (int64_t e = cs_ptr[i]; e < cs_ptr[i + 1]; ++e) m = std::min(m, new_of_old[cs[e]]);
+            for (int64_t e = cs_ptr[i]; e < cs_ptr[i + 1]; ++e) { int64_t& l = slot_lo[new_of_old[cs[e]]]; l = std::min(l, m); }
+        }
+        chol.set_structure(nfree, slot_lo);
+        mk_ptr.assign(Nm + 1, 0);
+        mk_obs.resize(Nto);
+        for (int64_t k = 0; k < Nto; ++k) mk_ptr[P.to_tag[k] + 1]++;
+        for (int64_t j = 0; j < Nm; ++j) mk_ptr[j + 1] += mk_ptr[j];
+        std::vector<int64_t> fill(mk_ptr.begin(), mk_ptr.end() - 1);
+        for (int64_t k = 0; k < Nto; ++k) mk_obs[fill[P.to_tag[k]]++] = k;
+    }
+
+    // ym (6 per marker, zeros for markers without columns) = solution of the reduced system
+    //   (C + D^2 - E^T (B + D^2)^-1 E) ym = g_m - E^T (B + D^2)^-1 g_c
+    bool solve(const Problem& P, const Linearization& lin, const std::vector<double>& scale, const std::vector<double>& Dsq,
+               const std::vector<double>& gs, const std::vector<double>& Binv, const std::vector<int64_t>& cam_ptr,
+               const std::vector<int64_t>& cam_obs, std::vector<double>& ym) {
+        const int64_t Nc = P.Nc, Nm = P.Nm, Nto = P.Nto;
+        Ek.assign((size_t)Nto * 36, 0.0);
+        Wk.assign((size_t)Nto * 36, 0.0);
+#pragma omp parallel for schedule(static)
+        for (int64_t k = 0; k < Nto; ++k) {
+            const int64_t i = P.to_cam[k], mi = P.to_tag[k];
+            if (slot_new[mi] < 0) continue;
+            const double* Jc = &lin.Jc[(size_t)k * 48];
+            const double* Jm = &lin.Jm[(size_t)k * 48];
+            double* E = &Ek[(size_t)k * 36];
+            for (int row = 0; row < 8; ++row)
+                for (int a = 0; a < 6; ++a)
+                    for (int b = 0; b < 6; ++b)
+                        E[a * 6 + b] += Jc[row * 6 + a] * scale[6 * i + a] * Jm[row * 6 + b] * scale[6 * Nc + 6 * mi + b];
+            const double* Bi = &Binv[(size_t)i * 36];
+            double* W = &Wk[(size_t)k * 36];
+            for (int a = 0; a < 6; ++a)
+                for (int b = 0; b < 6; ++b) {
+                    double s = 0.0;
+                    for (int c = 0; c < 6; ++c) s += Bi[a * 6 + c] * E[c * 6 + b];
+                    W[a * 6 + b] = s;
+                }
+        }
+        chol.clear(nfree);
+        std::vector<double> rhs((size_t)chol.n, 0.0);
+        // every marker owns its six rows of the matrix: no two threads write the same entry
+#pragma omp parallel for schedule(dynamic, 16)
+        for (int64_t j = 0; j < Nm; ++j) {
+            const int64_t s1 = slot_new[j];
+            if (s1 < 0) continue;
+            double Cj[36] = { 0 }, rj[6];
+            for (int a = 0; a < 6; ++a) rj[a] = gs[6 * Nc + 6 * j + a];
+            const double* sc = &scale[6 * Nc + 6 * j];
+            for (int64_t e1 = mk_ptr[j]; e1 < mk_ptr[j + 1]; ++e1) {
+                const int64_t k1 = mk_obs[e1], i = P.to_cam[k1];
+                const double* J = &lin.Jm[(size_t)k1 * 48];
+                for (int row = 0; row < 8; ++row)
+                    for (int a = 0; a < 6; ++a)
+                        for (int b = 0; b <= a; ++b) Cj[a * 6 + b] += J[row * 6 + a] * sc[a] * J[row * 6 + b] * sc[b];
+                const double* E1 = &Ek[(size_t)k1 * 36];
+                double bg[6];   // (B_i + D^2)^-1 g_c
+                for (int c = 0; c < 6; ++c) {
+                    bg[c] = 0.0;
+                    for (int d = 0; d < 6; ++d) bg[c] += Binv[(size_t)i * 36 + c * 6 + d] * gs[6 * i + d];
+                }
+                for (int a = 0; a < 6; ++a)
+                    for (int c = 0; c < 6; ++c) rj[a] -= E1[c * 6 + a] * bg[c];
+                for (int64_t e2 = cam_ptr[i]; e2 < cam_ptr[i + 1]; ++e2) {
+                    const int64_t k2 = cam_obs[e2];
+                    const int64_t s2 = slot_new[P.to_tag[k2]];
+                    if (s2 < 0 || s2 > s1) continue;
+                    const double* W2 = &Wk[(size_t)k2 * 36];
+                    double* dst = chol.entry(6 * s1, 6 * s2);
+                    for (int a = 0; a < 6; ++a)
+                        for (int b = 0; b < 6; ++b) {
+                            if (s1 == s2 && b > a) continue;
+                            double s = 0.0;
+                            for (int c = 0; c < 6; ++c) s += E1[c * 6 + a] * W2[c * 6 + b];
+                            dst[(size_t)a * kNB + b] -= s;
+                        }
+                }
+            }
+            double* dd = chol.entry(6 * s1, 6 * s1);
+            for (int a = 0; a < 6; ++a) {
+                for (int b = 0; b <= a; ++b) dd[(size_t)a * kNB + b] += Cj[a * 6 + b];
+                dd[(size_t)a * kNB + a] += Dsq[6 * Nc + 6 * j + a];
+                rhs[6 * s1 + a] = rj[a];
+            }
+        }
+        if (!chol.factor()) return false;
+        chol.solve(rhs.data());
+        ym.assign((size_t)6 * Nm, 0.0);
+        for (int64_t j = 0; j < Nm; ++j)
+            if (slot_new[j] >= 0)
+                for (int a = 0; a < 6; ++a) ym[6 * j + a] = rhs[6 * slot_new[j] + a];
+        return true;
+    }
+};
+
 }  // namespace
 
 // =====================================================================================
@@ -404,6 +754,9 @@ typedef struct {
     double max_lm_diagonal;
     int max_num_consecutive_invalid_steps;
     int jacobi_scaling;
+    int linear_solver;            // 0 = block-envelope Cholesky under a reverse Cuthill-McKee marker ordering (default),
+                                  // 1 = dense Cholesky of the marker-reduced system (the round-1 path, kept as a cross-check)
+    double max_solver_time_s;     // Ceres' max_solver_time_in_seconds (default 1e9): checked once per iteration
 } vmo_options;
 
 typedef struct {
@@ -437,6 +790,8 @@ void vmo_options_init(vmo_options* o) {
     o->max_lm_diagonal = 1e32;
     o->max_num_consecutive_invalid_steps = 5;
     o->jacobi_scaling = 1;
+    o->linear_solver = 0;
+    o->max_solver_time_s = 1e9;
 }
 
 int vmo_num_threads(void) {
@@ -584,6 +939,9 @@ int vmo_solve(const double* intr, int64_t Nc, double* cam_q, double* cam_t, int6
     { std::vector<int64_t> fill(cam_ptr.begin(), cam_ptr.end() - 1);
       for (int64_t k = 0; k < Nto; ++k) cam_obs[fill[to_cam[k]]++] = k; }
 
+    SparseReduced sparse;
+    if (opt->linear_solver != 1) sparse.setup(P, tag_active, cam_ptr, cam_obs);
+
     auto x_norm_of = [&](const State& S) {
         double s = 0.0;
         for (int64_t i = 0; i < Nc; ++i) if (cam_active[i]) {
@@ -682,6 +1040,7 @@ int vmo_solve(const double* intr, int64_t Nc, double* cam_q, double* cam_t, int6
     while (true) {
         // FinalizeIterationAndCheckIfMinimizerCanContinue
         if (iteration >= opt->max_num_iterations) { termination = 1; msg = "Maximum number of iterations reached."; break; }
+        if (secs(t_start, clk::now()) >= opt->max_solver_time_s) { termination = 1; msg = "Maximum solver time reached."; break; }
         if (gmax <= opt->gradient_tolerance) { termination = 0; msg = "Gradient tolerance reached."; break; }
         if (radius < opt->min_trust_region_radius) { termination = 0; msg = "Minimum trust region radius reached."; break; }
         ++iteration;
@@ -715,7 +1074,10 @@ int vmo_solve(const double* intr, int64_t Nc, double* cam_q, double* cam_t, int6
         std::vector<double> gs(ntan);   // scaled gradient J_s^T r
         for (int64_t i = 0; i < ntan; ++i) gs[i] = grad[i] * scale[i];
         std::fill(step.begin(), step.end(), 0.0);
-        if (solve_ok) {
+        std::vector<double> ym_m;   // reduced solution, six per marker
+        if (solve_ok && opt->linear_solver != 1) {
+            solve_ok = sparse.solve(P, lin, scale, Dsq, gs, Binv, cam_ptr, cam_obs, ym_m);
+        } else if (solve_ok) {
             S_red.assign((size_t)nred * nred, 0.0);
             rhs_red.assign(nred, 0.0);
             // marker diagonal blocks C_j + D^2 and rhs g_m
@@ -806,8 +1168,14 @@ int vmo_solve(const double* intr, int64_t Nc, double* cam_q, double* cam_t, int6
                 if (!dense_cholesky(S_red.data(), nred)) solve_ok = false;
                 else dense_cholesky_solve(S_red.data(), nred, ym.data());
             }
+            ym_m.assign((size_t)6 * Nm, 0.0);
+            for (int64_t j = 0; j < Nm; ++j) if (tag_active[j])
+                for (int a = 0; a < 6; ++a) ym_m[6 * j + a] = ym[6 * tag_slot[j] + a];
+        }
+        {
             if (solve_ok) {
                 // back-substitute cameras: y_c = Binv (g_c - sum_k E_k y_m)
+#pragma omp parallel for schedule(static)
                 for (int64_t i = 0; i < Nc; ++i) {
                     if (!cam_active[i]) continue;
                     double t[6];
@@ -816,12 +1184,11 @@ int vmo_solve(const double* intr, int64_t Nc, double* cam_q, double* cam_t, int6
                         const int64_t k = cam_obs[e];
                         const int64_t mi = to_tag[k];
                         if (!tag_active[mi]) continue;
-                        const int64_t s = tag_slot[mi];
                         const double* Jc = &lin.Jc[(size_t)k * 48];
                         const double* Jm = &lin.Jm[(size_t)k * 48];
                         for (int row = 0; row < 8; ++row) {
                             double jm = 0.0;
-                            for (int b = 0; b < 6; ++b) jm += Jm[row * 6 + b] * scale[6 * Nc + 6 * mi + b] * ym[6 * s + b];
+                            for (int b = 0; b < 6; ++b) jm += Jm[row * 6 + b] * scale[6 * Nc + 6 * mi + b] * ym_m[6 * mi + b];
                             for (int a = 0; a < 6; ++a) t[a] -= Jc[row * 6 + a] * scale[6 * i + a] * jm;
                         }
                     }
@@ -832,7 +1199,7 @@ int vmo_solve(const double* intr, int64_t Nc, double* cam_q, double* cam_t, int6
                     }
                 }
                 for (int64_t j = 0; j < Nm; ++j) if (tag_active[j])
-                    for (int a = 0; a < 6; ++a) step[6 * Nc + 6 * j + a] = -ym[6 * tag_slot[j] + a];
+                    for (int a = 0; a < 6; ++a) step[6 * Nc + 6 * j + a] = -ym_m[6 * j + a];
                 for (int64_t i = 0; i < ntan; ++i) if (!std::isfinite(step[i])) solve_ok = false;
             }
         }
@@ -930,6 +1297,181 @@ int vmo_solve(const double* intr, int64_t Nc, double* cam_q, double* cam_t, int6
     sum->num_jacobian_evals = n_jac;
     sum->num_residual_evals = n_res;
     std::snprintf(sum->message, sizeof(sum->message), "%s", msg);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Check of ONE Levenberg-Marquardt step computed elsewhere (the CUDA engine), matrix-free and without any
+// factorisation: with J, r from this file's dual-number evaluation at the given poses, the Jacobi scaling
+// of iteration 0 (scale = 1 / (1 + ||column||)) and D^2 = clamp(diag(J_s^T J_s), lo, hi) / radius,
+// an exact step satisfies  (J_s^T J_s + D^2) step_s + J_s^T r = 0,  step_s = delta / scale.
+// delta: tangent step [6Nc + 6Nm] in unscaled coordinates (what Plus is applied with).
+// out[0] = ||(J_s^T J_s + D^2) step_s + g_s||_2,  out[1] = ||g_s||_2,  out[2] = model cost change
+// -(J_s step_s).(r + J_s step_s / 2),  out[3] = cost at the given poses.
+// Two passes over J; linear in the number of corners, so it runs at C3/C4 scale.
+// ---------------------------------------------------------------------------------------------
+int vmo_lm_step_residual(const double* intr, int64_t Nc, const double* cam_q, const double* cam_t, int64_t Nm,
+                         const double* tag_q, const double* tag_t, const double* tag_wh, int64_t fixed_tag, int64_t Nto,
+                         const int32_t* to_cam, const int32_t* to_tag, const double* to_uv, int loss_kind, double loss_scale,
+                         int jacobi_scaling, double min_lm_diagonal, double max_lm_diagonal, double radius,
+                         const double* delta, double* out) {
+    Problem P = make_problem(intr, Nc, cam_q, cam_t, Nm, tag_q, tag_t, tag_wh, fixed_tag, Nto, to_cam, to_tag, to_uv);
+    State S;
+    S.cam_q.assign(cam_q, cam_q + 4 * Nc); S.cam_t.assign(cam_t, cam_t + 3 * Nc);
+    S.tag_q.assign(tag_q, tag_q + 4 * Nm); S.tag_t.assign(tag_t, tag_t + 3 * Nm);
+    Linearization lin;
+    evaluate_all(P, S, loss_kind, loss_scale, true, &lin, nullptr, nullptr, nullptr, nullptr);
+    std::vector<double> grad;
+    compute_gradient(P, lin.Jc, lin.Jm, lin.r, grad);
+    const int64_t ntan = 6 * (Nc + Nm);
+    std::vector<char> tag_free(Nm, 0), cam_free(Nc, 0);
+    for (int64_t k = 0; k < Nto; ++k) { tag_free[to_tag[k]] = 1; cam_free[to_cam[k]] = 1; }
+    if (fixed_tag >= 0 && fixed_tag < Nm) tag_free[fixed_tag] = 0;
+    std::vector<double> colsq(ntan, 0.0), scale(ntan, 1.0);
+    auto column_norms = [&](bool scaled) {
+        std::fill(colsq.begin(), colsq.end(), 0.0);
+        for (int64_t k = 0; k < Nto; ++k) {
+            const int64_t ci = to_cam[k], mi = to_tag[k];
+            for (int row = 0; row < 8; ++row)
+                for (int j = 0; j < 6; ++j) {
+                    const double a = lin.Jc[(size_t)k * 48 + row * 6 + j] * (scaled ? scale[6 * ci + j] : 1.0);
+                    colsq[6 * ci + j] += a * a;
+                    if (tag_free[mi]) {
+                        const double b = lin.Jm[(size_t)k * 48 + row * 6 + j] * (scaled ? scale[6 * Nc + 6 * mi + j] : 1.0);
+                        colsq[6 * Nc + 6 * mi + j] += b * b;
+                    }
+                }
+        }
+    };
+    if (jacobi_scaling) {
+        column_norms(false);
+        for (int64_t i = 0; i < ntan; ++i) scale[i] = 1.0 / (1.0 + std::sqrt(colsq[i]));
+    }
+    column_norms(true);
+    std::vector<double> res(ntan, 0.0), step(ntan, 0.0);
+    for (int64_t i = 0; i < Nc; ++i) if (cam_free[i]) for (int a = 0; a < 6; ++a) step[6 * i + a] = delta[6 * i + a] / scale[6 * i + a];
+    for (int64_t j = 0; j < Nm; ++j) if (tag_free[j]) for (int a = 0; a < 6; ++a) step[6 * (Nc + j) + a] = delta[6 * (Nc + j) + a] / scale[6 * (Nc + j) + a];
+    double model = 0.0;
+    for (int64_t k = 0; k < Nto; ++k) {
+        const int64_t ci = to_cam[k], mi = to_tag[k];
+        for (int row = 0; row < 8; ++row) {
+            double m = 0.0;
+            for (int a = 0; a < 6; ++a) {
+                m += lin.Jc[(size_t)k * 48 + row * 6 + a] * scale[6 * ci + a] * step[6 * ci + a];
+                if (tag_free[mi]) m += lin.Jm[(size_t)k * 48 + row * 6 + a] * scale[6 * Nc + 6 * mi + a] * step[6 * Nc + 6 * mi + a];
+            }
+            model += m * (lin.r[8 * k + row] + 0.5 * m);
+            for (int a = 0; a < 6; ++a) {
+                res[6 * ci + a] += lin.Jc[(size_t)k * 48 + row * 6 + a] * scale[6 * ci + a] * m;
+                if (tag_free[mi]) res[6 * Nc + 6 * mi + a] += lin.Jm[(size_t)k * 48 + row * 6 + a] * scale[6 * Nc + 6 * mi + a] * m;
+            }
+        }
+    }
+    double rn = 0.0, gn = 0.0;
+    for (int64_t i = 0; i < ntan; ++i) {
+        const bool free_col = i < 6 * Nc ? cam_free[i / 6] : tag_free[(i - 6 * Nc) / 6];
+        if (!free_col) continue;
+        const double d2 = std::min(std::max(colsq[i], min_lm_diagonal), max_lm_diagonal) / radius;
+        const double gsi = grad[i] * scale[i];
+        const double e = res[i] + d2 * step[i] + gsi;
+        rn += e * e;
+        gn += gsi * gsi;
+    }
+    out[0] = std::sqrt(rn);
+    out[1] = std::sqrt(gn);
+    out[2] = -model;
+    out[3] = lin.cost;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Marker-translation covariance for SELECTED markers at site scale (src/TagReconstructor.cpp:744-783):
+// the 3x3 translation block of (J^T J)^-1 = the translation block of the inverse of the marker-reduced
+// matrix C - E^T B^-1 E (no damping, no scaling), from the same envelope factorisation as the solver: three
+// right-hand sides per requested marker.  cov_out: [n_sel][3][3]; markers without columns get zeros.
+// Returns 1 when the normal equations are rank deficient.
+// ---------------------------------------------------------------------------------------------
+int vmo_marker_translation_covariance_sparse(const double* intr, int64_t Nc, const double* cam_q, const double* cam_t, int64_t Nm,
+                                             const double* tag_q, const double* tag_t, const double* tag_wh, int64_t fixed_tag,
+                                             int64_t Nto, const int32_t* to_cam, const int32_t* to_tag, const double* to_uv,
+                                             int loss_kind, double loss_scale, int64_t n_sel, const int64_t* sel, double* cov_out) {
+    Problem P = make_problem(intr, Nc, cam_q, cam_t, Nm, tag_q, tag_t, tag_wh, fixed_tag, Nto, to_cam, to_tag, to_uv);
+    State S;
+    S.cam_q.assign(cam_q, cam_q + 4 * Nc); S.cam_t.assign(cam_t, cam_t + 3 * Nc);
+    S.tag_q.assign(tag_q, tag_q + 4 * Nm); S.tag_t.assign(tag_t, tag_t + 3 * Nm);
+    Linearization lin;
+    evaluate_all(P, S, loss_kind, loss_scale, true, &lin, nullptr, nullptr, nullptr, nullptr);
+    std::vector<char> cam_active(Nc, 0), tag_active(Nm, 0);
+    for (int64_t k = 0; k < Nto; ++k) { cam_active[to_cam[k]] = 1; tag_active[to_tag[k]] = 1; }
+    if (fixed_tag >= 0 && fixed_tag < Nm) tag_active[fixed_tag] = 0;
+    std::vector<int64_t> cam_ptr(Nc + 1, 0), cam_obs(Nto);
+    for (int64_t k = 0; k < Nto; ++k) cam_ptr[to_cam[k] + 1]++;
+    for (int64_t i = 0; i < Nc; ++i) cam_ptr[i + 1] += cam_ptr[i];
+    { std::vector<int64_t> fill(cam_ptr.begin(), cam_ptr.end() - 1);
+      for (int64_t k = 0; k < Nto; ++k) cam_obs[fill[to_cam[k]]++] = k; }
+    const int64_t ntan = 6 * (Nc + Nm);
+    std::vector<double> scale(ntan, 1.0), zero(ntan, 0.0), Binv((size_t)Nc * 36, 0.0);
+    bool ok = true;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < Nc; ++i) {
+        if (!cam_active[i]) continue;
+        double B[36] = { 0 };
+        for (int64_t e = cam_ptr[i]; e < cam_ptr[i + 1]; ++e) {
+            const double* J = &lin.Jc[(size_t)cam_obs[e] * 48];
+            for (int row = 0; row < 8; ++row)
+                for (int a = 0; a < 6; ++a)
+                    for (int b = 0; b < 6; ++b) B[a * 6 + b] += J[row * 6 + a] * J[row * 6 + b];
+        }
+        if (!spd_inverse6(B, &Binv[(size_t)i * 36])) {
+#pragma omp atomic write
+            ok = false;
+        }
+    }
+    if (!ok) return 1;
+    SparseReduced sp;
+    sp.setup(P, tag_active, cam_ptr, cam_obs);
+    std::vector<double> ym;
+    if (!sp.solve(P, lin, scale, zero, zero, Binv, cam_ptr, cam_obs, ym)) return 1;   // factorises; the zero right-hand side is discarded
+    std::vector<double> rhs((size_t)sp.chol.n);
+    for (int64_t q = 0; q < n_sel; ++q) {
+        double* c = cov_out + 9 * q;
+        for (int a = 0; a < 9; ++a) c[a] = 0.0;
+        const int64_t s = sp.slot_new[sel[q]];
+        if (s < 0) continue;
+        for (int col = 0; col < 3; ++col) {
+            std::fill(rhs.begin(), rhs.end(), 0.0);
+            rhs[6 * s + col] = 1.0;
+            sp.chol.solve(rhs.data());
+            for (int row = 0; row < 3; ++row) c[row * 3 + col] = rhs[6 * s + row];
+        }
+    }
+    return 0;
+}
+
+// Structure report of the sparse path: out[0] = free markers, out[1] = scalar order (padded), out[2] = blocks stored,
+// out[3] = bytes of the factor, out[4] = flops of the factorisation (2 x multiply-adds of the trailing updates).
+int vmo_sparse_structure(int64_t Nc, int64_t Nm, int64_t fixed_tag, int64_t Nto, const int32_t* to_cam, const int32_t* to_tag, double* out) {
+    Problem P{};
+    P.Nc = Nc; P.Nm = Nm; P.Nto = Nto; P.to_cam = to_cam; P.to_tag = to_tag; P.fixed_tag = fixed_tag;
+    std::vector<char> tag_active(Nm, 0);
+    for (int64_t k = 0; k < Nto; ++k) tag_active[to_tag[k]] = 1;
+    if (fixed_tag >= 0 && fixed_tag < Nm) tag_active[fixed_tag] = 0;
+    std::vector<int64_t> cam_ptr(Nc + 1, 0), cam_obs(Nto);
+    for (int64_t k = 0; k < Nto; ++k) cam_ptr[to_cam[k] + 1]++;
+    for (int64_t i = 0; i < Nc; ++i) cam_ptr[i + 1] += cam_ptr[i];
+    { std::vector<int64_t> fill(cam_ptr.begin(), cam_ptr.end() - 1);
+      for (int64_t k = 0; k < Nto; ++k) cam_obs[fill[to_cam[k]]++] = k; }
+    SparseReduced sp;
+    sp.setup(P, tag_active, cam_ptr, cam_obs);
+    double flops = 0.0;
+    for (int64_t K = 0; K < sp.chol.nb; ++K) {
+        int64_t hi = K;
+        while (hi + 1 < sp.chol.nb && sp.chol.lo[hi + 1] <= K) ++hi;
+        const double rows = (double)(hi - K);
+        flops += rows * (rows + 1) / 2 * 2.0 * kNB * kNB * kNB + rows * (double)kNB * kNB * kNB;
+    }
+    out[0] = (double)sp.nfree; out[1] = (double)sp.chol.n; out[2] = (double)sp.chol.blocks();
+    out[3] = (double)sp.chol.blocks() * kNB * kNB * 8.0; out[4] = flops;
     return 0;
 }
 

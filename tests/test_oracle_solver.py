@@ -184,3 +184,62 @@ def test_tile_scene_replicas_are_disjoint_and_evaluate_alike(oracle):
     e3 = oracle.evaluate(t, oracle.LOSS_HUBER, 1.0, gradient=False)
     assert abs(e3.cost - 3 * e1.cost) <= 1e-12 * e3.cost
     assert np.array_equal(e3.residuals[:e1.residuals.shape[0]], e1.residuals)
+
+
+# ---- the sparse exact solve (block-envelope Cholesky under a reverse Cuthill-McKee marker order) -------------
+def test_envelope_and_dense_solvers_take_the_same_trajectory(oracle, scene_c2):
+    """Two factorisations of the same marker-reduced system (dense, round 1; block envelope in RCM order): every
+    iteration's cost, the iteration counts and the final poses agree to round-off."""
+    a = oracle.solve(scene_c2, max_num_iterations=50, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0, linear_solver=oracle.SOLVER_DENSE)
+    b = oracle.solve(scene_c2, max_num_iterations=50, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0, linear_solver=oracle.SOLVER_ENVELOPE)
+    assert a.summary.num_iterations == b.summary.num_iterations
+    assert np.abs(a.trace[:, 0] - b.trace[:, 0]).max() <= 1e-12 * a.trace[0, 0]
+    assert np.abs(a.cam_t - b.cam_t).max() < 1e-11 and np.abs(a.tag_t - b.tag_t).max() < 1e-11
+
+
+def test_envelope_is_sparse_on_a_site_and_dense_on_a_room(oracle, scene_c2):
+    site = synth.make_config("c3/8")
+    st = oracle.sparse_structure(site)
+    dense_blocks = (st["order"] // 96) * (st["order"] // 96 + 1) // 2
+    assert st["blocks"] < 0.35 * dense_blocks          # local co-visibility: the envelope stays narrow (C3: 0.096)
+    room = oracle.sparse_structure(scene_c2)
+    assert room["free_markers"] > 400
+
+
+def test_lm_step_residual_vanishes_for_the_oracles_own_step(oracle, scene_c1):
+    """The matrix-free normal-equation check used on the GPU step at C3/C4 scale, applied to a step this file knows:
+    one LM iteration of the oracle itself.  delta is recovered from the poses (inverse of Plus)."""
+    s = scene_c1
+    r = oracle.solve(s, max_num_iterations=1, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+    Nc, Nm = s.n_cameras, s.n_markers
+
+    def log_q(q_new, q_old):
+        # q_delta = q_new * conj(q_old) = (cos n, sin(n)/n d)
+        w0, x0, y0, z0 = q_old.T
+        c = np.stack([w0, -x0, -y0, -z0], axis=1) / np.sum(q_old * q_old, axis=1, keepdims=True)
+        a, b = q_new, c
+        w = a[:, 0] * b[:, 0] - a[:, 1] * b[:, 1] - a[:, 2] * b[:, 2] - a[:, 3] * b[:, 3]
+        v = np.stack([a[:, 0] * b[:, 1] + a[:, 1] * b[:, 0] + a[:, 2] * b[:, 3] - a[:, 3] * b[:, 2],
+                      a[:, 0] * b[:, 2] - a[:, 1] * b[:, 3] + a[:, 2] * b[:, 0] + a[:, 3] * b[:, 1],
+                      a[:, 0] * b[:, 3] + a[:, 1] * b[:, 2] - a[:, 2] * b[:, 1] + a[:, 3] * b[:, 0]], axis=1)
+        n = np.linalg.norm(v, axis=1)
+        ang = np.arctan2(n, w)
+        return v * np.where(n > 0, ang / np.maximum(n, 1e-300), 1.0)[:, None]
+
+    delta = np.zeros((Nc + Nm, 6))
+    delta[:Nc, :3] = r.cam_t - s.cam_t
+    delta[:Nc, 3:] = log_q(r.cam_q, s.cam_q)
+    delta[Nc:, :3] = r.tag_t - s.tag_t
+    delta[Nc:, 3:] = log_q(r.tag_q, s.tag_q)
+    chk = oracle.lm_step_residual(s, delta.reshape(-1), radius=1e4, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+    assert chk["relative"] < 1e-9, chk
+    wrong = oracle.lm_step_residual(s, 1.01 * delta.reshape(-1), radius=1e4, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+    assert wrong["relative"] > 1e-3           # the check does notice a 1 % error
+
+
+def test_sparse_covariance_equals_the_dense_inverse(oracle):
+    s = synth.make_scene(n_markers=40, n_cameras=90, markers_per_camera=8, seed=21)
+    ref = oracle.marker_translation_covariance(s)
+    sel = np.arange(s.n_markers)
+    cov = oracle.marker_translation_covariance_sparse(s, sel)
+    assert np.abs(cov - ref).max() <= 1e-8 * np.abs(ref).max()

@@ -78,7 +78,7 @@ struct vmm_ba_engine {
     std::string last_error;
     int64_t launches = 0;
 
-    bool have_intrinsics = false, have_problem = false;
+    bool have_intrinsics = false, have_problem = false, have_step = false;
     Intrinsics intr{};
 
     // global problem sizes
@@ -713,44 +713,59 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
             e->coarse.active = false;
         }
         PcgResult pr{};
-        const double tol = opt->parity_mode ? opt->pcg_parity_tolerance : opt->pcg_tolerance;
+        double tol = opt->parity_mode ? opt->pcg_parity_tolerance : opt->pcg_tolerance;
         const int max_it = opt->parity_mode ? opt->pcg_parity_max_iterations : opt->pcg_max_iterations;
-        rc = pcg_solve(e, tol, std::max(1, max_it), std::max(1, opt->pcg_min_iterations), &pr);
+        bool confirmed = opt->parity_mode || !(opt->pcg_confirm_tolerance > 0.0) || tol <= opt->pcg_confirm_tolerance;
+        // The step of this iteration: PCG on the reduced system to `tol`, back-substitution, candidate poses and their
+        // cost; the statistics of the step land in e->h_st.  Called a second time (tighter tolerance, same damped
+        // system; the right-hand side is re-formed because PCG leaves its residual in its place) when a convergence
+        // test fires on an inexact step.
+        auto compute_step = [&](bool again) -> int {
+            if (again) {
+                LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 0, (const double*)e->gm(), (const double*)nullptr, 1.0, e->zm.p);
+                if (nc > 0) LAUNCH(k_negate, gc_b, kThreads, 6 * nc, e->gc.p, e->pr.p);
+                if (e->seg_all.count > 0) schur_scatter(e, e->zm.p, 1.0, e->pr.p, nullptr);
+            }
+            int rc2 = pcg_solve(e, tol, std::max(1, max_it), std::max(1, opt->pcg_min_iterations), &pr);
+            if (rc2) return rc2;
+            sum->pcg_iterations += pr.iterations;
+            // back-substitution: dm = -Cinv (gm + E^T dc) = -Linv^T (zm + Es^T dc)
+            rc2 = schur_gather(e, e->px.p, e->w.p, nullptr);
+            if (rc2) return rc2;
+            rc2 = allreduce(e, e->w.p, 6 * (size_t)nm, NCCL_SUM);
+            if (rc2) return rc2;
+            LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 1, (const double*)e->w.p, (const double*)e->zm.p, -1.0, e->dm.p);
+            CU(cudaEventRecord(e->ev[3], e->stream));
+            e->have_step = true;
+            // ---- candidate point and its cost ----
+            const int cand = e->cur ^ 1;
+            CU(cudaMemsetAsync(e->st.p + ST_CAND_CAM, 0, sizeof(double) * 16, e->stream));
+            if (nc > 0)
+                LAUNCH(k_candidate, nblocks(nc, kThreads), kThreads, nc, e->cam_active.p, e->cam_q[e->cur].p, e->cam_t[e->cur].p,
+                       e->px.p, e->gc.p, e->lam_c.p, (const double*)e->pr.p, e->cam_q[cand].p, e->cam_t[cand].p, e->st.p + ST_CAND_CAM);
+            LAUNCH(k_candidate, nblocks(nm, kThreads), kThreads, nm, e->tag_active.p, e->tag_q[e->cur].p, e->tag_t[e->cur].p, e->dm.p,
+                   (const double*)e->gm(), e->lam_m.p, (const double*)nullptr, e->tag_q[cand].p, e->tag_t[cand].p, e->st.p + ST_CAND_MARK);
+            prepare_poses(e, cand);
+            if (e->Ntol > 0) {
+                LAUNCH(k_cost, e->n_cost_blocks, kThreads, e->intr, e->Ntol, e->uv.p, e->ocam.p, e->otag.p, e->camP[cand].p,
+                       e->mkP[cand].p, loss, loss_a, e->partials.p);
+                LAUNCH(k_sum_partials, 1, 256, e->n_cost_blocks, e->partials.p, e->st.p + ST_CAND_COST);
+            }
+            rc2 = allreduce(e, e->st.p + ST_CAND_CAM, 6, NCCL_SUM);   // 5 camera stats + candidate cost
+            if (rc2) return rc2;
+            CU(cudaEventRecord(e->ev[4], e->stream));
+            rc2 = read_stats(e);
+            if (rc2) return rc2;
+            CU(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); t_solve += ms * 1e-3;
+            CU(cudaEventElapsedTime(&ms, e->ev[3], e->ev[4])); t_cost += ms * 1e-3;
+            sum->num_cost_evaluations += 1;
+            return VMM_BA_OK;
+        };
+        rc = compute_step(false);
         if (rc) return rc;
-        sum->pcg_iterations += pr.iterations;
         pcg_last = pr.iterations;
         if (coarse_refreshed) { pcg_fresh = pr.iterations; coarse_fresh_known = true; coarse_refreshed = false; }
-        // back-substitution: dm = -Cinv (gm + E^T dc) = -Linv^T (zm + Es^T dc)
-        rc = schur_gather(e, e->px.p, e->w.p, nullptr);
-        if (rc) return rc;
-        rc = allreduce(e, e->w.p, 6 * (size_t)nm, NCCL_SUM);
-        if (rc) return rc;
-        LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 1, (const double*)e->w.p, (const double*)e->zm.p, -1.0, e->dm.p);
-        CU(cudaEventRecord(e->ev[3], e->stream));
-
-        // ---- candidate point and its cost ----
-        const int cand = e->cur ^ 1;
-        CU(cudaMemsetAsync(e->st.p + ST_CAND_CAM, 0, sizeof(double) * 16, e->stream));
-        if (nc > 0)
-            LAUNCH(k_candidate, nblocks(nc, kThreads), kThreads, nc, e->cam_active.p, e->cam_q[e->cur].p, e->cam_t[e->cur].p,
-                   e->px.p, e->gc.p, e->lam_c.p, (const double*)e->pr.p, e->cam_q[cand].p, e->cam_t[cand].p, e->st.p + ST_CAND_CAM);
-        LAUNCH(k_candidate, nblocks(nm, kThreads), kThreads, nm, e->tag_active.p, e->tag_q[e->cur].p, e->tag_t[e->cur].p, e->dm.p,
-               (const double*)e->gm(), e->lam_m.p, (const double*)nullptr, e->tag_q[cand].p, e->tag_t[cand].p, e->st.p + ST_CAND_MARK);
-        prepare_poses(e, cand);
-        if (e->Ntol > 0) {
-            LAUNCH(k_cost, e->n_cost_blocks, kThreads, e->intr, e->Ntol, e->uv.p, e->ocam.p, e->otag.p, e->camP[cand].p,
-                   e->mkP[cand].p, loss, loss_a, e->partials.p);
-            LAUNCH(k_sum_partials, 1, 256, e->n_cost_blocks, e->partials.p, e->st.p + ST_CAND_COST);
-        }
-        rc = allreduce(e, e->st.p + ST_CAND_CAM, 6, NCCL_SUM);   // 5 camera stats + candidate cost
-        if (rc) return rc;
-        CU(cudaEventRecord(e->ev[4], e->stream));
-        rc = read_stats(e);
-        if (rc) return rc;
-        CU(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); t_solve += ms * 1e-3;
-        CU(cudaEventElapsedTime(&ms, e->ev[3], e->ev[4])); t_cost += ms * 1e-3;
-        sum->num_cost_evaluations += 1;
-
+    evaluate_step:
         const double* cs = e->h_st + ST_CAND_CAM;
         const double* msx = e->h_st + ST_CAND_MARK;
         const double step_norm = std::sqrt(cs[0] + msx[0]);
@@ -775,16 +790,24 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         }
         num_consecutive_invalid = 0;
         if (!std::isfinite(cand_cost)) cand_cost = std::numeric_limits<double>::max();
-        if (step_norm <= opt->parameter_tolerance * (x_norm + opt->parameter_tolerance)) {
-            termination = VMM_BA_CONVERGENCE; msg = "Parameter tolerance reached."; break;
-        }
         const double cost_change = x_cost - cand_cost;
-        if (std::fabs(cost_change) <= opt->function_tolerance * x_cost) {
-            termination = VMM_BA_CONVERGENCE; msg = "Function tolerance reached."; break;
+        const bool param_conv = step_norm <= opt->parameter_tolerance * (x_norm + opt->parameter_tolerance);
+        const bool func_conv = std::fabs(cost_change) <= opt->function_tolerance * x_cost;
+        if ((param_conv || func_conv) && !confirmed) {
+            // an exact step might still move: repeat the test on a (nearly) exact step of the same system
+            confirmed = true;
+            tol = opt->pcg_confirm_tolerance;
+            CU(cudaEventRecord(e->ev[2], e->stream));
+            rc = compute_step(true);
+            if (rc) return rc;
+            ++sum->num_confirmations;
+            goto evaluate_step;
         }
+        if (param_conv) { termination = VMM_BA_CONVERGENCE; msg = "Parameter tolerance reached."; break; }
+        if (func_conv) { termination = VMM_BA_CONVERGENCE; msg = "Function tolerance reached."; break; }
         const double relative_decrease = cost_change / model_cost_change;
         if (relative_decrease > opt->min_relative_decrease) {
-            e->cur = cand;   // accept: candidate poses (and their prepared blocks) become current
+            e->cur ^= 1;   // accept: candidate poses (and their prepared blocks) become current
             x_norm = std::sqrt(cs[4] + msx[4]);
             CU(cudaEventRecord(e->ev[0], e->stream));
             rc = linearize(e, e->cur, loss, loss_a);
@@ -1291,6 +1314,7 @@ void vmm_ba_options_init(vmm_ba_options* o) {
     o->pcg_parity_max_iterations = 20000;
     o->verbose = 0;
     o->coarse_refresh_iterations = 8;
+    o->pcg_confirm_tolerance = 1e-4;
 }
 
 int vmm_ba_abi_version(void) { return VMM_BA_ABI_VERSION; }
@@ -1678,6 +1702,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         phase("camera clusters");
     }
     e->cur = 0;
+    e->have_step = false;
     CU(up(e->cam_q[0].p, cam_q + 4 * e->cam0, sizeof(double) * 4 * Ncl));
     CU(up(e->cam_t[0].p, cam_t + 3 * e->cam0, sizeof(double) * 3 * Ncl));
     CU(up(e->tag_q[0].p, tag_q, sizeof(double) * 4 * Nm));
@@ -1751,6 +1776,22 @@ int vmm_ba_get_poses(vmm_ba_handle e, double* cam_q, double* cam_t, double* tag_
     if (tag_q) CU(cudaMemcpyAsync(tag_q, e->tag_q[s].p, sizeof(double) * 4 * e->Nm, cudaMemcpyDeviceToHost, e->stream));
     if (tag_t) CU(cudaMemcpyAsync(tag_t, e->tag_t[s].p, sizeof(double) * 3 * e->Nm, cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
+    return VMM_BA_OK;
+}
+
+int vmm_ba_get_step(vmm_ba_handle e, double* delta_cam, double* delta_tag) {
+    if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
+    if (!e->have_problem || !e->have_step) return fail_with(e, VMM_BA_ERR_STATE, "no Levenberg-Marquardt step has been computed yet");
+    CU(cudaSetDevice(e->device));
+    if (delta_cam && e->Nc > 0) { int rc = gather_cameras(e, e->px.p, 6, delta_cam); if (rc) return rc; }
+    if (delta_tag) CU(cudaMemcpyAsync(delta_tag, e->dm.p, sizeof(double) * 6 * e->Nm, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    if (delta_cam)   // cameras without observations have no columns: their PCG entries are never written
+        for (int64_t i = 0; i < e->Nc; ++i) {
+            bool finite = true;
+            for (int a = 0; a < 6; ++a) finite = finite && std::isfinite(delta_cam[6 * i + a]);
+            if (!finite) for (int a = 0; a < 6; ++a) delta_cam[6 * i + a] = 0.0;
+        }
     return VMM_BA_OK;
 }
 

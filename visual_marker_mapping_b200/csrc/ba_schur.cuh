@@ -278,14 +278,27 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
-// Slot release.  The arrive is RELAXED: a releasing arrive makes ptxas track every earlier global
-// atomic of the thread (ATOMG with a scoreboard instead of fire-and-forget RED), which serialises the
-// scatter pass.  What the release really needs — the LDS reads of the slot being complete before the
-// async proxy overwrites it (measured otherwise: an arrive issued right behind the loads lets the next
-// bulk copy land under them) — is guaranteed by where it is placed: behind a store / reduction whose
-// operands depend on every loaded value.
+// Slot release.  The consumer's reads of the slot (generic proxy, LDS) must be ordered before the producer's next
+// cp.async.bulk into it (async proxy): a cross-proxy fence on shared memory, then the arrive.  The arrive itself is
+// RELAXED — a releasing arrive makes ptxas track every earlier global reduction of the thread (ATOMG with a
+// scoreboard instead of fire-and-forget RED), which serialises the scatter pass; the proxy fence orders exactly what
+// the ring needs (FENCE.VIEW.ASYNC.S in SASS, shared memory only) and leaves the reductions in flight.  It is
+// issued by every lane of the warp that read the slot, followed by __syncwarp() at the call sites, so that lane 0's
+// arrive comes after all 32 lanes' fences.
+#ifndef VMM_SP_RELEASE_MODE
+#define VMM_SP_RELEASE_MODE 1   // 1: proxy fence + relaxed arrive (product); 0: relaxed arrive alone, 2: releasing arrive (A/B builds, tools/)
+#endif
+__device__ __forceinline__ void slot_reads_done() {
+#if VMM_SP_RELEASE_MODE == 1
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
+}
 __device__ __forceinline__ void mbar_arrive_relaxed(uint64_t* b) {
+#if VMM_SP_RELEASE_MODE == 2
+    asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+#else
     asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+#endif
 }
 __device__ __forceinline__ void red_add(double* addr, double v) {
     asm volatile("red.relaxed.gpu.global.add.f64 [%0], %1;" ::"l"(addr), "d"(v) : "memory");
@@ -495,8 +508,11 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
             const double part = warp_reduce6(y, lane);
             SP_TS(4, part);
             if ((lane & 3) == 0 && ridx < 6) s_part[it & 1][g][wg][ridx] = part;
-            // the stored values depend on every E entry of every lane: the slot's loads are complete
-            if (has0 && lane == 0) mbar_arrive_relaxed(&s_empty[ring0]);
+            if (has0) {   // every lane's reads of the slot are fenced against the async proxy before lane 0 hands it back
+                slot_reads_done();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_relaxed(&s_empty[ring0]);
+            }
             group_barrier(g);
             SP_TS(5, 0.0);
             double w = 0.0;
@@ -515,9 +531,10 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
         }
         // ---- scatter pass ----
         if (v0) scatter_e_z(Er, z, sign, out_c + (size_t)c0 * 6);
-        if (MODE == SP_SCATTER) {
+        if (MODE == SP_SCATTER && has0) {
+            slot_reads_done();
             __syncwarp();
-            if (has0 && lane == 0) mbar_arrive_relaxed(&s_empty[ring0]);   // behind the reductions that consumed E
+            if (lane == 0) mbar_arrive_relaxed(&s_empty[ring0]);
         }
         if (has1) {
             if (v1) {
@@ -525,6 +542,7 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
                 slot_load_e(slot1, lane, Ek);
                 scatter_e_z(Ek, z, sign, out_c + (size_t)c1 * 6);
             }
+            slot_reads_done();
             __syncwarp();
             if (lane == 0) mbar_arrive_relaxed(&s_empty[ring1]);
         }

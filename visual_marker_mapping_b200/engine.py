@@ -24,7 +24,7 @@ ABI_SYMBOLS = [
     "vmm_ba_options_init", "vmm_ba_abi_version", "vmm_ba_device_count", "vmm_ba_create",
     "vmm_ba_create_distributed", "vmm_ba_nccl_unique_id", "vmm_ba_destroy", "vmm_ba_last_error",
     "vmm_ba_set_stream", "vmm_ba_set_intrinsics", "vmm_ba_set_problem", "vmm_ba_set_poses",
-    "vmm_ba_get_poses", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
+    "vmm_ba_get_poses", "vmm_ba_get_step", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
     "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_schur_multiply", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
     "vmm_ba_kernel_launches", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
     "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
@@ -56,6 +56,7 @@ class Options(C.Structure):
         ("pcg_parity_max_iterations", C.c_int),
         ("verbose", C.c_int),
         ("coarse_refresh_iterations", C.c_int),
+        ("pcg_confirm_tolerance", C.c_double),
     ]
 
 
@@ -77,6 +78,8 @@ class Summary(C.Structure):
         ("time_cost_eval_s", C.c_double),
         ("gradient_max_norm", C.c_double),
         ("trust_region_radius", C.c_double),
+        ("num_confirmations", C.c_int),
+        ("reserved", C.c_int),
         ("message", C.c_char * 256),
     ]
 
@@ -122,6 +125,7 @@ def load_library():
     lib.vmm_ba_set_problem.argtypes = [C.c_void_p, C.c_int64, dp, dp, C.c_int64, dp, dp, dp, C.c_int64, C.c_int64, ip, ip, dp]
     lib.vmm_ba_set_poses.argtypes = [C.c_void_p, dp, dp, dp, dp]
     lib.vmm_ba_get_poses.argtypes = [C.c_void_p, dp, dp, dp, dp]
+    lib.vmm_ba_get_step.argtypes = [C.c_void_p, dp, dp]
     lib.vmm_ba_solve.argtypes = [C.c_void_p, C.POINTER(Options), C.POINTER(Summary)]
     lib.vmm_ba_evaluate.argtypes = [C.c_void_p, C.c_int, C.c_double, dp, dp, dp, dp]
     lib.vmm_ba_evaluate_device.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp]
@@ -279,6 +283,12 @@ class BundleAdjuster:
         tq, tt = np.zeros((self.n_markers, 4)), np.zeros((self.n_markers, 3))
         self._check(self._lib.vmm_ba_get_poses(self._h, _dp(cq), _dp(ct), _dp(tq), _dp(tt)))
         return cq, ct, tq, tt
+
+    def get_step(self) -> np.ndarray:
+        """Tangent step of the last LM iteration, [6 * (n_cameras + n_markers)], cameras first (the oracle's layout)."""
+        d = np.zeros(6 * (self.n_cameras + self.n_markers))
+        self._check(self._lib.vmm_ba_get_step(self._h, _dp(d[:6 * self.n_cameras]), _dp(d[6 * self.n_cameras:])))
+        return d
 
     def solve(self, options: Optional[Options] = None, **kw) -> Summary:
         opt = options if options is not None else default_options(**kw)
