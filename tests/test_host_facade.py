@@ -276,7 +276,8 @@ def test_cli_closing_sequence_host_logic(host, oracle, abi_double, tmp_path):
     s.to_cam, s.to_tag, s.to_uv = s.to_cam[keep], s.to_tag[keep], s.to_uv[keep]
     s.to_uv[s.to_tag == s.fixed_tag] += 6.0       # the origin tag is never removed (:794)
     project_io.write_project(s, str(tmp_path), image_id_offset=7, tag_id_offset=20)
-    r = subprocess.run([CLI, "--project_path", str(tmp_path), "--start_tag_id", str(20 + s.fixed_tag), "--overwrite"], capture_output=True,
+    r = subprocess.run([CLI, "--project_path", str(tmp_path), "--start_tag_id", str(20 + s.fixed_tag), "--overwrite",
+                        "--initial_reconstruction", str(tmp_path / "initial_reconstruction.json")], capture_output=True,
                        text=True, env=abi_double)
     assert r.returncode == 0 and "Error" not in r.stderr, r.stderr
     sums = oracle.reprojection_error_sums(s)
@@ -366,7 +367,8 @@ def oracle_closing_sequence(oracle, s):
 def test_cli_closing_sequence_matches_oracle(host, oracle, tmp_path):
     s = culled_scene()
     project_io.write_project(s, str(tmp_path), image_id_offset=7, tag_id_offset=20)
-    r = subprocess.run([CLI, "--project_path", str(tmp_path), "--start_tag_id", "20", "--parity", "--overwrite"], capture_output=True, text=True)
+    r = subprocess.run([CLI, "--project_path", str(tmp_path), "--start_tag_id", "20", "--parity", "--overwrite",
+                        "--initial_reconstruction", str(tmp_path / "initial_reconstruction.json")], capture_output=True, text=True)
     assert r.returncode == 0 and "Error" not in r.stderr, r.stderr
     assert "Solution 0" in r.stdout and "Removing bad marker with id 25" in r.stdout
     tags, cams = project_io.read_reconstruction(str(tmp_path / "reconstruction.json"))

@@ -92,12 +92,12 @@ void parseReconstructions(const std::string& inputPath, std::map<int, Reconstruc
             cam.cameraId = n.get_int("id");
             cam.q = nodeVector<4>(n.get_child("rotation"));
             cam.t = nodeVector<3>(n.get_child("translation"));
-            reconstructedCameras[cam.cameraId] = cam;
+            reconstructedCameras.emplace(cam.cameraId, cam);   // a repeated id keeps the first entry, as the reference's emplace does (src/ReconstructionIO.cpp:106); tags: last wins (:119-128)
         } else if (section == "camera_model") {
             model.add_child(key, std::move(n));
         }
     });
-    for (const char* key : { "reconstructed_tags", "reconstructed_cameras" }) {
+    for (const char* key : { "reconstructed_tags", "reconstructed_cameras", "camera_model" }) {   // get_child throws on each (src/ReconstructionIO.cpp:141-143)
         bool found = false;
         for (const std::string& s : seen) found = found || s == key;
         if (!found) throw std::runtime_error(std::string("No such node (") + key + ")");

@@ -6,6 +6,7 @@
 
 #include "../../../../include/vmm_ba.h"
 
+#include <limits>
 #include <algorithm>
 #include <cmath>
 #include <functional>
@@ -286,13 +287,15 @@ void TagReconstructor::doBundleAdjustment(int maxNumIterations, size_t /*ceresTh
     // :744-783 — standard deviations of the tag translations from the covariance blocks, same lines as the reference
     // ("StdDevNorm" is the square root of the norm of the standard deviations, :772-773, reproduced as it is)
     if (printSummary) {
+        // nothing of an earlier call may be read as this one's result
+        tagCovariances_.clear();
+        markerPositionRms_ = std::numeric_limits<double>::quiet_NaN();
         std::vector<double> cov(9 * f.tagIds.size(), 0.0);
         const int rc = vmm_ba_marker_translation_covariance(engine_, opt.loss_kind, opt.loss_scale, cov.data());
         if (rc != VMM_BA_OK) {
             if (!quiet_) std::cout << "Covariance not available: " << vmm_ba_last_error(engine_) << std::endl;
             return;
         }
-        tagCovariances_.clear();
         double avg[3] = { 0.0, 0.0, 0.0 };
         for (size_t j = 0; j < f.tagIds.size(); ++j) {
             const double* c = cov.data() + 9 * j;

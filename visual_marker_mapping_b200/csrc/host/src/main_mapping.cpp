@@ -4,8 +4,9 @@
 //   --start_tag_id <id>    origin tag (default: lowest id)
 // Like the reference the tool starts from the detections alone: incremental PnP initialisation with a bundle
 // adjustment per added image (src/TagReconstructor.cpp:146-267; --wave: per round of images), then the closing
-// sequence BA(Huber) -> cull 2 px -> BA (:271-277).  Extension: when --initial_reconstruction is given (or
-// <dir>/initial_reconstruction.json exists) its poses are taken as the start and only the closing sequence runs.
+// sequence BA(Huber) -> cull 2 px -> BA (:271-277).  Extension: when --initial_reconstruction <json> is given its
+// poses are taken as the start and only the closing sequence runs (never picked up implicitly: the same directory
+// gives the same run as with the reference tool).
 #include "visual_marker_mapping/CameraUtilities.h"
 #include "visual_marker_mapping/DetectionIO.h"
 #include "visual_marker_mapping/ReconstructionIO.h"
@@ -79,8 +80,9 @@ int main(int argc, char** argv)
         std::map<int, ReconstructedTag> tags;
         std::map<int, Camera> cams;
         CameraModel ignored = camModel;
-        const std::string init = p.initialReconstruction.empty() ? p.projectPath + "/initial_reconstruction.json" : p.initialReconstruction;
-        const bool haveInit = !p.initialReconstruction.empty() || exists(init);
+        const std::string init = p.initialReconstruction;
+        const bool haveInit = !init.empty();
+        if (haveInit) std::cout << "Initial reconstruction from " << init << ": closing sequence only" << std::endl;
         if (haveInit) parseReconstructions(init, tags, cams, ignored);
         TagReconstructor reconstructor(std::move(detections));
         reconstructor.setCameraModel(camModel);
