@@ -21,6 +21,7 @@
 #include "ba_kernels.cuh"
 #include "ba_schur.cuh"
 #include "ba_coarse.cuh"
+#include "ba_pcg.cuh"
 #include "ba_stage.cuh"
 #include "ba_cov.cuh"
 #include "ba_peer.cuh"
@@ -145,6 +146,16 @@ struct vmm_ba_engine {
     DevBuf<double> px, pr, pz, pp, pq, w /* 6Nm + 2 (pbp slots) */, zm, dm, sc;
     DevBuf<double> partials, st;
     DevBuf<int> fail;
+    // persistent PCG (ba_pcg.cuh): units of at most kUnitCams cameras of one cluster, per-CTA unit ranges, scalar table
+    struct PcgPlan {
+        DevBuf<PcgUnit> units;
+        DevBuf<int> cta_unit, unit_cams, cl_unit_ptr;
+        DevBuf<double> rc_part, scal;
+        DevBuf<unsigned> barrier;
+        int nunits = 0;
+        bool with_clusters = false;
+    } pcgp;
+    bool pcg_result_pending = false;
     double* h_st = nullptr;   // pinned mirror of st (64) + sc (8)
     int* h_fail = nullptr;
     int n_cost_blocks = 0, n_lin_blocks = 0;
@@ -363,6 +374,7 @@ int linearize(vmm_ba_engine* e, int slot, int loss_kind, double loss_a) {
 
 int read_stats(vmm_ba_engine* e) {
     CU(cudaMemcpyAsync(e->h_st, e->st.p, sizeof(double) * ST_N, cudaMemcpyDeviceToHost, e->stream));
+    if (e->pcg_result_pending) CU(cudaMemcpyAsync(e->h_st + ST_SC, e->sc.p, sizeof(double) * SC_N, cudaMemcpyDeviceToHost, e->stream));
     CU(cudaMemcpyAsync(e->h_fail, e->fail.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
     if (e->profiling) profile_resolve(e);
@@ -525,12 +537,90 @@ int coarse_setup(vmm_ba_engine* e, int slot) {
     return VMM_BA_OK;
 }
 
+// Units of the persistent PCG kernel: the (active) local cameras cluster by cluster in runs of at most kUnitCams, every
+// CTA a contiguous range of units.  ncl == 0 (no coarse space for this problem): index order, cluster -1.
+int build_pcg_units(vmm_ba_engine* e, int ncl, const std::vector<int>& cl_ptr, const std::vector<int>& cl_cams, const std::vector<unsigned char>& cam_act) {
+    auto& P = e->pcgp;
+    std::vector<PcgUnit> units;
+    std::vector<int> cams, cl_unit_ptr(ncl + 1, 0);
+    auto add_run = [&](int cluster, const int* list, int n) {
+        for (int o = 0; o < n; o += kUnitCams) {
+            units.push_back(PcgUnit{ cluster, (int)cams.size(), std::min(kUnitCams, n - o), 0 });
+            cams.insert(cams.end(), list + o, list + o + std::min(kUnitCams, n - o));
+        }
+    };
+    if (ncl > 0) {
+        for (int c = 0; c < ncl; ++c) {
+            cl_unit_ptr[c] = (int)units.size();
+            add_run(c, cl_cams.data() + cl_ptr[c], cl_ptr[c + 1] - cl_ptr[c]);
+        }
+        cl_unit_ptr[ncl] = (int)units.size();
+    } else {
+        std::vector<int> act;
+        for (int64_t i = 0; i < e->Ncl; ++i) if (cam_act[i]) act.push_back((int)i);
+        add_run(-1, act.data(), (int)act.size());
+    }
+    const int G = e->sp_grid;
+    std::vector<int> cta_unit(G + 1);
+    for (int b = 0; b <= G; ++b) cta_unit[b] = (int)((int64_t)units.size() * b / G);
+    P.nunits = (int)units.size();
+    P.with_clusters = ncl > 0;
+    CU(P.units.alloc(std::max<size_t>(units.size(), 1))); CU(P.unit_cams.alloc(std::max<size_t>(cams.size(), 1)));
+    CU(P.cta_unit.alloc(G + 1)); CU(P.cl_unit_ptr.alloc(ncl + 1)); CU(P.rc_part.alloc(std::max<size_t>(6 * units.size(), 1)));
+    if (!P.barrier.p) { CU(P.barrier.alloc(4)); CU(cudaMemsetAsync(P.barrier.p, 0, 4 * sizeof(unsigned), e->stream)); }
+    auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
+    CU(up(P.units.p, units.data(), sizeof(PcgUnit) * units.size()));
+    CU(up(P.unit_cams.p, cams.data(), sizeof(int) * cams.size()));
+    CU(up(P.cta_unit.p, cta_unit.data(), sizeof(int) * (G + 1)));
+    CU(up(P.cl_unit_ptr.p, cl_unit_ptr.data(), sizeof(int) * (ncl + 1)));
+    CU(cudaStreamSynchronize(e->stream));   // host vectors go out of scope
+    return VMM_BA_OK;
+}
+
+// The whole PCG solve as one cooperative launch (ba_pcg.cuh).  The result (iterations, relative residual, ok) lands in
+// e->sc and reaches the host with the next read_stats: no host synchronisation inside the linear solve.
+int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it) {
+    auto& P = e->pcgp;
+    const size_t rows = (size_t)max_it + 2;
+    if (P.scal.n < rows * PS_STRIDE) CU(P.scal.alloc(rows * PS_STRIDE));
+    CU(cudaMemsetAsync(P.scal.p, 0, sizeof(double) * rows * PS_STRIDE, e->stream));
+    CU(cudaMemsetAsync(e->sc.p, 0, sizeof(double) * SC_N, e->stream));
+    CU(cudaMemsetAsync(P.barrier.p, 0, 4 * sizeof(unsigned), e->stream));   // arrivals, generation, abort flag
+    const bool two_level = e->coarse.active && P.with_clusters;
+    PcgArgs a{};
+    a.segs = e->seg_full.segs.p; a.cta_seg = e->seg_full.cta_seg.p; a.nseg = e->seg_full.count; a.slot_desc = e->seg_full.slots.p;
+    a.nslots_total = e->seg_full.nslots; a.Es = e->Es.p; a.mo_cam = e->mo_cam.p;
+    a.units = P.units.p; a.cta_unit = P.cta_unit.p; a.unit_cams = P.unit_cams.p;
+    a.Minv = e->Minv.p; a.B = e->B.p; a.lam = e->lam_c.p;
+    a.x = e->px.p; a.r = e->pr.p; a.z = e->pz.p; a.p = e->pp.p; a.q = e->pq.p;
+    a.ncl = two_level ? e->coarse.ncl : 0; a.nC = two_level ? e->coarse.nC : 0;
+    a.cl_unit_ptr = P.cl_unit_ptr.p; a.xbar = e->coarse.xbar.p; a.camP = e->camP[e->cur].p; a.Ainv = e->coarse.Ac.p;
+    a.rc_part = P.rc_part.p; a.yc = e->coarse.yc.p;
+    a.scal = P.scal.p; a.result = e->sc.p; a.barrier = P.barrier.p;
+    a.max_it = max_it; a.min_it = min_it; a.tol2 = tol * tol;
+    static const int kid = register_kernel("k_pcg_persistent");
+    cudaEvent_t eb = nullptr;
+    if (e->profiling) eb = profile_begin(e);
+    void* args[] = { &a };
+    CU(cudaLaunchCooperativeKernel((const void*)k_pcg_persistent, dim3(e->sp_grid), dim3(kSpThreads), args, kSpSmemBytes, e->stream));
+    if (eb) profile_end(e, kid, eb);
+    ++e->launches;
+    e->pcg_result_pending = true;
+    return VMM_BA_OK;
+}
+
 struct PcgResult { int iterations; bool ok; double rel; };
 
 // Solve (B_l - E C_l^-1 E^T) x = r0 (r0 in e->pr on entry). x -> e->px, final residual in e->pr.
 // The stopping test runs on the device (k_pcg_direction raises sc[SC_DONE], which turns every later
 // PCG launch into a no-op); the host only looks every `check_every` iterations.
 int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* out) {
+    static const bool legacy = std::getenv("VMM_BA_PCG_LEGACY") != nullptr;   // A/B: the five-launches-per-iteration loop of round 1
+    e->pcg_result_pending = false;
+    if (!legacy && e->world == 1 && e->seg_big.count == 0 && e->pcgp.nunits > 0) {
+        out->iterations = 0; out->ok = true; out->rel = 1.0;
+        return pcg_solve_persistent(e, tol, max_it, min_it);
+    }
     const int nc = (int)e->Ncl;
     const int nm = (int)e->Nm;
     const int gb = nblocks(std::max<int64_t>(nc, 1), kThreads);
@@ -728,7 +818,6 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
             }
             int rc2 = pcg_solve(e, tol, std::max(1, max_it), std::max(1, opt->pcg_min_iterations), &pr);
             if (rc2) return rc2;
-            sum->pcg_iterations += pr.iterations;
             // back-substitution: dm = -Cinv (gm + E^T dc) = -Linv^T (zm + Es^T dc)
             rc2 = schur_gather(e, e->px.p, e->w.p, nullptr);
             if (rc2) return rc2;
@@ -756,6 +845,14 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
             CU(cudaEventRecord(e->ev[4], e->stream));
             rc2 = read_stats(e);
             if (rc2) return rc2;
+            if (e->pcg_result_pending) {   // the persistent kernel's verdict came with the statistics
+                const double* h = e->h_st + ST_SC;
+                pr.iterations = (int)h[SC_ITERS];
+                pr.ok = std::isfinite(h[SC_REL2]) && std::isfinite(h[SC_RZ0]);
+                pr.rel = pr.ok ? std::sqrt(std::max(h[SC_REL2], 0.0)) : 1.0;
+                e->pcg_result_pending = false;
+            }
+            sum->pcg_iterations += pr.iterations;
             CU(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); t_solve += ms * 1e-3;
             CU(cudaEventElapsedTime(&ms, e->ev[3], e->ev[4])); t_cost += ms * 1e-3;
             sum->num_cost_evaluations += 1;
@@ -1191,7 +1288,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     CU(up(c.xbar.p, xbar.data(), sizeof(double) * 3 * ncl));
     CU(cudaStreamSynchronize(e->stream));
     c.available = true;
-    return VMM_BA_OK;
+    return build_pcg_units(e, ncl, cl_ptr, cl_cams, tag_active /* unused with clusters */);
 }
 
 // host mirror of perm_dev (camera-order position -> caller's tag-observation index), fetched when a
@@ -1345,7 +1442,8 @@ static int create_common(int device, vmm_ba_engine** out) {
     if (prop.major != 10)
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
     if ((err = cudaSetDevice(device)) != cudaSuccess) return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(err));
-    for (const void* f : { (const void*)k_schur_product<SP_FULL>, (const void*)k_schur_product<SP_GATHER>, (const void*)k_schur_product<SP_SCATTER> })
+    for (const void* f : { (const void*)k_schur_product<SP_FULL>, (const void*)k_schur_product<SP_GATHER>, (const void*)k_schur_product<SP_SCATTER>,
+                           (const void*)k_pcg_persistent })
         if ((err = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmemBytes)) != cudaSuccess)
             return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaFuncSetAttribute(shared memory %zu): %s", kSpSmemBytes, cudaGetErrorString(err));
     e = new vmm_ba_engine();
@@ -1699,6 +1797,10 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         rc = build_clusters(e, cam_q, cam_t, cam_count, Nto, to_cam, to_tag, h_mptr, h_mocam, h_tact, e->cam_order.empty() ? nullptr : &spatial_leaves,
                             &splits_ahead);
         if (rc) return rc;
+        if (!e->coarse.available) {   // no coarse space for this problem: the persistent PCG still needs its units
+            rc = build_pcg_units(e, 0, std::vector<int>(), std::vector<int>(), h_cact);
+            if (rc) return rc;
+        }
         phase("camera clusters");
     }
     e->cur = 0;

@@ -331,6 +331,9 @@ __device__ __forceinline__ void scatter_e_z(const double2 (&E)[18], const double
 #endif
     }
 }
+// COHERENT: the vector changes during the kernel's lifetime (persistent PCG): read it from L2 (ld.cg), never through the
+// non-coherent path.
+template <bool COHERENT>
 __device__ __forceinline__ void load_x6(const double* __restrict__ v, int cam, double (&x)[6]) {
 #ifdef VMM_SP_NO_X    // timing experiment only (tools/): results are wrong
     const double2* x2 = reinterpret_cast<const double2*>(v + (size_t)(cam & 31) * 6);
@@ -338,7 +341,7 @@ __device__ __forceinline__ void load_x6(const double* __restrict__ v, int cam, d
     const double2* x2 = reinterpret_cast<const double2*>(v + (size_t)cam * 6);
 #endif
 #pragma unroll
-    for (int i = 0; i < 3; ++i) { const double2 t = __ldg(x2 + i); x[2 * i] = t.x; x[2 * i + 1] = t.y; }
+    for (int i = 0; i < 3; ++i) { const double2 t = COHERENT ? __ldcg(x2 + i) : __ldg(x2 + i); x[2 * i] = t.x; x[2 * i + 1] = t.y; }
 }
 // lane's block inside a ring slot (tile = lane / 8, row = lane % 8)
 __device__ __forceinline__ void slot_load_e(const unsigned char* slot, int lane, double2 (&E)[18]) {
@@ -385,27 +388,38 @@ __device__ __forceinline__ int ring_acquire(int q, uint64_t* s_full, const volat
     return ring;
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(kSpThreads, 1)
-k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg, int nseg, const int2* __restrict__ slot_desc,
-                int nslots_total, const unsigned char* __restrict__ Es, const int* __restrict__ mo_cam,
-                const double* __restrict__ vin_c, double* __restrict__ mvec, double sign, double* __restrict__ out_c,
-                double* __restrict__ dot_acc, const double* __restrict__ done, double* zero0, double* zero1, double* zero2) {
-    if (done && *done != 0.0) return;
-    extern __shared__ __align__(128) unsigned char sp_ring[];
-    __shared__ uint64_t s_full[kSpRing], s_empty[kSpRing];
-    __shared__ double s_part[2][kSpGroups][kSpGroupWarps][6];
-    __shared__ volatile int s_lap[kSpRing];   // laps the producer has issued per ring position (see ring_acquire)
+// Shared state of one streamed pass (static shared memory of the calling kernel; the ring itself is dynamic).
+struct SpShared {
+    uint64_t full[kSpRing], empty[kSpRing];
+    double part[2][kSpGroups][kSpGroupWarps][6];
+    volatile int lap[kSpRing];   // laps the producer has issued per ring position (see ring_acquire)
+};
+
+// One streamed pass over a segment list, executed by ALL kSpThreads threads of the CTA (consumer groups + producer
+// warp); returns with every thread (no early exits: the persistent PCG kernel goes on to a grid barrier).  `reinit`:
+// the ring barriers have been used by an earlier pass of the same kernel and are invalidated first.
+// COHERENT: see load_x6.
+template <int MODE, bool COHERENT>
+__device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bool reinit, const SpSeg* __restrict__ segs,
+                                        const int* __restrict__ cta_seg, int nseg, const int2* __restrict__ slot_desc, int nslots_total,
+                                        const unsigned char* __restrict__ Es, const int* __restrict__ mo_cam,
+                                        const double* __restrict__ vin_c, double* __restrict__ mvec, double sign,
+                                        double* __restrict__ out_c, double* __restrict__ dot_acc) {
+    uint64_t* s_full = sh.full;
+    uint64_t* s_empty = sh.empty;
+    volatile int* s_lap = sh.lap;
     const int tid = threadIdx.x;
-    if (blockIdx.x == 0 && tid == 0) {   // recycle the other parity's PCG accumulators (nobody touches them in this launch)
-        if (zero0) *zero0 = 0.0;
-        if (zero1) *zero1 = 0.0;
-        if (zero2) *zero2 = 0.0;
-    }
     const int sb = cta_seg[blockIdx.x], se = cta_seg[blockIdx.x + 1];
-    if (sb >= se) return;
+    if (sb >= se) return;   // uniform for the CTA
+    __syncthreads();        // an earlier pass has left the ring
     if (tid == 0) {
-        for (int s = 0; s < kSpRing; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 1); s_lap[s] = 0; }
+        for (int s = 0; s < kSpRing; ++s) {
+            if (reinit) {
+                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&s_full[s])) : "memory");
+                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&s_empty[s])) : "memory");
+            }
+            mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 1); s_lap[s] = 0;
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -468,10 +482,10 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
         double x0[6], z[6];
         const int c0 = cam0, c1 = cam1;
         if (MODE != SP_SCATTER) {
-            if (v0) load_x6(vin_c, c0, x0);
+            if (v0) load_x6<COHERENT>(vin_c, c0, x0);
         } else {
 #pragma unroll
-            for (int b = 0; b < 6; ++b) z[b] = __ldg(mvec + (size_t)j * 6 + b);
+            for (int b = 0; b < 6; ++b) z[b] = COHERENT ? __ldcg(mvec + (size_t)j * 6 + b) : __ldg(mvec + (size_t)j * 6 + b);
         }
         d_cur = d_nxt;
         if (s + 2 * kSpGroups < se) d_nxt = __ldg(seg4 + s + 2 * kSpGroups);
@@ -489,7 +503,7 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
             slot1 = sp_ring + (size_t)ring1 * kSlotBytes;
             if (MODE != SP_SCATTER && v1) {
                 double x1[6];
-                load_x6(vin_c, c1, x1);   // requested here: prefetching it as well costs more in spills than it hides
+                load_x6<COHERENT>(vin_c, c1, x1);   // requested here: prefetching it as well costs more in spills than it hides
                 double2 Ek[18];
                 slot_load_e(slot1, lane, Ek);
                 et_times_x(Ek, x1, y);
@@ -507,7 +521,7 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
             SP_TS(3, y[0] + y[1] + y[2] + y[3] + y[4] + y[5]);
             const double part = warp_reduce6(y, lane);
             SP_TS(4, part);
-            if ((lane & 3) == 0 && ridx < 6) s_part[it & 1][g][wg][ridx] = part;
+            if ((lane & 3) == 0 && ridx < 6) sh.part[it & 1][g][wg][ridx] = part;
             if (has0) {   // every lane's reads of the slot are fenced against the async proxy before lane 0 hands it back
                 slot_reads_done();
                 __syncwarp();
@@ -518,7 +532,7 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
             double w = 0.0;
             if (lane < 6) {
 #pragma unroll
-                for (int q = 0; q < kSpGroupWarps; ++q) w += s_part[it & 1][g][q][lane];
+                for (int q = 0; q < kSpGroupWarps; ++q) w += sh.part[it & 1][g][q][lane];
             }
             if (MODE == SP_GATHER) {
                 if (wg == 0 && lane < 6) red_add(mvec + (size_t)j * 6 + lane, w);   // segments of a split marker meet here
@@ -552,6 +566,23 @@ k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg,
         const double dsum = warp_sum(lane < 6 ? dacc : 0.0);
         if (lane == 0) red_add(dot_acc, dsum);
     }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kSpThreads, 1)
+k_schur_product(const SpSeg* __restrict__ segs, const int* __restrict__ cta_seg, int nseg, const int2* __restrict__ slot_desc,
+                int nslots_total, const unsigned char* __restrict__ Es, const int* __restrict__ mo_cam,
+                const double* __restrict__ vin_c, double* __restrict__ mvec, double sign, double* __restrict__ out_c,
+                double* __restrict__ dot_acc, const double* __restrict__ done, double* zero0, double* zero1, double* zero2) {
+    if (done && *done != 0.0) return;
+    extern __shared__ __align__(128) unsigned char sp_ring[];
+    __shared__ SpShared sh;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {   // recycle the other parity's PCG accumulators (nobody touches them in this launch)
+        if (zero0) *zero0 = 0.0;
+        if (zero1) *zero1 = 0.0;
+        if (zero2) *zero2 = 0.0;
+    }
+    sp_pass<MODE, false>(sh, sp_ring, false, segs, cta_seg, nseg, slot_desc, nslots_total, Es, mo_cam, vin_c, mvec, sign, out_c, dot_acc);
 }
 
 // ------------------------------------------------------------------------------------------
