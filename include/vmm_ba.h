@@ -218,6 +218,14 @@ int vmm_ba_reprojection_error_sums(vmm_ba_handle h, double* per_tag_obs_sum);
  * VMM_BA_ERR_NUMERIC when the normal equations are rank deficient (Ceres: Compute() returns false). */
 int vmm_ba_marker_translation_covariance(vmm_ba_handle h, int loss_kind, double loss_scale, double* cov);
 
+/* Test entry (one GPU): the coarse matrix A_c = P^T S P of the two-level preconditioner at the current poses (damping
+ * for `radius`, Jacobi scaling as in the first LM iteration) and the inverse the hand-written kernel
+ * (csrc/ba_coarse_inv.cuh) computes from it.  Row-major, *leading_dimension x *leading_dimension doubles each (the
+ * order rounded up to the kernel's block size; the padding block is the identity), the lower triangle of `matrix` is
+ * what the inversion reads.  *order = 0 when the problem has no coarse space.  matrix == NULL: sizes only. */
+int vmm_ba_debug_coarse_matrix(vmm_ba_handle h, int loss_kind, double loss_scale, double radius, int64_t capacity, double* matrix,
+                               double* inverse, int* order, int* leading_dimension);
+
 /* Target number of cameras per cluster of the two-level preconditioner's coarse space (default 192; the
  * coarse matrix is 6 x clusters squared and dense, the library caps it at 256 clusters).  Takes effect at
  * the next vmm_ba_set_problem. */

@@ -302,3 +302,25 @@ def test_marker_translation_covariance_c1_and_limits(oracle):
         ba.set_scene(big)
         with pytest.raises(pkg.VmmBaError, match="limited to 4096 markers"):
             ba.marker_translation_covariance()
+
+
+# ---- coarse level of the two-level preconditioner -------------------------------------------------------------
+@pytest.mark.parametrize("cams_per_cluster", [64, 100, 192])
+def test_coarse_inverse_matches_numpy(cams_per_cluster):
+    """The hand-written in-place inversion of A_c (blocked sweep operator, csrc/ba_coarse_inv.cuh) against
+    numpy.linalg.inv of the matrix the device assembled, for orders that are and are not multiples of its block size."""
+    s = synth.make_config("c3/16")
+    with pkg.BundleAdjuster(0) as ba:
+        ba.set_coarse_cluster_size(cams_per_cluster)
+        ba.set_scene(s)
+        a, inv, n = ba.debug_coarse_matrix(pkg.LOSS_HUBER, 1.0, 1e4)
+    assert n > 0 and n % 6 == 0
+    low = np.tril(a)
+    full = low + np.tril(a, -1).T                       # the kernel reads the lower triangle only
+    assert np.allclose(full[:n, :n], a[:n, :n], rtol=1e-9, atol=1e-9 * np.abs(a).max())    # the assembly is symmetric
+    ref = np.linalg.inv(full)
+    assert np.abs(inv - ref).max() <= 1e-8 * np.abs(ref).max()
+    assert np.allclose(inv, inv.T, rtol=0, atol=1e-12 * np.abs(inv).max())
+    pad = a.shape[0] - n
+    if pad:
+        assert np.array_equal(inv[n:, n:], np.eye(pad)) and not inv[n:, :n].any()

@@ -273,6 +273,11 @@ __global__ void k_identity(int n, double* __restrict__ A) {
     A[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
 }
 
+// identity on the padding diagonal [n, ld) of a square matrix with leading dimension ld
+__global__ void k_pad_identity(int n, int ld, double* __restrict__ A) {
+    for (int i = n + threadIdx.x; i < ld; i += blockDim.x) A[(size_t)i * ld + i] = 1.0;
+}
+
 // m x m identity into a block of a column-major matrix with leading dimension ld
 __global__ void k_identity_block(int m, int ld, double* __restrict__ A) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -324,13 +329,13 @@ k_coarse_restrict(const int* __restrict__ cl_ptr, const int* __restrict__ cl_cam
 
 // yc = Ainv rc (dense symmetric, row-major), one warp per row; dot_acc += rc . yc (the coarse part of r.z)
 __global__ void __launch_bounds__(256)
-k_coarse_apply(int n, const double* __restrict__ Ainv, const double* __restrict__ rc, double* __restrict__ yc,
+k_coarse_apply(int n, int ld, const double* __restrict__ Ainv, const double* __restrict__ rc, double* __restrict__ yc,
                double* __restrict__ dot_acc, double* __restrict__ dot_acc2, const double* __restrict__ done) {
     if (done && *done != 0.0) return;
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     double s = 0.0;
     if (row < n) {
-        const double2* a2 = reinterpret_cast<const double2*>(Ainv + (size_t)row * n);
+        const double2* a2 = reinterpret_cast<const double2*>(Ainv + (size_t)row * ld);
         const double2* x2 = reinterpret_cast<const double2*>(rc);
         for (int k = lane; k < n / 2; k += 32) {
             const double2 a = __ldg(a2 + k), x = __ldg(x2 + k);

@@ -22,6 +22,7 @@
 #include "ba_schur.cuh"
 #include "ba_coarse.cuh"
 #include "ba_pcg.cuh"
+#include "ba_coarse_inv.cuh"
 #include "ba_stage.cuh"
 #include "ba_cov.cuh"
 #include "ba_peer.cuh"
@@ -124,7 +125,9 @@ struct vmm_ba_engine {
     struct Coarse {
         bool available = false;   // clusters exist for this problem
         bool active = false;      // A_c^-1 is valid for the current LM iteration
-        int ncl = 0, nC = 0, lwork = 0;
+        int ncl = 0, nC = 0, ldc = 0 /* nC rounded up to the block order of the inversion kernel */, lwork = 0;
+        DevBuf<double> Pt, Qt;    // panel scratch of k_coarse_sweep_invert
+        DevBuf<unsigned> inv_barrier;
         DevBuf<int> cl_of_cam, cl_ptr, cl_cams, mcl_ptr, mcl, info, d_lists, d_cnt, d_over;
         DevBuf<unsigned char> mo_lc, d_map;
         DevBuf<double> Linv, tmp; // inverse Cholesky factor of A_c and the GEMM scratch of its blocked inversion
@@ -449,52 +452,24 @@ int coarse_correction(vmm_ba_engine* e, double* acc, double* acc2, const double*
         if (!partial_in_tail) LAUNCH(k_pack2, 1, 32, acc, acc2, tail, done);
         int rc = allreduce(e, c.rc.p, (size_t)c.nC + (partial_in_tail ? 1 : 2), NCCL_SUM);
         if (rc) return rc;
-        LAUNCH(k_coarse_apply, (c.nC + 7) / 8, 256, c.nC, c.Ac.p, c.rc.p, c.yc.p, (double*)nullptr, (double*)nullptr, done);
+        LAUNCH(k_coarse_apply, (c.nC + 7) / 8, 256, c.nC, c.ldc, c.Ac.p, c.rc.p, c.yc.p, (double*)nullptr, (double*)nullptr, done);
         LAUNCH(k_coarse_dot, 1, 256, c.nC, c.rc.p, c.yc.p, tail, acc, acc2, done);
         return VMM_BA_OK;
     }
-    LAUNCH(k_coarse_apply, (c.nC + 7) / 8, 256, c.nC, c.Ac.p, c.rc.p, c.yc.p, acc, acc2, done);
+    LAUNCH(k_coarse_apply, (c.nC + 7) / 8, 256, c.nC, c.ldc, c.Ac.p, c.rc.p, c.yc.p, acc, acc2, done);
     return VMM_BA_OK;
 }
 
-// X[off.., off..] = inverse of the lower-triangular block L[off.., off..] of order m (column-major, leading dimension n;
-// X zero outside its lower triangle on entry).  tmp: m/2 x m/2 doubles at least.
-int invert_lower_triangular(vmm_ba_engine* e, const double* L, double* X, double* tmp, int n, int off, int m) {
-    const double one = 1.0, zero = 0.0, minus = -1.0;
-    const double* Ld = L + (size_t)off * n + off;
-    double* Xd = X + (size_t)off * n + off;
-    static const int leaf = std::getenv("VMM_BA_INV_LEAF") ? std::max(64, std::atoi(std::getenv("VMM_BA_INV_LEAF"))) : 256;
-    if (m <= leaf) {
-        LAUNCH(k_identity_block, nblocks((int64_t)m * m, kThreads), kThreads, m, n, Xd);
-        LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, m, m, &one, Ld, n, Xd,
-                                                 n) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
-        return VMM_BA_OK;
-    }
-    const int m1 = ((m / 2 + 63) / 64) * 64, m2 = m - m1;
-    int rc = invert_lower_triangular(e, L, X, tmp, n, off, m1);
-    if (!rc) rc = invert_lower_triangular(e, L, X, tmp, n, off + m1, m2);
-    if (rc) return rc;
-    // T = L21 X11 (m2 x m1), X21 = -X22 T
-    const double* L21 = Ld + m1;
-    const double* X11 = Xd;
-    const double* X22 = Xd + (size_t)m1 * n + m1;
-    double* X21 = Xd + m1;
-    LIBCALL_NAMED("cublasDgemm", cublasDgemm(e->cublas, CUBLAS_OP_N, CUBLAS_OP_N, m2, m1, m1, &one, L21, n, X11, n, &zero, tmp, m2) == CUBLAS_STATUS_SUCCESS,
-                  "cublasDgemm");
-    LIBCALL_NAMED("cublasDgemm", cublasDgemm(e->cublas, CUBLAS_OP_N, CUBLAS_OP_N, m2, m1, m2, &minus, X22, n, tmp, m2, &zero, X21, n) == CUBLAS_STATUS_SUCCESS,
-                  "cublasDgemm");
-    return VMM_BA_OK;
-}
-
-// A_c = P^T S P at the current linearisation and damping, then its inverse (dense: cuSOLVER potrf, blocked triangular
-// inversion with cuBLAS, syrk — plain library calls on a matrix of at most 1536 rows, when the kept inverse has aged).
-int coarse_setup(vmm_ba_engine* e, int slot) {
+// A_c = P^T S P at the current linearisation and damping, then its inverse (dense, in place, hand-written: ba_coarse_inv.cuh),
+// when the kept inverse has aged.
+int coarse_setup(vmm_ba_engine* e, int slot, bool need_host_verdict, double* host_copy_of_matrix = nullptr) {
     auto& c = e->coarse;
     c.active = false;
     if (!c.available) return VMM_BA_OK;
-    const size_t n = (size_t)c.nC;
+    const size_t n = (size_t)c.ldc;   // padded order: the padding block is the identity
     CU(cudaMemsetAsync(c.Ac.p, 0, sizeof(double) * n * n, e->stream));
-    LAUNCH(k_coarse_diag, c.ncl, kCoarseThreads, c.cl_ptr.p, c.cl_cams.p, c.xbar.p, e->camP[slot].p, e->B.p, e->lam_c.p, c.nC, c.Ac.p);
+    if (c.ldc > c.nC) LAUNCH(k_pad_identity, 1, 64, c.nC, c.ldc, c.Ac.p);
+    LAUNCH(k_coarse_diag, c.ncl, kCoarseThreads, c.cl_ptr.p, c.cl_cams.p, c.xbar.p, e->camP[slot].p, e->B.p, e->lam_c.p, c.ldc, c.Ac.p);
     if (c.n_w > 0) {
         if (e->world > 1) CU(cudaMemsetAsync(c.Wbuf.p, 0, sizeof(double) * 36 * c.n_w, e->stream));   // markers without local observations
         LAUNCH(k_coarse_w, (int)e->Nm, kCoarseThreads, e->mptr.p, e->tag_active.p, e->mtile.p, e->mo_cam.p, c.mo_lc.p, c.mcl_ptr.p,
@@ -504,36 +479,39 @@ int coarse_setup(vmm_ba_engine* e, int slot) {
         // the outer products are split over ranks by marker; the parts of A_c (diagonal blocks included) are summed below
         const int mine = (int)((e->Nm - e->rank + e->world - 1) / e->world);
         if (mine > 0)
-            LAUNCH(k_coarse_outer, mine, kCoarseThreads, (int)e->Nm, e->rank, e->world, e->tag_active.p, c.mcl_ptr.p, c.mcl.p, c.Wbuf.p, c.nC, c.Ac.p);
+            LAUNCH(k_coarse_outer, mine, kCoarseThreads, (int)e->Nm, e->rank, e->world, e->tag_active.p, c.mcl_ptr.p, c.mcl.p, c.Wbuf.p, c.ldc, c.Ac.p);
     }
     {
         int rc = allreduce(e, c.Ac.p, n * n, NCCL_SUM);
         if (rc) return rc;
     }
-    if (cusolverDnSetStream(e->cusolver, e->stream) != CUSOLVER_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cusolverDnSetStream failed");
-    LIBCALL_NAMED("cusolverDnDpotrf", cusolverDnDpotrf(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, c.work.p, c.lwork, c.info.p) == CUSOLVER_STATUS_SUCCESS,
-                  "cusolverDnDpotrf");
-    int h_info[2] = { 0, 0 };
-    CU(cudaMemcpyAsync(&h_info[0], c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    // A_c^-1 = L^-T L^-1.  X = L^-1 by recursive blocking, so that the n^3/3 flops run as fp64 tensor-core GEMMs
-    // (cuBLAS) instead of one triangular solve against a dense identity: for L = [L11 0; L21 L22],
-    // X = [X11 0; -X22 L21 X11, X22]; diagonal blocks of <= 256 rows by cublasDtrsm.  Then X^T X (cublasDsyrk).
-    // 0.9 + 0.9 ms at n = 3126 (521 clusters, before the cap at 256), where trsm + syrk took 2.6 + 0.9 and
-    // cusolverDnDpotri 7.8; 0.95 + 0.15 ms at n = 1536.  Replicated on every rank
-    // of a sharded engine (cheaper than solving by column blocks and all-gathering).
-    if (cublasSetStream(e->cublas, e->stream) != CUBLAS_STATUS_SUCCESS) return fail_with(e, VMM_BA_ERR_CUDA, "cublasSetStream failed");
-    const double one = 1.0, zero = 0.0;
-    CU(cudaMemsetAsync(c.Linv.p, 0, sizeof(double) * n * n, e->stream));
-    {
-        int rc = invert_lower_triangular(e, c.Ac.p, c.Linv.p, c.tmp.p, c.nC, 0, c.nC);
-        if (rc) return rc;
+    if (host_copy_of_matrix) {   // test entry: A_c as assembled, before it is overwritten by its inverse
+        CU(cudaMemcpyAsync(host_copy_of_matrix, c.Ac.p, sizeof(double) * n * n, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
     }
-    LIBCALL_NAMED("cublasDsyrk", cublasDsyrk(e->cublas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, c.nC, c.nC, &one, c.Linv.p, c.nC, &zero, c.Ac.p,
-                                             c.nC) == CUBLAS_STATUS_SUCCESS, "cublasDsyrk");
-    LAUNCH(k_symmetrize, nblocks((int64_t)n * n, kThreads), kThreads, c.nC, c.Ac.p);
-    CU(cudaStreamSynchronize(e->stream));
-    if (e->profiling) profile_resolve(e);
-    c.active = (h_info[0] == 0);   // not positive definite: this iteration runs block-Jacobi only
+    // A_c^-1 in place by the blocked sweep operator: one cooperative launch (ba_coarse_inv.cuh), no library call.  A
+    // pivot that is not positive raises c.info on the device; the persistent PCG kernel reads it there and runs
+    // block-Jacobi only for this iteration, so the host does not have to wait for the verdict.
+    CU(cudaMemsetAsync(c.info.p, 0, sizeof(int), e->stream));
+    CU(cudaMemsetAsync(c.inv_barrier.p, 0, 4 * sizeof(unsigned), e->stream));
+    {
+        static const int kid = register_kernel("k_coarse_sweep_invert");
+        cudaEvent_t eb = nullptr;
+        if (e->profiling) eb = profile_begin(e);
+        double* M = c.Ac.p; int nP = c.ldc, ld = c.ldc; double* Pt = c.Pt.p; double* Qt = c.Qt.p; int* info = c.info.p; unsigned* bar = c.inv_barrier.p;
+        void* args[] = { &M, &nP, &ld, &Pt, &Qt, &info, &bar };
+        CU(cudaLaunchCooperativeKernel((const void*)k_coarse_sweep_invert, dim3(e->sp_grid), dim3(kInvThreads), args, kInvSmemBytes, e->stream));
+        if (eb) profile_end(e, kid, eb);
+        ++e->launches;
+    }
+    c.active = true;
+    if (need_host_verdict) {   // the multi-launch PCG loop (sharded engines, split markers) decides on the host
+        int h_info = 0;
+        CU(cudaMemcpyAsync(&h_info, c.info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        if (e->profiling) profile_resolve(e);
+        c.active = (h_info == 0);   // not positive definite: this iteration runs block-Jacobi only
+    }
     return VMM_BA_OK;
 }
 
@@ -595,7 +573,7 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it) {
     a.x = e->px.p; a.r = e->pr.p; a.z = e->pz.p; a.p = e->pp.p; a.q = e->pq.p;
     a.ncl = two_level ? e->coarse.ncl : 0; a.nC = two_level ? e->coarse.nC : 0;
     a.cl_unit_ptr = P.cl_unit_ptr.p; a.xbar = e->coarse.xbar.p; a.camP = e->camP[e->cur].p; a.Ainv = e->coarse.Ac.p;
-    a.rc_part = P.rc_part.p; a.yc = e->coarse.yc.p;
+    a.rc_part = P.rc_part.p; a.yc = e->coarse.yc.p; a.ldc = e->coarse.ldc; a.coarse_info = e->coarse.info.p;
     a.scal = P.scal.p; a.result = e->sc.p; a.barrier = P.barrier.p;
     a.max_it = max_it; a.min_it = min_it; a.tol2 = tol * tol;
     static const int kid = register_kernel("k_pcg_persistent");
@@ -611,13 +589,17 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it) {
 
 struct PcgResult { int iterations; bool ok; double rel; };
 
+bool pcg_persistent_eligible(const vmm_ba_engine* e) {
+    static const bool legacy = std::getenv("VMM_BA_PCG_LEGACY") != nullptr;   // A/B: the five-launches-per-iteration loop of round 1
+    return !legacy && e->world == 1 && e->seg_big.count == 0 && e->pcgp.nunits > 0;
+}
+
 // Solve (B_l - E C_l^-1 E^T) x = r0 (r0 in e->pr on entry). x -> e->px, final residual in e->pr.
 // The stopping test runs on the device (k_pcg_direction raises sc[SC_DONE], which turns every later
 // PCG launch into a no-op); the host only looks every `check_every` iterations.
 int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* out) {
-    static const bool legacy = std::getenv("VMM_BA_PCG_LEGACY") != nullptr;   // A/B: the five-launches-per-iteration loop of round 1
     e->pcg_result_pending = false;
-    if (!legacy && e->world == 1 && e->seg_big.count == 0 && e->pcgp.nunits > 0) {
+    if (pcg_persistent_eligible(e)) {
         out->iterations = 0; out->ok = true; out->rel = 1.0;
         return pcg_solve_persistent(e, tol, max_it, min_it);
     }
@@ -794,7 +776,7 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
             // coarse_refresh_iterations above the first solve after the last refresh) and after a failed factorisation
             const bool stale = !coarse_fresh_known || pcg_last > pcg_fresh + opt->coarse_refresh_iterations;
             if (!e->coarse.active || opt->coarse_refresh_iterations <= 0 || stale) {
-                rc = coarse_setup(e, e->cur);
+                rc = coarse_setup(e, e->cur, !pcg_persistent_eligible(e));
                 if (rc) return rc;
                 coarse_fresh_known = false;
                 coarse_refreshed = true;
@@ -1271,15 +1253,11 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     const size_t n = (size_t)c.nC;
     CU(c.cl_ptr.alloc(ncl + 1)); CU(c.cl_cams.alloc(std::max<size_t>(cl_cams.size(), 1)));
     CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1)));
-    CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(n * n)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
+    c.ldc = (c.nC + kInvNB - 1) / kInvNB * kInvNB;
+    const size_t nP = (size_t)c.ldc;
+    CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(nP * nP)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
+    CU(c.Pt.alloc(nP * kInvNB)); CU(c.Qt.alloc(nP * kInvNB)); CU(c.inv_barrier.alloc(4));
     CU(c.Wbuf.alloc(std::max<size_t>(36 * c.n_w, 1)));
-    CU(c.Linv.alloc(n * n));
-    CU(c.tmp.alloc(std::max<size_t>((n / 2 + 64) * (n / 2 + 64), 1)));
-    int lw1 = 0;
-    if (cusolverDnDpotrf_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, c.nC, c.Ac.p, c.nC, &lw1) != CUSOLVER_STATUS_SUCCESS)
-        return fail_with(e, VMM_BA_ERR_CUDA, "cusolver buffer size query failed");
-    c.lwork = lw1;
-    CU(c.work.alloc(std::max(c.lwork, 1)));
     auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
     CU(up(c.cl_ptr.p, cl_ptr.data(), sizeof(int) * (ncl + 1)));
     CU(up(c.cl_cams.p, cl_cams.data(), sizeof(int) * cl_cams.size()));
@@ -1446,6 +1424,8 @@ static int create_common(int device, vmm_ba_engine** out) {
                            (const void*)k_pcg_persistent })
         if ((err = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmemBytes)) != cudaSuccess)
             return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaFuncSetAttribute(shared memory %zu): %s", kSpSmemBytes, cudaGetErrorString(err));
+    if ((err = cudaFuncSetAttribute((const void*)k_coarse_sweep_invert, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kInvSmemBytes)) != cudaSuccess)
+        return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaFuncSetAttribute(k_coarse_sweep_invert): %s", cudaGetErrorString(err));
     e = new vmm_ba_engine();
     e->device = device;
     e->sp_grid = prop.multiProcessorCount;   // persistent kernel: one CTA per SM
@@ -2084,6 +2064,40 @@ int vmm_ba_schur_multiply(vmm_ba_handle e, int loss_kind, double loss_scale, dou
     }
 #endif
     if (e->profiling) profile_resolve(e);
+    return VMM_BA_OK;
+}
+
+int vmm_ba_debug_coarse_matrix(vmm_ba_handle e, int loss_kind, double loss_scale, double radius, int64_t capacity, double* matrix, double* inverse,
+                               int* order, int* leading_dimension) {
+    if (!e || !order || !leading_dimension) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null argument");
+    if (!e->have_problem || !e->have_intrinsics) return fail_with(e, VMM_BA_ERR_STATE, "set_intrinsics and set_problem must be called first");
+    if (e->world != 1) return fail_with(e, VMM_BA_ERR_STATE, "vmm_ba_debug_coarse_matrix is a single-GPU test entry");
+    *order = e->coarse.available ? e->coarse.nC : 0;
+    *leading_dimension = e->coarse.available ? e->coarse.ldc : 0;
+    if (!e->coarse.available || !matrix || !inverse) return VMM_BA_OK;
+    const int64_t need = (int64_t)e->coarse.ldc * e->coarse.ldc;
+    if (capacity < need) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "buffers must hold %lld doubles", (long long)need);
+    CU(cudaSetDevice(e->device));
+    const int nc = (int)e->Ncl, nm = (int)e->Nm;
+    vmm_ba_options o;
+    vmm_ba_options_init(&o);
+    const int gc_b = nblocks(6 * nc, kThreads), gm_b = nblocks(6 * nm, kThreads);
+    prepare_poses(e, e->cur);
+    int rc = linearize(e, e->cur, loss_kind, loss_scale);
+    if (rc) return rc;
+    LAUNCH(k_jacobi_scale, gc_b, kThreads, 6 * nc, e->hdiag_c.p, e->scale_c.p, 1);
+    LAUNCH(k_jacobi_scale, gm_b, kThreads, 6 * nm, e->hdiag_m.p, e->scale_m.p, 1);
+    LAUNCH(k_lm_diagonal, gc_b, kThreads, 6 * nc, e->hdiag_c.p, e->scale_c.p, o.min_lm_diagonal, o.max_lm_diagonal, e->lmd_c.p);
+    LAUNCH(k_lm_diagonal, gm_b, kThreads, 6 * nm, e->hdiag_m.p, e->scale_m.p, o.min_lm_diagonal, o.max_lm_diagonal, e->lmd_m.p);
+    LAUNCH(k_lambda, gc_b, kThreads, 6 * nc, e->lmd_c.p, e->scale_c.p, radius, e->lam_c.p);
+    LAUNCH(k_lambda, gm_b, kThreads, 6 * nm, e->lmd_m.p, e->scale_m.p, radius, e->lam_m.p);
+    rc = factor_and_scale(e);
+    if (rc) return rc;
+    rc = coarse_setup(e, e->cur, true, matrix);
+    if (rc) return rc;
+    if (!e->coarse.active) return fail_with(e, VMM_BA_ERR_NUMERIC, "the coarse matrix is not positive definite");
+    CU(cudaMemcpyAsync(inverse, e->coarse.Ac.p, sizeof(double) * need, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
     return VMM_BA_OK;
 }
 

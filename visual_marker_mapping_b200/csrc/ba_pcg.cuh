@@ -44,7 +44,8 @@ struct PcgArgs {
     const double* Minv; const double* B; const double* lam;
     double *x, *r, *z, *p, *q;
     // coarse level (ncl == 0: block-Jacobi only)
-    int ncl, nC;
+    int ncl, nC, ldc;         // ldc: leading dimension of Ainv (nC rounded up to the inversion kernel's block order)
+    const int* coarse_info;   // != 0: the inversion of A_c met a non-positive pivot, run block-Jacobi only
     const int* cl_unit_ptr;   // units of cluster c: [cl_unit_ptr[c], cl_unit_ptr[c + 1])
     const double* xbar; const double* camP; const double* Ainv;
     double* rc_part;          // 6 per unit
@@ -223,7 +224,7 @@ __device__ __forceinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_r
     double dot = 0.0;
     const int nwarps = kSpThreads / 32;
     for (int row = blockIdx.x * nwarps + warp; row < A.nC; row += gridDim.x * nwarps) {
-        const double2* a2 = reinterpret_cast<const double2*>(A.Ainv + (size_t)row * A.nC);
+        const double2* a2 = reinterpret_cast<const double2*>(A.Ainv + (size_t)row * A.ldc);
         const double2* x2 = reinterpret_cast<const double2*>(s_rc);
         double s = 0.0;
         for (int k = lane; k < A.nC / 2; k += 32) {
@@ -242,7 +243,9 @@ __device__ __forceinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_r
 }
 
 __global__ void __launch_bounds__(kSpThreads, 1)
-k_pcg_persistent(const PcgArgs A) {
+k_pcg_persistent(const PcgArgs A_in) {
+    PcgArgs A = A_in;
+    if (A.ncl > 0 && __ldcg(A.coarse_info) != 0) A.ncl = 0;   // uniform for the grid
     extern __shared__ __align__(128) unsigned char sp_ring[];
     __shared__ SpShared sh;
     __shared__ double s_v[kSpThreads], s_c[kSpThreads], s_tot[8], s_red[kSpThreads / 32];

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "vmm_ba_create_distributed", "vmm_ba_nccl_unique_id", "vmm_ba_destroy", "vmm_ba_last_error",
     "vmm_ba_set_stream", "vmm_ba_set_intrinsics", "vmm_ba_set_problem", "vmm_ba_set_poses",
     "vmm_ba_get_poses", "vmm_ba_get_step", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
-    "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_schur_multiply", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
+    "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_schur_multiply", "vmm_ba_debug_coarse_matrix", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
     "vmm_ba_kernel_launches", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
     "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
 ]
@@ -133,6 +133,7 @@ def load_library():
     lib.vmm_ba_marker_translation_covariance.argtypes = [C.c_void_p, C.c_int, C.c_double, dp]
     lib.vmm_ba_set_coarse_cluster_size.argtypes = [C.c_void_p, C.c_int]
     lib.vmm_ba_schur_multiply.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, dp, dp]
+    lib.vmm_ba_debug_coarse_matrix.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int64, dp, dp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.vmm_ba_shard_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.vmm_ba_partition_cameras.argtypes = [C.c_int64, C.c_int64, ip, C.c_int, C.POINTER(C.c_int64)]
     lib.vmm_ba_shard_plan.argtypes = [C.c_int64, dp, dp, C.c_int64, C.c_int64, ip, ip, C.c_int, C.c_int, ip, ip]
@@ -328,6 +329,16 @@ class BundleAdjuster:
         y = np.zeros_like(x)
         self._check(self._lib.vmm_ba_schur_multiply(self._h, loss_kind, loss_scale, radius, path, _dp(x), _dp(y)))
         return y
+
+    def debug_coarse_matrix(self, loss_kind=LOSS_NONE, loss_scale=1.0, radius=1e4):
+        """(A_c, A_c^-1 as computed on the device, order) of the two-level preconditioner; (None, None, 0) without a coarse space."""
+        n, ld = C.c_int(0), C.c_int(0)
+        self._check(self._lib.vmm_ba_debug_coarse_matrix(self._h, loss_kind, loss_scale, radius, 0, None, None, C.byref(n), C.byref(ld)))
+        if n.value == 0:
+            return None, None, 0
+        a, inv = np.zeros((ld.value, ld.value)), np.zeros((ld.value, ld.value))
+        self._check(self._lib.vmm_ba_debug_coarse_matrix(self._h, loss_kind, loss_scale, radius, a.size, _dp(a), _dp(inv), C.byref(n), C.byref(ld)))
+        return a, inv, n.value
 
     def set_coarse_cluster_size(self, cameras_per_cluster: int):
         """Target cameras per cluster of the two-level preconditioner (before set_scene)."""
