@@ -62,7 +62,10 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", help="c3 (default), c2, c1 or c3/<divisor>")
-    ap.add_argument("--cpu-sample", default="c3/40", help="bounded CPU sample of the workload")
+    ap.add_argument("--cpu-iters", type=int, default=2, help="LM iterations of the CPU baseline leg of the GPU arm (on the workload itself)")
+    ap.add_argument("--cpu-time-cap", type=float, default=150.0, help="--impl reference: stop after the LM iteration that crosses this many seconds")
+    ap.add_argument("--no-cost-check", action="store_true")
+    ap.add_argument("--no-c2-pair", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--rj-iters", type=int, default=10)
@@ -135,69 +138,83 @@ def workload_description(scene, name):
 # oracle/vmm_oracle.cpp ("port": the reference itself needs Ceres/Eigen/OpenCV/Boost and cannot be
 # built on this image), on all host cores, on a bounded sample of the workload.
 # --------------------------------------------------------------------------------------------------
-def cpu_lm_sample(sample_name: str, full_corners: int, max_iters: int):
-    from oracle import oracle
-    from visual_marker_mapping_b200 import synth
+def host_cores() -> int:
+    """Cores this process may use.  torchrun exports OMP_NUM_THREADS=1 to its ranks: the CPU legs ask for every core
+    explicitly (oracle.set_num_threads) instead of inheriting that."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
-    s = synth.make_config(sample_name)
+
+CPU_SOLVER_NOTE = ("oracle/vmm_oracle.cpp: dual-number Jacobians, Ceres-semantics LM, exact sparse solve (cameras eliminated, block-envelope "
+                   "Cholesky of the marker system in reverse Cuthill-McKee order; own 96x96 blocked AVX2 kernel + OpenMP, not BLAS / SuiteSparse)")
+
+
+def cpu_lm_run(scene, name: str, max_iters: int, time_cap_s: float):
+    """The reference algorithm on the host cores ON THE GIVEN SCENE ITSELF (no sub-sampling, no extrapolation): LM
+    iterations until max_iters, convergence or the time cap (checked once per iteration, like Ceres' max_solver_time)."""
+    from oracle import oracle
+
+    oracle.set_num_threads(host_cores())
     t0 = time.perf_counter()
-    r = oracle.solve(s, max_num_iterations=max_iters, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+    r = oracle.solve(scene, max_num_iterations=max_iters, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0, max_solver_time_s=time_cap_s)
     dt = time.perf_counter() - t0
     its = max(1, r.summary.num_iterations - 1)
-    its_per_s_sample = its / dt
-    scale = s.n_corners / float(full_corners)          # linear-in-corners extrapolation (favours the CPU:
-    return {                                            # its exact factorisation grows super-linearly)
-        "value": its_per_s_sample * scale,
-        "unit": UNIT,
-        "cores": oracle.num_threads(),
-        "kind": "port",
-        "sample": f"{sample_name} ({s.n_markers} markers, {s.n_cameras} cameras, {s.n_corners} corners): {its} LM iterations in "
-                  f"{dt:.2f} s = {its_per_s_sample:.3f} it/s on the sample, scaled by corners {s.n_corners}/{full_corners}",
-        "final_cost": r.summary.final_cost,
-    }, s
+    return {
+        "value": its / dt, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port", "same_config": True,
+        "sample": f"{name} full scene ({scene.n_markers} markers, {scene.n_cameras} cameras, {scene.n_corners} corners): {its} LM iterations in {dt:.2f} s "
+                  f"(iteration cap {max_iters}, time cap {time_cap_s:.0f} s; {r.summary.message.decode()})",
+        "lm_iterations": its, "seconds": dt, "t_linear_solver_s": r.summary.time_linear_solver_s, "t_evaluate_s": r.summary.time_evaluate_s,
+        "initial_cost": r.summary.initial_cost, "cost_after": r.summary.final_cost, "cost_trace": [float(c) for c in r.trace[:, 0]],
+        "solver": CPU_SOLVER_NOTE,
+    }
 
 
 def cpu_rj_sample(scene, reps: int = 3):
     from oracle import oracle
 
+    oracle.set_num_threads(host_cores())
     oracle.evaluate(scene, oracle.LOSS_HUBER, 1.0, gradient=False)
     t0 = time.perf_counter()
     for _ in range(reps):
         oracle.evaluate(scene, oracle.LOSS_HUBER, 1.0, gradient=False)
     dt = (time.perf_counter() - t0) / reps
-    return {"value": scene.n_corners / dt, "unit": "corner evaluations/s", "cores": oracle.num_threads(), "kind": "port",
-            "sample": f"{scene.n_corners} corners, dual-number residual+Jacobian, {reps} passes"}
+    return {"value": scene.n_corners / dt, "unit": "corner evaluations/s", "cores": oracle.num_threads(), "kind": "port", "same_config": True,
+            "sample": f"all {scene.n_corners} corners of the workload, dual-number residual+Jacobian, {reps} passes"}
+
+
+def job_config(scene, name, world):
+    return {**workload_description(scene, name), "parallelism": f"camera shards x{world}, markers replicated"}
 
 
 def run_reference(args):
-    """--impl reference: the reference algorithm on the host cores (rank 0 only)."""
+    """--impl reference: the reference algorithm on the host cores, on the workload itself (rank 0 only)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    from oracle import oracle
     from visual_marker_mapping_b200 import synth
 
-    if args.workload == "c3":
-        full_corners = 4 * 100000 * 40    # nominal C3 size; generating it is not needed on this arm
-        wl = {"workload": "c3: 20000 markers, 100000 cameras, ~16M corners, radial-tangential distortion, Huber(1.0), fp64"}
-    else:
-        sc = synth.make_config(args.workload)
-        full_corners = sc.n_corners
-        wl = workload_description(sc, args.workload)
-    sample = args.cpu_sample if args.workload == "c3" else args.workload
-    # warm-up: thread pool + page faults
-    cpu_lm_sample("c1", 1656, 3)
+    scene = synth.make_config(args.workload)
+    oracle.set_num_threads(host_cores())
+    oracle.solve(synth.make_config("c1"), max_num_iterations=3, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)   # warm-up: thread pool
     t0 = time.perf_counter()
-    base, s = cpu_lm_sample(sample, full_corners, max(1, args.steps))
+    base = cpu_lm_run(scene, args.workload, max(1, args.steps), args.cpu_time_cap)
     wall = time.perf_counter() - t0
-    rj = cpu_rj_sample(s)
+    rj = cpu_rj_sample(scene, reps=2)
     line = {
-        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 / base["value"], "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": wl,
-        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": base["lm_iterations"],
+        "steps_requested": args.steps, "warmup": 0, "ms_per_step": 1e3 / base["value"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": job_config(scene, args.workload, args.gpus),
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "same_config", "solver")},
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "rj": {"value": rj["value"], "unit": rj["unit"], "sample": rj["sample"]},
+        "rj": {"value": rj["value"], "unit": rj["unit"], "sample": rj["sample"], "cores": rj["cores"]},
+        "solve": {"initial_cost": base["initial_cost"], "cost_after": base["cost_after"], "cost_trace": base["cost_trace"],
+                  "t_linear_solver_s": base["t_linear_solver_s"], "t_evaluate_s": base["t_evaluate_s"]},
         "gpu_launches": 0, "wall_s": wall,
+        "note": "steps = LM iterations actually run and timed on the workload itself (the first solve of the scene, stopped by the iteration "
+                "cap --steps, convergence or the time cap --cpu-time-cap); no warm-up steps are discarded (iteration 0's evaluation is inside the time)",
     }
     print(json.dumps(line), flush=True)
 
@@ -293,9 +310,10 @@ def run_b200(args):
 
     # ---- the same K steps with per-kernel CUDA events (roofline of the dominant kernel) ----
     ba.profile_enable(True)
-    ms_prof, _ = timed(lambda: lm_steps(args.steps))
+    ms_prof, sums_prof = timed(lambda: lm_steps(args.steps))
     prof = ba.profile()
     ba.profile_enable(False)
+    pcg_its_prof = int(sum(s.pcg_iterations for s in sums_prof))
 
     # ---- end to end through the C ABI from host buffers ----
     e2e = None
@@ -338,31 +356,98 @@ def run_b200(args):
             if name in KERNEL_BYTES_PER_TAG_OBS:
                 gbs = KERNEL_BYTES_PER_TAG_OBS[name] * ntol / (ms / n * 1e-3) / 1e9
                 ent.update({"gbs": gbs, "frac_hbm": gbs / peak})
+            elif name == "k_pcg_persistent":
+                # one launch = one whole PCG solve: every iteration streams the scaled E blocks once (292 B per tag observation);
+                # the grid barriers, the vector updates and the coarse mat-vec of each iteration are inside the measured time
+                per_launch = KERNEL_BYTES_PER_TAG_OBS["k_schur_product<SP_FULL>"] * ntol * pcg_its_prof / max(n, 1)
+                gbs = per_launch / (ms / n * 1e-3) / 1e9
+                ent.update({"gbs": gbs, "frac_hbm": gbs / peak, "pcg_iterations": pcg_its_prof, "ms_per_pcg_iteration": ms / max(pcg_its_prof, 1),
+                            "algorithmic_bytes_per_launch": per_launch})
             kernels[name] = ent
-        if top and top[0] in KERNEL_BYTES_PER_TAG_OBS:
+        if top and "gbs" in kernels[top[0]]:
             k = kernels[top[0]]
+            per_obs = KERNEL_BYTES_PER_TAG_OBS.get(top[0], KERNEL_BYTES_PER_TAG_OBS["k_schur_product<SP_FULL>"])
             roofline = {"bound": "hbm", "achieved": k["gbs"], "peak": peak, "unit": "GB/s", "frac": k["frac_hbm"],
                         "traffic": NCU_TRAFFIC_BYTES_C3.get(top[0]) if (args.workload == "c3" and world == 1) else None,
-                        "algorithmic_bytes": KERNEL_BYTES_PER_TAG_OBS[top[0]] * ntol,
-                        "kernel": top[0], "bytes_per_tag_obs": KERNEL_BYTES_PER_TAG_OBS[top[0]], "peak_source": peak_src,
-                        "share_of_step": k["share"]}
+                        "algorithmic_bytes": k.get("algorithmic_bytes_per_launch", per_obs * ntol),
+                        "kernel": top[0], "bytes_per_tag_obs": per_obs, "peak_source": peak_src, "share_of_step": k["share"],
+                        "launch_ms": k["ms_avg"]}
+            if top[0] == "k_pcg_persistent":
+                roofline["note"] = ("one launch = one PCG solve of %.1f iterations on average; per iteration 292 B per tag observation are streamed once; "
+                                    "traffic (ncu) is per launch of the captured solve" % (pcg_its_prof / max(k["launches"], 1)))
+            roofline["rj"] = rj
+        # ---- cost check (north_star: the solve reaches the reference's cost): default-tolerance solve, both modes at
+        #      function_tolerance 1e-12, and the oracle's exact-Cholesky solve of the same scene (committed fixture) ----
+        cost_check = None
+        if not args.no_cost_check and world == 1:
+            cost_check = {}
+            for label, kw in (("default", {}), ("parity_ftol_1e-12", dict(parity_mode=1, function_tolerance=1e-12)),
+                              ("product_ftol_1e-12", dict(function_tolerance=1e-12))):
+                ba.set_poses(*init)
+                sc = ba.solve(max_num_iterations=200, **opts, **kw)
+                cost_check[label] = {"final_cost": sc.final_cost, "lm_iterations": sc.num_iterations, "pcg_iterations": int(sc.pcg_iterations),
+                                     "confirmations": sc.num_confirmations, "termination": sc.message.decode()}
+            gpath = os.path.join(ROOT, "tests", "golden", args.workload.replace("/", "_") + "_oracle_solve.json")
+            if os.path.exists(gpath):
+                with open(gpath) as f:
+                    g = json.load(f)
+                cost_check["oracle_exact_solve"] = {"final_cost": g["summary"]["final_cost"], "lm_iterations": g["summary"]["num_iterations"] - 1,
+                                                    "source": "tests/golden/" + os.path.basename(gpath)}
+                cost_check["default_vs_oracle_rel"] = abs(cost_check["default"]["final_cost"] - g["summary"]["final_cost"]) / g["summary"]["final_cost"]
+            tight = cost_check["parity_ftol_1e-12"]["final_cost"]
+            cost_check["default_vs_tight_rel"] = (cost_check["default"]["final_cost"] - tight) / tight
+            cost_check["product_tight_vs_parity_tight_rel"] = (cost_check["product_ftol_1e-12"]["final_cost"] - tight) / tight
         cpu = None
         if not args.no_cpu_baseline and world == 1:
-            sample = args.cpu_sample if args.workload == "c3" else args.workload
-            cpu, s_cpu = cpu_lm_sample(sample, scene.n_corners, 8)
-            cpu["rj"] = cpu_rj_sample(s_cpu)
+            # the reference algorithm on this box's host cores, ON THE WORKLOAD ITSELF: a capped number of LM iterations
+            cpu = cpu_lm_run(scene, args.workload, args.cpu_iters, 1e9)
+            cpu["rj"] = cpu_rj_sample(scene)
+            cpu["gpu_over_cpu"] = {"value": value / cpu["value"], "e2e": (e2e["value"] / cpu["value"]) if e2e else None,
+                                   "rj": rj["value"] / cpu["rj"]["value"], "same_config": True}
+            if not args.no_c2_pair and args.workload != "c2":
+                # a second pair where BOTH arms run the whole solve to convergence: C2 (BASELINE.json configs[1])
+                from oracle import oracle
+                c2 = synth.make_config("c2")
+                t0 = time.perf_counter()
+                oc = oracle.solve(c2, max_num_iterations=50, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+                t_cpu = time.perf_counter() - t0
+                hc2 = {k: pinned(getattr(c2, k), np.int32 if k in ("to_cam", "to_tag") else np.float64)
+                       for k in ("cam_q", "cam_t", "tag_q", "tag_t", "tag_wh", "to_cam", "to_tag", "to_uv")}
+
+                def c2_solve():
+                    ba.set_problem(hc2["cam_q"], hc2["cam_t"], hc2["tag_q"], hc2["tag_t"], hc2["tag_wh"], c2.fixed_tag, hc2["to_cam"], hc2["to_tag"], hc2["to_uv"])
+                    sg = ba.solve(max_num_iterations=50, **opts)
+                    ba.get_poses()
+                    return sg
+                c2_solve()
+                t0 = time.perf_counter()
+                torch.cuda.synchronize()
+                sg = c2_solve()
+                torch.cuda.synchronize()
+                t_gpu = time.perf_counter() - t0
+                cpu["c2_full_solve_pair"] = {
+                    "workload": workload_description(c2, "c2")["workload"], "same_config": True,
+                    "cpu": {"lm_iterations": oc.summary.num_iterations - 1, "seconds": t_cpu, "value": (oc.summary.num_iterations - 1) / t_cpu,
+                            "final_cost": oc.summary.final_cost, "cores": oracle.num_threads()},
+                    "gpu_e2e": {"lm_iterations": sg.num_iterations, "seconds": t_gpu, "value": sg.num_iterations / t_gpu, "final_cost": sg.final_cost,
+                                "note": "host buffers -> vmm_ba_set_problem -> vmm_ba_solve -> vmm_ba_get_poses, wall clock"},
+                    "unit": UNIT, "final_cost_rel_diff": abs(sg.final_cost - oc.summary.final_cost) / oc.summary.final_cost,
+                    "time_to_solution_ratio": t_cpu / t_gpu}
         s0 = sums[0]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": {**workload_description(scene, args.workload), "parallelism": f"camera shards x{world}, markers replicated"},
+            "data": "synthetic", "config": job_config(scene, args.workload, world),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks.summary(),
             "rj": rj, "kernels": kernels,
             "solve": {"solves_in_timed_region": len(sums), "first_solve": {"iterations": s0.num_iterations, "initial_cost": s0.initial_cost,
                       "final_cost": s0.final_cost, "pcg_iterations": int(s0.pcg_iterations), "termination": s0.message.decode(),
                       "t_linearize_s": s0.time_linearize_s, "t_linear_solver_s": s0.time_linear_solver_s, "t_cost_s": s0.time_cost_eval_s}},
             "profiled_pass_ms_per_step": ms_prof / args.steps,
+            "fp64_peak_note": "FP64 fractions anywhere in this repo are against a builder-measured DFMA rate (vmm_ba_measure_fp64_peak, 34.3 TFLOP/s); "
+                              "MEASURED_PEAKS.json has no FP64 entry",
         }
+        line["solve"]["cost_check"] = cost_check
         print(json.dumps(line), flush=True)
     ba.close()
     if world > 1:

@@ -65,24 +65,34 @@ __device__ __forceinline__ bool grid_barrier(unsigned* bar, unsigned nblocks) {
     __shared__ int s_abort;
     __syncthreads();
     if (threadIdx.x == 0) {
-        volatile unsigned* gen = bar + 1;
-        volatile unsigned* abort_flag = bar + 2;
-        const unsigned g = *gen;
-        int ab = *abort_flag != 0;
-        __threadfence();
-        if (atomicAdd(bar, 1u) == nblocks - 1) {
-            bar[0] = 0;
-            __threadfence();
-            atomicAdd(bar + 1, 1u);
+        // release / acquire at gpu scope on the two words instead of three sequentially consistent fences: the CTA's
+        // writes (ordered before this thread by the bar.sync above) are released by the arriving atomic, the last
+        // arrival releases the new generation, the waiters acquire it.
+        unsigned g, old, cur, ab;
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(bar + 1) : "memory");
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(ab) : "l"(bar + 2) : "memory");
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(bar) : "memory");
+        if (old == nblocks - 1) {
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(bar), "r"(0u) : "memory");
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(bar + 1), "r"(g + 1) : "memory");
         } else {
-            long long t0 = clock64();
-            while (*gen == g) {
-                if (*abort_flag != 0) { ab = 1; break; }
-                if (clock64() - t0 > 4000000000LL) { *abort_flag = 1; ab = 1; break; }
-            }
+            const long long t0 = clock64();
+            unsigned spins = 0;
+            do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(cur) : "l"(bar + 1) : "memory");
+                if (cur != g) break;
+                if ((++spins & 1023u) == 0) {
+                    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(ab) : "l"(bar + 2) : "memory");
+                    if (ab) break;
+                    if (clock64() - t0 > 4000000000LL) {
+                        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(bar + 2), "r"(1u) : "memory");
+                        ab = 1;
+                        break;
+                    }
+                }
+            } while (true);
         }
-        __threadfence();
-        s_abort = ab;
+        s_abort = (int)ab;
     }
     __syncthreads();
     return s_abort == 0;
