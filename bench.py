@@ -321,14 +321,16 @@ def run_b200(args):
         host = {k: pinned(getattr(scene, k), np.int32 if k in ("to_cam", "to_tag") else np.float64)
                 for k in ("cam_q", "cam_t", "tag_q", "tag_t", "tag_wh", "to_cam", "to_tag", "to_uv")}
         lm_steps(1, e2e=True)
+        b0 = ba.h2d_bytes()
         ms_e2e, sums_e = timed(lambda: lm_steps(args.steps, e2e=True))
         ncalls = len(sums_e)
         a0, a1, ntol = ba.shard_info()
-        h2d = ncalls * (scene.n_tag_obs * (64 + 8) + (a1 - a0) * 56 + scene.n_markers * (56 + 16)) / args.steps
+        h2d = (ba.h2d_bytes() - b0) / args.steps        # counted by the library from the copies it issues
         d2h = ncalls * ((a1 - a0) * 56 + scene.n_markers * 56) / args.steps
         e2e = {"value": 1e3 / (ms_e2e / args.steps), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-               "solves": ncalls, "note": "vmm_ba_set_problem (H2D of the caller's arrays from pinned host memory, device-side sorts, host-side "
-                       "cluster/segment set-up) + vmm_ba_solve + vmm_ba_get_poses per solve"}
+               "solves": ncalls, "note": "per solve: vmm_ba_set_problem from pinned host buffers (the structure of the problem equals the previous "
+                       "call's, so the library keeps its plans and copies this rank's observations, marker sizes and poses) + vmm_ba_solve + "
+                       "vmm_ba_get_poses; VMM_BA_NO_PLAN_CACHE=1 rebuilds everything per call"}
 
     # ---- residual+Jacobian materialising pass (HBM roofline kernel) ----
     ba.set_poses(*init)

@@ -166,6 +166,11 @@ int vmm_ba_set_problem(vmm_ba_handle h, int64_t num_cameras, const double* cam_q
                        int64_t fixed_tag_index, int64_t num_tag_obs, const int32_t* to_cam, const int32_t* to_tag,
                        const double* to_uv);
 
+/* Bytes copied host -> device by this handle's set_problem / set_poses calls so far (bench.py: h2d_bytes_per_step).  A
+ * vmm_ba_set_problem call whose sizes and index arrays equal the previous call's keeps every derived plan (device orders,
+ * segment lists, camera clusters, shards) and copies only this rank's observations, the marker sizes and the poses. */
+int64_t vmm_ba_h2d_bytes(vmm_ba_handle h);
+
 /* Overwrite the current poses (same sizes as in set_problem). */
 int vmm_ba_set_poses(vmm_ba_handle h, const double* cam_q, const double* cam_t, const double* tag_q,
                      const double* tag_t);

@@ -324,3 +324,38 @@ def test_coarse_inverse_matches_numpy(cams_per_cluster):
     pad = a.shape[0] - n
     if pad:
         assert np.array_equal(inv[n:, n:], np.eye(pad)) and not inv[n:, :n].any()
+
+
+@pytest.mark.parametrize("shuffle", [False, True])
+def test_set_problem_with_unchanged_structure_refreshes_observations_and_poses(scene_c2, oracle, shuffle):
+    """A second vmm_ba_set_problem with the same sizes and index arrays keeps the plans and copies only observations,
+    marker sizes and poses (straight from a camera-sorted input, through the cached permutation otherwise): the
+    evaluation must be that of the NEW data, and a changed index array must rebuild."""
+    s = scene_c2.copy()
+    if shuffle:
+        perm = np.random.default_rng(3).permutation(s.n_tag_obs)
+        s.to_cam, s.to_tag, s.to_uv = s.to_cam[perm], s.to_tag[perm], s.to_uv[perm]
+    rng = np.random.default_rng(4)
+    s2 = s.copy()
+    s2.to_uv = s.to_uv + rng.normal(scale=0.7, size=s.to_uv.shape)
+    s2.cam_t = s.cam_t + rng.normal(scale=0.01, size=s.cam_t.shape)
+    s2.tag_t = s.tag_t + rng.normal(scale=0.01, size=s.tag_t.shape)
+    s2.tag_wh = s.tag_wh * 1.01
+    with pkg.BundleAdjuster(0) as ba:
+        ba.set_scene(s)
+        b0 = ba.h2d_bytes()
+        ba.set_scene(s2)                                   # same structure: refresh
+        assert ba.h2d_bytes() - b0 < s.n_tag_obs * 72      # no index arrays travelled
+        ev = ba.evaluate(pkg.LOSS_HUBER, 1.0)
+        ref = oracle.evaluate(s2, oracle.LOSS_HUBER, 1.0)
+        assert block_rel_err(ev.residuals, ref.residuals) < RJ_TOL and block_rel_err(ev.jacobians, ref.jac_local) < RJ_TOL
+        assert np.abs(ev.gradient - ref.gradient).max() / max(np.abs(ref.gradient).max(), 1.0) < 1e-11
+        summ = ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, parity_mode=1)
+        oref = oracle.solve(s2, max_num_iterations=50, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+        assert abs(summ.final_cost - oref.summary.final_cost) <= COST_TOL * oref.summary.final_cost
+        s3 = s2.copy()
+        s3.to_tag = s2.to_tag.copy()
+        s3.to_tag[5] = (s3.to_tag[5] + 1) % s3.n_markers   # one index differs: everything is rebuilt
+        ba.set_scene(s3)
+        ev3 = ba.evaluate(pkg.LOSS_NONE, 1.0, jacobians=False, gradient=False)
+        assert abs(ev3.cost - oracle.evaluate(s3, oracle.LOSS_NONE, 1.0, jac_local=False, gradient=False).cost) <= 1e-12 * ev3.cost

@@ -159,6 +159,13 @@ struct vmm_ba_engine {
         bool with_clusters = false;
     } pcgp;
     bool pcg_result_pending = false;
+    // structure of the last problem (sizes + hashes of the index arrays): a vmm_ba_set_problem call with the same structure
+    // keeps every derived plan and only refreshes observations and poses
+    struct ProblemKey { int64_t Nc = -1, Nm = -1, Nto = -1, fixed = -2; uint64_t h_cam = 0, h_tag = 0; } key;
+    bool perm_identity = false;     // the caller's observation order IS the device's camera order (one GPU, sorted input)
+    double* h_uv_stage = nullptr;   // pinned staging of this rank's observations in camera order
+    size_t h_uv_stage_cap = 0;
+    int64_t h2d_bytes = 0;          // bytes copied host -> device by set_problem / set_poses
     double* h_st = nullptr;   // pinned mirror of st (64) + sc (8)
     int* h_fail = nullptr;
     int n_cost_blocks = 0, n_lin_blocks = 0;
@@ -1358,6 +1365,68 @@ void peer_setup(vmm_ba_engine* e) {
 }
 }  // namespace
 
+namespace {
+// 64-bit hash of an int32 array, chunked over the host threads (chunk hashes combined in order)
+uint64_t hash_i32(const int32_t* a, int64_t n) {
+    const int T = n >= (1 << 18) ? host_threads() : 1;
+    std::vector<uint64_t> part(T, 0);
+    parallel_chunks(T, [&](int c, int chunks) {
+        uint64_t h = 0x9E3779B97F4A7C15ull ^ (uint64_t)c;
+        const int64_t k0 = n * c / chunks, k1 = n * (c + 1) / chunks;
+        for (int64_t k = k0; k < k1; ++k) {
+            h ^= (uint64_t)(uint32_t)a[k] + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+            h *= 0xFF51AFD7ED558CCDull;
+        }
+        part[c] = h;
+    });
+    uint64_t h = (uint64_t)n;
+    for (int c = 0; c < T; ++c) h = (h ^ part[c]) * 0xC4CEB9FE1A85EC53ull + 0x632BE59BD9B4E019ull;
+    return h;
+}
+
+// vmm_ba_set_problem with the structure of the previous call (same sizes, same index arrays): observations, marker
+// sizes and poses are refreshed, every derived plan (both device orders, segment lists, clusters, PCG units, shards)
+// is kept.  Each rank copies only ITS observations to the device: straight from the caller's array when that already
+// is the device's camera order (one GPU, input sorted by camera), else gathered on the host through the cached
+// permutation into a pinned staging buffer.
+int refresh_problem(vmm_ba_engine* e, const double* cam_q, const double* cam_t, const double* tag_q, const double* tag_t, const double* tag_wh,
+                    const double* to_uv) {
+    const int64_t Ntol = e->Ntol, Ncl = e->Ncl, Nm = e->Nm;
+    if (Ntol > 0) {
+        const double* src = to_uv;
+        if (!e->perm_identity) {
+            int rc = ensure_host_perm(e);
+            if (rc) return rc;
+            const size_t need = (size_t)Ntol * 8;
+            if (e->h_uv_stage_cap < need) {
+                if (e->h_uv_stage) cudaFreeHost(e->h_uv_stage);
+                e->h_uv_stage = nullptr; e->h_uv_stage_cap = 0;
+                CU(cudaMallocHost(&e->h_uv_stage, need * sizeof(double)));
+                e->h_uv_stage_cap = need;
+            }
+            double* dst = e->h_uv_stage;
+            const int* perm = e->perm_c.data();
+            parallel_chunks(Ntol >= (1 << 16) ? host_threads() : 1, [&](int c, int chunks) {
+                for (int64_t s = Ntol * c / chunks; s < Ntol * (c + 1) / chunks; ++s) std::memcpy(dst + 8 * s, to_uv + 8 * (size_t)perm[s], 64);
+            });
+            src = dst;
+        }
+        CU(cudaMemcpyAsync(e->uv.p, src, sizeof(double) * 8 * Ntol, cudaMemcpyHostToDevice, e->stream));
+        e->h2d_bytes += 64 * Ntol;
+        LAUNCH(k_stage_marker_order, nblocks(4 * Ntol, kThreads), kThreads, Ntol, e->mperm.p, e->ocam.p, e->uv.p, e->uv_stride, e->mo_cam.p, e->uvm.p,
+               e->cpos.p);
+    }
+    CU(cudaMemcpyAsync(e->tag_wh.p, tag_wh, sizeof(double) * 2 * Nm, cudaMemcpyHostToDevice, e->stream));
+    e->h2d_bytes += 16 * Nm;
+    e->cur = 0;
+    e->have_step = false;
+    e->coarse.active = false;
+    e->have_problem = true;
+    (void)Ncl;
+    return vmm_ba_set_poses(e, cam_q, cam_t, tag_q, tag_t);   // permutes the cameras of a sharded engine, synchronises
+}
+}  // namespace
+
 // =====================================================================================
 // C ABI
 // =====================================================================================
@@ -1507,6 +1576,7 @@ int vmm_ba_destroy(vmm_ba_handle e) {
     for (auto& ev : e->prof_free) cudaEventDestroy(ev);
     if (e->h_st) cudaFreeHost(e->h_st);
     if (e->h_fail) cudaFreeHost(e->h_fail);
+    if (e->h_uv_stage) cudaFreeHost(e->h_uv_stage);
     if (e->own_stream) cudaStreamDestroy(e->own_stream);
     delete e;
     return VMM_BA_OK;
@@ -1576,7 +1646,15 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     if (Nc > (int64_t)1 << 28 || Nm > (int64_t)1 << 28 || Nto > (int64_t)1 << 28)
         return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "problem too large for 32-bit block indices");
     CU(cudaSetDevice(e->device));
+    static const bool no_cache = std::getenv("VMM_BA_NO_PLAN_CACHE") != nullptr;   // A/B: rebuild every plan on every call
+    vmm_ba_engine::ProblemKey key;
+    key.Nc = Nc; key.Nm = Nm; key.Nto = Nto; key.fixed = fixed_tag;
+    key.h_cam = hash_i32(to_cam, Nto); key.h_tag = hash_i32(to_tag, Nto);
+    if (!no_cache && e->have_problem && key.Nc == e->key.Nc && key.Nm == e->key.Nm && key.Nto == e->key.Nto && key.fixed == e->key.fixed &&
+        key.h_cam == e->key.h_cam && key.h_tag == e->key.h_tag)
+        return refresh_problem(e, cam_q, cam_t, tag_q, tag_t, tag_wh, to_uv);
     e->have_problem = false;
+    e->key = vmm_ba_engine::ProblemKey();
     const bool timing = std::getenv("VMM_BA_TIMING") != nullptr;
     auto t_phase = std::chrono::steady_clock::now();
     auto phase = [&](const char* what) {
@@ -1791,8 +1869,13 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(up(e->tag_t[0].p, tag_t, sizeof(double) * 3 * Nm));
     CU(cudaStreamSynchronize(e->stream));   // host staging vectors go out of scope
     e->have_problem = true;
+    e->key = key;
+    e->perm_identity = sorted && e->world == 1;
+    e->h2d_bytes += Nto * (64 + 8) + Ncl * 56 + Nm * (56 + 16);
     return VMM_BA_OK;
 }
+
+int64_t vmm_ba_h2d_bytes(vmm_ba_handle e) { return e ? e->h2d_bytes : 0; }
 
 int vmm_ba_set_poses(vmm_ba_handle e, const double* cam_q, const double* cam_t, const double* tag_q, const double* tag_t) {
     if (!e) return VMM_BA_ERR_INVALID_ARGUMENT;
@@ -1817,6 +1900,7 @@ int vmm_ba_set_poses(vmm_ba_handle e, const double* cam_q, const double* cam_t, 
     CU(cudaMemcpyAsync(e->tag_q[s].p, tag_q, sizeof(double) * 4 * e->Nm, cudaMemcpyHostToDevice, e->stream));
     CU(cudaMemcpyAsync(e->tag_t[s].p, tag_t, sizeof(double) * 3 * e->Nm, cudaMemcpyHostToDevice, e->stream));
     CU(cudaStreamSynchronize(e->stream));
+    e->h2d_bytes += 56 * (e->Ncl + e->Nm);
     return VMM_BA_OK;
 }
 

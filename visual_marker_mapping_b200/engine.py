@@ -26,7 +26,7 @@ ABI_SYMBOLS = [
     "vmm_ba_set_stream", "vmm_ba_set_intrinsics", "vmm_ba_set_problem", "vmm_ba_set_poses",
     "vmm_ba_get_poses", "vmm_ba_get_step", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
     "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_schur_multiply", "vmm_ba_debug_coarse_matrix", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
-    "vmm_ba_kernel_launches", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
+    "vmm_ba_kernel_launches", "vmm_ba_h2d_bytes", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
     "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
 ]
 
@@ -116,6 +116,8 @@ def load_library():
     lib.vmm_ba_last_error.argtypes = [C.c_void_p]
     lib.vmm_ba_kernel_launches.restype = C.c_int64
     lib.vmm_ba_kernel_launches.argtypes = [C.c_void_p]
+    lib.vmm_ba_h2d_bytes.restype = C.c_int64
+    lib.vmm_ba_h2d_bytes.argtypes = [C.c_void_p]
     lib.vmm_ba_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
     lib.vmm_ba_create_distributed.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
     lib.vmm_ba_destroy.argtypes = [C.c_void_p]
@@ -348,6 +350,9 @@ class BundleAdjuster:
         a, b, n = C.c_int64(0), C.c_int64(0), C.c_int64(0)
         self._check(self._lib.vmm_ba_shard_info(self._h, C.byref(a), C.byref(b), C.byref(n)))
         return a.value, b.value, n.value
+
+    def h2d_bytes(self) -> int:
+        return int(self._lib.vmm_ba_h2d_bytes(self._h))
 
     def kernel_launches(self) -> int:
         return int(self._lib.vmm_ba_kernel_launches(self._h))
