@@ -22,6 +22,7 @@
 #include "ba_schur.cuh"
 #include "ba_coarse.cuh"
 #include "ba_pcg.cuh"
+#include "ba_pcg_dist.cuh"
 #include "ba_coarse_inv.cuh"
 #include "ba_stage.cuh"
 #include "ba_cov.cuh"
@@ -77,6 +78,12 @@ struct vmm_ba_engine {
     PeerView peer{};
     uint4* peer_own = nullptr;
     uint32_t peer_seq = 0;
+    // in-kernel exchanges of the persistent PCG (ba_pcg_dist.cuh): own buffer, own sequence space (device resident)
+    bool pcgx_ok = false;
+    uint4* pcgx_own = nullptr;
+    uint4* pcgx_buf[kPeerMaxWorld] = { nullptr };
+    DevBuf<unsigned> pcgx_seq;
+    DevBuf<double> wbl, cta_part;
     std::string last_error;
     int64_t launches = 0;
 
@@ -583,12 +590,37 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it) {
     a.rc_part = P.rc_part.p; a.yc = e->coarse.yc.p; a.ldc = e->coarse.ldc; a.coarse_info = e->coarse.info.p;
     a.scal = P.scal.p; a.result = e->sc.p; a.barrier = P.barrier.p;
     a.max_it = max_it; a.min_it = min_it; a.tol2 = tol * tol;
-    static const int kid = register_kernel("k_pcg_persistent");
+    const bool dist = e->world > 1 || e->seg_big.count > 0;
+    static const int kid = register_kernel("k_pcg_persistent"), kid_dist = register_kernel("k_pcg_persistent_dist");
     cudaEvent_t eb = nullptr;
     if (e->profiling) eb = profile_begin(e);
-    void* args[] = { &a };
-    CU(cudaLaunchCooperativeKernel((const void*)k_pcg_persistent, dim3(e->sp_grid), dim3(kSpThreads), args, kSpSmemBytes, e->stream));
-    if (eb) profile_end(e, kid, eb);
+    if (!dist) {
+        void* args[] = { &a };
+        CU(cudaLaunchCooperativeKernel((const void*)k_pcg_persistent, dim3(e->sp_grid), dim3(kSpThreads), args, kSpSmemBytes, e->stream));
+    } else {
+        PcgDistArgs d{};
+        d.a = a;
+        d.bsegs = e->seg_big.segs.p; d.bcta_seg = e->seg_big.cta_seg.p; d.bnseg = e->seg_big.count; d.bslot_desc = e->seg_big.slots.p;
+        d.bnslots_total = e->seg_big.nslots;
+        if (e->cta_part.n < (size_t)e->sp_grid) CU(e->cta_part.alloc(e->sp_grid));
+        d.cta_part = e->cta_part.p;
+        d.rank = e->rank; d.world = e->world;
+        if (e->world == 1) {
+            // split markers on one GPU: the boundary vector is indexed by marker
+            d.n_wb = e->seg_big.count > 0 ? 6 * (int)e->Nm : 0;
+            d.wbl = e->w.p; d.wb = e->w.p;
+        } else {
+            d.n_wb = 6 * (int)e->n_bnd;
+            if (e->wbl.n < 6 * (size_t)e->n_bnd + 4) CU(e->wbl.alloc(6 * (size_t)e->n_bnd + 4));
+            d.wbl = e->wbl.p; d.wb = e->wb.p;
+            for (int r = 0; r < e->world; ++r) d.xbuf[r] = e->pcgx_buf[r];
+            d.cap1 = kPcgxCap1; d.cap2 = kPcgxCap2; d.seq = e->pcgx_seq.p;
+        }
+        void* args[] = { &d };
+        const void* fn = e->world > 1 ? (const void*)k_pcg_persistent_dist<true> : (const void*)k_pcg_persistent_dist<false>;
+        CU(cudaLaunchCooperativeKernel(fn, dim3(e->sp_grid), dim3(kSpThreads), args, kSpSmemBytes, e->stream));
+    }
+    if (eb) profile_end(e, dist ? kid_dist : kid, eb);
     ++e->launches;
     e->pcg_result_pending = true;
     return VMM_BA_OK;
@@ -598,7 +630,11 @@ struct PcgResult { int iterations; bool ok; double rel; };
 
 bool pcg_persistent_eligible(const vmm_ba_engine* e) {
     static const bool legacy = std::getenv("VMM_BA_PCG_LEGACY") != nullptr;   // A/B: the five-launches-per-iteration loop of round 1
-    return !legacy && e->world == 1 && e->seg_big.count == 0 && e->pcgp.nunits > 0;
+    if (legacy || e->pcgp.nunits == 0) return false;
+    if (e->world == 1) return true;
+    // sharded: the two per-iteration sums travel inside the kernel through the mapped peer buffers
+    const size_t nC1 = (size_t)(e->coarse.available ? e->coarse.nC : 0) + 1;
+    return e->pcgx_ok && 6 * (size_t)e->n_bnd + 2 <= kPcgxCap1 && nC1 <= kPcgxCap2;
 }
 
 // Solve (B_l - E C_l^-1 E^T) x = r0 (r0 in e->pr on entry). x -> e->px, final residual in e->pr.
@@ -1311,57 +1347,74 @@ namespace {
 // Exchange buffers of the one-shot all-reduce: allocate, export, all-gather the IPC handles through NCCL, map the
 // peers'.  Every rank reaches the same verdict (the per-rank status is summed), so either all ranks use the peer
 // path or none does.  VMM_BA_NO_PEER=1 keeps everything on NCCL.
-void peer_setup(vmm_ba_engine* e) {
-    e->peer_ok = false;
-    if (e->world > kPeerMaxWorld) return;
-    const bool disabled = std::getenv("VMM_BA_NO_PEER") != nullptr;
-    const size_t bytes = peer_buffer_bytes(e->world);
-    int ok = !disabled;
-    if (ok && cudaMalloc(&e->peer_own, bytes) != cudaSuccess) { e->peer_own = nullptr; ok = 0; cudaGetLastError(); }
-    if (e->peer_own) { cudaMemset(e->peer_own, 0, bytes); cudaDeviceSynchronize(); }   // flags are zero before any peer can map the buffer
+// One exchange buffer per rank, mapped by all peers: allocate, export, all-gather the IPC handles through NCCL, map the
+// peers'.  Every rank reaches the same verdict (the per-rank status is summed), so either all ranks use it or none does.
+bool peer_map_buffer(vmm_ba_engine* e, size_t bytes, uint4** own_out, uint4** mapped /* [world] */) {
+    uint4* own = nullptr;
+    int ok = 1;
+    if (cudaMalloc(&own, bytes) != cudaSuccess) { own = nullptr; ok = 0; cudaGetLastError(); }
+    if (own) { cudaMemset(own, 0, bytes); cudaDeviceSynchronize(); }   // flags are zero before any peer can map the buffer
+    *own_out = own;
     cudaIpcMemHandle_t mine{};
-    if (ok && cudaIpcGetMemHandle(&mine, e->peer_own) != cudaSuccess) { ok = 0; cudaGetLastError(); }
+    if (ok && cudaIpcGetMemHandle(&mine, own) != cudaSuccess) { ok = 0; cudaGetLastError(); }
     // all-gather of (handle, status): 64 + 8 bytes per rank, as doubles
     constexpr int kWords = (int)(sizeof(cudaIpcMemHandle_t) / sizeof(double)) + 1;
     double h_send[kWords];
     std::memcpy(h_send, &mine, sizeof(mine));
     h_send[kWords - 1] = ok ? 1.0 : 0.0;
     double* d_all = nullptr;
-    if (cudaMalloc(&d_all, sizeof(double) * kWords * e->world) != cudaSuccess) { cudaGetLastError(); return; }
+    if (cudaMalloc(&d_all, sizeof(double) * kWords * e->world) != cudaSuccess) { cudaGetLastError(); return false; }
     std::vector<double> h_all((size_t)kWords * e->world, 0.0);
     cudaMemcpyAsync(d_all + (size_t)kWords * e->rank, h_send, sizeof(h_send), cudaMemcpyHostToDevice, e->stream);
     const int nrc = nccl_api().AllGather(d_all + (size_t)kWords * e->rank, d_all, kWords, NCCL_FLOAT64, e->comm, e->stream);
     cudaMemcpyAsync(h_all.data(), d_all, sizeof(double) * kWords * e->world, cudaMemcpyDeviceToHost, e->stream);
     cudaStreamSynchronize(e->stream);
     cudaFree(d_all);
-    if (nrc) return;
+    if (nrc) return false;
     int all_ok = 1;
     for (int r = 0; r < e->world; ++r) all_ok &= (h_all[(size_t)kWords * r + kWords - 1] == 1.0);
     // second round: did every rank manage to map every peer?
-    int mapped = all_ok;
+    int mapped_ok = all_ok;
     if (all_ok) {
-        for (int r = 0; r < e->world && mapped; ++r) {
-            if (r == e->rank) { e->peer.buf[r] = e->peer_own; continue; }
+        for (int r = 0; r < e->world && mapped_ok; ++r) {
+            if (r == e->rank) { mapped[r] = own; continue; }
             cudaIpcMemHandle_t h;
             std::memcpy(&h, &h_all[(size_t)kWords * r], sizeof(h));
             void* p = nullptr;
-            if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); mapped = 0; break; }
-            e->peer.buf[r] = static_cast<uint4*>(p);
+            if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); mapped_ok = 0; break; }
+            mapped[r] = static_cast<uint4*>(p);
         }
     }
     double* d_flag = nullptr;
-    if (cudaMalloc(&d_flag, sizeof(double)) != cudaSuccess) { cudaGetLastError(); return; }
-    const double mine_ok = mapped ? 0.0 : 1.0;   // number of ranks that failed
+    if (cudaMalloc(&d_flag, sizeof(double)) != cudaSuccess) { cudaGetLastError(); return false; }
+    const double mine_ok = mapped_ok ? 0.0 : 1.0;   // number of ranks that failed
     double total = 1.0;
     cudaMemcpyAsync(d_flag, &mine_ok, sizeof(double), cudaMemcpyHostToDevice, e->stream);
     const int arc = nccl_api().AllReduce(d_flag, d_flag, 1, NCCL_FLOAT64, NCCL_SUM, e->comm, e->stream);
     cudaMemcpyAsync(&total, d_flag, sizeof(double), cudaMemcpyDeviceToHost, e->stream);
     cudaStreamSynchronize(e->stream);
     cudaFree(d_flag);
+    return arc == 0 && total == 0.0;
+}
+
+// Exchange buffers over NVLink peer memory: the one-shot all-reduce of ba_peer.cuh and the in-kernel exchanges of the
+// persistent PCG (ba_pcg_dist.cuh).  VMM_BA_NO_PEER=1 keeps everything on NCCL (and the PCG on the multi-launch loop).
+void peer_setup(vmm_ba_engine* e) {
+    e->peer_ok = false;
+    e->pcgx_ok = false;
+    if (e->world > kPeerMaxWorld) return;
+    if (std::getenv("VMM_BA_NO_PEER") != nullptr) return;
     e->peer.rank = e->rank;
     e->peer.world = e->world;
     e->peer_seq = 0;
-    e->peer_ok = (arc == 0 && total == 0.0);
+    e->peer_ok = peer_map_buffer(e, peer_buffer_bytes(e->world), &e->peer_own, e->peer.buf);
+    if (!e->peer_ok) return;
+    const size_t words = (size_t)2 * e->world * (kPcgxCap1 + kPcgxCap2);
+    e->pcgx_ok = peer_map_buffer(e, words * sizeof(uint4), &e->pcgx_own, e->pcgx_buf);
+    if (e->pcgx_ok) {
+        if (e->pcgx_seq.alloc(1) != cudaSuccess) { e->pcgx_ok = false; return; }
+        cudaMemset(e->pcgx_seq.p, 0, sizeof(unsigned));
+    }
 }
 }  // namespace
 
@@ -1490,7 +1543,7 @@ static int create_common(int device, vmm_ba_engine** out) {
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
     if ((err = cudaSetDevice(device)) != cudaSuccess) return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(err));
     for (const void* f : { (const void*)k_schur_product<SP_FULL>, (const void*)k_schur_product<SP_GATHER>, (const void*)k_schur_product<SP_SCATTER>,
-                           (const void*)k_pcg_persistent })
+                           (const void*)k_pcg_persistent, (const void*)k_pcg_persistent_dist<true>, (const void*)k_pcg_persistent_dist<false> })
         if ((err = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmemBytes)) != cudaSuccess)
             return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaFuncSetAttribute(shared memory %zu): %s", kSpSmemBytes, cudaGetErrorString(err));
     if ((err = cudaFuncSetAttribute((const void*)k_coarse_sweep_invert, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kInvSmemBytes)) != cudaSuccess)
@@ -1569,6 +1622,9 @@ int vmm_ba_destroy(vmm_ba_handle e) {
         if (e->peer.buf[r] && e->peer.buf[r] != e->peer_own) cudaIpcCloseMemHandle(e->peer.buf[r]);
     if (e->comm) nccl_api().CommDestroy(e->comm);
     if (e->peer_own) cudaFree(e->peer_own);
+    for (int r = 0; r < e->world && r < kPeerMaxWorld; ++r)
+        if (e->pcgx_buf[r] && e->pcgx_buf[r] != e->pcgx_own) cudaIpcCloseMemHandle(e->pcgx_buf[r]);
+    if (e->pcgx_own) cudaFree(e->pcgx_own);
     if (e->cusolver) cusolverDnDestroy(e->cusolver);
     if (e->cublas) cublasDestroy(e->cublas);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);

@@ -112,7 +112,7 @@ __device__ __forceinline__ double cta_sum(double v, double* s_red) {
 
 // Phase B of one unit.  first: x = 0, r is the right-hand side (no p, q yet).
 __device__ __forceinline__ double pcg_update_unit(const PcgArgs& A, const PcgUnit u, bool first, double alpha, double* s_v, double* s_c,
-                                                  double* s_tot, int unit_index) {
+                                                  double* s_tot, int unit_index, bool coarse) {
     const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
     const bool valid = cs < u.count;
     int cam = 0;
@@ -134,7 +134,7 @@ __device__ __forceinline__ double pcg_update_unit(const PcgArgs& A, const PcgUni
     s_v[t] = rv;
     __syncthreads();
     double rz = 0.0, contrib = 0.0;
-    const bool restrict_unit = A.ncl > 0 && u.cluster >= 0;   // uniform for the CTA
+    const bool restrict_unit = coarse && u.cluster >= 0;   // uniform for the CTA
     if (valid) {
         const double* rr = s_v + cs * 6;
         const double zt = row_dot6(A.Minv + idx * 6, rr);
@@ -180,7 +180,7 @@ __device__ __forceinline__ double pcg_update_unit(const PcgArgs& A, const PcgUni
 }
 
 // Phase D of one unit: p = z + P yc + beta p, q = (B + lambda) p; returns the thread's share of p.q
-__device__ __forceinline__ double pcg_direction_unit(const PcgArgs& A, const PcgUnit u, bool first, double beta, double* s_v) {
+__device__ __forceinline__ double pcg_direction_unit(const PcgArgs& A, const PcgUnit u, bool first, double beta, double* s_v, bool coarse) {
     const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
     const bool valid = cs < u.count;
     double pv = 0.0;
@@ -189,7 +189,7 @@ __device__ __forceinline__ double pcg_direction_unit(const PcgArgs& A, const Pcg
         const int cam = __ldg(A.unit_cams + u.first + cs);
         idx = (size_t)cam * 6 + a;
         pv = A.z[idx];
-        if (u.cluster >= 0 && A.ncl > 0) {
+        if (u.cluster >= 0 && coarse) {
             const double* y = A.yc + (size_t)u.cluster * 6;
             const double* xb = A.xbar + 3 * (size_t)u.cluster;
             const int k = a < 3 ? a : a - 3;
@@ -253,9 +253,8 @@ __device__ __forceinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_r
 }
 
 __global__ void __launch_bounds__(kSpThreads, 1)
-k_pcg_persistent(const PcgArgs A_in) {
-    PcgArgs A = A_in;
-    if (A.ncl > 0 && __ldcg(A.coarse_info) != 0) A.ncl = 0;   // uniform for the grid
+k_pcg_persistent(const PcgArgs A) {
+    const bool coarse = A.ncl > 0 && __ldcg(A.coarse_info) == 0;   // uniform for the grid
     extern __shared__ __align__(128) unsigned char sp_ring[];
     __shared__ SpShared sh;
     __shared__ double s_v[kSpThreads], s_c[kSpThreads], s_tot[8], s_red[kSpThreads / 32];
@@ -263,7 +262,6 @@ k_pcg_persistent(const PcgArgs A_in) {
     const unsigned G = gridDim.x;
     const int ub = A.cta_unit[blockIdx.x], ue = A.cta_unit[blockIdx.x + 1];
     const PcgUnit* units = A.units;
-    const bool coarse = A.ncl > 0;
     volatile double* scal = A.scal;
     bool aborted = false;
     int it = 0, iterations = 0;
@@ -273,7 +271,7 @@ k_pcg_persistent(const PcgArgs A_in) {
     // ---- start: z = M^-1 r, r.z, restriction; coarse solve; first direction ----
     {
         double rz = 0.0;
-        for (int u = ub; u < ue; ++u) rz += pcg_update_unit(A, units[u], true, 0.0, s_v, s_c, s_tot, u);
+        for (int u = ub; u < ue; ++u) rz += pcg_update_unit(A, units[u], true, 0.0, s_v, s_c, s_tot, u, coarse);
         rz = cta_sum(rz, s_red);
         if (threadIdx.x == 0) red_add(A.scal + PS_RZ, rz);
     }
@@ -285,7 +283,7 @@ k_pcg_persistent(const PcgArgs A_in) {
     }
     {
         double pq = 0.0;
-        for (int u = ub; u < ue; ++u) pq += pcg_direction_unit(A, units[u], true, 0.0, s_v);
+        for (int u = ub; u < ue; ++u) pq += pcg_direction_unit(A, units[u], true, 0.0, s_v, coarse);
         pq = cta_sum(pq, s_red);
         if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
     }
@@ -307,7 +305,7 @@ k_pcg_persistent(const PcgArgs A_in) {
             const double alpha = (rz_s != 0.0) ? rz_s / denom : 0.0;
             {
                 double rz = 0.0;
-                for (int u = ub; u < ue; ++u) rz += pcg_update_unit(A, units[u], false, alpha, s_v, s_c, s_tot, u);
+                for (int u = ub; u < ue; ++u) rz += pcg_update_unit(A, units[u], false, alpha, s_v, s_c, s_tot, u, coarse);
                 rz = cta_sum(rz, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, rz);
             }
@@ -327,7 +325,7 @@ k_pcg_persistent(const PcgArgs A_in) {
             const double beta = (rz_s != 0.0) ? rz_new / rz_s : 0.0;
             {
                 double pq = 0.0;
-                for (int u = ub; u < ue; ++u) pq += pcg_direction_unit(A, units[u], false, beta, s_v);
+                for (int u = ub; u < ue; ++u) pq += pcg_direction_unit(A, units[u], false, beta, s_v, coarse);
                 pq = cta_sum(pq, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
             }
