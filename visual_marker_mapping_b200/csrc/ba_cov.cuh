@@ -4,8 +4,8 @@
 // the 3x3 blocks of (J^T J)^-1 that belong to every marker's translation, at the current poses.  With the cameras
 // eliminated,  (H^-1)_mm = (C - E^T B^-1 E)^-1 =: R^-1,  R dense of order 6 x markers (the reference prints this
 // once, for maps of tens to a few hundred markers).  R is assembled camera by camera from the E blocks of the
-// linearisation, factored (cusolverDnDpotrf), X = L^-1 by one triangular solve, and the wanted blocks are the
-// Gram matrices of X's column triples:  cov_j = X[:, 6j..6j+2]^T X[:, 6j..6j+2].
+// linearisation and inverted in place by the blocked sweep operator (k_coarse_sweep_invert, ba_coarse_inv.cuh — hand-written,
+// no library call); the wanted blocks are the translation 3x3 blocks on its diagonal.
 #pragma once
 #include "ba_kernels.cuh"
 #include "ba_schur.cuh"
@@ -73,41 +73,13 @@ __global__ void k_cov_add_marker_blocks(int nm, const double* __restrict__ C, co
     else *dst = (r == c) ? 1.0 : 0.0;
 }
 
-// cov_j = X[:, 6j..6j+2]^T X[:, 6j..6j+2], X = L^-1 column-major lower triangular (rows >= column index are non-zero).
-// One CTA per marker; zeros for markers without columns.
-__global__ void __launch_bounds__(256)
-k_cov_translation_blocks(int n, const double* __restrict__ X, const unsigned char* __restrict__ tag_active, double* __restrict__ cov) {
-    const int j = blockIdx.x;
-    double acc[6] = { 0, 0, 0, 0, 0, 0 };   // xx xy xz yy yz zz
-    if (tag_active[j]) {
-        const double* c0 = X + (size_t)(6 * j) * n;
-        const double* c1 = c0 + n;
-        const double* c2 = c1 + n;
-        for (int r = 6 * j + threadIdx.x; r < n; r += 256) {
-            const double a = c0[r], b = c1[r], c = c2[r];
-            acc[0] += a * a; acc[1] += a * b; acc[2] += a * c; acc[3] += b * b; acc[4] += b * c; acc[5] += c * c;
-        }
-    }
-    __shared__ double s_p[8][6];
-#pragma unroll
-    for (int k = 0; k < 6; ++k) {
-        const double s = warp_sum(acc[k]);
-        if ((threadIdx.x & 31) == 0) s_p[threadIdx.x >> 5][k] = s;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double t[6];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) {
-            t[k] = 0.0;
-#pragma unroll
-            for (int w = 0; w < 8; ++w) t[k] += s_p[w][k];
-        }
-        double* o = cov + (size_t)j * 9;
-        o[0] = t[0]; o[1] = t[1]; o[2] = t[2];
-        o[3] = t[1]; o[4] = t[3]; o[5] = t[4];
-        o[6] = t[2]; o[7] = t[4]; o[8] = t[5];
-    }
+// cov_j = the translation 3x3 block of the inverted matrix (row-major, leading dimension n); zeros for markers without columns.
+__global__ void k_cov_diagonal_blocks(int nm, int n, const double* __restrict__ Rinv, const unsigned char* __restrict__ tag_active,
+                                      double* __restrict__ cov) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nm) return;
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) cov[(size_t)j * 9 + r * 3 + c] = tag_active[j] ? Rinv[(size_t)(6 * j + r) * n + 6 * j + c] : 0.0;
 }
 
 }  // namespace vmm

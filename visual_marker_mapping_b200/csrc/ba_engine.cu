@@ -28,8 +28,6 @@
 #include "ba_cov.cuh"
 #include "ba_peer.cuh"
 #include "nccl_dyn.h"
-#include <cublas_v2.h>
-#include <cusolverDn.h>
 
 using namespace vmm;
 
@@ -98,7 +96,7 @@ struct vmm_ba_engine {
     // perm_dev[s] = caller's tag-observation index of camera-order position s (host mirror fetched on demand)
     DevBuf<int> raw_cam, raw_tag, perm_all, perm_dev, mperm, sort_keys, sort_keys2, sort_iota;
     DevBuf<int> cpos, cam_ptr_dev;    // marker-order position per camera-order observation; CSR of the camera order
-    DevBuf<double> covR, covX, cov_out;
+    DevBuf<double> covR, cov_out;
     DevBuf<double2> raw_uv;
     DevBuf<unsigned char> sort_tmp;
     std::vector<int> perm_c;
@@ -141,8 +139,6 @@ struct vmm_ba_engine {
         DevBuf<double> xbar, Ac, rc /* nC + 2: r.z partials ride along in its tail when sharded */, yc, work, Wbuf;
         size_t n_w = 0;           // (marker, touched cluster) pairs: Wbuf holds 36 doubles for each
     } coarse;
-    cusolverDnHandle_t cusolver = nullptr;
-    cublasHandle_t cublas = nullptr;
     int coarse_cams_per_cluster = 192;
     DevBuf<unsigned char> cam_active, tag_active;
     // poses: current and candidate (pointer-swapped on acceptance)
@@ -285,18 +281,6 @@ int fail_with(vmm_ba_engine* e, int code, const char* fmt, ...) {
         ++e->launches;                                                     \
     } while (0)
 #define LAUNCH(kernel, grid, block, ...) LAUNCH_NAMED(#kernel, kernel, grid, block, 0, __VA_ARGS__)
-// A library call on the engine's stream (cuSOLVER), timed like a kernel under its own name.
-#define LIBCALL_NAMED(name, ok_expr, what)                                 \
-    do {                                                                   \
-        static const int _kid = register_kernel(name);                     \
-        cudaEvent_t _eb = nullptr;                                         \
-        if (e->profiling) _eb = profile_begin(e);                          \
-        const bool _ok = (ok_expr);                                        \
-        if (_eb) profile_end(e, _kid, _eb);                                \
-        ++e->launches;                                                     \
-        if (!_ok) return fail_with(e, VMM_BA_ERR_CUDA, what " failed");    \
-    } while (0)
-
 int nccl_check(vmm_ba_engine* e, int rc, const char* what) {
     if (rc == 0) return VMM_BA_OK;
     return fail_with(e, VMM_BA_ERR_NCCL, "%s failed: %s", what, nccl_api().GetErrorString(rc));
@@ -1551,14 +1535,6 @@ static int create_common(int device, vmm_ba_engine** out) {
     e = new vmm_ba_engine();
     e->device = device;
     e->sp_grid = prop.multiProcessorCount;   // persistent kernel: one CTA per SM
-    if (cusolverDnCreate(&e->cusolver) != CUSOLVER_STATUS_SUCCESS) {
-        delete e;
-        return fail_with(nullptr, VMM_BA_ERR_CUDA, "cusolverDnCreate failed");
-    }
-    if (cublasCreate(&e->cublas) != CUBLAS_STATUS_SUCCESS) {
-        delete e;
-        return fail_with(nullptr, VMM_BA_ERR_CUDA, "cublasCreate failed");
-    }
     if ((err = cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
         delete e;
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(err));
@@ -1625,8 +1601,6 @@ int vmm_ba_destroy(vmm_ba_handle e) {
     for (int r = 0; r < e->world && r < kPeerMaxWorld; ++r)
         if (e->pcgx_buf[r] && e->pcgx_buf[r] != e->pcgx_own) cudaIpcCloseMemHandle(e->pcgx_buf[r]);
     if (e->pcgx_own) cudaFree(e->pcgx_own);
-    if (e->cusolver) cusolverDnDestroy(e->cusolver);
-    if (e->cublas) cublasDestroy(e->cublas);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
     for (auto& p : e->prof_pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto& ev : e->prof_free) cudaEventDestroy(ev);
@@ -2112,13 +2086,23 @@ int vmm_ba_marker_translation_covariance(vmm_ba_handle e, int loss_kind, double 
     const int64_t kMaxMarkers = 4096;   // dense marker-reduced system: (6 Nm)^2 doubles, twice
     if (e->Nm > kMaxMarkers) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "covariance is limited to %lld markers (dense reduced system)", (long long)kMaxMarkers);
     CU(cudaSetDevice(e->device));
-    const int nm = (int)e->Nm, nc = (int)e->Ncl, n = 6 * nm;
+    // dense marker-reduced normal matrix R = C - sum_i E_i^T B_i^-1 E_i (cameras eliminated), order 6 Nm padded to the block
+    // order of the inversion kernel; inverted in place by the blocked sweep operator (ba_coarse_inv.cuh — the kernel that
+    // inverts the coarse matrix of the preconditioner; no library call), the covariance blocks are its diagonal 3x3 blocks.
+    const int nm = (int)e->Nm, nc = (int)e->Ncl, n6 = 6 * nm, n = (n6 + kInvNB - 1) / kInvNB * kInvNB;
     prepare_poses(e, e->cur);
     int rc = linearize(e, e->cur, loss_kind, loss_scale);
     if (rc) return rc;
-    CU(e->covR.alloc((size_t)n * n)); CU(e->covX.alloc((size_t)n * n)); CU(e->cov_out.alloc((size_t)9 * nm));
+    DevBuf<double> Pt, Qt;
+    DevBuf<int> info;
+    DevBuf<unsigned> bar;
+    CU(e->covR.alloc((size_t)n * n)); CU(e->cov_out.alloc((size_t)9 * nm));
+    CU(Pt.alloc((size_t)n * kInvNB)); CU(Qt.alloc((size_t)n * kInvNB)); CU(info.alloc(1)); CU(bar.alloc(4));
     CU(cudaMemsetAsync(e->covR.p, 0, sizeof(double) * n * n, e->stream));
     CU(cudaMemsetAsync(e->fail.p, 0, sizeof(int), e->stream));
+    CU(cudaMemsetAsync(info.p, 0, sizeof(int), e->stream));
+    CU(cudaMemsetAsync(bar.p, 0, 4 * sizeof(unsigned), e->stream));
+    if (n > n6) LAUNCH(k_pad_identity, 1, 64, n6, n, e->covR.p);
     if (nc > 0) {
         LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->B.p, (const double*)nullptr, e->cam_active.p, e->Minv.p, e->fail.p);
         if (e->Ntol > 0)
@@ -2126,30 +2110,27 @@ int vmm_ba_marker_translation_covariance(vmm_ba_handle e, int loss_kind, double 
                    e->Et.p, n, e->covR.p);
     }
     LAUNCH(k_cov_add_marker_blocks, nblocks((int64_t)nm * 36, kThreads), kThreads, nm, e->C.p, e->tag_active.p, n, e->covR.p);
-    int lwork = 0;
-    if (cusolverDnSetStream(e->cusolver, e->stream) != CUSOLVER_STATUS_SUCCESS || cublasSetStream(e->cublas, e->stream) != CUBLAS_STATUS_SUCCESS ||
-        cusolverDnDpotrf_bufferSize(e->cusolver, CUBLAS_FILL_MODE_LOWER, n, e->covR.p, n, &lwork) != CUSOLVER_STATUS_SUCCESS)
-        return fail_with(e, VMM_BA_ERR_CUDA, "cusolver set-up failed");
-    DevBuf<double> work;
-    DevBuf<int> info;
-    CU(work.alloc(std::max(lwork, 1))); CU(info.alloc(1));
-    LIBCALL_NAMED("cusolverDnDpotrf", cusolverDnDpotrf(e->cusolver, CUBLAS_FILL_MODE_LOWER, n, e->covR.p, n, work.p, lwork, info.p) == CUSOLVER_STATUS_SUCCESS,
-                  "cusolverDnDpotrf");
+    {
+        static const int kid = register_kernel("k_coarse_sweep_invert");
+        cudaEvent_t eb = nullptr;
+        if (e->profiling) eb = profile_begin(e);
+        double* M = e->covR.p; int nP = n, ld = n; double* pt = Pt.p; double* qt = Qt.p; int* inf = info.p; unsigned* b = bar.p;
+        void* args[] = { &M, &nP, &ld, &pt, &qt, &inf, &b };
+        CU(cudaLaunchCooperativeKernel((const void*)k_coarse_sweep_invert, dim3(e->sp_grid), dim3(kInvThreads), args, kInvSmemBytes, e->stream));
+        if (eb) profile_end(e, kid, eb);
+        ++e->launches;
+    }
     int h_info = 0, h_fail = 0;
     CU(cudaMemcpyAsync(&h_info, info.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaMemcpyAsync(&h_fail, e->fail.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
     if (h_info != 0 || h_fail != 0)   // Ceres: "Jacobian is rank deficient" (a camera or marker block without enough observations)
-        return fail_with(e, VMM_BA_ERR_NUMERIC, "the normal equations are rank deficient (potrf info %d): no covariance", h_info);
-    LAUNCH(k_identity, nblocks((int64_t)n * n, kThreads), kThreads, n, e->covX.p);
-    const double one = 1.0;
-    LIBCALL_NAMED("cublasDtrsm", cublasDtrsm(e->cublas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, n, n, &one, e->covR.p, n,
-                                             e->covX.p, n) == CUBLAS_STATUS_SUCCESS, "cublasDtrsm");
-    LAUNCH(k_cov_translation_blocks, nm, 256, n, e->covX.p, e->tag_active.p, e->cov_out.p);
+        return fail_with(e, VMM_BA_ERR_NUMERIC, "the normal equations are rank deficient (pivot info %d): no covariance", h_info);
+    LAUNCH(k_cov_diagonal_blocks, nblocks(nm, 128), 128, nm, n, e->covR.p, e->tag_active.p, e->cov_out.p);
     CU(cudaMemcpyAsync(cov, e->cov_out.p, sizeof(double) * 9 * nm, cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
     if (e->profiling) profile_resolve(e);
-    e->covR.release(); e->covX.release();   // up to 2 x 4.8 GB: not kept
+    e->covR.release();   // up to 4.8 GB: not kept
     return VMM_BA_OK;
 }
 
