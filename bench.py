@@ -312,6 +312,7 @@ def run_b200(args):
     ba.profile_enable(True)
     ms_prof, sums_prof = timed(lambda: lm_steps(args.steps))
     prof = ba.profile()
+    pcg_phases = ba.pcg_phase_ns()
     ba.profile_enable(False)
     pcg_its_prof = int(sum(s.pcg_iterations for s in sums_prof))
 
@@ -364,7 +365,8 @@ def run_b200(args):
                 per_launch = KERNEL_BYTES_PER_TAG_OBS["k_schur_product<SP_FULL>"] * ntol * pcg_its_prof / max(n, 1)
                 gbs = per_launch / (ms / n * 1e-3) / 1e9
                 ent.update({"gbs": gbs, "frac_hbm": gbs / peak, "pcg_iterations": pcg_its_prof, "ms_per_pcg_iteration": ms / max(pcg_its_prof, 1),
-                            "algorithmic_bytes_per_launch": per_launch})
+                            "algorithmic_bytes_per_launch": per_launch,
+                            "phase_us_per_iteration_cta0": {k: v / 1e3 / max(pcg_its_prof, 1) for k, v in pcg_phases.items()}})
             kernels[name] = ent
         if top and "gbs" in kernels[top[0]]:
             k = kernels[top[0]]

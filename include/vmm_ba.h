@@ -78,8 +78,8 @@ typedef struct {
     int jacobi_scaling;                   /* 1     */
     /* linear solver: block-Jacobi PCG on the reduced camera system (markers eliminated) */
     int preconditioner;                   /* vmm_ba_preconditioner, default TWO_LEVEL */
-    double pcg_tolerance;                 /* stop when sqrt(r.M^-1 r / r0.M^-1 r0) <= tol; default 5e-2 (C2/C3/C4: the LM iteration
-                                             counts and final accuracy of 1e-2 with 40 % fewer PCG iterations; Ceres' eta default is 1e-1) */
+    double pcg_tolerance;                 /* stop when sqrt(r.M^-1 r / r0.M^-1 r0) <= tol; default 1e-2 (5e-2 saved 40 % of the PCG
+                                             iterations on C2/C3 but sent c3/8 into another local minimum; Ceres' eta default is 1e-1) */
     int pcg_max_iterations;               /* default 500 */
     int pcg_min_iterations;               /* default 1 */
     int parity_mode;                      /* 1: solve every LM step to pcg_parity_tolerance so that the
@@ -97,7 +97,8 @@ typedef struct {
                                              an inexact step (pcg_tolerance above this value), the same damped system is
                                              solved again to this tolerance and the test is repeated on that step: the
                                              solve only stops where a (nearly) exact step would also have stopped it.
-                                             default 1e-4; 0 = off (stop on the inexact step).  Unused in parity mode. */
+                                             default 1e-3; 0 = off (stop on the inexact step).  Unused in parity mode.  On one GPU the
+                                             confirming solve CONTINUES the PCG iteration that produced the inexact step. */
 } vmm_ba_options;
 
 /* replaces: ceres::Solver::Summary (the reference only prints termination_type / FullReport) */
@@ -219,9 +220,16 @@ int vmm_ba_reprojection_error_sums(vmm_ba_handle h, double* per_tag_obs_sum);
  * cov[9*j .. 9*j+8] = the 3x3 block (row-major) of (J^T J)^-1 that belongs to the translation of marker j at the
  * current poses, under the given loss (the reference calls it after the final solve, which runs without a loss);
  * zeros for the constant origin tag (as ceres::Covariance returns for constant blocks) and for unobserved markers.
- * Dense in the markers (cameras are eliminated first): limited to 4096 markers, single-GPU engines.
- * VMM_BA_ERR_NUMERIC when the normal equations are rank deficient (Ceres: Compute() returns false). */
+ * Cameras are eliminated first.  Up to 1024 markers the marker-reduced matrix is inverted densely; larger maps go through
+ * the breadth-first levels of the co-observation graph, which make that matrix block tridiagonal, and the exact two-sweep
+ * recursion for the diagonal blocks of its inverse (csrc/ba_cov_block.cuh) — the reference calls this on the final, full
+ * problem.  Single-GPU engines.  VMM_BA_ERR_NUMERIC when the normal equations are rank deficient (Ceres: Compute()
+ * returns false); VMM_BA_ERR_INVALID_ARGUMENT when the level blocks do not fit the device memory. */
 int vmm_ba_marker_translation_covariance(vmm_ba_handle h, int loss_kind, double loss_scale, double* cov);
+
+typedef enum { VMM_BA_COV_AUTO = 0, VMM_BA_COV_DENSE = 1 /* <= 4096 markers */, VMM_BA_COV_BLOCK_TRIDIAGONAL = 2 } vmm_ba_covariance_method;
+/* The same with the route chosen by the caller (tests compare the two). */
+int vmm_ba_marker_translation_covariance_ex(vmm_ba_handle h, int loss_kind, double loss_scale, int method, double* cov);
 
 /* Test entry (one GPU): the coarse matrix A_c = P^T S P of the two-level preconditioner at the current poses (damping
  * for `radius`, Jacobi scaling as in the first LM iteration) and the inverse the hand-written kernel
@@ -273,6 +281,10 @@ int64_t vmm_ba_kernel_launches(vmm_ba_handle h);
  * by a CUDA-event pair on the launching stream.  enable(…) also clears the counters.  Kernel indices
  * run over [0, vmm_ba_profile_num_kernels()); a kernel appears once it has been launched. */
 int vmm_ba_profile_enable(vmm_ba_handle h, int on);
+/* Phase clock of the persistent PCG kernel, summed over the launches since vmm_ba_profile_enable(h, 1): nanoseconds CTA 0
+ * spent in the streamed product, the update + restriction, the coarse mat-vec, the direction [0..3] and in grid
+ * barriers (waiting for the slowest CTA included) [4]. */
+int vmm_ba_pcg_phase_ns(vmm_ba_handle h, double* out5);
 int vmm_ba_profile_num_kernels(void);
 const char* vmm_ba_profile_kernel_name(int index);
 int vmm_ba_profile_get(vmm_ba_handle h, int index, int64_t* launches, double* total_ms);

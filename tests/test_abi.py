@@ -37,7 +37,7 @@ def test_abi_version_and_defaults(lib):
     assert o.initial_trust_region_radius == 1e4 and o.max_trust_region_radius == 1e16
     assert o.min_relative_decrease == 1e-3 and o.min_lm_diagonal == 1e-6 and o.max_lm_diagonal == 1e32
     assert o.max_num_consecutive_invalid_steps == 5 and o.jacobi_scaling == 1
-    assert o.loss_kind == pkg.LOSS_NONE and o.loss_scale == 1.0 and o.parity_mode == 0 and o.pcg_confirm_tolerance == 1e-4
+    assert o.loss_kind == pkg.LOSS_NONE and o.loss_scale == 1.0 and o.parity_mode == 0 and o.pcg_confirm_tolerance == 1e-3 and o.pcg_tolerance == 1e-2
 
 
 def test_struct_layout_matches_header():

@@ -15,10 +15,11 @@ init = (s.cam_q, s.cam_t, s.tag_q, s.tag_t)
 runs = [("parity ftol=1e-12", dict(parity_mode=1, function_tolerance=1e-12)),
         ("parity default", dict(parity_mode=1)),
         ("product default", dict()),
-        ("product confirm=1e-3", dict(pcg_confirm_tolerance=1e-3)),
-        ("product confirm=1e-5", dict(pcg_confirm_tolerance=1e-5)),
+        ("product confirm=1e-4", dict(pcg_confirm_tolerance=1e-4)),
         ("product no-confirm", dict(pcg_confirm_tolerance=0.0)),
-        ("product pcg=1e-2", dict(pcg_tolerance=1e-2)),
+        ("product pcg=2e-2", dict(pcg_tolerance=2e-2)),
+        ("product pcg=5e-2", dict(pcg_tolerance=5e-2)),
+        ("product pcg=3e-3", dict(pcg_tolerance=3e-3)),
         ("product ftol=1e-12", dict(function_tolerance=1e-12))]
 ref = None
 with pkg.BundleAdjuster(0) as ba:

@@ -7,7 +7,7 @@ and csrc/host/ (C++ TagReconstructor facade); this package is the Python plumbin
 from . import synth  # noqa: F401
 from .engine import (  # noqa: F401
     BundleAdjuster, Options, Summary, VmmBaError, default_options, device_count, load_library,
-    partition_cameras, shard_plan, LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY, CONVERGENCE, NO_CONVERGENCE, FAILURE,
+    partition_cameras, shard_plan, LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY, CONVERGENCE, NO_CONVERGENCE, FAILURE, COV_AUTO, COV_DENSE, COV_BLOCK_TRIDIAGONAL,
 )
 
 __all__ = [

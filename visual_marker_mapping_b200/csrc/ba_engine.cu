@@ -26,6 +26,7 @@
 #include "ba_coarse_inv.cuh"
 #include "ba_stage.cuh"
 #include "ba_cov.cuh"
+#include "ba_cov_block.cuh"
 #include "ba_peer.cuh"
 #include "nccl_dyn.h"
 
@@ -130,6 +131,7 @@ struct vmm_ba_engine {
     struct Coarse {
         bool available = false;   // clusters exist for this problem
         bool active = false;      // A_c^-1 is valid for the current LM iteration
+        std::string why;          // why there is no coarse space for this problem (diagnostics)
         int ncl = 0, nC = 0, ldc = 0 /* nC rounded up to the block order of the inversion kernel */, lwork = 0;
         DevBuf<double> Pt, Qt;    // panel scratch of k_coarse_sweep_invert
         DevBuf<unsigned> inv_barrier;
@@ -158,6 +160,7 @@ struct vmm_ba_engine {
         DevBuf<int> cta_unit, unit_cams, cl_unit_ptr;
         DevBuf<double> rc_part, scal;
         DevBuf<unsigned> barrier;
+        DevBuf<unsigned long long> phase_ns;   // 8: in-kernel phase clock of the persistent PCG (profiling only)
         int nunits = 0;
         bool with_clusters = false;
     } pcgp;
@@ -543,6 +546,7 @@ int build_pcg_units(vmm_ba_engine* e, int ncl, const std::vector<int>& cl_ptr, c
     P.with_clusters = ncl > 0;
     CU(P.units.alloc(std::max<size_t>(units.size(), 1))); CU(P.unit_cams.alloc(std::max<size_t>(cams.size(), 1)));
     CU(P.cta_unit.alloc(G + 1)); CU(P.cl_unit_ptr.alloc(ncl + 1)); CU(P.rc_part.alloc(std::max<size_t>(6 * units.size(), 1)));
+    if (!P.phase_ns.p) { CU(P.phase_ns.alloc(8)); CU(cudaMemsetAsync(P.phase_ns.p, 0, 8 * sizeof(unsigned long long), e->stream)); }
     if (!P.barrier.p) { CU(P.barrier.alloc(4)); CU(cudaMemsetAsync(P.barrier.p, 0, 4 * sizeof(unsigned), e->stream)); }
     auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
     CU(up(P.units.p, units.data(), sizeof(PcgUnit) * units.size()));
@@ -555,18 +559,18 @@ int build_pcg_units(vmm_ba_engine* e, int ncl, const std::vector<int>& cl_ptr, c
 
 // The whole PCG solve as one cooperative launch (ba_pcg.cuh).  The result (iterations, relative residual, ok) lands in
 // e->sc and reaches the host with the next read_stats: no host synchronisation inside the linear solve.
-int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it) {
+int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, bool resume) {
     auto& P = e->pcgp;
     const size_t rows = (size_t)max_it + 2;
     if (P.scal.n < rows * PS_STRIDE) CU(P.scal.alloc(rows * PS_STRIDE));
     CU(cudaMemsetAsync(P.scal.p, 0, sizeof(double) * rows * PS_STRIDE, e->stream));
-    CU(cudaMemsetAsync(e->sc.p, 0, sizeof(double) * SC_N, e->stream));
+    if (!resume) CU(cudaMemsetAsync(e->sc.p, 0, sizeof(double) * SC_N, e->stream));
     CU(cudaMemsetAsync(P.barrier.p, 0, 4 * sizeof(unsigned), e->stream));   // arrivals, generation, abort flag
     const bool two_level = e->coarse.active && P.with_clusters;
     PcgArgs a{};
     a.segs = e->seg_full.segs.p; a.cta_seg = e->seg_full.cta_seg.p; a.nseg = e->seg_full.count; a.slot_desc = e->seg_full.slots.p;
     a.nslots_total = e->seg_full.nslots; a.Es = e->Es.p; a.mo_cam = e->mo_cam.p;
-    a.units = P.units.p; a.cta_unit = P.cta_unit.p; a.unit_cams = P.unit_cams.p;
+    a.units = P.units.p; a.cta_unit = P.cta_unit.p; a.unit_cams = P.unit_cams.p; a.nunits = P.nunits;
     a.Minv = e->Minv.p; a.B = e->B.p; a.lam = e->lam_c.p;
     a.x = e->px.p; a.r = e->pr.p; a.z = e->pz.p; a.p = e->pp.p; a.q = e->pq.p;
     a.ncl = two_level ? e->coarse.ncl : 0; a.nC = two_level ? e->coarse.nC : 0;
@@ -574,6 +578,8 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it) {
     a.rc_part = P.rc_part.p; a.yc = e->coarse.yc.p; a.ldc = e->coarse.ldc; a.coarse_info = e->coarse.info.p;
     a.scal = P.scal.p; a.result = e->sc.p; a.barrier = P.barrier.p;
     a.max_it = max_it; a.min_it = min_it; a.tol2 = tol * tol;
+    a.phase_ns = e->profiling ? P.phase_ns.p : nullptr;
+    a.resume = resume ? 1 : 0;
     const bool dist = e->world > 1 || e->seg_big.count > 0;
     static const int kid = register_kernel("k_pcg_persistent"), kid_dist = register_kernel("k_pcg_persistent_dist");
     cudaEvent_t eb = nullptr;
@@ -615,6 +621,8 @@ struct PcgResult { int iterations; bool ok; double rel; };
 bool pcg_persistent_eligible(const vmm_ba_engine* e) {
     static const bool legacy = std::getenv("VMM_BA_PCG_LEGACY") != nullptr;   // A/B: the five-launches-per-iteration loop of round 1
     if (legacy || e->pcgp.nunits == 0) return false;
+    // the restricted residual and the unit partials are staged in the (idle) ring of the streamed product
+    if (sizeof(double) * ((size_t)(e->coarse.available ? e->coarse.nC : 0) + 16 + 6 * (size_t)e->pcgp.nunits) > kSpSmemBytes) return false;
     if (e->world == 1) return true;
     // sharded: the two per-iteration sums travel inside the kernel through the mapped peer buffers
     const size_t nC1 = (size_t)(e->coarse.available ? e->coarse.nC : 0) + 1;
@@ -624,11 +632,15 @@ bool pcg_persistent_eligible(const vmm_ba_engine* e) {
 // Solve (B_l - E C_l^-1 E^T) x = r0 (r0 in e->pr on entry). x -> e->px, final residual in e->pr.
 // The stopping test runs on the device (k_pcg_direction raises sc[SC_DONE], which turns every later
 // PCG launch into a no-op); the host only looks every `check_every` iterations.
-int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* out) {
+// resume: continue the previous solve of the same system to a tighter tolerance (one GPU, persistent kernel without a
+// boundary path; the caller checks pcg_can_resume)
+bool pcg_can_resume(const vmm_ba_engine* e) { return pcg_persistent_eligible(e) && e->world == 1 && e->seg_big.count == 0; }
+
+int pcg_solve(vmm_ba_engine* e, double tol, int max_it, int min_it, PcgResult* out, bool resume = false) {
     e->pcg_result_pending = false;
     if (pcg_persistent_eligible(e)) {
         out->iterations = 0; out->ok = true; out->rel = 1.0;
-        return pcg_solve_persistent(e, tol, max_it, min_it);
+        return pcg_solve_persistent(e, tol, max_it, min_it, resume);
     }
     const int nc = (int)e->Ncl;
     const int nm = (int)e->Nm;
@@ -820,12 +832,14 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         // system; the right-hand side is re-formed because PCG leaves its residual in its place) when a convergence
         // test fires on an inexact step.
         auto compute_step = [&](bool again) -> int {
-            if (again) {
+            const bool resume = again && pcg_can_resume(e) && pr.ok && pr.iterations > 0;
+            const int its_before = resume ? pr.iterations : 0;
+            if (again && !resume) {
                 LAUNCH(k_marker_apply, nblocks(nm, kThreads), kThreads, nm, e->Linv.p, 0, (const double*)e->gm(), (const double*)nullptr, 1.0, e->zm.p);
                 if (nc > 0) LAUNCH(k_negate, gc_b, kThreads, 6 * nc, e->gc.p, e->pr.p);
                 if (e->seg_all.count > 0) schur_scatter(e, e->zm.p, 1.0, e->pr.p, nullptr);
             }
-            int rc2 = pcg_solve(e, tol, std::max(1, max_it), std::max(1, opt->pcg_min_iterations), &pr);
+            int rc2 = pcg_solve(e, tol, std::max(1, max_it), std::max(1, opt->pcg_min_iterations), &pr, resume);
             if (rc2) return rc2;
             // back-substitution: dm = -Cinv (gm + E^T dc) = -Linv^T (zm + Es^T dc)
             rc2 = schur_gather(e, e->px.p, e->w.p, nullptr);
@@ -861,7 +875,7 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
                 pr.rel = pr.ok ? std::sqrt(std::max(h[SC_REL2], 0.0)) : 1.0;
                 e->pcg_result_pending = false;
             }
-            sum->pcg_iterations += pr.iterations;
+            sum->pcg_iterations += pr.iterations - its_before;   // a resumed solve reports the total of both launches
             CU(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); t_solve += ms * 1e-3;
             CU(cudaEventElapsedTime(&ms, e->ev[3], e->ev[4])); t_cost += ms * 1e-3;
             sum->num_cost_evaluations += 1;
@@ -1171,6 +1185,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     auto& c = e->coarse;
     c.available = false;
     c.active = false;
+    c.why = "no cameras";
     const int64_t Nc = e->Nc, Ncl = e->Ncl, Nm = e->Nm;
     if (Nc == 0) return VMM_BA_OK;
     std::vector<int> act;
@@ -1180,6 +1195,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     if (have_ahead) act.swap(ahead->act);
     else for (int64_t i = 0; i < Nc; ++i) if (cam_count[i] > 0) act.push_back((int)i);
     const int target = coarse_leaf_target(e->coarse_cams_per_cluster, act.size());
+    c.why = "fewer than two clusters of cameras (" + std::to_string(act.size()) + " active cameras, " + std::to_string(target) + " per cluster)";
     if ((int64_t)act.size() < 2 * (int64_t)target) return VMM_BA_OK;   // one cluster = the gauge mode of a single block: nothing to gain
     if (have_ahead) { ctr.swap(ahead->ctr); leaves.swap(ahead->leaves); }
     else {
@@ -1225,6 +1241,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
         CU(cudaMemcpyAsync(cnt.data(), d_cnt.p, sizeof(int) * Nm, cudaMemcpyDeviceToHost, e->stream));
         CU(cudaMemcpyAsync(&h_over, d_over.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
         CU(cudaStreamSynchronize(e->stream));
+        c.why = "a marker is seen from more than " + std::to_string(kCoarseMaxTouched) + " clusters";
         if (h_over) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
     } else {
         // sharded: every rank lists the clusters its own observations touch (same kernel), the lists are all-gathered and
@@ -1262,6 +1279,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
                 }
             }
         }
+        c.why = "a marker is seen from more than " + std::to_string(kCoarseMaxTouched) + " clusters";
         if (overflow) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off (the same verdict on every rank)
         DevBuf<unsigned char>& d_map = c.d_map;
         CU(d_map.alloc(map.size()));
@@ -1293,6 +1311,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     CU(up(c.xbar.p, xbar.data(), sizeof(double) * 3 * ncl));
     CU(cudaStreamSynchronize(e->stream));
     c.available = true;
+    c.why.clear();
     return build_pcg_units(e, ncl, cl_ptr, cl_cams, tag_active /* unused with clusters */);
 }
 
@@ -1464,6 +1483,185 @@ int refresh_problem(vmm_ba_engine* e, const double* cam_q, const double* cam_t, 
 }
 }  // namespace
 
+namespace {
+// Breadth-first levels of the co-observation graph of the markers with columns (two markers are adjacent when one camera
+// sees both), component by component from a pseudo-peripheral start.  cam_ptr / otag: the camera order of the device.
+// level_of[j] = -1 for markers without columns.  Returns the number of levels.
+int marker_bfs_levels(int64_t ncam, const std::vector<int>& cam_ptr, const std::vector<int>& otag, int64_t nm,
+                      const std::vector<unsigned char>& active, std::vector<int>& level_of) {
+    std::vector<int> mk_ptr(nm + 1, 0), mk_cams(otag.size());
+    for (int j : otag) mk_ptr[j + 1]++;
+    for (int64_t j = 0; j < nm; ++j) mk_ptr[j + 1] += mk_ptr[j];
+    {
+        std::vector<int> fill(mk_ptr.begin(), mk_ptr.end() - 1);
+        for (int64_t i = 0; i < ncam; ++i)
+            for (int s = cam_ptr[i]; s < cam_ptr[i + 1]; ++s) mk_cams[fill[otag[s]]++] = (int)i;
+    }
+    level_of.assign(nm, -1);
+    std::vector<unsigned char> seen_c(ncam, 0);
+    std::vector<int> frontier, next, touched_m, touched_c;
+    // one sweep from `start`: levels base, base + 1, ...; returns the last marker reached and the number of levels
+    auto sweep = [&](int start, int base, int& last) {
+        frontier.assign(1, start);
+        level_of[start] = base;
+        touched_m.assign(1, start);
+        touched_c.clear();
+        int lev = base;
+        while (!frontier.empty()) {
+            next.clear();
+            for (int u : frontier)
+                for (int q = mk_ptr[u]; q < mk_ptr[u + 1]; ++q) {
+                    const int i = mk_cams[q];
+                    if (seen_c[i]) continue;
+                    seen_c[i] = 1;
+                    touched_c.push_back(i);
+                    for (int s = cam_ptr[i]; s < cam_ptr[i + 1]; ++s) {
+                        const int v = otag[s];
+                        if (!active[v] || level_of[v] >= 0) continue;
+                        level_of[v] = lev + 1;
+                        next.push_back(v);
+                        touched_m.push_back(v);
+                    }
+                }
+            if (!next.empty()) { ++lev; last = next.back(); }
+            frontier.swap(next);
+        }
+        return lev - base + 1;
+    };
+    int nlevels = 0;
+    for (int64_t j0 = 0; j0 < nm; ++j0) {
+        if (!active[j0] || level_of[j0] >= 0) continue;
+        int start = (int)j0, last = (int)j0;
+        for (int probe = 0; probe < 2; ++probe) {   // pseudo-peripheral start: the far end of two successive sweeps
+            sweep(start, 0, last);
+            start = last;
+            for (int v : touched_m) level_of[v] = -1;
+            for (int c : touched_c) seen_c[c] = 0;
+        }
+        nlevels += sweep(start, nlevels, last);
+    }
+    return nlevels;
+}
+
+int launch_sweep_invert(vmm_ba_engine* e, double* M, int n, double* Pt, double* Qt, int* info, unsigned* bar) {
+    CU(cudaMemsetAsync(bar, 0, 4 * sizeof(unsigned), e->stream));
+    static const int kid = register_kernel("k_coarse_sweep_invert");
+    cudaEvent_t eb = nullptr;
+    if (e->profiling) eb = profile_begin(e);
+    int nP = n, ld = n;
+    void* args[] = { &M, &nP, &ld, &Pt, &Qt, &info, &bar };
+    CU(cudaLaunchCooperativeKernel((const void*)k_coarse_sweep_invert, dim3(e->sp_grid), dim3(kInvThreads), args, kInvSmemBytes, e->stream));
+    if (eb) profile_end(e, kid, eb);
+    ++e->launches;
+    return VMM_BA_OK;
+}
+
+// Site-scale covariance: block-tridiagonal selected inversion over the breadth-first levels (ba_cov_block.cuh).
+// The caller has linearised at the current poses (e->B, e->C, e->Et valid).
+int covariance_block_tridiagonal(vmm_ba_engine* e, double* cov) {
+    const int nm = (int)e->Nm, nc = (int)e->Ncl;
+    std::vector<int> cam_ptr(nc + 1, 0), otag(std::max<int64_t>(e->Ntol, 1));
+    std::vector<unsigned char> active(nm);
+    if (nc > 0) CU(cudaMemcpyAsync(cam_ptr.data(), e->cam_ptr_dev.p, sizeof(int) * (nc + 1), cudaMemcpyDeviceToHost, e->stream));
+    if (e->Ntol > 0) CU(cudaMemcpyAsync(otag.data(), e->otag.p, sizeof(int) * e->Ntol, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(active.data(), e->tag_active.p, nm, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    otag.resize(e->Ntol);
+    std::vector<int> level_of;
+    const int nlevels = marker_bfs_levels(nc, cam_ptr, otag, nm, active, level_of);
+    std::vector<double> zero9((size_t)9 * nm, 0.0);
+    std::memcpy(cov, zero9.data(), sizeof(double) * 9 * nm);
+    if (nlevels == 0) return VMM_BA_OK;
+    // blocks = levels; a level of fewer than 32 markers joins its predecessor (consecutive levels stay block tridiagonal)
+    std::vector<int> count(nlevels, 0), block_of_level(nlevels, 0);
+    for (int j = 0; j < nm; ++j) if (level_of[j] >= 0) count[level_of[j]]++;
+    std::vector<int> bsize;
+    for (int l = 0; l < nlevels; ++l) {
+        if (l > 0 && count[l] < 32) bsize.back() += count[l];
+        else bsize.push_back(count[l]);
+        block_of_level[l] = (int)bsize.size() - 1;
+    }
+    const int nb = (int)bsize.size();
+    std::vector<int> ld(nb), fill(nb, 0);
+    std::vector<CovPlace> place(nm, CovPlace{ -1, 0 });
+    for (int j = 0; j < nm; ++j) if (level_of[j] >= 0) { const int b = block_of_level[level_of[j]]; place[j] = CovPlace{ b, 6 * fill[b]++ }; }
+    size_t total = 0, max_ld = 0, max_sub = 0;
+    std::vector<size_t> off_d(nb), off_s(nb, 0);
+    for (int b = 0; b < nb; ++b) { ld[b] = (6 * bsize[b] + kInvNB - 1) / kInvNB * kInvNB; max_ld = std::max<size_t>(max_ld, ld[b]); }
+    for (int b = 0; b < nb; ++b) {
+        off_d[b] = total; total += (size_t)ld[b] * ld[b];
+        if (b + 1 < nb) { off_s[b] = total; total += (size_t)ld[b + 1] * ld[b]; max_sub = std::max(max_sub, (size_t)ld[b + 1] * ld[b]); }
+    }
+    const size_t scratch = 2 * max_sub + 2 * max_ld * kInvNB;   // T / U buffers and the panels of the inversion
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    if ((total + scratch) * sizeof(double) > free_b / 10 * 9)
+        return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "covariance: the block-tridiagonal factors need %.1f GB (largest level: %zu markers), %.1f GB are free",
+                         (total + scratch) * 8e-9, max_ld / 6, free_b * 1e-9);
+    DevBuf<double> store, work;
+    DevBuf<double*> d_diag, d_sub;
+    DevBuf<int> d_ld, info;
+    DevBuf<CovPlace> d_place;
+    DevBuf<unsigned> bar;
+    CU(store.alloc(total)); CU(work.alloc(scratch)); CU(d_diag.alloc(nb)); CU(d_sub.alloc(nb)); CU(d_ld.alloc(nb)); CU(info.alloc(2));
+    CU(d_place.alloc(nm)); CU(bar.alloc(4)); CU(e->cov_out.alloc((size_t)9 * nm));
+    std::vector<double*> h_diag(nb), h_sub(nb, nullptr);
+    for (int b = 0; b < nb; ++b) { h_diag[b] = store.p + off_d[b]; if (b + 1 < nb) h_sub[b] = store.p + off_s[b]; }
+    CU(cudaMemcpyAsync(d_diag.p, h_diag.data(), sizeof(double*) * nb, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(d_sub.p, h_sub.data(), sizeof(double*) * nb, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(d_ld.p, ld.data(), sizeof(int) * nb, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(d_place.p, place.data(), sizeof(CovPlace) * nm, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemsetAsync(store.p, 0, sizeof(double) * total, e->stream));
+    CU(cudaMemsetAsync(info.p, 0, 2 * sizeof(int), e->stream));
+    CU(cudaMemsetAsync(e->fail.p, 0, sizeof(int), e->stream));
+    CU(cudaMemsetAsync(e->cov_out.p, 0, sizeof(double) * 9 * nm, e->stream));
+    for (int b = 0; b < nb; ++b)
+        if (ld[b] > 6 * bsize[b]) LAUNCH(k_pad_identity, 1, 64, 6 * bsize[b], ld[b], h_diag[b]);
+    if (nc > 0) {
+        LAUNCH(k_invert_blocks, nblocks(nc, 128), 128, nc, e->B.p, (const double*)nullptr, e->cam_active.p, e->Minv.p, e->fail.p);
+        if (e->Ntol > 0)
+            LAUNCH(k_covb_eliminate_cameras, nc, 128, e->cam_ptr_dev.p, e->otag.p, e->cpos.p, e->mptr.p, e->mtile.p, d_place.p, e->Minv.p, e->Et.p,
+                   d_diag.p, d_sub.p, d_ld.p, info.p + 1);
+    }
+    LAUNCH(k_covb_add_marker_blocks, nblocks((int64_t)nm * 36, kThreads), kThreads, nm, e->C.p, d_place.p, d_diag.p, d_ld.p);
+    double* Tbuf = work.p;
+    double* Ubuf = work.p + max_sub;
+    double* Pt = work.p + 2 * max_sub;
+    double* Qt = Pt + max_ld * kInvNB;
+    auto gemm = [&](int m, int n, int k, double alpha, const double* X, int ldx, int tx, const double* Y, int ldy, int ty, double beta, double* Cm, int ldc) {
+        const int tiles = (m / kInvNB) * (n / kInvNB);
+        LAUNCH_NAMED("k_dgemm64", k_dgemm64, std::min(tiles, 8 * e->sp_grid), kInvThreads, kGemmSmemBytes, m, n, k, alpha, X, ldx, tx, Y, ldy, ty, beta, Cm, ldc);
+    };
+    // forward: S_k in place of D_k, inverted in place; T_k = L_k S_k^-1 in place of L_k
+    for (int b = 0; b < nb; ++b) {
+        int rc = launch_sweep_invert(e, h_diag[b], ld[b], Pt, Qt, info.p, bar.p);
+        if (rc) return rc;
+        if (b + 1 < nb) {
+            gemm(ld[b + 1], ld[b], ld[b], 1.0, h_sub[b], ld[b], 0, h_diag[b], ld[b], 0, 0.0, Tbuf, ld[b]);                 // T = L S^-1
+            gemm(ld[b + 1], ld[b + 1], ld[b], -1.0, Tbuf, ld[b], 0, h_sub[b], ld[b], 1, 1.0, h_diag[b + 1], ld[b + 1]);     // D_{k+1} -= T L^T
+            CU(cudaMemcpyAsync(h_sub[b], Tbuf, sizeof(double) * (size_t)ld[b + 1] * ld[b], cudaMemcpyDeviceToDevice, e->stream));
+        }
+    }
+    // backward: G_k in place of S_k^-1
+    for (int b = nb - 1; b >= 0; --b) {
+        if (b + 1 < nb) {
+            gemm(ld[b + 1], ld[b], ld[b + 1], 1.0, h_diag[b + 1], ld[b + 1], 0, h_sub[b], ld[b], 0, 0.0, Ubuf, ld[b]);     // U = G_{k+1} T
+            gemm(ld[b], ld[b], ld[b + 1], 1.0, h_sub[b], ld[b], 1, Ubuf, ld[b], 0, 1.0, h_diag[b], ld[b]);                  // G_k = S^-1 + T^T U
+        }
+        LAUNCH(k_covb_collect, nblocks(nm, 128), 128, nm, b, d_place.p, h_diag[b], ld[b], e->cov_out.p);
+    }
+    int h_info[2] = { 0, 0 }, h_fail = 0;
+    CU(cudaMemcpyAsync(h_info, info.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(&h_fail, e->fail.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(cov, e->cov_out.p, sizeof(double) * 9 * nm, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    if (e->profiling) profile_resolve(e);
+    if (h_info[1]) return fail_with(e, VMM_BA_ERR_NUMERIC, "covariance: markers more than one level apart share a camera (internal error)");
+    if (h_info[0] || h_fail) return fail_with(e, VMM_BA_ERR_NUMERIC, "the normal equations are rank deficient (pivot info %d): no covariance", h_info[0]);
+    return VMM_BA_OK;
+}
+}  // namespace
+
 // =====================================================================================
 // C ABI
 // =====================================================================================
@@ -1487,7 +1685,8 @@ void vmm_ba_options_init(vmm_ba_options* o) {
     o->jacobi_scaling = 1;
     o->preconditioner = VMM_BA_PRECOND_TWO_LEVEL;   // block-Jacobi + rigid-motion coarse space over camera clusters (falls back to
                                                     // block-Jacobi when the problem has fewer than two clusters or is sharded)
-    o->pcg_tolerance = 5e-2;   // forcing term of the inexact Newton step (Ceres' own default for iterative solvers, eta, is 1e-1)
+    o->pcg_tolerance = 1e-2;   // forcing term of the inexact Newton step.  5e-2 (round 1) took c3/8 into a different local minimum
+                               // (one camera 0.34 rad off, cost +3.8e-5: profiles/r02_convergence.md); Ceres' eta default is 1e-1
     o->pcg_max_iterations = 500;
     o->pcg_min_iterations = 1;
     o->parity_mode = 0;
@@ -1495,7 +1694,7 @@ void vmm_ba_options_init(vmm_ba_options* o) {
     o->pcg_parity_max_iterations = 20000;
     o->verbose = 0;
     o->coarse_refresh_iterations = 8;
-    o->pcg_confirm_tolerance = 1e-4;
+    o->pcg_confirm_tolerance = 1e-3;
 }
 
 int vmm_ba_abi_version(void) { return VMM_BA_ABI_VERSION; }
@@ -1530,6 +1729,8 @@ static int create_common(int device, vmm_ba_engine** out) {
                            (const void*)k_pcg_persistent, (const void*)k_pcg_persistent_dist<true>, (const void*)k_pcg_persistent_dist<false> })
         if ((err = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmemBytes)) != cudaSuccess)
             return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaFuncSetAttribute(shared memory %zu): %s", kSpSmemBytes, cudaGetErrorString(err));
+    if ((err = cudaFuncSetAttribute((const void*)k_dgemm64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes)) != cudaSuccess)
+        return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaFuncSetAttribute(k_dgemm64): %s", cudaGetErrorString(err));
     if ((err = cudaFuncSetAttribute((const void*)k_coarse_sweep_invert, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kInvSmemBytes)) != cudaSuccess)
         return fail_with(nullptr, VMM_BA_ERR_CUDA, "cudaFuncSetAttribute(k_coarse_sweep_invert): %s", cudaGetErrorString(err));
     e = new vmm_ba_engine();
@@ -2079,13 +2280,26 @@ int vmm_ba_reprojection_error_sums(vmm_ba_handle e, double* out) {
 }
 
 int vmm_ba_marker_translation_covariance(vmm_ba_handle e, int loss_kind, double loss_scale, double* cov) {
+    return vmm_ba_marker_translation_covariance_ex(e, loss_kind, loss_scale, VMM_BA_COV_AUTO, cov);
+}
+
+int vmm_ba_marker_translation_covariance_ex(vmm_ba_handle e, int loss_kind, double loss_scale, int method, double* cov) {
     if (!e || !cov) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "null argument");
     if (!e->have_problem || !e->have_intrinsics) return fail_with(e, VMM_BA_ERR_STATE, "set_intrinsics and set_problem must be called first");
     if (e->world != 1) return fail_with(e, VMM_BA_ERR_STATE, "vmm_ba_marker_translation_covariance needs a single-GPU engine");
     if (loss_kind < 0 || loss_kind > 2 || !(loss_scale > 0)) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "bad loss");
-    const int64_t kMaxMarkers = 4096;   // dense marker-reduced system: (6 Nm)^2 doubles, twice
-    if (e->Nm > kMaxMarkers) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "covariance is limited to %lld markers (dense reduced system)", (long long)kMaxMarkers);
+    if (method < VMM_BA_COV_AUTO || method > VMM_BA_COV_BLOCK_TRIDIAGONAL) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "bad covariance method");
+    const int64_t kMaxMarkers = 4096;   // dense marker-reduced system: (6 Nm)^2 doubles
+    if (method == VMM_BA_COV_AUTO) method = e->Nm <= 1024 ? VMM_BA_COV_DENSE : VMM_BA_COV_BLOCK_TRIDIAGONAL;
+    if (method == VMM_BA_COV_DENSE && e->Nm > kMaxMarkers)
+        return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "the dense covariance route is limited to %lld markers", (long long)kMaxMarkers);
     CU(cudaSetDevice(e->device));
+    if (method == VMM_BA_COV_BLOCK_TRIDIAGONAL) {
+        prepare_poses(e, e->cur);
+        int rc0 = linearize(e, e->cur, loss_kind, loss_scale);
+        if (rc0) return rc0;
+        return covariance_block_tridiagonal(e, cov);
+    }
     // dense marker-reduced normal matrix R = C - sum_i E_i^T B_i^-1 E_i (cameras eliminated), order 6 Nm padded to the block
     // order of the inversion kernel; inverted in place by the blocked sweep operator (ba_coarse_inv.cuh — the kernel that
     // inverts the coarse matrix of the preconditioner; no library call), the covariance blocks are its diagonal 3x3 blocks.
@@ -2195,6 +2409,7 @@ int vmm_ba_debug_coarse_matrix(vmm_ba_handle e, int loss_kind, double loss_scale
     if (e->world != 1) return fail_with(e, VMM_BA_ERR_STATE, "vmm_ba_debug_coarse_matrix is a single-GPU test entry");
     *order = e->coarse.available ? e->coarse.nC : 0;
     *leading_dimension = e->coarse.available ? e->coarse.ldc : 0;
+    if (!e->coarse.available) e->last_error = "no coarse space: " + e->coarse.why;
     if (!e->coarse.available || !matrix || !inverse) return VMM_BA_OK;
     const int64_t need = (int64_t)e->coarse.ldc * e->coarse.ldc;
     if (capacity < need) return fail_with(e, VMM_BA_ERR_INVALID_ARGUMENT, "buffers must hold %lld doubles", (long long)need);
@@ -2245,8 +2460,20 @@ int vmm_ba_profile_enable(vmm_ba_handle e, int on) {
     CU(cudaStreamSynchronize(e->stream));
     profile_resolve(e);
     e->profiling = on != 0;
+    if (e->pcgp.phase_ns.p && on) CU(cudaMemsetAsync(e->pcgp.phase_ns.p, 0, 8 * sizeof(unsigned long long), e->stream));
     std::fill(e->prof_ms.begin(), e->prof_ms.end(), 0.0);
     std::fill(e->prof_n.begin(), e->prof_n.end(), 0);
+    return VMM_BA_OK;
+}
+
+int vmm_ba_pcg_phase_ns(vmm_ba_handle e, double* out5) {
+    if (!e || !out5) return VMM_BA_ERR_INVALID_ARGUMENT;
+    for (int k = 0; k < 5; ++k) out5[k] = 0.0;
+    if (!e->pcgp.phase_ns.p) return VMM_BA_OK;
+    CU(cudaSetDevice(e->device));
+    unsigned long long h[8];
+    CU(cudaMemcpy(h, e->pcgp.phase_ns.p, sizeof(h), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 5; ++k) out5[k] = (double)h[k];
     return VMM_BA_OK;
 }
 

@@ -39,7 +39,7 @@ struct PcgArgs {
     const SpSeg* segs; const int* cta_seg; int nseg; const int2* slot_desc; int nslots_total;
     const unsigned char* Es; const int* mo_cam;
     // units
-    const PcgUnit* units; const int* cta_unit; const int* unit_cams;
+    const PcgUnit* units; const int* cta_unit; const int* unit_cams; int nunits;
     // camera-space data
     const double* Minv; const double* B; const double* lam;
     double *x, *r, *z, *p, *q;
@@ -56,6 +56,9 @@ struct PcgArgs {
     unsigned* barrier;        // [0] arrivals, [1] generation, [2] abort flag (grid_barrier)
     int max_it, min_it;
     double tol2;
+    int resume;               // 1: continue the solve the previous launch stopped (same system, tighter tolerance): x, r, z, p and the
+                              //    scalars it left in `result` are taken up where they were
+    unsigned long long* phase_ns;   // optional (debug / bench): CTA 0 accumulates the time of the phases A, B, C, D, barriers excluded [0..3], barriers [4]
 };
 
 // bar[0] arrivals, bar[1] generation, bar[2] abort flag.  A CTA that polls for more than ~2 s (a lost CTA: the launch was
@@ -110,126 +113,214 @@ __device__ __forceinline__ double cta_sum(double v, double* s_red) {
     return t;
 }
 
-// Phase B of one unit.  first: x = 0, r is the right-hand side (no p, q yet).
-__device__ __forceinline__ double pcg_update_unit(const PcgArgs& A, const PcgUnit u, bool first, double alpha, double* s_v, double* s_c,
-                                                  double* s_tot, int unit_index, bool coarse) {
+// ---- phases B and D: the CTA's units one after the other, the inputs of the NEXT unit requested before the current one is
+// worked on (the passes are short chains of dependent L2 accesses and block barriers: unpipelined they cost 3-4 us each) ----
+struct PcgUpdateIn {
+    PcgUnit u;
+    int cam;
+    double xv, pv, rv, qv;
+    double2 m0, m1, m2;   // row a of M^-1
+    double R0, R1, R2;    // column k of R_i (coarse restriction)
+};
+__device__ __forceinline__ void pcg_update_load(const PcgArgs& A, int ui, bool first, bool coarse, PcgUpdateIn& in) {
+    const int4 d = __ldg(reinterpret_cast<const int4*>(A.units) + ui);
+    in.u = PcgUnit{ d.x, d.y, d.z, d.w };
     const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
-    const bool valid = cs < u.count;
-    int cam = 0;
-    double rv = 0.0;
-    size_t idx = 0;
-    if (valid) {
-        cam = __ldg(A.unit_cams + u.first + cs);
-        idx = (size_t)cam * 6 + a;
-        if (first) {
-            A.x[idx] = 0.0;
-            rv = A.r[idx];
-        } else {
-            A.x[idx] += alpha * A.p[idx];
-            rv = A.r[idx] - alpha * __ldcg(A.q + idx);
-            A.r[idx] = rv;
-        }
-    }
-    __syncthreads();   // s_v / s_c of the previous unit are no longer read
-    s_v[t] = rv;
-    __syncthreads();
-    double rz = 0.0, contrib = 0.0;
-    const bool restrict_unit = coarse && u.cluster >= 0;   // uniform for the CTA
-    if (valid) {
-        const double* rr = s_v + cs * 6;
-        const double zt = row_dot6(A.Minv + idx * 6, rr);
-        A.z[idx] = zt;
-        rz = zt * rv;
-        if (restrict_unit) {
-            // column k of R_i against the translation (a < 3) or rotation (a >= 3) half of r: V = sum R^T r_t, W = sum R^T r_theta
+    in.cam = -1;
+    if (cs < in.u.count) {
+        in.cam = __ldg(A.unit_cams + in.u.first + cs);
+        const size_t idx = (size_t)in.cam * 6 + a;
+        in.rv = A.r[idx];
+        if (!first) { in.xv = A.x[idx]; in.pv = A.p[idx]; in.qv = A.q[idx]; }
+        const double2* m = reinterpret_cast<const double2*>(A.Minv + idx * 6);
+        in.m0 = __ldg(m); in.m1 = __ldg(m + 1); in.m2 = __ldg(m + 2);
+        if (coarse && in.u.cluster >= 0) {
             const int k = a < 3 ? a : a - 3;
-            const double* R = A.camP + (size_t)cam * CAM_PREP;
-            const double* r3 = rr + (a < 3 ? 0 : 3);
-            contrib = __ldg(R + k) * r3[0] + __ldg(R + 3 + k) * r3[1] + __ldg(R + 6 + k) * r3[2];
+            const double* R = A.camP + (size_t)in.cam * CAM_PREP;
+            in.R0 = R[k]; in.R1 = R[3 + k]; in.R2 = R[6 + k];
         }
     }
-    if (restrict_unit) {
-        s_c[t] = contrib;
+}
+
+// x += alpha p, r -= alpha q, z = M^-1 r, restriction partials of the CTA's units; returns the thread's share of r.z
+__device__ __noinline__ double pcg_phase_update(const PcgArgs& A, int ub, int ue, bool first, double alpha, bool coarse, double* s_v, double* s_c,
+                                                   double* s_tot) {
+    const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
+    double rz = 0.0;
+    PcgUpdateIn cur, nxt;
+    if (ub < ue) pcg_update_load(A, ub, first, coarse, cur);
+    for (int ui = ub; ui < ue; ++ui) {
+        if (ui + 1 < ue) pcg_update_load(A, ui + 1, first, coarse, nxt);
+        const bool valid = cur.cam >= 0;
+        const size_t idx = (size_t)max(cur.cam, 0) * 6 + a;
+        double rv = 0.0;
+        if (valid) {
+            if (first) {
+                A.x[idx] = 0.0;
+                rv = cur.rv;
+            } else {
+                A.x[idx] = cur.xv + alpha * cur.pv;
+                rv = cur.rv - alpha * cur.qv;
+                A.r[idx] = rv;
+            }
+        }
+        __syncthreads();   // s_v / s_c of the previous unit are no longer read
+        s_v[t] = rv;
         __syncthreads();
-        // 96 threads: component a2 = t / 16 summed over 16 parts of 5 cameras, then over the half-warp
-        if (t < 96) {
-            const int a2 = t >> 4, part = t & 15;
-            double s = 0.0;
+        const bool restrict_unit = coarse && cur.u.cluster >= 0;   // uniform for the CTA
+        double contrib = 0.0;
+        if (valid) {
+            const double* rr = s_v + cs * 6;
+            const double zt = cur.m0.x * rr[0] + cur.m0.y * rr[1] + cur.m1.x * rr[2] + cur.m1.y * rr[3] + cur.m2.x * rr[4] + cur.m2.y * rr[5];
+            A.z[idx] = zt;
+            rz += zt * rv;
+            if (restrict_unit) {
+                // column k of R_i against the translation (a < 3) or rotation (a >= 3) half of r: V = sum R^T r_t, W = sum R^T r_theta
+                const double* r3 = rr + (a < 3 ? 0 : 3);
+                contrib = cur.R0 * r3[0] + cur.R1 * r3[1] + cur.R2 * r3[2];
+            }
+        }
+        if (restrict_unit) {
+            s_c[t] = contrib;
+            __syncthreads();
+            // 96 threads: component a2 = t / 16 summed over 16 parts of 5 cameras, then over the half-warp
+            if (t < 96) {
+                const int a2 = t >> 4, part = t & 15;
+                double sum = 0.0;
 #pragma unroll
-            for (int i = 0; i < kUnitCams / 16; ++i) s += s_c[(part * (kUnitCams / 16) + i) * 6 + a2];
-            s += __shfl_xor_sync(0xffffffffu, s, 8);
-            s += __shfl_xor_sync(0xffffffffu, s, 4);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            if (part == 0) s_tot[a2] = s;
+                for (int i = 0; i < kUnitCams / 16; ++i) sum += s_c[(part * (kUnitCams / 16) + i) * 6 + a2];
+                sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+                sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+                sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+                sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                if (part == 0) s_tot[a2] = sum;
+            }
+            __syncthreads();
+            if (t < 6) {
+                // P^T r = [ -V ; -(V x xbar) - W / 2 ]
+                const double* xb = A.xbar + 3 * (size_t)cur.u.cluster;
+                const double V0 = s_tot[0], V1 = s_tot[1], V2 = s_tot[2];
+                double o;
+                if (t < 3) o = -s_tot[t];
+                else if (t == 3) o = -(V1 * xb[2] - V2 * xb[1]) - 0.5 * s_tot[3];
+                else if (t == 4) o = -(V2 * xb[0] - V0 * xb[2]) - 0.5 * s_tot[4];
+                else o = -(V0 * xb[1] - V1 * xb[0]) - 0.5 * s_tot[5];
+                A.rc_part[(size_t)ui * 6 + t] = o;
+            }
         }
-        __syncthreads();
-        if (t < 6) {
-            // P^T r = [ -V ; -(V x xbar) - W / 2 ]
-            const double* xb = A.xbar + 3 * (size_t)u.cluster;
-            const double V0 = s_tot[0], V1 = s_tot[1], V2 = s_tot[2];
-            double o;
-            if (t < 3) o = -s_tot[t];
-            else if (t == 3) o = -(V1 * xb[2] - V2 * xb[1]) - 0.5 * s_tot[3];
-            else if (t == 4) o = -(V2 * xb[0] - V0 * xb[2]) - 0.5 * s_tot[4];
-            else o = -(V0 * xb[1] - V1 * xb[0]) - 0.5 * s_tot[5];
-            A.rc_part[(size_t)unit_index * 6 + t] = o;
-        }
+        cur = nxt;
     }
     return rz;
 }
 
-// Phase D of one unit: p = z + P yc + beta p, q = (B + lambda) p; returns the thread's share of p.q
-__device__ __forceinline__ double pcg_direction_unit(const PcgArgs& A, const PcgUnit u, bool first, double beta, double* s_v, bool coarse) {
+struct PcgDirectionIn {
+    PcgUnit u;
+    int cam;
+    double zv, pv, lam;
+    double2 b0, b1, b2;   // row a of B
+    double R0, R1, R2;    // row k of R_i (coarse prolongation)
+};
+__device__ __forceinline__ void pcg_direction_load(const PcgArgs& A, int ui, bool first, bool coarse, PcgDirectionIn& in) {
+    const int4 d = __ldg(reinterpret_cast<const int4*>(A.units) + ui);
+    in.u = PcgUnit{ d.x, d.y, d.z, d.w };
     const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
-    const bool valid = cs < u.count;
-    double pv = 0.0;
-    size_t idx = 0;
-    if (valid) {
-        const int cam = __ldg(A.unit_cams + u.first + cs);
-        idx = (size_t)cam * 6 + a;
-        pv = A.z[idx];
-        if (u.cluster >= 0 && coarse) {
-            const double* y = A.yc + (size_t)u.cluster * 6;
-            const double* xb = A.xbar + 3 * (size_t)u.cluster;
+    in.cam = -1;
+    if (cs < in.u.count) {
+        in.cam = __ldg(A.unit_cams + in.u.first + cs);
+        const size_t idx = (size_t)in.cam * 6 + a;
+        in.zv = A.z[idx];
+        if (!first) in.pv = A.p[idx];
+        in.lam = __ldg(A.lam + idx);
+        const double2* b = reinterpret_cast<const double2*>(A.B + idx * 6);
+        in.b0 = __ldg(b); in.b1 = __ldg(b + 1); in.b2 = __ldg(b + 2);
+        if (coarse && in.u.cluster >= 0) {
             const int k = a < 3 ? a : a - 3;
-            const double* R = A.camP + (size_t)cam * CAM_PREP + 3 * k;
-            const double y3 = __ldcg(y + 3), y4 = __ldcg(y + 4), y5 = __ldcg(y + 5);
-            if (a >= 3) {
-                pv += -0.5 * (__ldg(R) * y3 + __ldg(R + 1) * y4 + __ldg(R + 2) * y5);
-            } else {
-                const double ux = __ldcg(y) + (xb[1] * y5 - xb[2] * y4);
-                const double uy = __ldcg(y + 1) + (xb[2] * y3 - xb[0] * y5);
-                const double uz = __ldcg(y + 2) + (xb[0] * y4 - xb[1] * y3);
-                pv += -(__ldg(R) * ux + __ldg(R + 1) * uy + __ldg(R + 2) * uz);
-            }
+            const double* R = A.camP + (size_t)in.cam * CAM_PREP + 3 * k;
+            in.R0 = R[0]; in.R1 = R[1]; in.R2 = R[2];
         }
-        if (!first) pv += beta * A.p[idx];
-        A.p[idx] = pv;
     }
-    __syncthreads();
-    s_v[t] = pv;
-    __syncthreads();
+}
+
+// p = z + P yc + beta p, q = (B + lambda) p over the CTA's units; returns the thread's share of p.q
+__device__ __noinline__ double pcg_phase_direction(const PcgArgs& A, int ub, int ue, bool first, double beta, bool coarse, double* s_v) {
+    const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
     double pq = 0.0;
-    if (valid) {
-        const double qt = __ldg(A.lam + idx) * pv + row_dot6(A.B + idx * 6, s_v + cs * 6);
-        A.q[idx] = qt;
-        pq = qt * pv;
+    PcgDirectionIn cur, nxt;
+    // the coarse correction of a cluster as the thread needs it: u = y_tau + xbar x y_theta (rows 0-2) or y_theta (rows 3-5);
+    // consecutive units mostly share their cluster, so this is reloaded rarely
+    int cl_cached = -1;
+    double u0 = 0.0, u1 = 0.0, u2 = 0.0;
+    if (ub < ue) pcg_direction_load(A, ub, first, coarse, cur);
+    for (int ui = ub; ui < ue; ++ui) {
+        if (ui + 1 < ue) pcg_direction_load(A, ui + 1, first, coarse, nxt);
+        const bool valid = cur.cam >= 0;
+        const size_t idx = (size_t)max(cur.cam, 0) * 6 + a;
+        double pv = 0.0;
+        if (valid) {
+            pv = cur.zv;
+            if (coarse && cur.u.cluster >= 0) {
+                if (cur.u.cluster != cl_cached) {
+                    cl_cached = cur.u.cluster;
+                    const double* y = A.yc + (size_t)cl_cached * 6;
+                    const double y3 = y[3], y4 = y[4], y5 = y[5];
+                    if (a >= 3) {
+                        u0 = y3; u1 = y4; u2 = y5;
+                    } else {
+                        const double* xb = A.xbar + 3 * (size_t)cl_cached;
+                        const double x0 = __ldg(xb), x1 = __ldg(xb + 1), x2 = __ldg(xb + 2);
+                        u0 = y[0] + (x1 * y5 - x2 * y4);
+                        u1 = y[1] + (x2 * y3 - x0 * y5);
+                        u2 = y[2] + (x0 * y4 - x1 * y3);
+                    }
+                }
+                pv += (a >= 3 ? -0.5 : -1.0) * (cur.R0 * u0 + cur.R1 * u1 + cur.R2 * u2);
+            }
+            if (!first) pv += beta * cur.pv;
+            A.p[idx] = pv;
+        }
+        __syncthreads();
+        s_v[t] = pv;
+        __syncthreads();
+        if (valid) {
+            const double* pp = s_v + cs * 6;
+            const double qt = cur.lam * pv + cur.b0.x * pp[0] + cur.b0.y * pp[1] + cur.b1.x * pp[2] + cur.b1.y * pp[3] + cur.b2.x * pp[4] + cur.b2.y * pp[5];
+            A.q[idx] = qt;
+            pq += qt * pv;
+        }
+        cur = nxt;
     }
     return pq;
 }
 
-// Phase C: rc = sum of the unit partials (every CTA forms the whole vector in shared memory), then the rows of
-// A_c^-1 rc this CTA's warps own.  Returns (in every thread) the CTA's share of rc . yc.
-__device__ __forceinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_rc, double* s_red) {
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+// The passes of the streamed product as real calls: each keeps the register allocation it has as a kernel of its own
+// instead of sharing one with the vector phases.
+template <int MODE>
+__device__ __noinline__ void sp_pass_call(SpShared& sh, unsigned char* sp_ring, bool reinit, const SpSeg* segs, const int* cta_seg, int nseg,
+                                          const int2* slot_desc, int nslots_total, const unsigned char* Es, const int* mo_cam, const double* vin_c,
+                                          double* mvec, double sign, double* out_c, double* dot_acc) {
+    sp_pass<MODE, true>(sh, sp_ring, reinit, segs, cta_seg, nseg, slot_desc, nslots_total, Es, mo_cam, vin_c, mvec, sign, out_c, dot_acc);
+}
+
+// rc = sum of the unit partials: all partials into shared memory with independent loads, then summed per cluster.
+// s_rc: nC (+1) doubles; s_part: 6 per unit (both in the idle ring).
+__device__ __forceinline__ void pcg_assemble_rc(const PcgArgs& A, int nC, int nunits, double* s_rc, double* s_part) {
+    const int t = threadIdx.x;
+    for (int e = t; e < 6 * nunits; e += kSpThreads) s_part[e] = A.rc_part[e];
     __syncthreads();
-    for (int e = t; e < A.nC; e += kSpThreads) {
+    for (int e = t; e < nC; e += kSpThreads) {
         const int c = e / 6, comp = e - c * 6;
         double s = 0.0;
-        for (int u = __ldg(A.cl_unit_ptr + c); u < __ldg(A.cl_unit_ptr + c + 1); ++u) s += __ldcg(A.rc_part + (size_t)u * 6 + comp);
+        for (int u = __ldg(A.cl_unit_ptr + c); u < __ldg(A.cl_unit_ptr + c + 1); ++u) s += s_part[u * 6 + comp];
         s_rc[e] = s;
     }
+}
+
+// Phase C: every CTA forms the whole restricted residual in shared memory, then the rows of A_c^-1 rc this CTA's warps
+// own.  Returns (in every thread) the CTA's share of rc . yc.
+__device__ __noinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_rc, double* s_red) {
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    __syncthreads();
+    pcg_assemble_rc(A, A.nC, A.nunits, s_rc, s_rc + ((A.nC + 8) & ~1));
     __syncthreads();
     double dot = 0.0;
     const int nwarps = kSpThreads / 32;
@@ -238,7 +329,7 @@ __device__ __forceinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_r
         const double2* x2 = reinterpret_cast<const double2*>(s_rc);
         double s = 0.0;
         for (int k = lane; k < A.nC / 2; k += 32) {
-            const double2 av = __ldg(a2 + k), xv = x2[k];
+            const double2 av = a2[k], xv = x2[k];
             s += av.x * xv.x + av.y * xv.y;
         }
         s = warp_sum(s);
@@ -261,75 +352,107 @@ k_pcg_persistent(const PcgArgs A) {
     double* s_rc = reinterpret_cast<double*>(sp_ring);   // phase C scratch: the ring is idle between products
     const unsigned G = gridDim.x;
     const int ub = A.cta_unit[blockIdx.x], ue = A.cta_unit[blockIdx.x + 1];
-    const PcgUnit* units = A.units;
     volatile double* scal = A.scal;
     bool aborted = false;
+    unsigned long long t_prev = 0;
+    // phase clock (CTA 0, thread 0; only when the host asked for it): time since the previous tick into slot `k`
+    auto tick = [&](int k) {
+        if (A.phase_ns && blockIdx.x == 0 && threadIdx.x == 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (k >= 0) A.phase_ns[k] += now - t_prev;
+            t_prev = now;
+        }
+    };
     int it = 0, iterations = 0;
     bool ok = true, ring_used = false;
-    double rel2 = 1.0, rz0 = 0.0;
+    double rel2 = 1.0, rz0 = 0.0, rz_last = 0.0, rz_before = 0.0;
 
-    // ---- start: z = M^-1 r, r.z, restriction; coarse solve; first direction ----
-    {
-        double rz = 0.0;
-        for (int u = ub; u < ue; ++u) rz += pcg_update_unit(A, units[u], true, 0.0, s_v, s_c, s_tot, u, coarse);
-        rz = cta_sum(rz, s_red);
-        if (threadIdx.x == 0) red_add(A.scal + PS_RZ, rz);
-    }
-    if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
-    if (coarse) {
-        const double d = pcg_coarse_apply(A, s_rc, s_red);
-        if (threadIdx.x == 0) red_add(A.scal + PS_RZ, d);
+    int it_base = 0;
+    if (!A.resume) {
+        // ---- start: z = M^-1 r, r.z, restriction; coarse solve; first direction ----
+        {
+            double rz = pcg_phase_update(A, ub, ue, true, 0.0, coarse, s_v, s_c, s_tot);
+            rz = cta_sum(rz, s_red);
+            if (threadIdx.x == 0) red_add(A.scal + PS_RZ, rz);
+        }
+        if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+        if (coarse) {
+            const double d = pcg_coarse_apply(A, s_rc, s_red);
+            if (threadIdx.x == 0) red_add(A.scal + PS_RZ, d);
+            if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+        }
+        {
+            double pq = pcg_phase_direction(A, ub, ue, true, 0.0, coarse, s_v);
+            pq = cta_sum(pq, s_red);
+            if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
+        }
+        if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+        rz0 = scal[PS_RZ];
+    } else {
+        // ---- resume: the stopped solve had x, r, z updated and yc formed, but not the direction ----
+        rz0 = __ldcg(A.result + SC_RZ0);
+        const double rz_new = __ldcg(A.result + SC_RZ), rz_prev = __ldcg(A.result + SC_RZ + 1);
+        it_base = (int)__ldcg(A.result + SC_ITERS);
+        if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }   // every CTA has read the old scalars
+        if (blockIdx.x == 0 && threadIdx.x == 0) A.scal[PS_RZ] = rz_new;
+        {
+            double pq = pcg_phase_direction(A, ub, ue, false, rz_prev != 0.0 ? rz_new / rz_prev : 0.0, coarse, s_v);
+            pq = cta_sum(pq, s_red);
+            if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
+        }
         if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
     }
-    {
-        double pq = 0.0;
-        for (int u = ub; u < ue; ++u) pq += pcg_direction_unit(A, units[u], true, 0.0, s_v, coarse);
-        pq = cta_sum(pq, s_red);
-        if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
-    }
-    if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
     rz0 = scal[PS_RZ];
     ok = isfinite(rz0);
     if (ok && rz0 > 0.0) {
+        tick(-1);
         for (it = 0; it < A.max_it; ++it) {
             double* row = A.scal + (size_t)it * PS_STRIDE;
             double* nxt = row + PS_STRIDE;
             // ---- A: q -= Es Es^T p ----
-            sp_pass<SP_FULL, true>(sh, sp_ring, ring_used, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr,
+            sp_pass_call<SP_FULL>(sh, sp_ring, ring_used, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr,
                                    -1.0, A.q, row + PS_WW);
             ring_used = true;
+            tick(0);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            tick(4);
             // ---- B ----
             const double rz_s = scal[(size_t)it * PS_STRIDE + PS_RZ];
             const double denom = scal[(size_t)it * PS_STRIDE + PS_PBP] - scal[(size_t)it * PS_STRIDE + PS_WW];
             const double alpha = (rz_s != 0.0) ? rz_s / denom : 0.0;
             {
-                double rz = 0.0;
-                for (int u = ub; u < ue; ++u) rz += pcg_update_unit(A, units[u], false, alpha, s_v, s_c, s_tot, u, coarse);
+                double rz = pcg_phase_update(A, ub, ue, false, alpha, coarse, s_v, s_c, s_tot);
                 rz = cta_sum(rz, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, rz);
             }
+            tick(1);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            tick(4);
             // ---- C ----
             if (coarse) {
                 const double d = pcg_coarse_apply(A, s_rc, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, d);
+                tick(2);
                 if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+                tick(4);
             }
             // ---- D ----
             const double rz_new = scal[(size_t)(it + 1) * PS_STRIDE + PS_RZ];
+            rz_last = rz_new; rz_before = rz_s;
             iterations = it + 1;
             rel2 = rz_new / rz0;
             if (!isfinite(rz_new)) { ok = false; break; }
             if (iterations >= A.min_it && rz_new <= A.tol2 * rz0) break;
             const double beta = (rz_s != 0.0) ? rz_new / rz_s : 0.0;
             {
-                double pq = 0.0;
-                for (int u = ub; u < ue; ++u) pq += pcg_direction_unit(A, units[u], false, beta, s_v, coarse);
+                double pq = pcg_phase_direction(A, ub, ue, false, beta, coarse, s_v);
                 pq = cta_sum(pq, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
             }
+            tick(3);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            tick(4);
         }
     } else if (ok) {
         rel2 = 0.0;   // zero right-hand side: x = 0 is the solution
@@ -338,7 +461,9 @@ finish:
     if (aborted) ok = false;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         A.result[SC_RZ0] = rz0;
-        A.result[SC_ITERS] = (double)iterations;
+        A.result[SC_RZ] = rz_last;          // for a resumed launch: r.z at the stop and the one before it
+        A.result[SC_RZ + 1] = rz_before;
+        A.result[SC_ITERS] = (double)(it_base + iterations);
         A.result[SC_REL2] = ok ? rel2 : nan("");
         A.result[SC_DONE] = 1.0;
     }

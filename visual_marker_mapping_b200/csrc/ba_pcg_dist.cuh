@@ -68,15 +68,6 @@ __device__ __forceinline__ double pcg_fixed_dot(const double* s_rc, const double
     return t;
 }
 
-// The three passes of the streamed product as real calls: each keeps the register allocation it has as a kernel of its
-// own instead of sharing one with the other two and the vector phases (inlined: 550 bytes of spills).
-template <int MODE>
-__device__ __noinline__ void sp_pass_call(SpShared& sh, unsigned char* sp_ring, bool reinit, const SpSeg* segs, const int* cta_seg, int nseg,
-                                          const int2* slot_desc, int nslots_total, const unsigned char* Es, const int* mo_cam, const double* vin_c,
-                                          double* mvec, double sign, double* out_c, double* dot_acc) {
-    sp_pass<MODE, true>(sh, sp_ring, reinit, segs, cta_seg, nseg, slot_desc, nslots_total, Es, mo_cam, vin_c, mvec, sign, out_c, dot_acc);
-}
-
 // X1: wb = sum over ranks of wbl (+ two scalars in the tail).  Returns the thread's share of sum wb_i^2.
 template <bool SHARDED>
 __device__ __forceinline__ double pcg_exchange_boundary(const PcgDistArgs& D, unsigned seq, double tail0, double tail1) {
@@ -109,16 +100,13 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     __syncthreads();
     if (!SHARDED || (int)blockIdx.x < D.world) {
-        // this rank's restricted residual from the unit partials
-        for (int e = t; e <= nC; e += kSpThreads) {
-            double s = rz_local;
-            if (e < nC) {
-                const int c = e / 6, comp = e - c * 6;
-                s = 0.0;
-                for (int u = __ldg(A.cl_unit_ptr + c); u < __ldg(A.cl_unit_ptr + c + 1); ++u) s += __ldcg(A.rc_part + (size_t)u * 6 + comp);
-            }
-            if (SHARDED) st_word_pair(x2_slot(D, (int)blockIdx.x, (int)(seq & 1u), D.rank) + e, s, seq);
-            else s_rc[e] = s;
+        // this rank's restricted residual from the unit partials (tail: its r.z partial)
+        pcg_assemble_rc(A, nC, A.nunits, s_rc, s_rc + ((nC + 8) & ~1));
+        if (t == 0) s_rc[nC] = rz_local;
+        __syncthreads();
+        if (SHARDED) {
+            for (int e = t; e <= nC; e += kSpThreads) st_word_pair(x2_slot(D, (int)blockIdx.x, (int)(seq & 1u), D.rank) + e, s_rc[e], seq);
+            __syncthreads();   // s_rc is overwritten with the sums over ranks next
         }
     }
     if (SHARDED) {
@@ -136,7 +124,7 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
         const double2* x2 = reinterpret_cast<const double2*>(s_rc);
         double s = 0.0;
         for (int k = lane; k < nC / 2; k += 32) {
-            const double2 av = __ldg(a2 + k), xv = x2[k];
+            const double2 av = a2[k], xv = x2[k];
             s += av.x * xv.x + av.y * xv.y;
         }
         s = warp_sum(s);
@@ -155,7 +143,6 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
     double* s_rc = reinterpret_cast<double*>(sp_ring);   // restricted residual (+ tail): the ring is idle between products
     const unsigned G = gridDim.x;
     const int ub = A.cta_unit[blockIdx.x], ue = A.cta_unit[blockIdx.x + 1];
-    const PcgUnit* units = A.units;
     const int nC = coarse ? A.nC : 0;
     const bool boundary = D.n_wb > 0;
     volatile double* scal = A.scal;
@@ -167,8 +154,7 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
 
     // ---- start ----
     {
-        double rz = 0.0;
-        for (int u = ub; u < ue; ++u) rz += pcg_update_unit(A, units[u], true, 0.0, s_v, s_c, s_tot, u, coarse);
+        double rz = pcg_phase_update(A, ub, ue, true, 0.0, coarse, s_v, s_c, s_tot);
         rz = cta_sum(rz, s_red);
         if (threadIdx.x == 0) red_add(A.scal + PS_RZ, rz);
         if (boundary) for (int i = blockIdx.x * kSpThreads + threadIdx.x; i < D.n_wb; i += G * kSpThreads) D.wbl[i] = 0.0;
@@ -178,8 +164,7 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
     if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
     rz0 = s_rc[nC] + pcg_fixed_dot(s_rc, A.yc, nC, s_red);
     {
-        double pq = 0.0;
-        for (int u = ub; u < ue; ++u) pq += pcg_direction_unit(A, units[u], true, 0.0, s_v, coarse);
+        double pq = pcg_phase_direction(A, ub, ue, true, 0.0, coarse, s_v);
         pq = cta_sum(pq, s_red);
         if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
     }
@@ -220,8 +205,7 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
             // ---- B ----
             const double alpha = (rz_s != 0.0) ? rz_s / (pbp_tot - ww_tot) : 0.0;
             {
-                double rz = 0.0;
-                for (int u = ub; u < ue; ++u) rz += pcg_update_unit(A, units[u], false, alpha, s_v, s_c, s_tot, u, coarse);
+                double rz = pcg_phase_update(A, ub, ue, false, alpha, coarse, s_v, s_c, s_tot);
                 rz = cta_sum(rz, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, rz);
                 if (boundary) for (int i = blockIdx.x * kSpThreads + threadIdx.x; i < D.n_wb; i += G * kSpThreads) D.wbl[i] = 0.0;
@@ -239,8 +223,7 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
             const double beta = (rz_s != 0.0) ? rz_new / rz_s : 0.0;
             rz_s = rz_new;
             {
-                double pq = 0.0;
-                for (int u = ub; u < ue; ++u) pq += pcg_direction_unit(A, units[u], false, beta, s_v, coarse);
+                double pq = pcg_phase_direction(A, ub, ue, false, beta, coarse, s_v);
                 pq = cta_sum(pq, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
             }

@@ -331,8 +331,9 @@ __device__ __forceinline__ void scatter_e_z(const double2 (&E)[18], const double
 #endif
     }
 }
-// COHERENT: the vector changes during the kernel's lifetime (persistent PCG): read it from L2 (ld.cg), never through the
-// non-coherent path.
+// COHERENT: the vector changes during the kernel's lifetime (persistent PCG).  Plain (L1-cached, coherent) loads: the
+// acquire of the grid barrier that precedes the pass invalidates this SM's L1, so the entries are fetched from L2 once per
+// pass and then shared by the ~40 observations of a camera; the non-coherent path (ld.global.nc) must not be used.
 template <bool COHERENT>
 __device__ __forceinline__ void load_x6(const double* __restrict__ v, int cam, double (&x)[6]) {
 #ifdef VMM_SP_NO_X    // timing experiment only (tools/): results are wrong
@@ -341,7 +342,7 @@ __device__ __forceinline__ void load_x6(const double* __restrict__ v, int cam, d
     const double2* x2 = reinterpret_cast<const double2*>(v + (size_t)cam * 6);
 #endif
 #pragma unroll
-    for (int i = 0; i < 3; ++i) { const double2 t = COHERENT ? __ldcg(x2 + i) : __ldg(x2 + i); x[2 * i] = t.x; x[2 * i + 1] = t.y; }
+    for (int i = 0; i < 3; ++i) { const double2 t = COHERENT ? x2[i] : __ldg(x2 + i); x[2 * i] = t.x; x[2 * i + 1] = t.y; }
 }
 // lane's block inside a ring slot (tile = lane / 8, row = lane % 8)
 __device__ __forceinline__ void slot_load_e(const unsigned char* slot, int lane, double2 (&E)[18]) {
@@ -485,7 +486,7 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
             if (v0) load_x6<COHERENT>(vin_c, c0, x0);
         } else {
 #pragma unroll
-            for (int b = 0; b < 6; ++b) z[b] = COHERENT ? __ldcg(mvec + (size_t)j * 6 + b) : __ldg(mvec + (size_t)j * 6 + b);
+            for (int b = 0; b < 6; ++b) z[b] = COHERENT ? mvec[(size_t)j * 6 + b] : __ldg(mvec + (size_t)j * 6 + b);
         }
         d_cur = d_nxt;
         if (s + 2 * kSpGroups < se) d_nxt = __ldg(seg4 + s + 2 * kSpGroups);

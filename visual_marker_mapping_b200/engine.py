@@ -18,6 +18,7 @@ from . import _build
 LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY = 0, 1, 2
 CONVERGENCE, NO_CONVERGENCE, FAILURE = 0, 1, 2
 PRECOND_JACOBI, PRECOND_SCHUR_JACOBI, PRECOND_TWO_LEVEL = 0, 1, 2
+COV_AUTO, COV_DENSE, COV_BLOCK_TRIDIAGONAL = 0, 1, 2
 
 # every symbol include/vmm_ba.h declares
 ABI_SYMBOLS = [
@@ -25,9 +26,9 @@ ABI_SYMBOLS = [
     "vmm_ba_create_distributed", "vmm_ba_nccl_unique_id", "vmm_ba_destroy", "vmm_ba_last_error",
     "vmm_ba_set_stream", "vmm_ba_set_intrinsics", "vmm_ba_set_problem", "vmm_ba_set_poses",
     "vmm_ba_get_poses", "vmm_ba_get_step", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
-    "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_schur_multiply", "vmm_ba_debug_coarse_matrix", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
+    "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_marker_translation_covariance_ex", "vmm_ba_schur_multiply", "vmm_ba_debug_coarse_matrix", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
     "vmm_ba_kernel_launches", "vmm_ba_h2d_bytes", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
-    "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
+    "vmm_ba_pcg_phase_ns", "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
 ]
 
 
@@ -133,6 +134,7 @@ def load_library():
     lib.vmm_ba_evaluate_device.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp]
     lib.vmm_ba_reprojection_error_sums.argtypes = [C.c_void_p, dp]
     lib.vmm_ba_marker_translation_covariance.argtypes = [C.c_void_p, C.c_int, C.c_double, dp]
+    lib.vmm_ba_marker_translation_covariance_ex.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, dp]
     lib.vmm_ba_set_coarse_cluster_size.argtypes = [C.c_void_p, C.c_int]
     lib.vmm_ba_schur_multiply.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.vmm_ba_debug_coarse_matrix.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int64, dp, dp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -143,6 +145,7 @@ def load_library():
     lib.vmm_ba_measure_fp64_peak.argtypes = [C.c_void_p, dp]
     lib.vmm_ba_measure_copy_bandwidth.argtypes = [C.c_void_p, C.c_size_t, dp]
     lib.vmm_ba_nccl_unique_id.argtypes = [C.c_void_p, C.c_size_t]
+    lib.vmm_ba_pcg_phase_ns.argtypes = [C.c_void_p, dp]
     lib.vmm_ba_profile_enable.argtypes = [C.c_void_p, C.c_int]
     lib.vmm_ba_profile_kernel_name.restype = C.c_char_p
     lib.vmm_ba_profile_kernel_name.argtypes = [C.c_int]
@@ -318,10 +321,10 @@ class BundleAdjuster:
         self._check(self._lib.vmm_ba_reprojection_error_sums(self._h, _dp(out)))
         return out
 
-    def marker_translation_covariance(self, loss_kind=LOSS_NONE, loss_scale=1.0) -> np.ndarray:
+    def marker_translation_covariance(self, loss_kind=LOSS_NONE, loss_scale=1.0, method=COV_AUTO) -> np.ndarray:
         """3x3 blocks of (J^T J)^-1 of every marker's translation at the current poses: [n_markers, 3, 3]."""
         out = np.zeros((self.n_markers, 3, 3))
-        self._check(self._lib.vmm_ba_marker_translation_covariance(self._h, int(loss_kind), float(loss_scale), _dp(out)))
+        self._check(self._lib.vmm_ba_marker_translation_covariance_ex(self._h, int(loss_kind), float(loss_scale), int(method), _dp(out)))
         return out
 
     def schur_multiply(self, x, loss_kind=LOSS_NONE, loss_scale=1.0, radius=1e4, path=0) -> np.ndarray:
@@ -337,6 +340,7 @@ class BundleAdjuster:
         n, ld = C.c_int(0), C.c_int(0)
         self._check(self._lib.vmm_ba_debug_coarse_matrix(self._h, loss_kind, loss_scale, radius, 0, None, None, C.byref(n), C.byref(ld)))
         if n.value == 0:
+            self.coarse_unavailable_reason = self._lib.vmm_ba_last_error(self._h).decode()
             return None, None, 0
         a, inv = np.zeros((ld.value, ld.value)), np.zeros((ld.value, ld.value))
         self._check(self._lib.vmm_ba_debug_coarse_matrix(self._h, loss_kind, loss_scale, radius, a.size, _dp(a), _dp(inv), C.byref(n), C.byref(ld)))
@@ -370,6 +374,12 @@ class BundleAdjuster:
             if n.value:
                 out[self._lib.vmm_ba_profile_kernel_name(i).decode()] = (n.value, ms.value)
         return out
+
+    def pcg_phase_ns(self) -> dict:
+        """In-kernel phase clock of the persistent PCG since profile_enable(True) (CTA 0)."""
+        v = np.zeros(5)
+        self._check(self._lib.vmm_ba_pcg_phase_ns(self._h, _dp(v)))
+        return dict(zip(("product", "update_restrict", "coarse_matvec", "direction", "grid_barriers"), (float(x) for x in v)))
 
     def measure_fp64_peak(self) -> float:
         v = C.c_double(0)
