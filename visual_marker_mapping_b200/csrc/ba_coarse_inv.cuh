@@ -23,7 +23,7 @@ namespace vmm {
 constexpr int kInvNB = 64;
 constexpr int kInvThreads = 256;
 constexpr int kInvPitch = kInvNB + 1;   // shared-memory row pitch of the pivot block (odd: conflict-free columns)
-constexpr size_t kInvSmemBytes = sizeof(double) * ((size_t)kInvNB * kInvPitch + 2 * (size_t)kInvNB * kInvNB + kInvNB);
+constexpr size_t kInvSmemBytes = sizeof(double) * ((size_t)kInvNB * kInvPitch + 2 * (size_t)kInvNB * kInvNB + 2 * kInvNB);
 
 // element (i, j), i >= j, of the lower triangle
 __device__ __forceinline__ double* inv_at(double* M, int ld, int i, int j) { return M + (size_t)i * ld + j; }
@@ -39,35 +39,57 @@ __device__ __forceinline__ void inv_load_panel_block_T(const double* M, int ld, 
 }
 
 // In-place symmetric sweep of all 64 pivots of the block S (pitch kInvPitch): S <- -S^-1.  Returns false on a
-// non-positive pivot.
-__device__ __forceinline__ bool inv_sweep_block(double* S, double* col) {
-    __shared__ int s_bad;
-    if (threadIdx.x == 0) s_bad = 0;
-    const int ti = threadIdx.x / 16, tj = threadIdx.x % 16;   // 16 x 16 threads, 4 x 4 entries each (interleaved)
+// non-positive pivot.  Thread (ti, tj) keeps its 16 entries S[ti + 16 a][tj + 16 b] in registers for all 64 pivots; per
+// pivot only the pivot column travels through shared memory (double-buffered: one block barrier per pivot), and the
+// update is branch-free:  S_ij -= u_i d u_j  with u = the pivot column, u_p = piv - 1 (which turns row and column p into
+// d x the old values), then S_pp = -d.
+__device__ __forceinline__ bool inv_sweep_block(double* S, double* col /* 2 x 64 */) {
+    const int ti = threadIdx.x / 16, tj = threadIdx.x % 16;
+    double s[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) s[a][b] = S[(ti + 16 * a) * kInvPitch + tj + 16 * b];
+    bool good = true;
     for (int p = 0; p < kInvNB; ++p) {
+        double* c = col + (p & 1) * kInvNB;
+        const int pb = p >> 4, pj = p & 15;
+        if (tj == pj) {
+#pragma unroll
+            for (int b = 0; b < 4; ++b)
+                if (b == pb) {
+#pragma unroll
+                    for (int a = 0; a < 4; ++a) c[ti + 16 * a] = s[a][b];
+                }
+        }
         __syncthreads();
-        if (threadIdx.x < kInvNB) col[threadIdx.x] = S[threadIdx.x * kInvPitch + p];
-        __syncthreads();
-        const double piv = col[p];
-        if (!(piv > 0.0)) { if (threadIdx.x == 0) s_bad = 1; break; }   // uniform: every thread reads the same value
+        const double piv = c[p];
+        if (!(piv > 0.0)) { good = false; break; }   // uniform: every thread reads the same value
         const double d = 1.0 / piv;
+        double ui[4], uj[4];
 #pragma unroll
-        for (int a = 0; a < 4; ++a) {
-            const int i = ti + 16 * a;
+        for (int a = 0; a < 4; ++a) ui[a] = (ti + 16 * a == p) ? piv - 1.0 : c[ti + 16 * a];
 #pragma unroll
-            for (int b = 0; b < 4; ++b) {
-                const int j = tj + 16 * b;
-                double v;
-                if (i == p && j == p) v = -d;
-                else if (i == p) v = d * col[j];
-                else if (j == p) v = col[i] * d;
-                else v = S[i * kInvPitch + j] - col[i] * d * col[j];
-                S[i * kInvPitch + j] = v;
-            }
+        for (int b = 0; b < 4; ++b) uj[b] = d * ((tj + 16 * b == p) ? piv - 1.0 : c[tj + 16 * b]);
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) s[a][b] -= ui[a] * uj[b];
+        if (ti == pj && tj == pj) {
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b)
+                    if (a == pb && b == pb) s[a][b] = -d;
         }
     }
     __syncthreads();
-    return s_bad == 0;
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) S[(ti + 16 * a) * kInvPitch + tj + 16 * b] = s[a][b];
+    __syncthreads();
+    return good;
 }
 
 // C (64 x 64, registers: thread (ti, tj) owns rows ti*4.., cols tj*4..) = sum_k At[k][i] * Bt[k][j]
@@ -97,6 +119,7 @@ __device__ __forceinline__ void inv_tile_product(const double* At, const double*
 __global__ void __launch_bounds__(kInvThreads, 1)
 k_coarse_sweep_invert(double* __restrict__ M, int n, int ld, double* __restrict__ Pt, double* __restrict__ Qt, int* __restrict__ info,
                       unsigned* __restrict__ barrier) {
+    double* Dbuf = Qt + (size_t)n * kInvNB;   // 64 x 64 behind the Q panels: the next pivot block, inverted ahead by CTA 0
     extern __shared__ __align__(16) unsigned char inv_smem[];
     double* S = reinterpret_cast<double*>(inv_smem);       // pivot block / its negative inverse, pitch kInvPitch
     double* At = S + kInvNB * kInvPitch;                    // 64 x 64, k-major
@@ -106,16 +129,26 @@ k_coarse_sweep_invert(double* __restrict__ M, int n, int ld, double* __restrict_
     const unsigned G = gridDim.x;
     const int ti = threadIdx.x / 16, tj = threadIdx.x % 16;
     bool good = true;
+    const bool look = G > 1;   // look-ahead: CTA 0 updates and inverts the NEXT pivot block while the others update the tiles
     for (int K = 0; K < nb && good; ++K) {
-        // ---- pivot block: every CTA inverts it for itself ----
-        for (int e = threadIdx.x; e < kInvNB * kInvNB; e += kInvThreads) {
-            const int r = e / kInvNB, c = e % kInvNB;
-            const int i = K * kInvNB + max(r, c), j = K * kInvNB + min(r, c);
-            S[r * kInvPitch + c] = __ldcg(M + (size_t)i * ld + j);
+        if (K == 0 || !look) {
+            // ---- pivot block: every CTA inverts it for itself ----
+            for (int e = threadIdx.x; e < kInvNB * kInvNB; e += kInvThreads) {
+                const int r = e / kInvNB, c = e % kInvNB;
+                const int i = K * kInvNB + max(r, c), j = K * kInvNB + min(r, c);
+                S[r * kInvPitch + c] = __ldcg(M + (size_t)i * ld + j);
+            }
+            __syncthreads();
+            good = inv_sweep_block(S, col);   // S = -D
+            if (!good) { if (blockIdx.x == 0 && threadIdx.x == 0) *info = 1; break; }   // the same verdict in every CTA
+        } else {
+            // ---- pivot block: inverted by CTA 0 during the previous step ----
+            good = __ldcg(info) == 0;
+            if (!good) break;
+            __syncthreads();
+            for (int e = threadIdx.x; e < kInvNB * kInvNB; e += kInvThreads) S[(e / kInvNB) * kInvPitch + (e % kInvNB)] = __ldcg(Dbuf + e);
+            __syncthreads();
         }
-        __syncthreads();
-        good = inv_sweep_block(S, col);   // S = -D
-        if (!good) { if (blockIdx.x == 0 && threadIdx.x == 0) *info = 1; break; }   // the same verdict in every CTA
         // ---- panel: Q_I (old column block) and P_I = Q_I D for the block rows this CTA owns ----
         for (int I = blockIdx.x; I < nb; I += G) {
             if (I == K) continue;
@@ -138,7 +171,12 @@ k_coarse_sweep_invert(double* __restrict__ M, int n, int ld, double* __restrict_
         // ---- tiles: M_IJ -= P_I Q_J^T over the lower triangle without row / column K; panel and pivot written back ----
         const int m = nb - 1;                               // block indices without K
         const int ntiles = m * (m + 1) / 2;
-        for (int t = blockIdx.x; t < ntiles + nb; t += G) {
+        // the tile of the next pivot block (indices without K: K + 1 -> K) goes to CTA 0 alone, which then inverts it
+        const int t_ahead = (look && K + 1 < nb) ? K * (K + 1) / 2 + K : -1;
+        const int n_items = ntiles + nb - (t_ahead >= 0 ? 1 : 0);
+        const int first = t_ahead >= 0 ? (int)blockIdx.x - 1 : (int)blockIdx.x, step = t_ahead >= 0 ? (int)G - 1 : (int)G;
+        for (int it = (blockIdx.x == 0 && t_ahead >= 0) ? -1 : first; it < n_items; it += step) {
+            const int t = it < 0 ? t_ahead : ((t_ahead >= 0 && it >= t_ahead) ? it + 1 : it);
             if (t >= ntiles) {
                 // write-back of the panel block I (= t - ntiles) and, for I == K, of the pivot block
                 const int I = t - ntiles;
@@ -180,6 +218,21 @@ k_coarse_sweep_invert(double* __restrict__ M, int n, int ld, double* __restrict_
                         *dst = __ldcg(dst) - acc[a][b];
                     }
                 }
+            if (it < 0) {
+                // CTA 0: the freshly updated block (K+1, K+1) is the next pivot block — invert it now, off the critical path
+                __threadfence();
+                __syncthreads();
+                for (int e = threadIdx.x; e < kInvNB * kInvNB; e += kInvThreads) {
+                    const int r = e / kInvNB, c = e % kInvNB;
+                    const int i = (K + 1) * kInvNB + max(r, c), j = (K + 1) * kInvNB + min(r, c);
+                    S[r * kInvPitch + c] = __ldcg(M + (size_t)i * ld + j);
+                }
+                __syncthreads();
+                const bool ok_next = inv_sweep_block(S, col);
+                if (!ok_next && threadIdx.x == 0) *info = 1;
+                for (int e = threadIdx.x; e < kInvNB * kInvNB; e += kInvThreads) Dbuf[e] = S[(e / kInvNB) * kInvPitch + (e % kInvNB)];
+                break;   // CTA 0 takes no other item of this step
+            }
         }
         if (!grid_barrier(barrier, G)) return;
     }

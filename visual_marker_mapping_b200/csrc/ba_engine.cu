@@ -1301,7 +1301,7 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
     c.ldc = (c.nC + kInvNB - 1) / kInvNB * kInvNB;
     const size_t nP = (size_t)c.ldc;
     CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(nP * nP)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
-    CU(c.Pt.alloc(nP * kInvNB)); CU(c.Qt.alloc(nP * kInvNB)); CU(c.inv_barrier.alloc(4));
+    CU(c.Pt.alloc(nP * kInvNB)); CU(c.Qt.alloc((nP + kInvNB) * kInvNB)); CU(c.inv_barrier.alloc(4));
     CU(c.Wbuf.alloc(std::max<size_t>(36 * c.n_w, 1)));
     auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
     CU(up(c.cl_ptr.p, cl_ptr.data(), sizeof(int) * (ncl + 1)));
@@ -1592,7 +1592,7 @@ int covariance_block_tridiagonal(vmm_ba_engine* e, double* cov) {
         off_d[b] = total; total += (size_t)ld[b] * ld[b];
         if (b + 1 < nb) { off_s[b] = total; total += (size_t)ld[b + 1] * ld[b]; max_sub = std::max(max_sub, (size_t)ld[b + 1] * ld[b]); }
     }
-    const size_t scratch = 2 * max_sub + 2 * max_ld * kInvNB;   // T / U buffers and the panels of the inversion
+    const size_t scratch = 2 * max_sub + (2 * max_ld + kInvNB) * kInvNB;   // T / U buffers and the panels of the inversion (+ look-ahead block)
     size_t free_b = 0, total_b = 0;
     CU(cudaMemGetInfo(&free_b, &total_b));
     if ((total + scratch) * sizeof(double) > free_b / 10 * 9)
@@ -2311,7 +2311,7 @@ int vmm_ba_marker_translation_covariance_ex(vmm_ba_handle e, int loss_kind, doub
     DevBuf<int> info;
     DevBuf<unsigned> bar;
     CU(e->covR.alloc((size_t)n * n)); CU(e->cov_out.alloc((size_t)9 * nm));
-    CU(Pt.alloc((size_t)n * kInvNB)); CU(Qt.alloc((size_t)n * kInvNB)); CU(info.alloc(1)); CU(bar.alloc(4));
+    CU(Pt.alloc((size_t)n * kInvNB)); CU(Qt.alloc(((size_t)n + kInvNB) * kInvNB)); CU(info.alloc(1)); CU(bar.alloc(4));
     CU(cudaMemsetAsync(e->covR.p, 0, sizeof(double) * n * n, e->stream));
     CU(cudaMemsetAsync(e->fail.p, 0, sizeof(int), e->stream));
     CU(cudaMemsetAsync(info.p, 0, sizeof(int), e->stream));
