@@ -17,9 +17,12 @@ runs = [("parity ftol=1e-12", dict(parity_mode=1, function_tolerance=1e-12)),
         ("product default", dict()),
         ("product confirm=1e-4", dict(pcg_confirm_tolerance=1e-4)),
         ("product no-confirm", dict(pcg_confirm_tolerance=0.0)),
-        ("product pcg=2e-2", dict(pcg_tolerance=2e-2)),
+        ("polish 2e-2 below 1e-2", dict(pcg_polish_tolerance=2e-2)),
+        ("polish 5e-2 below 1e-2", dict(pcg_polish_tolerance=5e-2)),
+        ("polish 5e-2 below 1e-3", dict(pcg_polish_tolerance=5e-2, pcg_polish_threshold=1e-3)),
+        ("polish 1e-1 below 1e-2", dict(pcg_polish_tolerance=1e-1)),
+        ("early 3e-3, polish 5e-2", dict(pcg_tolerance=3e-3, pcg_polish_tolerance=5e-2)),
         ("product pcg=5e-2", dict(pcg_tolerance=5e-2)),
-        ("product pcg=3e-3", dict(pcg_tolerance=3e-3)),
         ("product ftol=1e-12", dict(function_tolerance=1e-12))]
 ref = None
 with pkg.BundleAdjuster(0) as ba:

@@ -156,8 +156,9 @@ struct vmm_ba_engine {
     DevBuf<int> fail;
     // persistent PCG (ba_pcg.cuh): units of at most kUnitCams cameras of one cluster, per-CTA unit ranges, scalar table
     struct PcgPlan {
-        DevBuf<PcgUnit> units;
-        DevBuf<int> cta_unit, unit_cams, cl_unit_ptr;
+        DevBuf<int> cta_unit /* per-CTA ranges of the camera list */, unit_cams /* cameras in cluster order */, cl_unit_ptr /* partials per cluster */;
+        DevBuf<int> cam_cl, cta_cl_first, cta_part;
+        int nparts = 0;
         DevBuf<double> rc_part, scal;
         DevBuf<unsigned> barrier;
         DevBuf<unsigned long long> phase_ns;   // 8: in-kernel phase clock of the persistent PCG (profiling only)
@@ -516,43 +517,64 @@ int coarse_setup(vmm_ba_engine* e, int slot, bool need_host_verdict, double* hos
     return VMM_BA_OK;
 }
 
-// Units of the persistent PCG kernel: the (active) local cameras cluster by cluster in runs of at most kUnitCams, every
-// CTA a contiguous range of units.  ncl == 0 (no coarse space for this problem): index order, cluster -1.
+// Plan of the persistent PCG kernel: the (active) local cameras in cluster order, every CTA a contiguous range of that
+// list, and per (CTA, cluster it touches) one restriction partial.  ncl == 0 (no coarse space for this problem): index
+// order, cluster -1.  (The name is round-2 history: the first version worked on "units" of 80 cameras.)
 int build_pcg_units(vmm_ba_engine* e, int ncl, const std::vector<int>& cl_ptr, const std::vector<int>& cl_cams, const std::vector<unsigned char>& cam_act) {
     auto& P = e->pcgp;
-    std::vector<PcgUnit> units;
-    std::vector<int> cams, cl_unit_ptr(ncl + 1, 0);
-    auto add_run = [&](int cluster, const int* list, int n) {
-        for (int o = 0; o < n; o += kUnitCams) {
-            units.push_back(PcgUnit{ cluster, (int)cams.size(), std::min(kUnitCams, n - o), 0 });
-            cams.insert(cams.end(), list + o, list + o + std::min(kUnitCams, n - o));
-        }
-    };
+    std::vector<int> cams, cam_cl;
     if (ncl > 0) {
-        for (int c = 0; c < ncl; ++c) {
-            cl_unit_ptr[c] = (int)units.size();
-            add_run(c, cl_cams.data() + cl_ptr[c], cl_ptr[c + 1] - cl_ptr[c]);
-        }
-        cl_unit_ptr[ncl] = (int)units.size();
+        cams.assign(cl_cams.begin(), cl_cams.begin() + cl_ptr[ncl]);
+        cam_cl.resize(cams.size());
+        for (int c = 0; c < ncl; ++c) std::fill(cam_cl.begin() + cl_ptr[c], cam_cl.begin() + cl_ptr[c + 1], c);
     } else {
-        std::vector<int> act;
-        for (int64_t i = 0; i < e->Ncl; ++i) if (cam_act[i]) act.push_back((int)i);
-        add_run(-1, act.data(), (int)act.size());
+        for (int64_t i = 0; i < e->Ncl; ++i) if (cam_act[i]) cams.push_back((int)i);
+        cam_cl.assign(cams.size(), -1);
     }
-    const int G = e->sp_grid;
-    std::vector<int> cta_unit(G + 1);
-    for (int b = 0; b <= G; ++b) cta_unit[b] = (int)((int64_t)units.size() * b / G);
-    P.nunits = (int)units.size();
+    const int G = e->sp_grid, n = (int)cams.size();
+    std::vector<int> cta_cam(G + 1), cta_cl_first(G, 0), cta_part(G + 1, 0), cl_part_ptr(ncl + 1, 0);
+    for (int b = 0; b <= G; ++b) cta_cam[b] = (int)((int64_t)n * b / G);
+    bool fits = true;
+    std::vector<int> per_cluster(std::max(ncl, 1), 0);
+    for (int b = 0; b < G; ++b) {
+        int slots = 0;
+        if (ncl > 0 && cta_cam[b] < cta_cam[b + 1]) {
+            cta_cl_first[b] = cam_cl[cta_cam[b]];
+            slots = cam_cl[cta_cam[b + 1] - 1] - cta_cl_first[b] + 1;
+            for (int c = cta_cl_first[b]; c < cta_cl_first[b] + slots; ++c) per_cluster[c]++;
+        }
+        fits = fits && slots <= kPcgMaxSlots;
+        cta_part[b + 1] = cta_part[b] + slots;
+    }
+    // the partials of a cluster are consecutive in (CTA, slot) order: a cluster is the last one of the first CTA that touches
+    // it, the only one of the CTAs in the middle and the first one of the last
+    for (int c = 0; c < ncl; ++c) cl_part_ptr[c + 1] = cl_part_ptr[c] + per_cluster[c];
+    if (ncl > 0) {
+        // (CTA, slot) order visits cluster c's partials at positions cl_part_ptr[c] ..: check the claim above once
+        std::vector<int> seen(ncl, 0);
+        for (int b = 0; b < G && fits; ++b)
+            for (int q = cta_part[b]; q < cta_part[b + 1]; ++q) {
+                const int c = cta_cl_first[b] + (q - cta_part[b]);
+                // empty clusters between two touched ones also get a (zero) partial, which keeps the numbering consecutive
+                fits = fits && q == cl_part_ptr[c] + seen[c]++;
+            }
+    }
+    P.nunits = fits ? std::max(n, 1) : 0;   // 0: this plan cannot be used (the multi-launch loop runs instead)
     P.with_clusters = ncl > 0;
-    CU(P.units.alloc(std::max<size_t>(units.size(), 1))); CU(P.unit_cams.alloc(std::max<size_t>(cams.size(), 1)));
-    CU(P.cta_unit.alloc(G + 1)); CU(P.cl_unit_ptr.alloc(ncl + 1)); CU(P.rc_part.alloc(std::max<size_t>(6 * units.size(), 1)));
+    P.nparts = cta_part[G];
+    CU(P.unit_cams.alloc(std::max<size_t>(cams.size(), 1))); CU(P.cam_cl.alloc(std::max<size_t>(cams.size(), 1)));
+    CU(P.cta_unit.alloc(G + 1)); CU(P.cta_cl_first.alloc(G)); CU(P.cta_part.alloc(G + 1)); CU(P.cl_unit_ptr.alloc(ncl + 1));
+    CU(P.rc_part.alloc(std::max<size_t>(6 * (size_t)P.nparts, 1)));
+    CU(cudaMemsetAsync(P.rc_part.p, 0, sizeof(double) * std::max<size_t>(6 * (size_t)P.nparts, 1), e->stream));
     if (!P.phase_ns.p) { CU(P.phase_ns.alloc(8)); CU(cudaMemsetAsync(P.phase_ns.p, 0, 8 * sizeof(unsigned long long), e->stream)); }
     if (!P.barrier.p) { CU(P.barrier.alloc(4)); CU(cudaMemsetAsync(P.barrier.p, 0, 4 * sizeof(unsigned), e->stream)); }
     auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
-    CU(up(P.units.p, units.data(), sizeof(PcgUnit) * units.size()));
     CU(up(P.unit_cams.p, cams.data(), sizeof(int) * cams.size()));
-    CU(up(P.cta_unit.p, cta_unit.data(), sizeof(int) * (G + 1)));
-    CU(up(P.cl_unit_ptr.p, cl_unit_ptr.data(), sizeof(int) * (ncl + 1)));
+    CU(up(P.cam_cl.p, cam_cl.data(), sizeof(int) * cam_cl.size()));
+    CU(up(P.cta_unit.p, cta_cam.data(), sizeof(int) * (G + 1)));
+    CU(up(P.cta_cl_first.p, cta_cl_first.data(), sizeof(int) * G));
+    CU(up(P.cta_part.p, cta_part.data(), sizeof(int) * (G + 1)));
+    CU(up(P.cl_unit_ptr.p, cl_part_ptr.data(), sizeof(int) * (ncl + 1)));
     CU(cudaStreamSynchronize(e->stream));   // host vectors go out of scope
     return VMM_BA_OK;
 }
@@ -570,11 +592,11 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, b
     PcgArgs a{};
     a.segs = e->seg_full.segs.p; a.cta_seg = e->seg_full.cta_seg.p; a.nseg = e->seg_full.count; a.slot_desc = e->seg_full.slots.p;
     a.nslots_total = e->seg_full.nslots; a.Es = e->Es.p; a.mo_cam = e->mo_cam.p;
-    a.units = P.units.p; a.cta_unit = P.cta_unit.p; a.unit_cams = P.unit_cams.p; a.nunits = P.nunits;
+    a.cams = P.unit_cams.p; a.cam_cl = P.cam_cl.p; a.cta_cam = P.cta_unit.p; a.cta_cl_first = P.cta_cl_first.p; a.cta_part = P.cta_part.p; a.nparts = P.nparts;
     a.Minv = e->Minv.p; a.B = e->B.p; a.lam = e->lam_c.p;
     a.x = e->px.p; a.r = e->pr.p; a.z = e->pz.p; a.p = e->pp.p; a.q = e->pq.p;
     a.ncl = two_level ? e->coarse.ncl : 0; a.nC = two_level ? e->coarse.nC : 0;
-    a.cl_unit_ptr = P.cl_unit_ptr.p; a.xbar = e->coarse.xbar.p; a.camP = e->camP[e->cur].p; a.Ainv = e->coarse.Ac.p;
+    a.cl_part_ptr = P.cl_unit_ptr.p; a.xbar = e->coarse.xbar.p; a.camP = e->camP[e->cur].p; a.Ainv = e->coarse.Ac.p;
     a.rc_part = P.rc_part.p; a.yc = e->coarse.yc.p; a.ldc = e->coarse.ldc; a.coarse_info = e->coarse.info.p;
     a.scal = P.scal.p; a.result = e->sc.p; a.barrier = P.barrier.p;
     a.max_it = max_it; a.min_it = min_it; a.tol2 = tol * tol;
@@ -622,7 +644,7 @@ bool pcg_persistent_eligible(const vmm_ba_engine* e) {
     static const bool legacy = std::getenv("VMM_BA_PCG_LEGACY") != nullptr;   // A/B: the five-launches-per-iteration loop of round 1
     if (legacy || e->pcgp.nunits == 0) return false;
     // the restricted residual and the unit partials are staged in the (idle) ring of the streamed product
-    if (sizeof(double) * ((size_t)(e->coarse.available ? e->coarse.nC : 0) + 16 + 6 * (size_t)e->pcgp.nunits) > kSpSmemBytes) return false;
+    if (sizeof(double) * ((size_t)(e->coarse.available ? e->coarse.nC : 0) + 16 + 6 * (size_t)e->pcgp.nparts) > kSpSmemBytes) return false;
     if (e->world == 1) return true;
     // sharded: the two per-iteration sums travel inside the kernel through the mapped peer buffers
     const size_t nC1 = (size_t)(e->coarse.available ? e->coarse.nC : 0) + 1;
@@ -775,6 +797,7 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
     e->coarse.active = false;   // every solve starts with a fresh coarse matrix
     bool coarse_fresh_known = false, coarse_refreshed = false;
     int pcg_fresh = 0, pcg_last = 0;
+    double last_relative_decrease = 1.0;   // of the cost, by the last accepted step
     if (!std::isfinite(x_cost)) {
         termination = VMM_BA_FAILURE;
         msg = "Initial cost is not finite.";
@@ -825,6 +848,7 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         }
         PcgResult pr{};
         double tol = opt->parity_mode ? opt->pcg_parity_tolerance : opt->pcg_tolerance;
+        if (!opt->parity_mode && opt->pcg_polish_tolerance > 0.0 && last_relative_decrease < opt->pcg_polish_threshold) tol = opt->pcg_polish_tolerance;
         const int max_it = opt->parity_mode ? opt->pcg_parity_max_iterations : opt->pcg_max_iterations;
         bool confirmed = opt->parity_mode || !(opt->pcg_confirm_tolerance > 0.0) || tol <= opt->pcg_confirm_tolerance;
         // The step of this iteration: PCG on the reduced system to `tol`, back-substitution, candidate poses and their
@@ -913,7 +937,11 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
         const double cost_change = x_cost - cand_cost;
         const bool param_conv = step_norm <= opt->parameter_tolerance * (x_norm + opt->parameter_tolerance);
         const bool func_conv = std::fabs(cost_change) <= opt->function_tolerance * x_cost;
-        if ((param_conv || func_conv) && !confirmed) {
+        // (an inexact step is never longer, and never lowers the model further, than the exact one: a test passed with a factor
+        // of ten to spare is taken as it is)
+        const bool clearly = (!func_conv || std::fabs(cost_change) <= 0.1 * opt->function_tolerance * x_cost) &&
+                             (!param_conv || step_norm <= 0.1 * opt->parameter_tolerance * (x_norm + opt->parameter_tolerance));
+        if ((param_conv || func_conv) && !confirmed && !clearly) {
             // an exact step might still move: repeat the test on a (nearly) exact step of the same system
             confirmed = true;
             tol = opt->pcg_confirm_tolerance;
@@ -937,6 +965,7 @@ int do_solve(vmm_ba_engine* e, const vmm_ba_options* opt, vmm_ba_summary* sum) {
             if (rc) return rc;
             CU(cudaEventElapsedTime(&ms, e->ev[0], e->ev[1])); t_lin += ms * 1e-3;
             sum->num_linearizations += 1;
+            last_relative_decrease = x_cost > 0.0 ? (x_cost - e->h_st[ST_COST]) / x_cost : 0.0;
             x_cost = e->h_st[ST_COST];
             gmax = std::max(e->h_st[ST_GMAX_CAM], e->h_st[ST_GMAX_MARK]);
             radius = radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * relative_decrease - 1.0, 3));
@@ -1203,116 +1232,131 @@ int build_clusters(vmm_ba_engine* e, const double* cam_q, const double* cam_t, c
         if (spatial_leaves) leaves = *spatial_leaves;   // sharded: the cameras are already numbered leaf by leaf (act[k] == k)
         else kd_leaves(act, ctr, target, leaves);
     }
-    const int ncl = (int)leaves.size();
-    if (ncl < 2) return VMM_BA_OK;
-    std::vector<int> cl_of_g(Nc, -1), cl_of(std::max<int64_t>(Ncl, 1), -1), cl_ptr(ncl + 1, 0), cl_cams;
-    std::vector<double> xbar(3 * (size_t)ncl, 0.0);
-    cl_cams.reserve(Ncl);
-    for (int cidx = 0; cidx < ncl; ++cidx) {
-        const auto [lo, hi] = leaves[cidx];
-        cl_ptr[cidx] = (int)cl_cams.size();
-        for (int k = lo; k < hi; ++k) {
-            const int g = act[k];
-            cl_of_g[g] = cidx;
-            for (int a = 0; a < 3; ++a) xbar[3 * (size_t)cidx + a] += ctr[3 * (size_t)g + a] / (hi - lo);
+    // One attempt with the given leaves; a marker whose cameras fall into more than kCoarseMaxTouched clusters makes it
+    // fail (`overflowed`), after which neighbouring leaves are merged in pairs (siblings of the k-d tree: the leaves
+    // are in depth-first order) and the attempt is repeated with half as many, twice as large clusters.
+    bool overflowed = false;
+    auto attempt = [&]() -> int {
+        overflowed = false;
+        const int ncl = (int)leaves.size();
+        if (ncl < 2) return VMM_BA_OK;
+        std::vector<int> cl_of_g(Nc, -1), cl_of(std::max<int64_t>(Ncl, 1), -1), cl_ptr(ncl + 1, 0), cl_cams;
+        std::vector<double> xbar(3 * (size_t)ncl, 0.0);
+        cl_cams.reserve(Ncl);
+        for (int cidx = 0; cidx < ncl; ++cidx) {
+            const auto [lo, hi] = leaves[cidx];
+            cl_ptr[cidx] = (int)cl_cams.size();
+            for (int k = lo; k < hi; ++k) {
+                const int g = act[k];
+                cl_of_g[g] = cidx;
+                for (int a = 0; a < 3; ++a) xbar[3 * (size_t)cidx + a] += ctr[3 * (size_t)g + a] / (hi - lo);
+            }
+            // this rank's cameras of the cluster, ascending (fixed summation order)
+            const size_t first = cl_cams.size();
+            for (int k = lo; k < hi; ++k)
+                if (act[k] >= e->cam0 && act[k] < e->cam1) cl_cams.push_back((int)(act[k] - e->cam0));
+            std::sort(cl_cams.begin() + first, cl_cams.end());
+            for (size_t q = first; q < cl_cams.size(); ++q) cl_of[cl_cams[q]] = cidx;
         }
-        // this rank's cameras of the cluster, ascending (fixed summation order)
-        const size_t first = cl_cams.size();
-        for (int k = lo; k < hi; ++k)
-            if (act[k] >= e->cam0 && act[k] < e->cam1) cl_cams.push_back((int)(act[k] - e->cam0));
-        std::sort(cl_cams.begin() + first, cl_cams.end());
-        for (size_t q = first; q < cl_cams.size(); ++q) cl_of[cl_cams[q]] = cidx;
-    }
-    cl_ptr[ncl] = (int)cl_cams.size();
-    std::vector<int> lst((size_t)Nm * kCoarseMaxTouched), cnt(Nm, 0);
-    std::vector<unsigned char> mo_lc;
-    CU(c.cl_of_cam.alloc(std::max<int64_t>(Ncl, 1)));
-    CU(c.mo_lc.alloc(std::max<size_t>((size_t)e->Ntol, 1)));
-    CU(cudaMemcpyAsync(c.cl_of_cam.p, cl_of.data(), sizeof(int) * Ncl, cudaMemcpyHostToDevice, e->stream));
-    if (e->world == 1) {
-        // one GPU: the marker-order arrays are on the device already — lists and positions are built there
-        auto& d_lists = c.d_lists; auto& d_cnt = c.d_cnt; auto& d_over = c.d_over;   // kept across set_problem calls
-        CU(d_lists.alloc((size_t)Nm * kCoarseMaxTouched)); CU(d_cnt.alloc(Nm)); CU(d_over.alloc(1));
-        CU(cudaMemsetAsync(d_over.p, 0, sizeof(int), e->stream));
-        LAUNCH(k_marker_cluster_lists, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, e->tag_active.p, e->mo_cam.p, c.cl_of_cam.p, d_lists.p, d_cnt.p,
-               c.mo_lc.p, d_over.p);
-        int h_over = 0;
-        CU(cudaMemcpyAsync(lst.data(), d_lists.p, sizeof(int) * lst.size(), cudaMemcpyDeviceToHost, e->stream));
-        CU(cudaMemcpyAsync(cnt.data(), d_cnt.p, sizeof(int) * Nm, cudaMemcpyDeviceToHost, e->stream));
-        CU(cudaMemcpyAsync(&h_over, d_over.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-        CU(cudaStreamSynchronize(e->stream));
-        c.why = "a marker is seen from more than " + std::to_string(kCoarseMaxTouched) + " clusters";
-        if (h_over) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off
-    } else {
-        // sharded: every rank lists the clusters its own observations touch (same kernel), the lists are all-gathered and
-        // merged in rank order — the same merged list on every rank — and the local positions are renumbered on the device
-        const int W = e->world;
-        const size_t per = (size_t)Nm * kCoarseMaxTouched + Nm + 1;   // lists | counts | overflow flag
-        CU(c.d_lists.alloc(per * W));
-        int* mine = c.d_lists.p + per * e->rank;
-        CU(cudaMemsetAsync(mine + per - 1, 0, sizeof(int), e->stream));
-        LAUNCH(k_marker_cluster_lists, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, e->tag_active.p, e->mo_cam.p, c.cl_of_cam.p, mine,
-               mine + (size_t)Nm * kCoarseMaxTouched, c.mo_lc.p, mine + per - 1);
-        {
-            const int nrc = nccl_api().AllGather(mine, c.d_lists.p, per, NCCL_INT32, e->comm, e->stream);
-            if (nrc) return nccl_check(e, nrc, "ncclAllGather");
-        }
-        std::vector<int> all(per * W);
-        CU(cudaMemcpyAsync(all.data(), c.d_lists.p, sizeof(int) * per * W, cudaMemcpyDeviceToHost, e->stream));
-        CU(cudaStreamSynchronize(e->stream));
-        std::vector<unsigned char> map((size_t)Nm * kCoarseMaxTouched, 0);
-        bool overflow = false;
-        for (int r = 0; r < W; ++r) overflow = overflow || all[per * r + per - 1] != 0;
-        for (int64_t j = 0; j < Nm && !overflow; ++j) {
-            int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
-            for (int r = 0; r < W && !overflow; ++r) {
-                const int* lr = all.data() + per * r + (size_t)j * kCoarseMaxTouched;
-                const int nr = all[per * r + (size_t)Nm * kCoarseMaxTouched + j];
-                for (int t = 0; t < nr; ++t) {
-                    int pos = 0;
-                    while (pos < cnt[j] && l[pos] != lr[t]) ++pos;
-                    if (pos == cnt[j]) {
-                        if (cnt[j] >= kCoarseMaxTouched) { overflow = true; break; }
-                        l[cnt[j]++] = lr[t];
+        cl_ptr[ncl] = (int)cl_cams.size();
+        std::vector<int> lst((size_t)Nm * kCoarseMaxTouched), cnt(Nm, 0);
+        std::vector<unsigned char> mo_lc;
+        CU(c.cl_of_cam.alloc(std::max<int64_t>(Ncl, 1)));
+        CU(c.mo_lc.alloc(std::max<size_t>((size_t)e->Ntol, 1)));
+        CU(cudaMemcpyAsync(c.cl_of_cam.p, cl_of.data(), sizeof(int) * Ncl, cudaMemcpyHostToDevice, e->stream));
+        if (e->world == 1) {
+            // one GPU: the marker-order arrays are on the device already — lists and positions are built there
+            auto& d_lists = c.d_lists; auto& d_cnt = c.d_cnt; auto& d_over = c.d_over;   // kept across set_problem calls
+            CU(d_lists.alloc((size_t)Nm * kCoarseMaxTouched)); CU(d_cnt.alloc(Nm)); CU(d_over.alloc(1));
+            CU(cudaMemsetAsync(d_over.p, 0, sizeof(int), e->stream));
+            LAUNCH(k_marker_cluster_lists, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, e->tag_active.p, e->mo_cam.p, c.cl_of_cam.p, d_lists.p, d_cnt.p,
+                   c.mo_lc.p, d_over.p);
+            int h_over = 0;
+            CU(cudaMemcpyAsync(lst.data(), d_lists.p, sizeof(int) * lst.size(), cudaMemcpyDeviceToHost, e->stream));
+            CU(cudaMemcpyAsync(cnt.data(), d_cnt.p, sizeof(int) * Nm, cudaMemcpyDeviceToHost, e->stream));
+            CU(cudaMemcpyAsync(&h_over, d_over.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+            CU(cudaStreamSynchronize(e->stream));
+            c.why = "a marker is seen from more than " + std::to_string(kCoarseMaxTouched) + " clusters";
+            if (h_over) { overflowed = true; return VMM_BA_OK; }   // a marker seen from too many clusters: coarser clusters next
+        } else {
+            // sharded: every rank lists the clusters its own observations touch (same kernel), the lists are all-gathered and
+            // merged in rank order — the same merged list on every rank — and the local positions are renumbered on the device
+            const int W = e->world;
+            const size_t per = (size_t)Nm * kCoarseMaxTouched + Nm + 1;   // lists | counts | overflow flag
+            CU(c.d_lists.alloc(per * W));
+            int* mine = c.d_lists.p + per * e->rank;
+            CU(cudaMemsetAsync(mine + per - 1, 0, sizeof(int), e->stream));
+            LAUNCH(k_marker_cluster_lists, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, e->tag_active.p, e->mo_cam.p, c.cl_of_cam.p, mine,
+                   mine + (size_t)Nm * kCoarseMaxTouched, c.mo_lc.p, mine + per - 1);
+            {
+                const int nrc = nccl_api().AllGather(mine, c.d_lists.p, per, NCCL_INT32, e->comm, e->stream);
+                if (nrc) return nccl_check(e, nrc, "ncclAllGather");
+            }
+            std::vector<int> all(per * W);
+            CU(cudaMemcpyAsync(all.data(), c.d_lists.p, sizeof(int) * per * W, cudaMemcpyDeviceToHost, e->stream));
+            CU(cudaStreamSynchronize(e->stream));
+            std::vector<unsigned char> map((size_t)Nm * kCoarseMaxTouched, 0);
+            bool overflow = false;
+            for (int r = 0; r < W; ++r) overflow = overflow || all[per * r + per - 1] != 0;
+            for (int64_t j = 0; j < Nm && !overflow; ++j) {
+                int* l = lst.data() + (size_t)j * kCoarseMaxTouched;
+                for (int r = 0; r < W && !overflow; ++r) {
+                    const int* lr = all.data() + per * r + (size_t)j * kCoarseMaxTouched;
+                    const int nr = all[per * r + (size_t)Nm * kCoarseMaxTouched + j];
+                    for (int t = 0; t < nr; ++t) {
+                        int pos = 0;
+                        while (pos < cnt[j] && l[pos] != lr[t]) ++pos;
+                        if (pos == cnt[j]) {
+                            if (cnt[j] >= kCoarseMaxTouched) { overflow = true; break; }
+                            l[cnt[j]++] = lr[t];
+                        }
+                        if (r == e->rank) map[(size_t)j * kCoarseMaxTouched + t] = (unsigned char)pos;
                     }
-                    if (r == e->rank) map[(size_t)j * kCoarseMaxTouched + t] = (unsigned char)pos;
                 }
             }
+            c.why = "a marker is seen from more than " + std::to_string(kCoarseMaxTouched) + " clusters";
+            if (overflow) { overflowed = true; return VMM_BA_OK; }   // (the same verdict on every rank)
+            DevBuf<unsigned char>& d_map = c.d_map;
+            CU(d_map.alloc(map.size()));
+            CU(cudaMemcpyAsync(d_map.p, map.data(), map.size(), cudaMemcpyHostToDevice, e->stream));
+            LAUNCH(k_remap_cluster_positions, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, d_map.p, c.mo_lc.p);
+            CU(cudaStreamSynchronize(e->stream));   // map goes out of scope
         }
-        c.why = "a marker is seen from more than " + std::to_string(kCoarseMaxTouched) + " clusters";
-        if (overflow) return VMM_BA_OK;   // a marker seen from everywhere: coarse level off (the same verdict on every rank)
-        DevBuf<unsigned char>& d_map = c.d_map;
-        CU(d_map.alloc(map.size()));
-        CU(cudaMemcpyAsync(d_map.p, map.data(), map.size(), cudaMemcpyHostToDevice, e->stream));
-        LAUNCH(k_remap_cluster_positions, nblocks(Nm, 4), 128, (int)Nm, e->mptr.p, d_map.p, c.mo_lc.p);
-        CU(cudaStreamSynchronize(e->stream));   // map goes out of scope
+        std::vector<int> mcl_ptr(Nm + 1, 0), mcl;
+        for (int64_t j = 0; j < Nm; ++j) {
+            mcl.insert(mcl.end(), lst.begin() + (size_t)j * kCoarseMaxTouched, lst.begin() + (size_t)j * kCoarseMaxTouched + cnt[j]);
+            mcl_ptr[j + 1] = (int)mcl.size();
+        }
+        c.ncl = ncl;
+        c.nC = 6 * ncl;
+        c.n_w = mcl.size();
+        const size_t n = (size_t)c.nC;
+        CU(c.cl_ptr.alloc(ncl + 1)); CU(c.cl_cams.alloc(std::max<size_t>(cl_cams.size(), 1)));
+        CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1)));
+        c.ldc = (c.nC + kInvNB - 1) / kInvNB * kInvNB;
+        const size_t nP = (size_t)c.ldc;
+        CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(nP * nP)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
+        CU(c.Pt.alloc(nP * kInvNB)); CU(c.Qt.alloc((nP + kInvNB) * kInvNB)); CU(c.inv_barrier.alloc(4));
+        CU(c.Wbuf.alloc(std::max<size_t>(36 * c.n_w, 1)));
+        auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
+        CU(up(c.cl_ptr.p, cl_ptr.data(), sizeof(int) * (ncl + 1)));
+        CU(up(c.cl_cams.p, cl_cams.data(), sizeof(int) * cl_cams.size()));
+        CU(up(c.mcl_ptr.p, mcl_ptr.data(), sizeof(int) * (Nm + 1)));
+        CU(up(c.mcl.p, mcl.data(), sizeof(int) * mcl.size()));
+        CU(up(c.xbar.p, xbar.data(), sizeof(double) * 3 * ncl));
+        CU(cudaStreamSynchronize(e->stream));
+        c.available = true;
+        c.why.clear();
+        return build_pcg_units(e, ncl, cl_ptr, cl_cams, tag_active /* unused with clusters */);
+    };
+    for (;;) {
+        const int rc = attempt();
+        if (rc || c.available || !overflowed || leaves.size() < 4) return rc;
+        std::vector<std::pair<int, int>> merged;
+        for (size_t k = 0; k + 1 < leaves.size(); k += 2) merged.push_back({ leaves[k].first, leaves[k + 1].second });
+        if (leaves.size() & 1) merged.back().second = leaves.back().second;
+        leaves.swap(merged);
     }
-    std::vector<int> mcl_ptr(Nm + 1, 0), mcl;
-    for (int64_t j = 0; j < Nm; ++j) {
-        mcl.insert(mcl.end(), lst.begin() + (size_t)j * kCoarseMaxTouched, lst.begin() + (size_t)j * kCoarseMaxTouched + cnt[j]);
-        mcl_ptr[j + 1] = (int)mcl.size();
-    }
-    c.ncl = ncl;
-    c.nC = 6 * ncl;
-    c.n_w = mcl.size();
-    const size_t n = (size_t)c.nC;
-    CU(c.cl_ptr.alloc(ncl + 1)); CU(c.cl_cams.alloc(std::max<size_t>(cl_cams.size(), 1)));
-    CU(c.mcl_ptr.alloc(Nm + 1)); CU(c.mcl.alloc(std::max<size_t>(mcl.size(), 1)));
-    c.ldc = (c.nC + kInvNB - 1) / kInvNB * kInvNB;
-    const size_t nP = (size_t)c.ldc;
-    CU(c.xbar.alloc(3 * (size_t)ncl)); CU(c.Ac.alloc(nP * nP)); CU(c.rc.alloc(n + 2)); CU(c.yc.alloc(n)); CU(c.info.alloc(1));
-    CU(c.Pt.alloc(nP * kInvNB)); CU(c.Qt.alloc((nP + kInvNB) * kInvNB)); CU(c.inv_barrier.alloc(4));
-    CU(c.Wbuf.alloc(std::max<size_t>(36 * c.n_w, 1)));
-    auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
-    CU(up(c.cl_ptr.p, cl_ptr.data(), sizeof(int) * (ncl + 1)));
-    CU(up(c.cl_cams.p, cl_cams.data(), sizeof(int) * cl_cams.size()));
-    CU(up(c.mcl_ptr.p, mcl_ptr.data(), sizeof(int) * (Nm + 1)));
-    CU(up(c.mcl.p, mcl.data(), sizeof(int) * mcl.size()));
-    CU(up(c.xbar.p, xbar.data(), sizeof(double) * 3 * ncl));
-    CU(cudaStreamSynchronize(e->stream));
-    c.available = true;
-    c.why.clear();
-    return build_pcg_units(e, ncl, cl_ptr, cl_cams, tag_active /* unused with clusters */);
 }
 
 // host mirror of perm_dev (camera-order position -> caller's tag-observation index), fetched when a
@@ -1695,6 +1739,8 @@ void vmm_ba_options_init(vmm_ba_options* o) {
     o->verbose = 0;
     o->coarse_refresh_iterations = 8;
     o->pcg_confirm_tolerance = 1e-3;
+    o->pcg_polish_tolerance = 0.0;
+    o->pcg_polish_threshold = 1e-2;
 }
 
 int vmm_ba_abi_version(void) { return VMM_BA_ABI_VERSION; }

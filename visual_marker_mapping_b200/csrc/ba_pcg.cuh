@@ -11,9 +11,9 @@
 //   C  yc = A_c^-1 P^T r              dense symmetric mat-vec, one warp per row, rows spread over the whole grid
 //   D  stop test; p = z + P yc + b p; q = (B + lambda) p; p.q
 //
-// Phases B and D work on *units*: at most kUnitCams cameras of one cluster of the coarse space (six threads per
-// camera, one pass of the CTA).  Every CTA owns a fixed, contiguous range of units, so x, r, z, p are only ever
-// touched by the CTA that owns them; q (reduced into by phase A of all CTAs), the restriction partials and yc cross
+// Phases B and D work on the cameras in cluster order: every CTA owns a fixed, contiguous range of that list (six lanes
+// per camera, five cameras per warp step, no block barrier inside the loops), so x, r, z, p are only ever touched by
+// the CTA that owns them; q (reduced into by phase A of all CTAs), the restriction partials and yc cross
 // CTAs and are read with ld.cg after the barrier.  The PCG scalars live in a table with one row per iteration
 // (zeroed by the host before the launch), so no accumulator is ever recycled inside the kernel.
 #pragma once
@@ -23,14 +23,7 @@
 
 namespace vmm {
 
-constexpr int kUnitCams = kSpThreads / 6;   // 80 cameras: one pass of the CTA's 480 threads
-
-struct __align__(16) PcgUnit {
-    int cluster;   // cluster of the coarse space (-1: none)
-    int first;     // position of the unit's first camera in the unit camera list
-    int count;     // cameras (<= kUnitCams)
-    int pad;
-};
+constexpr int kPcgMaxSlots = 16;   // clusters one CTA's camera range may touch (host: else the clusters are too small for this path)
 
 enum { PS_RZ = 0, PS_WW = 1, PS_PBP = 2, PS_STRIDE = 4 };   // scalar table: row k = (r.z, w.w, p.(B+lambda)p) of iteration k
 
@@ -38,17 +31,18 @@ struct PcgArgs {
     // streamed product (SP_FULL segment list)
     const SpSeg* segs; const int* cta_seg; int nseg; const int2* slot_desc; int nslots_total;
     const unsigned char* Es; const int* mo_cam;
-    // units
-    const PcgUnit* units; const int* cta_unit; const int* unit_cams; int nunits;
+    // cameras in cluster order (cluster of every position; -1 without a coarse space), per-CTA ranges of that list,
+    // per CTA its first cluster and the index of its first restriction partial
+    const int* cams; const int* cam_cl; const int* cta_cam; const int* cta_cl_first; const int* cta_part; int nparts;
     // camera-space data
     const double* Minv; const double* B; const double* lam;
     double *x, *r, *z, *p, *q;
     // coarse level (ncl == 0: block-Jacobi only)
     int ncl, nC, ldc;         // ldc: leading dimension of Ainv (nC rounded up to the inversion kernel's block order)
     const int* coarse_info;   // != 0: the inversion of A_c met a non-positive pivot, run block-Jacobi only
-    const int* cl_unit_ptr;   // units of cluster c: [cl_unit_ptr[c], cl_unit_ptr[c + 1])
+    const int* cl_part_ptr;   // restriction partials of cluster c: [cl_part_ptr[c], cl_part_ptr[c + 1])
     const double* xbar; const double* camP; const double* Ainv;
-    double* rc_part;          // 6 per unit
+    double* rc_part;          // 6 per (CTA, cluster it touches)
     double* yc;
     // control
     double* scal;             // (max_it + 2) rows of PS_STRIDE
@@ -82,7 +76,7 @@ __device__ __forceinline__ bool grid_barrier(unsigned* bar, unsigned nblocks) {
             const long long t0 = clock64();
             unsigned spins = 0;
             do {
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(cur) : "l"(bar + 1) : "memory");
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(cur) : "l"(bar + 1) : "memory");   // the acquire comes once, after the loop
                 if (cur != g) break;
                 if ((++spins & 1023u) == 0) {
                     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(ab) : "l"(bar + 2) : "memory");
@@ -95,6 +89,7 @@ __device__ __forceinline__ bool grid_barrier(unsigned* bar, unsigned nblocks) {
                 }
             } while (true);
         }
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
         s_abort = (int)ab;
     }
     __syncthreads();
@@ -113,154 +108,147 @@ __device__ __forceinline__ double cta_sum(double v, double* s_red) {
     return t;
 }
 
-// ---- phases B and D: the CTA's units one after the other, the inputs of the NEXT unit requested before the current one is
-// worked on (the passes are short chains of dependent L2 accesses and block barriers: unpipelined they cost 3-4 us each) ----
-struct PcgUpdateIn {
-    PcgUnit u;
-    int cam;
-    double xv, pv, rv, qv;
-    double2 m0, m1, m2;   // row a of M^-1
-    double R0, R1, R2;    // column k of R_i (coarse restriction)
+// ---- phases B and D: warp-autonomous.  A warp works on five cameras at a time (six lanes per camera, lanes 30 / 31
+// idle); a camera's 6-vector is exchanged with shuffles, so there is no block barrier inside the loop and the fifteen
+// warps stream through the CTA's camera range independently, each with the next chunk's loads in flight. ----
+struct PcgChunkIn {
+    int cam, cl;
+    double v0, v1, v2, v3;   // update: x, p, r, q      direction: z, p, lambda, -
+    double2 m0, m1, m2;      // row a of M^-1 (update) / of B (direction)
+    double R0, R1, R2;       // column k (update) / row k (direction) of R_i
 };
-__device__ __forceinline__ void pcg_update_load(const PcgArgs& A, int ui, bool first, bool coarse, PcgUpdateIn& in) {
-    const int4 d = __ldg(reinterpret_cast<const int4*>(A.units) + ui);
-    in.u = PcgUnit{ d.x, d.y, d.z, d.w };
-    const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
+
+__device__ __forceinline__ void pcg_chunk_load(const PcgArgs& A, bool update, bool first, bool coarse, int pos, int pos_end, int a, bool lane_ok,
+                                               PcgChunkIn& in) {
     in.cam = -1;
-    if (cs < in.u.count) {
-        in.cam = __ldg(A.unit_cams + in.u.first + cs);
+    in.cl = -1;
+    if (lane_ok && pos < pos_end) {
+        in.cam = __ldg(A.cams + pos);
+        in.cl = __ldg(A.cam_cl + pos);
         const size_t idx = (size_t)in.cam * 6 + a;
-        in.rv = A.r[idx];
-        if (!first) { in.xv = A.x[idx]; in.pv = A.p[idx]; in.qv = A.q[idx]; }
-        const double2* m = reinterpret_cast<const double2*>(A.Minv + idx * 6);
-        in.m0 = __ldg(m); in.m1 = __ldg(m + 1); in.m2 = __ldg(m + 2);
-        if (coarse && in.u.cluster >= 0) {
-            const int k = a < 3 ? a : a - 3;
-            const double* R = A.camP + (size_t)in.cam * CAM_PREP;
-            in.R0 = R[k]; in.R1 = R[3 + k]; in.R2 = R[6 + k];
+        const int k = a < 3 ? a : a - 3;
+        const double* R = A.camP + (size_t)in.cam * CAM_PREP;
+        if (update) {
+            in.v2 = A.r[idx];
+            if (!first) { in.v0 = A.x[idx]; in.v1 = A.p[idx]; in.v3 = A.q[idx]; }
+            const double2* m = reinterpret_cast<const double2*>(A.Minv + idx * 6);
+            in.m0 = __ldg(m); in.m1 = __ldg(m + 1); in.m2 = __ldg(m + 2);
+            if (coarse && in.cl >= 0) { in.R0 = R[k]; in.R1 = R[3 + k]; in.R2 = R[6 + k]; }
+        } else {
+            in.v0 = A.z[idx];
+            if (!first) in.v1 = A.p[idx];
+            in.v2 = __ldg(A.lam + idx);
+            const double2* b = reinterpret_cast<const double2*>(A.B + idx * 6);
+            in.m0 = __ldg(b); in.m1 = __ldg(b + 1); in.m2 = __ldg(b + 2);
+            if (coarse && in.cl >= 0) { in.R0 = R[3 * k]; in.R1 = R[3 * k + 1]; in.R2 = R[3 * k + 2]; }
         }
     }
 }
 
-// x += alpha p, r -= alpha q, z = M^-1 r, restriction partials of the CTA's units; returns the thread's share of r.z
-__device__ __noinline__ double pcg_phase_update(const PcgArgs& A, int ub, int ue, bool first, double alpha, bool coarse, double* s_v, double* s_c,
-                                                   double* s_tot) {
-    const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
-    double rz = 0.0;
-    PcgUpdateIn cur, nxt;
-    if (ub < ue) pcg_update_load(A, ub, first, coarse, cur);
-    for (int ui = ub; ui < ue; ++ui) {
-        if (ui + 1 < ue) pcg_update_load(A, ui + 1, first, coarse, nxt);
+// x += alpha p, r -= alpha q, z = M^-1 r over the CTA's cameras, the restriction P^T r per cluster the CTA touches
+// (written to rc_part); returns the thread's share of r.z.  s_acc: kPcgMaxSlots x 6 doubles.
+__device__ __noinline__ double pcg_phase_update(const PcgArgs& A, bool first, double alpha, bool coarse, double* s_acc) {
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = kSpThreads / 32;
+    const int g = lane / 6, a = lane - 6 * g;
+    const bool lane_ok = lane < 30;
+    const int c0 = __ldg(A.cta_cam + blockIdx.x), c1 = __ldg(A.cta_cam + blockIdx.x + 1);
+    const int cl_first = __ldg(A.cta_cl_first + blockIdx.x);
+    for (int i = t; i < kPcgMaxSlots * 6; i += kSpThreads) s_acc[i] = 0.0;
+    __syncthreads();
+    double rz = 0.0, acc = 0.0;
+    int acc_cl = -1;   // lanes 0..5: running restriction sum of component `lane` for cluster acc_cl
+    PcgChunkIn cur, nxt;
+    int base = c0 + warp * 5;
+    pcg_chunk_load(A, true, first, coarse, base + g, c1, a, lane_ok, cur);
+    for (; base < c1; base += nwarps * 5) {
+        pcg_chunk_load(A, true, first, coarse, base + nwarps * 5 + g, c1, a, lane_ok, nxt);
         const bool valid = cur.cam >= 0;
         const size_t idx = (size_t)max(cur.cam, 0) * 6 + a;
         double rv = 0.0;
         if (valid) {
             if (first) {
                 A.x[idx] = 0.0;
-                rv = cur.rv;
+                rv = cur.v2;
             } else {
-                A.x[idx] = cur.xv + alpha * cur.pv;
-                rv = cur.rv - alpha * cur.qv;
+                A.x[idx] = cur.v0 + alpha * cur.v1;
+                rv = cur.v2 - alpha * cur.v3;
                 A.r[idx] = rv;
             }
         }
-        __syncthreads();   // s_v / s_c of the previous unit are no longer read
-        s_v[t] = rv;
-        __syncthreads();
-        const bool restrict_unit = coarse && cur.u.cluster >= 0;   // uniform for the CTA
+        double r6[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) r6[k] = __shfl_sync(0xffffffffu, rv, min(6 * g + k, 31));
         double contrib = 0.0;
         if (valid) {
-            const double* rr = s_v + cs * 6;
-            const double zt = cur.m0.x * rr[0] + cur.m0.y * rr[1] + cur.m1.x * rr[2] + cur.m1.y * rr[3] + cur.m2.x * rr[4] + cur.m2.y * rr[5];
+            const double zt = cur.m0.x * r6[0] + cur.m0.y * r6[1] + cur.m1.x * r6[2] + cur.m1.y * r6[3] + cur.m2.x * r6[4] + cur.m2.y * r6[5];
             A.z[idx] = zt;
             rz += zt * rv;
-            if (restrict_unit) {
+            if (coarse && cur.cl >= 0) {
                 // column k of R_i against the translation (a < 3) or rotation (a >= 3) half of r: V = sum R^T r_t, W = sum R^T r_theta
-                const double* r3 = rr + (a < 3 ? 0 : 3);
-                contrib = cur.R0 * r3[0] + cur.R1 * r3[1] + cur.R2 * r3[2];
+                contrib = a < 3 ? cur.R0 * r6[0] + cur.R1 * r6[1] + cur.R2 * r6[2] : cur.R0 * r6[3] + cur.R1 * r6[4] + cur.R2 * r6[5];
             }
         }
-        if (restrict_unit) {
-            s_c[t] = contrib;
-            __syncthreads();
-            // 96 threads: component a2 = t / 16 summed over 16 parts of 5 cameras, then over the half-warp
-            if (t < 96) {
-                const int a2 = t >> 4, part = t & 15;
-                double sum = 0.0;
+        if (coarse) {
+            // lanes 0..5 collect component `lane` of the five cameras, cluster by cluster
 #pragma unroll
-                for (int i = 0; i < kUnitCams / 16; ++i) sum += s_c[(part * (kUnitCams / 16) + i) * 6 + a2];
-                sum += __shfl_xor_sync(0xffffffffu, sum, 8);
-                sum += __shfl_xor_sync(0xffffffffu, sum, 4);
-                sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-                sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-                if (part == 0) s_tot[a2] = sum;
-            }
-            __syncthreads();
-            if (t < 6) {
-                // P^T r = [ -V ; -(V x xbar) - W / 2 ]
-                const double* xb = A.xbar + 3 * (size_t)cur.u.cluster;
-                const double V0 = s_tot[0], V1 = s_tot[1], V2 = s_tot[2];
-                double o;
-                if (t < 3) o = -s_tot[t];
-                else if (t == 3) o = -(V1 * xb[2] - V2 * xb[1]) - 0.5 * s_tot[3];
-                else if (t == 4) o = -(V2 * xb[0] - V0 * xb[2]) - 0.5 * s_tot[4];
-                else o = -(V0 * xb[1] - V1 * xb[0]) - 0.5 * s_tot[5];
-                A.rc_part[(size_t)ui * 6 + t] = o;
+            for (int gg = 0; gg < 5; ++gg) {
+                const double v = __shfl_sync(0xffffffffu, contrib, min(6 * gg + lane, 31));
+                const int clg = __shfl_sync(0xffffffffu, cur.cl, 6 * gg);
+                if (lane < 6 && clg >= 0) {
+                    if (clg != acc_cl) {
+                        if (acc_cl >= 0) atomicAdd(&s_acc[(acc_cl - cl_first) * 6 + lane], acc);
+                        acc_cl = clg;
+                        acc = 0.0;
+                    }
+                    acc += v;
+                }
             }
         }
         cur = nxt;
     }
+    if (coarse && lane < 6 && acc_cl >= 0) atomicAdd(&s_acc[(acc_cl - cl_first) * 6 + lane], acc);
+    __syncthreads();
+    if (coarse) {
+        // P^T r = [ -V ; -(V x xbar) - W / 2 ] per touched cluster
+        const int p0 = __ldg(A.cta_part + blockIdx.x), nslots = __ldg(A.cta_part + blockIdx.x + 1) - p0;
+        if (t < nslots * 6) {
+            const int slot = t / 6, comp = t - 6 * slot;
+            const double* sv = s_acc + slot * 6;
+            const double* xb = A.xbar + 3 * (size_t)(cl_first + slot);
+            double o;
+            if (comp < 3) o = -sv[comp];
+            else if (comp == 3) o = -(sv[1] * xb[2] - sv[2] * xb[1]) - 0.5 * sv[3];
+            else if (comp == 4) o = -(sv[2] * xb[0] - sv[0] * xb[2]) - 0.5 * sv[4];
+            else o = -(sv[0] * xb[1] - sv[1] * xb[0]) - 0.5 * sv[5];
+            A.rc_part[(size_t)(p0 + slot) * 6 + comp] = o;
+        }
+    }
     return rz;
 }
 
-struct PcgDirectionIn {
-    PcgUnit u;
-    int cam;
-    double zv, pv, lam;
-    double2 b0, b1, b2;   // row a of B
-    double R0, R1, R2;    // row k of R_i (coarse prolongation)
-};
-__device__ __forceinline__ void pcg_direction_load(const PcgArgs& A, int ui, bool first, bool coarse, PcgDirectionIn& in) {
-    const int4 d = __ldg(reinterpret_cast<const int4*>(A.units) + ui);
-    in.u = PcgUnit{ d.x, d.y, d.z, d.w };
-    const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
-    in.cam = -1;
-    if (cs < in.u.count) {
-        in.cam = __ldg(A.unit_cams + in.u.first + cs);
-        const size_t idx = (size_t)in.cam * 6 + a;
-        in.zv = A.z[idx];
-        if (!first) in.pv = A.p[idx];
-        in.lam = __ldg(A.lam + idx);
-        const double2* b = reinterpret_cast<const double2*>(A.B + idx * 6);
-        in.b0 = __ldg(b); in.b1 = __ldg(b + 1); in.b2 = __ldg(b + 2);
-        if (coarse && in.u.cluster >= 0) {
-            const int k = a < 3 ? a : a - 3;
-            const double* R = A.camP + (size_t)in.cam * CAM_PREP + 3 * k;
-            in.R0 = R[0]; in.R1 = R[1]; in.R2 = R[2];
-        }
-    }
-}
-
-// p = z + P yc + beta p, q = (B + lambda) p over the CTA's units; returns the thread's share of p.q
-__device__ __noinline__ double pcg_phase_direction(const PcgArgs& A, int ub, int ue, bool first, double beta, bool coarse, double* s_v) {
-    const int t = threadIdx.x, cs = t / 6, a = t - cs * 6;
+// p = z + P yc + beta p, q = (B + lambda) p over the CTA's cameras; returns the thread's share of p.q
+__device__ __noinline__ double pcg_phase_direction(const PcgArgs& A, bool first, double beta, bool coarse) {
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = kSpThreads / 32;
+    const int g = lane / 6, a = lane - 6 * g;
+    const bool lane_ok = lane < 30;
+    const int c0 = __ldg(A.cta_cam + blockIdx.x), c1 = __ldg(A.cta_cam + blockIdx.x + 1);
     double pq = 0.0;
-    PcgDirectionIn cur, nxt;
-    // the coarse correction of a cluster as the thread needs it: u = y_tau + xbar x y_theta (rows 0-2) or y_theta (rows 3-5);
-    // consecutive units mostly share their cluster, so this is reloaded rarely
+    // the coarse correction of a cluster as this lane needs it: u = y_tau + xbar x y_theta (rows 0-2) or y_theta (rows 3-5)
     int cl_cached = -1;
     double u0 = 0.0, u1 = 0.0, u2 = 0.0;
-    if (ub < ue) pcg_direction_load(A, ub, first, coarse, cur);
-    for (int ui = ub; ui < ue; ++ui) {
-        if (ui + 1 < ue) pcg_direction_load(A, ui + 1, first, coarse, nxt);
+    PcgChunkIn cur, nxt;
+    int base = c0 + warp * 5;
+    pcg_chunk_load(A, false, first, coarse, base + g, c1, a, lane_ok, cur);
+    for (; base < c1; base += nwarps * 5) {
+        pcg_chunk_load(A, false, first, coarse, base + nwarps * 5 + g, c1, a, lane_ok, nxt);
         const bool valid = cur.cam >= 0;
         const size_t idx = (size_t)max(cur.cam, 0) * 6 + a;
         double pv = 0.0;
         if (valid) {
-            pv = cur.zv;
-            if (coarse && cur.u.cluster >= 0) {
-                if (cur.u.cluster != cl_cached) {
-                    cl_cached = cur.u.cluster;
+            pv = cur.v0;
+            if (coarse && cur.cl >= 0) {
+                if (cur.cl != cl_cached) {
+                    cl_cached = cur.cl;
                     const double* y = A.yc + (size_t)cl_cached * 6;
                     const double y3 = y[3], y4 = y[4], y5 = y[5];
                     if (a >= 3) {
@@ -275,15 +263,14 @@ __device__ __noinline__ double pcg_phase_direction(const PcgArgs& A, int ub, int
                 }
                 pv += (a >= 3 ? -0.5 : -1.0) * (cur.R0 * u0 + cur.R1 * u1 + cur.R2 * u2);
             }
-            if (!first) pv += beta * cur.pv;
+            if (!first) pv += beta * cur.v1;
             A.p[idx] = pv;
         }
-        __syncthreads();
-        s_v[t] = pv;
-        __syncthreads();
+        double p6[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) p6[k] = __shfl_sync(0xffffffffu, pv, min(6 * g + k, 31));
         if (valid) {
-            const double* pp = s_v + cs * 6;
-            const double qt = cur.lam * pv + cur.b0.x * pp[0] + cur.b0.y * pp[1] + cur.b1.x * pp[2] + cur.b1.y * pp[3] + cur.b2.x * pp[4] + cur.b2.y * pp[5];
+            const double qt = cur.v2 * pv + cur.m0.x * p6[0] + cur.m0.y * p6[1] + cur.m1.x * p6[2] + cur.m1.y * p6[3] + cur.m2.x * p6[4] + cur.m2.y * p6[5];
             A.q[idx] = qt;
             pq += qt * pv;
         }
@@ -301,16 +288,16 @@ __device__ __noinline__ void sp_pass_call(SpShared& sh, unsigned char* sp_ring, 
     sp_pass<MODE, true>(sh, sp_ring, reinit, segs, cta_seg, nseg, slot_desc, nslots_total, Es, mo_cam, vin_c, mvec, sign, out_c, dot_acc);
 }
 
-// rc = sum of the unit partials: all partials into shared memory with independent loads, then summed per cluster.
-// s_rc: nC (+1) doubles; s_part: 6 per unit (both in the idle ring).
-__device__ __forceinline__ void pcg_assemble_rc(const PcgArgs& A, int nC, int nunits, double* s_rc, double* s_part) {
+// rc = sum of the restriction partials: all partials into shared memory with independent loads, then summed per cluster.
+// s_rc: nC (+1) doubles; s_part: 6 per partial (both in the idle ring).
+__device__ __forceinline__ void pcg_assemble_rc(const PcgArgs& A, int nC, double* s_rc, double* s_part) {
     const int t = threadIdx.x;
-    for (int e = t; e < 6 * nunits; e += kSpThreads) s_part[e] = A.rc_part[e];
+    for (int e = t; e < 6 * A.nparts; e += kSpThreads) s_part[e] = A.rc_part[e];
     __syncthreads();
     for (int e = t; e < nC; e += kSpThreads) {
         const int c = e / 6, comp = e - c * 6;
         double s = 0.0;
-        for (int u = __ldg(A.cl_unit_ptr + c); u < __ldg(A.cl_unit_ptr + c + 1); ++u) s += s_part[u * 6 + comp];
+        for (int u = __ldg(A.cl_part_ptr + c); u < __ldg(A.cl_part_ptr + c + 1); ++u) s += s_part[u * 6 + comp];
         s_rc[e] = s;
     }
 }
@@ -320,7 +307,7 @@ __device__ __forceinline__ void pcg_assemble_rc(const PcgArgs& A, int nC, int nu
 __device__ __noinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_rc, double* s_red) {
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     __syncthreads();
-    pcg_assemble_rc(A, A.nC, A.nunits, s_rc, s_rc + ((A.nC + 8) & ~1));
+    pcg_assemble_rc(A, A.nC, s_rc, s_rc + ((A.nC + 8) & ~1));
     __syncthreads();
     double dot = 0.0;
     const int nwarps = kSpThreads / 32;
@@ -348,10 +335,9 @@ k_pcg_persistent(const PcgArgs A) {
     const bool coarse = A.ncl > 0 && __ldcg(A.coarse_info) == 0;   // uniform for the grid
     extern __shared__ __align__(128) unsigned char sp_ring[];
     __shared__ SpShared sh;
-    __shared__ double s_v[kSpThreads], s_c[kSpThreads], s_tot[8], s_red[kSpThreads / 32];
+    __shared__ double s_acc[kPcgMaxSlots * 6], s_red[kSpThreads / 32];
     double* s_rc = reinterpret_cast<double*>(sp_ring);   // phase C scratch: the ring is idle between products
     const unsigned G = gridDim.x;
-    const int ub = A.cta_unit[blockIdx.x], ue = A.cta_unit[blockIdx.x + 1];
     volatile double* scal = A.scal;
     bool aborted = false;
     unsigned long long t_prev = 0;
@@ -372,7 +358,7 @@ k_pcg_persistent(const PcgArgs A) {
     if (!A.resume) {
         // ---- start: z = M^-1 r, r.z, restriction; coarse solve; first direction ----
         {
-            double rz = pcg_phase_update(A, ub, ue, true, 0.0, coarse, s_v, s_c, s_tot);
+            double rz = pcg_phase_update(A, true, 0.0, coarse, s_acc);
             rz = cta_sum(rz, s_red);
             if (threadIdx.x == 0) red_add(A.scal + PS_RZ, rz);
         }
@@ -383,7 +369,7 @@ k_pcg_persistent(const PcgArgs A) {
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
         }
         {
-            double pq = pcg_phase_direction(A, ub, ue, true, 0.0, coarse, s_v);
+            double pq = pcg_phase_direction(A, true, 0.0, coarse);
             pq = cta_sum(pq, s_red);
             if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
         }
@@ -397,7 +383,7 @@ k_pcg_persistent(const PcgArgs A) {
         if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }   // every CTA has read the old scalars
         if (blockIdx.x == 0 && threadIdx.x == 0) A.scal[PS_RZ] = rz_new;
         {
-            double pq = pcg_phase_direction(A, ub, ue, false, rz_prev != 0.0 ? rz_new / rz_prev : 0.0, coarse, s_v);
+            double pq = pcg_phase_direction(A, false, rz_prev != 0.0 ? rz_new / rz_prev : 0.0, coarse);
             pq = cta_sum(pq, s_red);
             if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
         }
@@ -422,7 +408,7 @@ k_pcg_persistent(const PcgArgs A) {
             const double denom = scal[(size_t)it * PS_STRIDE + PS_PBP] - scal[(size_t)it * PS_STRIDE + PS_WW];
             const double alpha = (rz_s != 0.0) ? rz_s / denom : 0.0;
             {
-                double rz = pcg_phase_update(A, ub, ue, false, alpha, coarse, s_v, s_c, s_tot);
+                double rz = pcg_phase_update(A, false, alpha, coarse, s_acc);
                 rz = cta_sum(rz, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, rz);
             }
@@ -446,7 +432,7 @@ k_pcg_persistent(const PcgArgs A) {
             if (iterations >= A.min_it && rz_new <= A.tol2 * rz0) break;
             const double beta = (rz_s != 0.0) ? rz_new / rz_s : 0.0;
             {
-                double pq = pcg_phase_direction(A, ub, ue, false, beta, coarse, s_v);
+                double pq = pcg_phase_direction(A, false, beta, coarse);
                 pq = cta_sum(pq, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
             }

@@ -52,6 +52,26 @@ __device__ __forceinline__ uint4* x2_slot(const PcgDistArgs& D, int dst_rank, in
     return D.xbuf[dst_rank] + (size_t)2 * D.world * D.cap1 + ((size_t)parity * D.world + src_rank) * D.cap2;
 }
 
+// ld_word_pair of ba_peer.cuh with a way out: a word that does not arrive within ~2 s (a peer died or left the kernel)
+// raises this rank's abort flag (the third word of the grid barrier), after which every barrier winds the kernel down.
+__device__ __forceinline__ double ld_word_pair_guarded(const uint4* p, uint32_t seq, unsigned* abort_flag) {
+    uint32_t lo, f1, hi, f2;
+    unsigned spins = 0;
+    long long t0 = 0;
+    do {
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(f1), "=r"(hi), "=r"(f2) : "l"(p) : "memory");
+        if (f1 == seq && f2 == seq) break;
+        if ((++spins & 4095u) == 0) {
+            if (t0 == 0) t0 = clock64();
+            if (clock64() - t0 > 4000000000LL || *reinterpret_cast<volatile unsigned*>(abort_flag) != 0) {
+                *reinterpret_cast<volatile unsigned*>(abort_flag) = 1;
+                return 0.0;
+            }
+        }
+    } while (true);
+    return __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
+}
+
 // rc . yc in a fixed order, the same bits in every CTA of every rank: thread t sums its strided entries, the 15 warp
 // totals are added in warp order.
 __device__ __forceinline__ double pcg_fixed_dot(const double* s_rc, const double* yc, int n, double* s_red) {
@@ -86,7 +106,7 @@ __device__ __forceinline__ double pcg_exchange_boundary(const PcgDistArgs& D, un
     }
     for (int i = t0; i < n + 2; i += stride) {
         double s = 0.0;
-        for (int r = 0; r < D.world; ++r) s += ld_word_pair(x1_slot(D, D.rank, parity, r) + i, seq);
+        for (int r = 0; r < D.world; ++r) s += ld_word_pair_guarded(x1_slot(D, D.rank, parity, r) + i, seq, D.a.barrier + 2);
         D.wb[i] = s;
         if (i < n) sq += s * s;
     }
@@ -101,7 +121,7 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
     __syncthreads();
     if (!SHARDED || (int)blockIdx.x < D.world) {
         // this rank's restricted residual from the unit partials (tail: its r.z partial)
-        pcg_assemble_rc(A, nC, A.nunits, s_rc, s_rc + ((nC + 8) & ~1));
+        pcg_assemble_rc(A, nC, s_rc, s_rc + ((nC + 8) & ~1));
         if (t == 0) s_rc[nC] = rz_local;
         __syncthreads();
         if (SHARDED) {
@@ -113,7 +133,7 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
         const int parity = (int)(seq & 1u);
         for (int e = t; e <= nC; e += kSpThreads) {
             double s = 0.0;
-            for (int r = 0; r < D.world; ++r) s += ld_word_pair(x2_slot(D, D.rank, parity, r) + e, seq);
+            for (int r = 0; r < D.world; ++r) s += ld_word_pair_guarded(x2_slot(D, D.rank, parity, r) + e, seq, D.a.barrier + 2);
             s_rc[e] = s;
         }
     }
@@ -139,10 +159,9 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
     const bool coarse = A.ncl > 0 && __ldcg(A.coarse_info) == 0;   // uniform for the grid (and, the matrix being replicated, for all ranks)
     extern __shared__ __align__(128) unsigned char sp_ring[];
     __shared__ SpShared sh;
-    __shared__ double s_v[kSpThreads], s_c[kSpThreads], s_tot[8], s_red[kSpThreads / 32];
+    __shared__ double s_acc[kPcgMaxSlots * 6], s_red[kSpThreads / 32];
     double* s_rc = reinterpret_cast<double*>(sp_ring);   // restricted residual (+ tail): the ring is idle between products
     const unsigned G = gridDim.x;
-    const int ub = A.cta_unit[blockIdx.x], ue = A.cta_unit[blockIdx.x + 1];
     const int nC = coarse ? A.nC : 0;
     const bool boundary = D.n_wb > 0;
     volatile double* scal = A.scal;
@@ -154,7 +173,7 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
 
     // ---- start ----
     {
-        double rz = pcg_phase_update(A, ub, ue, true, 0.0, coarse, s_v, s_c, s_tot);
+        double rz = pcg_phase_update(A, true, 0.0, coarse, s_acc);
         rz = cta_sum(rz, s_red);
         if (threadIdx.x == 0) red_add(A.scal + PS_RZ, rz);
         if (boundary) for (int i = blockIdx.x * kSpThreads + threadIdx.x; i < D.n_wb; i += G * kSpThreads) D.wbl[i] = 0.0;
@@ -164,7 +183,7 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
     if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
     rz0 = s_rc[nC] + pcg_fixed_dot(s_rc, A.yc, nC, s_red);
     {
-        double pq = pcg_phase_direction(A, ub, ue, true, 0.0, coarse, s_v);
+        double pq = pcg_phase_direction(A, true, 0.0, coarse);
         pq = cta_sum(pq, s_red);
         if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
     }
@@ -205,7 +224,7 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
             // ---- B ----
             const double alpha = (rz_s != 0.0) ? rz_s / (pbp_tot - ww_tot) : 0.0;
             {
-                double rz = pcg_phase_update(A, ub, ue, false, alpha, coarse, s_v, s_c, s_tot);
+                double rz = pcg_phase_update(A, false, alpha, coarse, s_acc);
                 rz = cta_sum(rz, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, rz);
                 if (boundary) for (int i = blockIdx.x * kSpThreads + threadIdx.x; i < D.n_wb; i += G * kSpThreads) D.wbl[i] = 0.0;
@@ -223,7 +242,7 @@ k_pcg_persistent_dist(const PcgDistArgs D) {
             const double beta = (rz_s != 0.0) ? rz_new / rz_s : 0.0;
             rz_s = rz_new;
             {
-                double pq = pcg_phase_direction(A, ub, ue, false, beta, coarse, s_v);
+                double pq = pcg_phase_direction(A, false, beta, coarse);
                 pq = cta_sum(pq, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
             }

@@ -58,6 +58,8 @@ class Options(C.Structure):
         ("verbose", C.c_int),
         ("coarse_refresh_iterations", C.c_int),
         ("pcg_confirm_tolerance", C.c_double),
+        ("pcg_polish_tolerance", C.c_double),
+        ("pcg_polish_threshold", C.c_double),
     ]
 
 
