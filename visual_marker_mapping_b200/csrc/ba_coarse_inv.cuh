@@ -38,12 +38,46 @@ __device__ __forceinline__ void inv_load_panel_block_T(const double* M, int ld, 
     }
 }
 
+// Round-2 first version (every entry through shared memory, four cases per entry): kept as the checked reference.
+// In-place symmetric sweep of all 64 pivots of the block S (pitch kInvPitch): S <- -S^-1.  Returns false on a
+// non-positive pivot.
+__device__ __forceinline__ bool inv_sweep_block_v1(double* S, double* col) {
+    __shared__ int s_bad;
+    if (threadIdx.x == 0) s_bad = 0;
+    const int ti = threadIdx.x / 16, tj = threadIdx.x % 16;   // 16 x 16 threads, 4 x 4 entries each (interleaved)
+    for (int p = 0; p < kInvNB; ++p) {
+        __syncthreads();
+        if (threadIdx.x < kInvNB) col[threadIdx.x] = S[threadIdx.x * kInvPitch + p];
+        __syncthreads();
+        const double piv = col[p];
+        if (!(piv > 0.0)) { if (threadIdx.x == 0) s_bad = 1; break; }   // uniform: every thread reads the same value
+        const double d = 1.0 / piv;
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int i = ti + 16 * a;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int j = tj + 16 * b;
+                double v;
+                if (i == p && j == p) v = -d;
+                else if (i == p) v = d * col[j];
+                else if (j == p) v = col[i] * d;
+                else v = S[i * kInvPitch + j] - col[i] * d * col[j];
+                S[i * kInvPitch + j] = v;
+            }
+        }
+    }
+    __syncthreads();
+    return s_bad == 0;
+}
+
+
 // In-place symmetric sweep of all 64 pivots of the block S (pitch kInvPitch): S <- -S^-1.  Returns false on a
 // non-positive pivot.  Thread (ti, tj) keeps its 16 entries S[ti + 16 a][tj + 16 b] in registers for all 64 pivots; per
 // pivot only the pivot column travels through shared memory (double-buffered: one block barrier per pivot), and the
 // update is branch-free:  S_ij -= u_i d u_j  with u = the pivot column, u_p = piv - 1 (which turns row and column p into
 // d x the old values), then S_pp = -d.
-__device__ __forceinline__ bool inv_sweep_block(double* S, double* col /* 2 x 64 */) {
+__device__ __forceinline__ bool inv_sweep_block_v2(double* S, double* col /* 2 x 64 */) {
     const int ti = threadIdx.x / 16, tj = threadIdx.x % 16;
     double s[4][4];
 #pragma unroll
@@ -92,6 +126,20 @@ __device__ __forceinline__ bool inv_sweep_block(double* S, double* col /* 2 x 64
     return good;
 }
 
+#ifndef VMM_INV_SWEEP_V2
+#define VMM_INV_SWEEP_V2 0   // 1: register-resident branch-free pivot sweep (under test on the device)
+#endif
+#ifndef VMM_INV_LOOKAHEAD
+#define VMM_INV_LOOKAHEAD 0  // 1: CTA 0 inverts the next pivot block during the tile phase (under test on the device)
+#endif
+__device__ __forceinline__ bool inv_sweep_block(double* S, double* col) {
+#if VMM_INV_SWEEP_V2
+    return inv_sweep_block_v2(S, col);
+#else
+    return inv_sweep_block_v1(S, col);
+#endif
+}
+
 // C (64 x 64, registers: thread (ti, tj) owns rows ti*4.., cols tj*4..) = sum_k At[k][i] * Bt[k][j]
 __device__ __forceinline__ void inv_tile_product(const double* At, const double* Bt, double (&acc)[4][4]) {
     const int ti = threadIdx.x / 16, tj = threadIdx.x % 16;
@@ -129,7 +177,7 @@ k_coarse_sweep_invert(double* __restrict__ M, int n, int ld, double* __restrict_
     const unsigned G = gridDim.x;
     const int ti = threadIdx.x / 16, tj = threadIdx.x % 16;
     bool good = true;
-    const bool look = G > 1;   // look-ahead: CTA 0 updates and inverts the NEXT pivot block while the others update the tiles
+    const bool look = VMM_INV_LOOKAHEAD && G > 1;   // look-ahead: CTA 0 updates and inverts the NEXT pivot block while the others update the tiles
     for (int K = 0; K < nb && good; ++K) {
         if (K == 0 || !look) {
             // ---- pivot block: every CTA inverts it for itself ----

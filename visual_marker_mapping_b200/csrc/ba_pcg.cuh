@@ -118,13 +118,15 @@ struct PcgChunkIn {
     double R0, R1, R2;       // column k (update) / row k (direction) of R_i
 };
 
-__device__ __forceinline__ void pcg_chunk_load(const PcgArgs& A, bool update, bool first, bool coarse, int pos, int pos_end, int a, bool lane_ok,
-                                               PcgChunkIn& in) {
-    in.cam = -1;
-    in.cl = -1;
-    if (lane_ok && pos < pos_end) {
-        in.cam = __ldg(A.cams + pos);
-        in.cl = __ldg(A.cam_cl + pos);
+// the camera (and its cluster) at position pos of the cluster-ordered list; -1 beyond the CTA's range / for the idle lanes
+__device__ __forceinline__ int2 pcg_chunk_index(const PcgArgs& A, int pos, int pos_end, bool lane_ok) {
+    if (lane_ok && pos < pos_end) return make_int2(__ldg(A.cams + pos), __ldg(A.cam_cl + pos));
+    return make_int2(-1, -1);
+}
+__device__ __forceinline__ void pcg_chunk_load(const PcgArgs& A, bool update, bool first, bool coarse, int2 cc, int a, PcgChunkIn& in) {
+    in.cam = cc.x;
+    in.cl = cc.y;
+    if (cc.x >= 0) {
         const size_t idx = (size_t)in.cam * 6 + a;
         const int k = a < 3 ? a : a - 3;
         const double* R = A.camP + (size_t)in.cam * CAM_PREP;
@@ -157,11 +159,14 @@ __device__ __noinline__ double pcg_phase_update(const PcgArgs& A, bool first, do
     __syncthreads();
     double rz = 0.0, acc = 0.0;
     int acc_cl = -1;   // lanes 0..5: running restriction sum of component `lane` for cluster acc_cl
-    PcgChunkIn cur, nxt;
+    // only the camera index of the NEXT chunk is requested ahead (one dependent L2 access less per chunk); holding a whole
+    // chunk of operands ahead as well cost more in spills than it hid
+    PcgChunkIn cur;
     int base = c0 + warp * 5;
-    pcg_chunk_load(A, true, first, coarse, base + g, c1, a, lane_ok, cur);
+    int2 cc = pcg_chunk_index(A, base + g, c1, lane_ok);
     for (; base < c1; base += nwarps * 5) {
-        pcg_chunk_load(A, true, first, coarse, base + nwarps * 5 + g, c1, a, lane_ok, nxt);
+        pcg_chunk_load(A, true, first, coarse, cc, a, cur);
+        cc = pcg_chunk_index(A, base + nwarps * 5 + g, c1, lane_ok);
         const bool valid = cur.cam >= 0;
         const size_t idx = (size_t)max(cur.cam, 0) * 6 + a;
         double rv = 0.0;
@@ -204,7 +209,6 @@ __device__ __noinline__ double pcg_phase_update(const PcgArgs& A, bool first, do
                 }
             }
         }
-        cur = nxt;
     }
     if (coarse && lane < 6 && acc_cl >= 0) atomicAdd(&s_acc[(acc_cl - cl_first) * 6 + lane], acc);
     __syncthreads();
@@ -236,11 +240,12 @@ __device__ __noinline__ double pcg_phase_direction(const PcgArgs& A, bool first,
     // the coarse correction of a cluster as this lane needs it: u = y_tau + xbar x y_theta (rows 0-2) or y_theta (rows 3-5)
     int cl_cached = -1;
     double u0 = 0.0, u1 = 0.0, u2 = 0.0;
-    PcgChunkIn cur, nxt;
+    PcgChunkIn cur;
     int base = c0 + warp * 5;
-    pcg_chunk_load(A, false, first, coarse, base + g, c1, a, lane_ok, cur);
+    int2 cc = pcg_chunk_index(A, base + g, c1, lane_ok);
     for (; base < c1; base += nwarps * 5) {
-        pcg_chunk_load(A, false, first, coarse, base + nwarps * 5 + g, c1, a, lane_ok, nxt);
+        pcg_chunk_load(A, false, first, coarse, cc, a, cur);
+        cc = pcg_chunk_index(A, base + nwarps * 5 + g, c1, lane_ok);
         const bool valid = cur.cam >= 0;
         const size_t idx = (size_t)max(cur.cam, 0) * 6 + a;
         double pv = 0.0;
@@ -274,13 +279,11 @@ __device__ __noinline__ double pcg_phase_direction(const PcgArgs& A, bool first,
             A.q[idx] = qt;
             pq += qt * pv;
         }
-        cur = nxt;
     }
     return pq;
 }
 
-// The passes of the streamed product as real calls: each keeps the register allocation it has as a kernel of its own
-// instead of sharing one with the vector phases.
+// A pass of the streamed product inside a persistent kernel (coherent loads of the vectors that change between passes).
 template <int MODE>
 __device__ __noinline__ void sp_pass_call(SpShared& sh, unsigned char* sp_ring, bool reinit, const SpSeg* segs, const int* cta_seg, int nseg,
                                           const int2* slot_desc, int nslots_total, const unsigned char* Es, const int* mo_cam, const double* vin_c,
@@ -331,7 +334,7 @@ __device__ __noinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_rc, 
 }
 
 __global__ void __launch_bounds__(kSpThreads, 1)
-k_pcg_persistent(const PcgArgs A) {
+k_pcg_persistent(const __grid_constant__ PcgArgs A) {   // __grid_constant__: the fields are read from the parameter bank where they are used
     const bool coarse = A.ncl > 0 && __ldcg(A.coarse_info) == 0;   // uniform for the grid
     extern __shared__ __align__(128) unsigned char sp_ring[];
     __shared__ SpShared sh;
@@ -343,6 +346,9 @@ k_pcg_persistent(const PcgArgs A) {
     unsigned long long t_prev = 0;
     // phase clock (CTA 0, thread 0; only when the host asked for it): time since the previous tick into slot `k`
     auto tick = [&](int k) {
+#ifdef VMM_PCG_NO_TICK
+        return;
+#endif
         if (A.phase_ns && blockIdx.x == 0 && threadIdx.x == 0) {
             unsigned long long now;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));

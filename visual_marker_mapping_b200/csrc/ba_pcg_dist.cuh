@@ -154,7 +154,7 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
 
 template <bool SHARDED>
 __global__ void __launch_bounds__(kSpThreads, 1)
-k_pcg_persistent_dist(const PcgDistArgs D) {
+k_pcg_persistent_dist(const __grid_constant__ PcgDistArgs D) {
     const PcgArgs& A = D.a;
     const bool coarse = A.ncl > 0 && __ldcg(A.coarse_info) == 0;   // uniform for the grid (and, the matrix being replicated, for all ranks)
     extern __shared__ __align__(128) unsigned char sp_ring[];

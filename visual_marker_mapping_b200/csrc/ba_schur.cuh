@@ -232,14 +232,20 @@ k_scale_e(const int* __restrict__ mptr, const unsigned char* __restrict__ tag_ac
 // Algorithmic bytes per tag observation: 288 (Es) + 4 (camera index).
 // ------------------------------------------------------------------------------------------
 enum { SP_FULL = 0, SP_GATHER = 1, SP_SCATTER = 2 };
-constexpr int kSpGroups = 2;
+#ifndef VMM_SP_GROUPS
+#define VMM_SP_GROUPS 2
+#endif
+constexpr int kSpGroups = VMM_SP_GROUPS;
 #ifndef VMM_SP_GROUP_WARPS
 #define VMM_SP_GROUP_WARPS 7   // 2 x 7 consumer warps + producer = 15 warps: 128 registers per thread (17 warps: 96, spills)
 #endif
 constexpr int kSpGroupWarps = VMM_SP_GROUP_WARPS;
 constexpr int kSpConsumerThreads = kSpGroups * kSpGroupWarps * 32;
 constexpr int kSpThreads = kSpConsumerThreads + 32;                  // + producer warp
-constexpr int kSpRing = 20;                                          // slots of kSlotBytes: 184,320 B
+#ifndef VMM_SP_RING
+#define VMM_SP_RING 20
+#endif
+constexpr int kSpRing = VMM_SP_RING;                                 // slots of kSlotBytes: 184,320 B at 20
 constexpr int kSegRegObs = kSpGroupWarps * 32;                       // observations of a segment held in registers
 constexpr int kSegMaxObs = 2 * kSegRegObs;                           // the second half stays in its ring slot
 constexpr size_t kSpSmemBytes = (size_t)kSpRing * kSlotBytes;
