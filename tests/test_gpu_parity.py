@@ -376,3 +376,18 @@ def test_set_problem_with_unchanged_structure_refreshes_observations_and_poses(s
         ba.set_scene(s3)
         ev3 = ba.evaluate(pkg.LOSS_NONE, 1.0, jacobians=False, gradient=False)
         assert abs(ev3.cost - oracle.evaluate(s3, oracle.LOSS_NONE, 1.0, jac_local=False, gradient=False).cost) <= 1e-12 * ev3.cost
+
+
+def test_solve_with_split_markers_matches_oracle(oracle):
+    """Markers with more observations than one segment of the streamed product holds go through the boundary path
+    (gather / local sum / scatter inside the persistent kernel): the solve must still be the oracle's."""
+    s = synth.make_scene(seed=77, **SCHUR_SCENES["split"])
+    assert np.bincount(s.to_tag, minlength=s.n_markers).max() > 512
+    oref = oracle.solve(s, max_num_iterations=50, loss_kind=oracle.LOSS_HUBER, loss_scale=1.0)
+    with pkg.BundleAdjuster(0) as ba:
+        ba.set_scene(s)
+        summ = ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, parity_mode=1)
+        cq, ct, tq, tt = ba.get_poses()
+    assert abs(summ.final_cost - oref.summary.final_cost) <= COST_TOL * oref.summary.final_cost
+    assert summ.num_iterations + 1 == oref.summary.num_iterations
+    assert np.abs(ct - oref.cam_t).max() < TRANS_TOL and np.abs(tt - oref.tag_t).max() < TRANS_TOL

@@ -75,8 +75,7 @@ __device__ __forceinline__ bool inv_sweep_block_v1(double* S, double* col) {
 // In-place symmetric sweep of all 64 pivots of the block S (pitch kInvPitch): S <- -S^-1.  Returns false on a
 // non-positive pivot.  Thread (ti, tj) keeps its 16 entries S[ti + 16 a][tj + 16 b] in registers for all 64 pivots; per
 // pivot only the pivot column travels through shared memory (double-buffered: one block barrier per pivot), and the
-// update is branch-free:  S_ij -= u_i d u_j  with u = the pivot column, u_p = piv - 1 (which turns row and column p into
-// d x the old values), then S_pp = -d.
+// update is S_ij -= c_i d c_j with row / column p selected to d c_j / c_i d, then S_pp = -d.
 __device__ __forceinline__ bool inv_sweep_block_v2(double* S, double* col /* 2 x 64 */) {
     const int ti = threadIdx.x / 16, tj = threadIdx.x % 16;
     double s[4][4];
@@ -100,15 +99,25 @@ __device__ __forceinline__ bool inv_sweep_block_v2(double* S, double* col /* 2 x
         const double piv = c[p];
         if (!(piv > 0.0)) { good = false; break; }   // uniform: every thread reads the same value
         const double d = 1.0 / piv;
-        double ui[4], uj[4];
+        // S_ij -= c_i d c_j;  row p: d c_j;  column p: c_i d  (selected, not folded into the product: the folded form
+        // u_p = piv - 1 cancels catastrophically for the large pivots of a coarse matrix — measured: pivots went negative)
+        double ci[4], cjd[4];
 #pragma unroll
-        for (int a = 0; a < 4; ++a) ui[a] = (ti + 16 * a == p) ? piv - 1.0 : c[ti + 16 * a];
+        for (int a = 0; a < 4; ++a) ci[a] = c[ti + 16 * a];
 #pragma unroll
-        for (int b = 0; b < 4; ++b) uj[b] = d * ((tj + 16 * b == p) ? piv - 1.0 : c[tj + 16 * b]);
+        for (int b = 0; b < 4; ++b) cjd[b] = d * c[tj + 16 * b];
 #pragma unroll
-        for (int a = 0; a < 4; ++a)
+        for (int a = 0; a < 4; ++a) {
+            const bool rowp = ti + 16 * a == p;
 #pragma unroll
-            for (int b = 0; b < 4; ++b) s[a][b] -= ui[a] * uj[b];
+            for (int b = 0; b < 4; ++b) {
+                const bool colp = tj + 16 * b == p;
+                double v = s[a][b] - ci[a] * cjd[b];
+                v = rowp ? cjd[b] : v;
+                v = colp ? ci[a] * d : v;
+                s[a][b] = v;
+            }
+        }
         if (ti == pj && tj == pj) {
 #pragma unroll
             for (int a = 0; a < 4; ++a)
@@ -127,10 +136,10 @@ __device__ __forceinline__ bool inv_sweep_block_v2(double* S, double* col /* 2 x
 }
 
 #ifndef VMM_INV_SWEEP_V2
-#define VMM_INV_SWEEP_V2 0   // 1: register-resident branch-free pivot sweep (under test on the device)
+#define VMM_INV_SWEEP_V2 0   // 1: register-resident pivot sweep (under test on the device)
 #endif
 #ifndef VMM_INV_LOOKAHEAD
-#define VMM_INV_LOOKAHEAD 0  // 1: CTA 0 inverts the next pivot block during the tile phase (under test on the device)
+#define VMM_INV_LOOKAHEAD 1  // CTA 0 inverts the next pivot block during the tile phase (0: every CTA at the start of the step)
 #endif
 __device__ __forceinline__ bool inv_sweep_block(double* S, double* col) {
 #if VMM_INV_SWEEP_V2

@@ -607,11 +607,10 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, b
     cudaEvent_t eb = nullptr;
     if (e->profiling) eb = profile_begin(e);
     if (!dist) {
-        void* args[] = { &a };
-        CU(cudaLaunchCooperativeKernel((const void*)k_pcg_persistent, dim3(e->sp_grid), dim3(kSpThreads), args, kSpSmemBytes, e->stream));
+        CU(cudaMemcpyToSymbolAsync(c_pcg, &a, sizeof(a), 0, cudaMemcpyHostToDevice, e->stream));
+        CU(cudaLaunchCooperativeKernel((const void*)k_pcg_persistent, dim3(e->sp_grid), dim3(kSpThreads), nullptr, kSpSmemBytes, e->stream));
     } else {
         PcgDistArgs d{};
-        d.a = a;
         d.bsegs = e->seg_big.segs.p; d.bcta_seg = e->seg_big.cta_seg.p; d.bnseg = e->seg_big.count; d.bslot_desc = e->seg_big.slots.p;
         d.bnslots_total = e->seg_big.nslots;
         if (e->cta_part.n < (size_t)e->sp_grid) CU(e->cta_part.alloc(e->sp_grid));
@@ -628,9 +627,10 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, b
             for (int r = 0; r < e->world; ++r) d.xbuf[r] = e->pcgx_buf[r];
             d.cap1 = kPcgxCap1; d.cap2 = kPcgxCap2; d.seq = e->pcgx_seq.p;
         }
-        void* args[] = { &d };
         const void* fn = e->world > 1 ? (const void*)k_pcg_persistent_dist<true> : (const void*)k_pcg_persistent_dist<false>;
-        CU(cudaLaunchCooperativeKernel(fn, dim3(e->sp_grid), dim3(kSpThreads), args, kSpSmemBytes, e->stream));
+        CU(cudaMemcpyToSymbolAsync(c_pcg, &a, sizeof(a), 0, cudaMemcpyHostToDevice, e->stream));
+        CU(cudaMemcpyToSymbolAsync(c_pcgd, &d, sizeof(d), 0, cudaMemcpyHostToDevice, e->stream));
+        CU(cudaLaunchCooperativeKernel(fn, dim3(e->sp_grid), dim3(kSpThreads), nullptr, kSpSmemBytes, e->stream));
     }
     if (eb) profile_end(e, dist ? kid_dist : kid, eb);
     ++e->launches;
@@ -1973,7 +1973,11 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     std::vector<int32_t> to_cam_p;
     std::vector<std::pair<int, int>> spatial_leaves;
     e->cam_order.clear();
-    if (e->world > 1 && Nc > 0) {   // (on one GPU the renumbering was measured neutral for the solve: 0.0898 vs 0.0905 s at C3)
+    // One GPU: round 1 measured the renumbering neutral for the multi-launch loop (0.0898 vs 0.0905 s at C3); the persistent
+    // PCG kernel walks the cameras cluster by cluster, which the spatial numbering turns into coalesced accesses
+    // (VMM_BA_SPATIAL_ORDER=1; under measurement).
+    static const bool spatial_one_gpu = std::getenv("VMM_BA_SPATIAL_ORDER") != nullptr;
+    if ((e->world > 1 || spatial_one_gpu) && Nc > 0) {
         std::vector<int> order;
         spatial_camera_order(cam_q, cam_t, cam_count, Nc, e->coarse_cams_per_cluster, order, &spatial_leaves);
         std::vector<int> pos(Nc);
@@ -2007,7 +2011,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
         std::thread& t;
         ~Joiner() { if (t.joinable()) t.join(); }
     } splits_joiner{ splits_thread };
-    if (e->world == 1 && Nc > 0 && !std::getenv("VMM_BA_KD_SERIAL")) {
+    if (e->world == 1 && !spatial_one_gpu && Nc > 0 && !std::getenv("VMM_BA_KD_SERIAL")) {
         const int cpc = e->coarse_cams_per_cluster;
         splits_thread = std::thread([&splits_ahead, &cam_count, cam_q, cam_t, Nc, cpc] { cluster_splits(cam_q, cam_t, cam_count, Nc, cpc, splits_ahead); });
     }
@@ -2147,7 +2151,7 @@ int vmm_ba_set_problem(vmm_ba_handle e, int64_t Nc, const double* cam_q, const d
     CU(cudaStreamSynchronize(e->stream));   // host staging vectors go out of scope
     e->have_problem = true;
     e->key = key;
-    e->perm_identity = sorted && e->world == 1;
+    e->perm_identity = sorted && e->world == 1 && e->cam_order.empty();
     e->h2d_bytes += Nto * (64 + 8) + Ncl * 56 + Nm * (56 + 16);
     return VMM_BA_OK;
 }
@@ -2183,9 +2187,17 @@ int vmm_ba_set_poses(vmm_ba_handle e, const double* cam_q, const double* cam_t, 
 
 // gather a camera-sharded array (per-camera `width` doubles) into a full host array
 static int gather_cameras(vmm_ba_engine* e, const double* local_dev, int width, double* host_out) {
-    if (e->world == 1) {
+    if (e->world == 1 && e->cam_order.empty()) {
         if (e->Ncl > 0) CU(cudaMemcpyAsync(host_out, local_dev, sizeof(double) * width * e->Ncl, cudaMemcpyDeviceToHost, e->stream));
         CU(cudaStreamSynchronize(e->stream));
+        return VMM_BA_OK;
+    }
+    if (e->world == 1) {   // one GPU with the spatial numbering: internal camera order -> caller's
+        std::vector<double> tmp((size_t)width * e->Nc);
+        if (e->Ncl > 0) CU(cudaMemcpyAsync(tmp.data(), local_dev, sizeof(double) * width * e->Ncl, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        for (int64_t i = 0; i < e->Nc; ++i)
+            for (int a = 0; a < width; ++a) host_out[(size_t)width * e->cam_order[i] + a] = tmp[(size_t)width * i + a];
         return VMM_BA_OK;
     }
     const size_t n = (size_t)width * e->Nc;

@@ -5,8 +5,8 @@
 //   ocam/otag int32[Nto]       local camera index / marker index of each tag observation
 //   camP      double[12*Nc]    prepared camera blocks (R row-major | t)
 //   mkP       double[12*Nm]    prepared marker blocks (a | b | t | pad)
-//   Ec        double[36*Nto]   E_k = Jc^T Jm (camera rows, marker cols), camera order
-//   Em        double[36*Nto]   the same blocks in marker order (second copy: both Schur products stream)
+//   Et, Es    bytes            E_k = Jc^T Jm (camera rows, marker cols) and the scaled blocks Es_k = E_k L_j^-T, ONE copy each, in
+//                              marker order as 8-observation tiles of 18 double2 planes (ba_schur.cuh): what cp.async.bulk moves
 //   B, C      double[36*Nc], double[36*Nm]   diagonal blocks of J^T J; gc, gm gradients
 //   res/jac   double[2][Nobs], double[24][Nobs]  component-major output of the materialising pass
 //

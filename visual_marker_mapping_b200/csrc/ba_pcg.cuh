@@ -55,6 +55,14 @@ struct PcgArgs {
     unsigned long long* phase_ns;   // optional (debug / bench): CTA 0 accumulates the time of the phases A, B, C, D, barriers excluded [0..3], barriers [4]
 };
 
+// The arguments live in constant memory (copied there, stream-ordered, before every launch): every phase — each its own
+// function with its own register allocation — reads the fields it needs from the constant bank with immediate offsets,
+// so no pointer is passed, kept in a register across a call or spilled.  (With the arguments as a kernel parameter the
+// phases had to be inlined into one body to see the parameter bank, and that body spilled inside the camera loops; with
+// 184 KB of the SM's memory in the ring there is no L1 left to catch local memory.)  One solve at a time per device and
+// process, which the handle's threading rule (include/vmm_ba.h) already demands.
+__constant__ PcgArgs c_pcg;
+
 // bar[0] arrivals, bar[1] generation, bar[2] abort flag.  A CTA that polls for more than ~2 s (a lost CTA: the launch was
 // not co-resident, or another CTA faulted) raises the abort flag; every barrier then returns false and the kernel
 // winds down instead of hanging the device.
@@ -111,94 +119,68 @@ __device__ __forceinline__ double cta_sum(double v, double* s_red) {
 // ---- phases B and D: warp-autonomous.  A warp works on five cameras at a time (six lanes per camera, lanes 30 / 31
 // idle); a camera's 6-vector is exchanged with shuffles, so there is no block barrier inside the loop and the fifteen
 // warps stream through the CTA's camera range independently, each with the next chunk's loads in flight. ----
-struct PcgChunkIn {
-    int cam, cl;
-    double v0, v1, v2, v3;   // update: x, p, r, q      direction: z, p, lambda, -
-    double2 m0, m1, m2;      // row a of M^-1 (update) / of B (direction)
-    double R0, R1, R2;       // column k (update) / row k (direction) of R_i
-};
-
 // the camera (and its cluster) at position pos of the cluster-ordered list; -1 beyond the CTA's range / for the idle lanes
-__device__ __forceinline__ int2 pcg_chunk_index(const PcgArgs& A, int pos, int pos_end, bool lane_ok) {
-    if (lane_ok && pos < pos_end) return make_int2(__ldg(A.cams + pos), __ldg(A.cam_cl + pos));
+__device__ __forceinline__ int2 pcg_chunk_index(int pos, int pos_end, bool lane_ok) {
+    if (lane_ok && pos < pos_end) return make_int2(__ldg(c_pcg.cams + pos), __ldg(c_pcg.cam_cl + pos));
     return make_int2(-1, -1);
-}
-__device__ __forceinline__ void pcg_chunk_load(const PcgArgs& A, bool update, bool first, bool coarse, int2 cc, int a, PcgChunkIn& in) {
-    in.cam = cc.x;
-    in.cl = cc.y;
-    if (cc.x >= 0) {
-        const size_t idx = (size_t)in.cam * 6 + a;
-        const int k = a < 3 ? a : a - 3;
-        const double* R = A.camP + (size_t)in.cam * CAM_PREP;
-        if (update) {
-            in.v2 = A.r[idx];
-            if (!first) { in.v0 = A.x[idx]; in.v1 = A.p[idx]; in.v3 = A.q[idx]; }
-            const double2* m = reinterpret_cast<const double2*>(A.Minv + idx * 6);
-            in.m0 = __ldg(m); in.m1 = __ldg(m + 1); in.m2 = __ldg(m + 2);
-            if (coarse && in.cl >= 0) { in.R0 = R[k]; in.R1 = R[3 + k]; in.R2 = R[6 + k]; }
-        } else {
-            in.v0 = A.z[idx];
-            if (!first) in.v1 = A.p[idx];
-            in.v2 = __ldg(A.lam + idx);
-            const double2* b = reinterpret_cast<const double2*>(A.B + idx * 6);
-            in.m0 = __ldg(b); in.m1 = __ldg(b + 1); in.m2 = __ldg(b + 2);
-            if (coarse && in.cl >= 0) { in.R0 = R[3 * k]; in.R1 = R[3 * k + 1]; in.R2 = R[3 * k + 2]; }
-        }
-    }
 }
 
 // x += alpha p, r -= alpha q, z = M^-1 r over the CTA's cameras, the restriction P^T r per cluster the CTA touches
 // (written to rc_part); returns the thread's share of r.z.  s_acc: kPcgMaxSlots x 6 doubles.
-__device__ __noinline__ double pcg_phase_update(const PcgArgs& A, bool first, double alpha, bool coarse, double* s_acc) {
+__device__ __noinline__ double pcg_phase_update(bool first, double alpha, bool coarse, double* s_acc) {
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = kSpThreads / 32;
-    const int g = lane / 6, a = lane - 6 * g;
+    const int g = lane / 6, a = lane - 6 * g, k = a < 3 ? a : a - 3;
     const bool lane_ok = lane < 30;
-    const int c0 = __ldg(A.cta_cam + blockIdx.x), c1 = __ldg(A.cta_cam + blockIdx.x + 1);
-    const int cl_first = __ldg(A.cta_cl_first + blockIdx.x);
+    const int c0 = __ldg(c_pcg.cta_cam + blockIdx.x), c1 = __ldg(c_pcg.cta_cam + blockIdx.x + 1);
+    const int cl_first = __ldg(c_pcg.cta_cl_first + blockIdx.x);
     for (int i = t; i < kPcgMaxSlots * 6; i += kSpThreads) s_acc[i] = 0.0;
     __syncthreads();
     double rz = 0.0, acc = 0.0;
     int acc_cl = -1;   // lanes 0..5: running restriction sum of component `lane` for cluster acc_cl
-    // only the camera index of the NEXT chunk is requested ahead (one dependent L2 access less per chunk); holding a whole
-    // chunk of operands ahead as well cost more in spills than it hid
-    PcgChunkIn cur;
+    // only the camera index of the NEXT chunk is requested ahead (one dependent L2 access less per chunk)
     int base = c0 + warp * 5;
-    int2 cc = pcg_chunk_index(A, base + g, c1, lane_ok);
+    int2 cc = pcg_chunk_index(base + g, c1, lane_ok);
     for (; base < c1; base += nwarps * 5) {
-        pcg_chunk_load(A, true, first, coarse, cc, a, cur);
-        cc = pcg_chunk_index(A, base + nwarps * 5 + g, c1, lane_ok);
-        const bool valid = cur.cam >= 0;
-        const size_t idx = (size_t)max(cur.cam, 0) * 6 + a;
+        const int cam = cc.x, cl = cc.y;
+        cc = pcg_chunk_index(base + nwarps * 5 + g, c1, lane_ok);
+        const bool valid = cam >= 0;
+        const size_t idx = (size_t)max(cam, 0) * 6 + a;
         double rv = 0.0;
+        double2 m0 = make_double2(0.0, 0.0), m1 = m0, m2 = m0;
+        double R0 = 0.0, R1 = 0.0, R2 = 0.0;
         if (valid) {
+            const double2* m = reinterpret_cast<const double2*>(c_pcg.Minv + idx * 6);
+            m0 = __ldg(m); m1 = __ldg(m + 1); m2 = __ldg(m + 2);
+            if (coarse && cl >= 0) {
+                const double* R = c_pcg.camP + (size_t)cam * CAM_PREP;
+                R0 = R[k]; R1 = R[3 + k]; R2 = R[6 + k];
+            }
+            rv = c_pcg.r[idx];
             if (first) {
-                A.x[idx] = 0.0;
-                rv = cur.v2;
+                c_pcg.x[idx] = 0.0;
             } else {
-                A.x[idx] = cur.v0 + alpha * cur.v1;
-                rv = cur.v2 - alpha * cur.v3;
-                A.r[idx] = rv;
+                c_pcg.x[idx] += alpha * c_pcg.p[idx];
+                rv -= alpha * c_pcg.q[idx];
+                c_pcg.r[idx] = rv;
             }
         }
-        double r6[6];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) r6[k] = __shfl_sync(0xffffffffu, rv, min(6 * g + k, 31));
+        const int src = min(6 * g, 26);
+        const double r0 = __shfl_sync(0xffffffffu, rv, src), r1 = __shfl_sync(0xffffffffu, rv, src + 1), r2 = __shfl_sync(0xffffffffu, rv, src + 2);
+        const double r3 = __shfl_sync(0xffffffffu, rv, src + 3), r4 = __shfl_sync(0xffffffffu, rv, src + 4), r5 = __shfl_sync(0xffffffffu, rv, src + 5);
         double contrib = 0.0;
         if (valid) {
-            const double zt = cur.m0.x * r6[0] + cur.m0.y * r6[1] + cur.m1.x * r6[2] + cur.m1.y * r6[3] + cur.m2.x * r6[4] + cur.m2.y * r6[5];
-            A.z[idx] = zt;
+            const double zt = m0.x * r0 + m0.y * r1 + m1.x * r2 + m1.y * r3 + m2.x * r4 + m2.y * r5;
+            c_pcg.z[idx] = zt;
             rz += zt * rv;
-            if (coarse && cur.cl >= 0) {
-                // column k of R_i against the translation (a < 3) or rotation (a >= 3) half of r: V = sum R^T r_t, W = sum R^T r_theta
-                contrib = a < 3 ? cur.R0 * r6[0] + cur.R1 * r6[1] + cur.R2 * r6[2] : cur.R0 * r6[3] + cur.R1 * r6[4] + cur.R2 * r6[5];
-            }
+            // column k of R_i against the translation (a < 3) or rotation (a >= 3) half of r: V = sum R^T r_t, W = sum R^T r_theta
+            contrib = a < 3 ? R0 * r0 + R1 * r1 + R2 * r2 : R0 * r3 + R1 * r4 + R2 * r5;
         }
         if (coarse) {
             // lanes 0..5 collect component `lane` of the five cameras, cluster by cluster
 #pragma unroll
             for (int gg = 0; gg < 5; ++gg) {
                 const double v = __shfl_sync(0xffffffffu, contrib, min(6 * gg + lane, 31));
-                const int clg = __shfl_sync(0xffffffffu, cur.cl, 6 * gg);
+                const int clg = __shfl_sync(0xffffffffu, cl, 6 * gg);
                 if (lane < 6 && clg >= 0) {
                     if (clg != acc_cl) {
                         if (acc_cl >= 0) atomicAdd(&s_acc[(acc_cl - cl_first) * 6 + lane], acc);
@@ -214,76 +196,86 @@ __device__ __noinline__ double pcg_phase_update(const PcgArgs& A, bool first, do
     __syncthreads();
     if (coarse) {
         // P^T r = [ -V ; -(V x xbar) - W / 2 ] per touched cluster
-        const int p0 = __ldg(A.cta_part + blockIdx.x), nslots = __ldg(A.cta_part + blockIdx.x + 1) - p0;
+        const int p0 = __ldg(c_pcg.cta_part + blockIdx.x), nslots = __ldg(c_pcg.cta_part + blockIdx.x + 1) - p0;
         if (t < nslots * 6) {
             const int slot = t / 6, comp = t - 6 * slot;
             const double* sv = s_acc + slot * 6;
-            const double* xb = A.xbar + 3 * (size_t)(cl_first + slot);
+            const double* xb = c_pcg.xbar + 3 * (size_t)(cl_first + slot);
             double o;
             if (comp < 3) o = -sv[comp];
             else if (comp == 3) o = -(sv[1] * xb[2] - sv[2] * xb[1]) - 0.5 * sv[3];
             else if (comp == 4) o = -(sv[2] * xb[0] - sv[0] * xb[2]) - 0.5 * sv[4];
             else o = -(sv[0] * xb[1] - sv[1] * xb[0]) - 0.5 * sv[5];
-            A.rc_part[(size_t)(p0 + slot) * 6 + comp] = o;
+            c_pcg.rc_part[(size_t)(p0 + slot) * 6 + comp] = o;
         }
     }
     return rz;
 }
 
 // p = z + P yc + beta p, q = (B + lambda) p over the CTA's cameras; returns the thread's share of p.q
-__device__ __noinline__ double pcg_phase_direction(const PcgArgs& A, bool first, double beta, bool coarse) {
+__device__ __noinline__ double pcg_phase_direction(bool first, double beta, bool coarse) {
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = kSpThreads / 32;
-    const int g = lane / 6, a = lane - 6 * g;
+    const int g = lane / 6, a = lane - 6 * g, k = a < 3 ? a : a - 3;
     const bool lane_ok = lane < 30;
-    const int c0 = __ldg(A.cta_cam + blockIdx.x), c1 = __ldg(A.cta_cam + blockIdx.x + 1);
+    const int c0 = __ldg(c_pcg.cta_cam + blockIdx.x), c1 = __ldg(c_pcg.cta_cam + blockIdx.x + 1);
     double pq = 0.0;
     // the coarse correction of a cluster as this lane needs it: u = y_tau + xbar x y_theta (rows 0-2) or y_theta (rows 3-5)
     int cl_cached = -1;
     double u0 = 0.0, u1 = 0.0, u2 = 0.0;
-    PcgChunkIn cur;
     int base = c0 + warp * 5;
-    int2 cc = pcg_chunk_index(A, base + g, c1, lane_ok);
+    int2 cc = pcg_chunk_index(base + g, c1, lane_ok);
     for (; base < c1; base += nwarps * 5) {
-        pcg_chunk_load(A, false, first, coarse, cc, a, cur);
-        cc = pcg_chunk_index(A, base + nwarps * 5 + g, c1, lane_ok);
-        const bool valid = cur.cam >= 0;
-        const size_t idx = (size_t)max(cur.cam, 0) * 6 + a;
-        double pv = 0.0;
+        const int cam = cc.x, cl = cc.y;
+        cc = pcg_chunk_index(base + nwarps * 5 + g, c1, lane_ok);
+        const bool valid = cam >= 0;
+        const size_t idx = (size_t)max(cam, 0) * 6 + a;
+        double pv = 0.0, lam = 0.0;
+        double2 b0 = make_double2(0.0, 0.0), b1 = b0, b2 = b0;
         if (valid) {
-            pv = cur.v0;
-            if (coarse && cur.cl >= 0) {
-                if (cur.cl != cl_cached) {
-                    cl_cached = cur.cl;
-                    const double* y = A.yc + (size_t)cl_cached * 6;
+            const double2* b = reinterpret_cast<const double2*>(c_pcg.B + idx * 6);
+            b0 = __ldg(b); b1 = __ldg(b + 1); b2 = __ldg(b + 2);
+            lam = __ldg(c_pcg.lam + idx);
+            pv = c_pcg.z[idx];
+            if (coarse && cl >= 0) {
+                const double* R = c_pcg.camP + (size_t)cam * CAM_PREP + 3 * k;
+                const double R0 = R[0], R1 = R[1], R2 = R[2];
+                if (cl != cl_cached) {
+                    cl_cached = cl;
+                    const double* y = c_pcg.yc + (size_t)cl * 6;
                     const double y3 = y[3], y4 = y[4], y5 = y[5];
                     if (a >= 3) {
                         u0 = y3; u1 = y4; u2 = y5;
                     } else {
-                        const double* xb = A.xbar + 3 * (size_t)cl_cached;
+                        const double* xb = c_pcg.xbar + 3 * (size_t)cl;
                         const double x0 = __ldg(xb), x1 = __ldg(xb + 1), x2 = __ldg(xb + 2);
                         u0 = y[0] + (x1 * y5 - x2 * y4);
                         u1 = y[1] + (x2 * y3 - x0 * y5);
                         u2 = y[2] + (x0 * y4 - x1 * y3);
                     }
                 }
-                pv += (a >= 3 ? -0.5 : -1.0) * (cur.R0 * u0 + cur.R1 * u1 + cur.R2 * u2);
+                pv += (a >= 3 ? -0.5 : -1.0) * (R0 * u0 + R1 * u1 + R2 * u2);
             }
-            if (!first) pv += beta * cur.v1;
-            A.p[idx] = pv;
+            if (!first) pv += beta * c_pcg.p[idx];
+            c_pcg.p[idx] = pv;
         }
-        double p6[6];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) p6[k] = __shfl_sync(0xffffffffu, pv, min(6 * g + k, 31));
+        const int src = min(6 * g, 26);
+        const double p0 = __shfl_sync(0xffffffffu, pv, src), p1 = __shfl_sync(0xffffffffu, pv, src + 1), p2 = __shfl_sync(0xffffffffu, pv, src + 2);
+        const double p3 = __shfl_sync(0xffffffffu, pv, src + 3), p4 = __shfl_sync(0xffffffffu, pv, src + 4), p5 = __shfl_sync(0xffffffffu, pv, src + 5);
         if (valid) {
-            const double qt = cur.v2 * pv + cur.m0.x * p6[0] + cur.m0.y * p6[1] + cur.m1.x * p6[2] + cur.m1.y * p6[3] + cur.m2.x * p6[4] + cur.m2.y * p6[5];
-            A.q[idx] = qt;
+            const double qt = lam * pv + b0.x * p0 + b0.y * p1 + b1.x * p2 + b1.y * p3 + b2.x * p4 + b2.y * p5;
+            c_pcg.q[idx] = qt;
             pq += qt * pv;
         }
     }
     return pq;
 }
 
-// A pass of the streamed product inside a persistent kernel (coherent loads of the vectors that change between passes).
+// The interior pass of the plain kernel: all arguments from constant memory.
+__device__ __noinline__ void pcg_phase_product(SpShared& sh, unsigned char* sp_ring, bool reinit, double* dot_acc) {
+    const PcgArgs& A = c_pcg;
+    sp_pass<SP_FULL, true>(sh, sp_ring, reinit, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr, -1.0, A.q, dot_acc);
+}
+
 template <int MODE>
 __device__ __noinline__ void sp_pass_call(SpShared& sh, unsigned char* sp_ring, bool reinit, const SpSeg* segs, const int* cta_seg, int nseg,
                                           const int2* slot_desc, int nslots_total, const unsigned char* Es, const int* mo_cam, const double* vin_c,
@@ -293,7 +285,8 @@ __device__ __noinline__ void sp_pass_call(SpShared& sh, unsigned char* sp_ring, 
 
 // rc = sum of the restriction partials: all partials into shared memory with independent loads, then summed per cluster.
 // s_rc: nC (+1) doubles; s_part: 6 per partial (both in the idle ring).
-__device__ __forceinline__ void pcg_assemble_rc(const PcgArgs& A, int nC, double* s_rc, double* s_part) {
+__device__ __forceinline__ void pcg_assemble_rc(int nC, double* s_rc, double* s_part) {
+    const PcgArgs& A = c_pcg;
     const int t = threadIdx.x;
     for (int e = t; e < 6 * A.nparts; e += kSpThreads) s_part[e] = A.rc_part[e];
     __syncthreads();
@@ -307,10 +300,11 @@ __device__ __forceinline__ void pcg_assemble_rc(const PcgArgs& A, int nC, double
 
 // Phase C: every CTA forms the whole restricted residual in shared memory, then the rows of A_c^-1 rc this CTA's warps
 // own.  Returns (in every thread) the CTA's share of rc . yc.
-__device__ __noinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_rc, double* s_red) {
+__device__ __noinline__ double pcg_coarse_apply(double* s_rc, double* s_red) {
+    const PcgArgs& A = c_pcg;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     __syncthreads();
-    pcg_assemble_rc(A, A.nC, s_rc, s_rc + ((A.nC + 8) & ~1));
+    pcg_assemble_rc(A.nC, s_rc, s_rc + ((A.nC + 8) & ~1));
     __syncthreads();
     double dot = 0.0;
     const int nwarps = kSpThreads / 32;
@@ -334,7 +328,8 @@ __device__ __noinline__ double pcg_coarse_apply(const PcgArgs& A, double* s_rc, 
 }
 
 __global__ void __launch_bounds__(kSpThreads, 1)
-k_pcg_persistent(const __grid_constant__ PcgArgs A) {   // __grid_constant__: the fields are read from the parameter bank where they are used
+k_pcg_persistent() {
+    const PcgArgs& A = c_pcg;
     const bool coarse = A.ncl > 0 && __ldcg(A.coarse_info) == 0;   // uniform for the grid
     extern __shared__ __align__(128) unsigned char sp_ring[];
     __shared__ SpShared sh;
@@ -342,13 +337,9 @@ k_pcg_persistent(const __grid_constant__ PcgArgs A) {   // __grid_constant__: th
     double* s_rc = reinterpret_cast<double*>(sp_ring);   // phase C scratch: the ring is idle between products
     const unsigned G = gridDim.x;
     volatile double* scal = A.scal;
-    bool aborted = false;
     unsigned long long t_prev = 0;
     // phase clock (CTA 0, thread 0; only when the host asked for it): time since the previous tick into slot `k`
     auto tick = [&](int k) {
-#ifdef VMM_PCG_NO_TICK
-        return;
-#endif
         if (A.phase_ns && blockIdx.x == 0 && threadIdx.x == 0) {
             unsigned long long now;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
@@ -356,98 +347,88 @@ k_pcg_persistent(const __grid_constant__ PcgArgs A) {   // __grid_constant__: th
             t_prev = now;
         }
     };
-    int it = 0, iterations = 0;
-    bool ok = true, ring_used = false;
-    double rel2 = 1.0, rz0 = 0.0, rz_last = 0.0, rz_before = 0.0;
-
-    int it_base = 0;
-    if (!A.resume) {
-        // ---- start: z = M^-1 r, r.z, restriction; coarse solve; first direction ----
-        {
-            double rz = pcg_phase_update(A, true, 0.0, coarse, s_acc);
-            rz = cta_sum(rz, s_red);
-            if (threadIdx.x == 0) red_add(A.scal + PS_RZ, rz);
-        }
-        if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
-        if (coarse) {
-            const double d = pcg_coarse_apply(A, s_rc, s_red);
-            if (threadIdx.x == 0) red_add(A.scal + PS_RZ, d);
-            if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
-        }
-        {
-            double pq = pcg_phase_direction(A, true, 0.0, coarse);
-            pq = cta_sum(pq, s_red);
-            if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
-        }
-        if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
-        rz0 = scal[PS_RZ];
-    } else {
-        // ---- resume: the stopped solve had x, r, z updated and yc formed, but not the direction ----
+    // ONE loop, every phase inlined exactly once (the start, the resumed start and the iterations are the same code
+    // under flags: three inlined copies of each phase made the register allocator spill inside the camera loops, and
+    // with 184 KB of the SM's memory in the ring there is no L1 left for local memory).
+    //   pass -1 (fresh):    B(first) -> C -> D(first)           rows: r.z_0, p.q_0
+    //   pass -1 (resumed):  D(beta from the stopped launch)
+    //   pass it >= 0:       A -> B -> C -> stop test -> D
+    bool first = !A.resume, resumed = A.resume != 0, aborted = false, ok = true, ring_used = false;
+    int it = -1, iterations = 0, it_base = 0;
+    double rel2 = 1.0, rz0 = 0.0, rz_s = 0.0, rz_new = 0.0, rz_last = 0.0, rz_before = 0.0;
+    if (resumed) {
         rz0 = __ldcg(A.result + SC_RZ0);
-        const double rz_new = __ldcg(A.result + SC_RZ), rz_prev = __ldcg(A.result + SC_RZ + 1);
+        rz_new = __ldcg(A.result + SC_RZ);
+        rz_s = __ldcg(A.result + SC_RZ + 1);
         it_base = (int)__ldcg(A.result + SC_ITERS);
-        if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }   // every CTA has read the old scalars
+        if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }   // every CTA has read the scalars of the stopped launch
         if (blockIdx.x == 0 && threadIdx.x == 0) A.scal[PS_RZ] = rz_new;
-        {
-            double pq = pcg_phase_direction(A, false, rz_prev != 0.0 ? rz_new / rz_prev : 0.0, coarse);
-            pq = cta_sum(pq, s_red);
-            if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
-        }
-        if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
     }
-    rz0 = scal[PS_RZ];
-    ok = isfinite(rz0);
-    if (ok && rz0 > 0.0) {
-        tick(-1);
-        for (it = 0; it < A.max_it; ++it) {
-            double* row = A.scal + (size_t)it * PS_STRIDE;
-            double* nxt = row + PS_STRIDE;
+    tick(-1);
+    for (;;) {
+        double* row = A.scal + (size_t)max(it, 0) * PS_STRIDE;
+        double* nxt = A.scal + (size_t)(it + 1) * PS_STRIDE;
+        if (it >= 0) {
             // ---- A: q -= Es Es^T p ----
-            sp_pass_call<SP_FULL>(sh, sp_ring, ring_used, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr,
-                                   -1.0, A.q, row + PS_WW);
+            pcg_phase_product(sh, sp_ring, ring_used, row + PS_WW);
             ring_used = true;
             tick(0);
-            if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            if (!grid_barrier(A.barrier, G)) { aborted = true; break; }
             tick(4);
+        }
+        if (!resumed) {
             // ---- B ----
-            const double rz_s = scal[(size_t)it * PS_STRIDE + PS_RZ];
-            const double denom = scal[(size_t)it * PS_STRIDE + PS_PBP] - scal[(size_t)it * PS_STRIDE + PS_WW];
-            const double alpha = (rz_s != 0.0) ? rz_s / denom : 0.0;
+            double alpha = 0.0;
+            if (it >= 0) {
+                rz_s = scal[(size_t)it * PS_STRIDE + PS_RZ];
+                const double denom = scal[(size_t)it * PS_STRIDE + PS_PBP] - scal[(size_t)it * PS_STRIDE + PS_WW];
+                alpha = (rz_s != 0.0) ? rz_s / denom : 0.0;
+            }
             {
-                double rz = pcg_phase_update(A, false, alpha, coarse, s_acc);
+                double rz = pcg_phase_update(first, alpha, coarse, s_acc);
                 rz = cta_sum(rz, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, rz);
             }
             tick(1);
-            if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            if (!grid_barrier(A.barrier, G)) { aborted = true; break; }
             tick(4);
             // ---- C ----
             if (coarse) {
-                const double d = pcg_coarse_apply(A, s_rc, s_red);
+                const double d = pcg_coarse_apply(s_rc, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, d);
                 tick(2);
-                if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+                if (!grid_barrier(A.barrier, G)) { aborted = true; break; }
                 tick(4);
             }
-            // ---- D ----
-            const double rz_new = scal[(size_t)(it + 1) * PS_STRIDE + PS_RZ];
+            rz_new = scal[(size_t)(it + 1) * PS_STRIDE + PS_RZ];
+        }
+        // ---- stop test ----
+        if (first) {
+            rz0 = rz_new;
+            ok = isfinite(rz0);
+            if (!ok) break;
+            if (!(rz0 > 0.0)) { rel2 = 0.0; break; }   // zero right-hand side: x = 0 is the solution
+        } else if (!resumed) {
             rz_last = rz_new; rz_before = rz_s;
             iterations = it + 1;
             rel2 = rz_new / rz0;
             if (!isfinite(rz_new)) { ok = false; break; }
             if (iterations >= A.min_it && rz_new <= A.tol2 * rz0) break;
-            const double beta = (rz_s != 0.0) ? rz_new / rz_s : 0.0;
-            {
-                double pq = pcg_phase_direction(A, false, beta, coarse);
-                pq = cta_sum(pq, s_red);
-                if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
-            }
-            tick(3);
-            if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
-            tick(4);
+            if (iterations >= A.max_it) break;
         }
-    } else if (ok) {
-        rel2 = 0.0;   // zero right-hand side: x = 0 is the solution
+        // ---- D ----
+        {
+            const double beta = (first || rz_s == 0.0) ? 0.0 : rz_new / rz_s;
+            double pq = pcg_phase_direction(first, beta, coarse);
+            pq = cta_sum(pq, s_red);
+            if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
+        }
+        tick(3);
+        if (!grid_barrier(A.barrier, G)) { aborted = true; break; }
+        tick(4);
+        first = false;
+        resumed = false;
+        ++it;
     }
 finish:
     if (aborted) ok = false;

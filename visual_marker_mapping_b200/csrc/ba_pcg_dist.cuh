@@ -30,7 +30,6 @@ constexpr size_t kPcgxCap1 = 256 * 1024;   // words (one double each) per slot o
 constexpr size_t kPcgxCap2 = 2048;         // ... of the coarse exchange (order of A_c + 1 <= 1537)
 
 struct PcgDistArgs {
-    PcgArgs a;
     // boundary path of the product: segment list of the split / shared markers (marker field = position in wbl)
     const SpSeg* bsegs; const int* bcta_seg; int bnseg; const int2* bslot_desc; int bnslots_total;
     int n_wb;                 // entries of the boundary vector (6 per boundary marker); 0: no boundary path
@@ -44,6 +43,8 @@ struct PcgDistArgs {
     size_t cap1, cap2;
     unsigned* seq;            // device-resident sequence base (advanced by the kernel, the same on every rank)
 };
+
+__constant__ PcgDistArgs c_pcgd;
 
 __device__ __forceinline__ uint4* x1_slot(const PcgDistArgs& D, int dst_rank, int parity, int src_rank) {
     return D.xbuf[dst_rank] + ((size_t)parity * D.world + src_rank) * D.cap1;
@@ -106,7 +107,7 @@ __device__ __forceinline__ double pcg_exchange_boundary(const PcgDistArgs& D, un
     }
     for (int i = t0; i < n + 2; i += stride) {
         double s = 0.0;
-        for (int r = 0; r < D.world; ++r) s += ld_word_pair_guarded(x1_slot(D, D.rank, parity, r) + i, seq, D.a.barrier + 2);
+        for (int r = 0; r < D.world; ++r) s += ld_word_pair_guarded(x1_slot(D, D.rank, parity, r) + i, seq, c_pcg.barrier + 2);
         D.wb[i] = s;
         if (i < n) sq += s * s;
     }
@@ -121,7 +122,7 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
     __syncthreads();
     if (!SHARDED || (int)blockIdx.x < D.world) {
         // this rank's restricted residual from the unit partials (tail: its r.z partial)
-        pcg_assemble_rc(A, nC, s_rc, s_rc + ((nC + 8) & ~1));
+        pcg_assemble_rc(nC, s_rc, s_rc + ((nC + 8) & ~1));
         if (t == 0) s_rc[nC] = rz_local;
         __syncthreads();
         if (SHARDED) {
@@ -133,7 +134,7 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
         const int parity = (int)(seq & 1u);
         for (int e = t; e <= nC; e += kSpThreads) {
             double s = 0.0;
-            for (int r = 0; r < D.world; ++r) s += ld_word_pair_guarded(x2_slot(D, D.rank, parity, r) + e, seq, D.a.barrier + 2);
+            for (int r = 0; r < D.world; ++r) s += ld_word_pair_guarded(x2_slot(D, D.rank, parity, r) + e, seq, c_pcg.barrier + 2);
             s_rc[e] = s;
         }
     }
@@ -154,8 +155,9 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
 
 template <bool SHARDED>
 __global__ void __launch_bounds__(kSpThreads, 1)
-k_pcg_persistent_dist(const __grid_constant__ PcgDistArgs D) {
-    const PcgArgs& A = D.a;
+k_pcg_persistent_dist() {
+    const PcgDistArgs& D = c_pcgd;   // constant memory, like c_pcg (ba_pcg.cuh)
+    const PcgArgs& A = c_pcg;
     const bool coarse = A.ncl > 0 && __ldcg(A.coarse_info) == 0;   // uniform for the grid (and, the matrix being replicated, for all ranks)
     extern __shared__ __align__(128) unsigned char sp_ring[];
     __shared__ SpShared sh;
@@ -173,7 +175,7 @@ k_pcg_persistent_dist(const __grid_constant__ PcgDistArgs D) {
 
     // ---- start ----
     {
-        double rz = pcg_phase_update(A, true, 0.0, coarse, s_acc);
+        double rz = pcg_phase_update(true, 0.0, coarse, s_acc);
         rz = cta_sum(rz, s_red);
         if (threadIdx.x == 0) red_add(A.scal + PS_RZ, rz);
         if (boundary) for (int i = blockIdx.x * kSpThreads + threadIdx.x; i < D.n_wb; i += G * kSpThreads) D.wbl[i] = 0.0;
@@ -183,7 +185,7 @@ k_pcg_persistent_dist(const __grid_constant__ PcgDistArgs D) {
     if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
     rz0 = s_rc[nC] + pcg_fixed_dot(s_rc, A.yc, nC, s_red);
     {
-        double pq = pcg_phase_direction(A, true, 0.0, coarse);
+        double pq = pcg_phase_direction(true, 0.0, coarse);
         pq = cta_sum(pq, s_red);
         if (threadIdx.x == 0) red_add(A.scal + PS_PBP, pq);
     }
@@ -224,7 +226,7 @@ k_pcg_persistent_dist(const __grid_constant__ PcgDistArgs D) {
             // ---- B ----
             const double alpha = (rz_s != 0.0) ? rz_s / (pbp_tot - ww_tot) : 0.0;
             {
-                double rz = pcg_phase_update(A, false, alpha, coarse, s_acc);
+                double rz = pcg_phase_update(false, alpha, coarse, s_acc);
                 rz = cta_sum(rz, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, rz);
                 if (boundary) for (int i = blockIdx.x * kSpThreads + threadIdx.x; i < D.n_wb; i += G * kSpThreads) D.wbl[i] = 0.0;
@@ -242,7 +244,7 @@ k_pcg_persistent_dist(const __grid_constant__ PcgDistArgs D) {
             const double beta = (rz_s != 0.0) ? rz_new / rz_s : 0.0;
             rz_s = rz_new;
             {
-                double pq = pcg_phase_direction(A, false, beta, coarse);
+                double pq = pcg_phase_direction(false, beta, coarse);
                 pq = cta_sum(pq, s_red);
                 if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
             }

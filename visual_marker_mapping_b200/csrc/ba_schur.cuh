@@ -243,7 +243,7 @@ constexpr int kSpGroupWarps = VMM_SP_GROUP_WARPS;
 constexpr int kSpConsumerThreads = kSpGroups * kSpGroupWarps * 32;
 constexpr int kSpThreads = kSpConsumerThreads + 32;                  // + producer warp
 #ifndef VMM_SP_RING
-#define VMM_SP_RING 20
+#define VMM_SP_RING 16
 #endif
 constexpr int kSpRing = VMM_SP_RING;                                 // slots of kSlotBytes: 184,320 B at 20
 constexpr int kSegRegObs = kSpGroupWarps * 32;                       // observations of a segment held in registers
