@@ -100,8 +100,8 @@ typedef struct {
                                              default 1e-3; 0 = off (stop on the inexact step).  Unused in parity mode.  On one GPU the
                                              confirming solve CONTINUES the PCG iteration that produced the inexact step. */
     double pcg_polish_tolerance;          /* forcing term once the solve is in its polishing phase, i.e. after an accepted step
-                                             lowered the cost by less than pcg_polish_threshold (relative); 0 (default) = the same
-                                             tolerance throughout.  Loose tolerances are only dangerous while the steps are large. */
+                                             lowered the cost by less than pcg_polish_threshold (relative); 0 = the same tolerance
+                                             throughout; default 5e-2.  A loose tolerance is only dangerous while the steps are large. */
     double pcg_polish_threshold;          /* default 1e-2 */
 } vmm_ba_options;
 

@@ -136,7 +136,7 @@ __device__ __forceinline__ bool inv_sweep_block_v2(double* S, double* col /* 2 x
 }
 
 #ifndef VMM_INV_SWEEP_V2
-#define VMM_INV_SWEEP_V2 0   // 1: register-resident pivot sweep (under test on the device)
+#define VMM_INV_SWEEP_V2 1   // register-resident pivot sweep (0: the round-2 first version, every entry through shared memory)
 #endif
 #ifndef VMM_INV_LOOKAHEAD
 #define VMM_INV_LOOKAHEAD 1  // CTA 0 inverts the next pivot block during the tile phase (0: every CTA at the start of the step)
