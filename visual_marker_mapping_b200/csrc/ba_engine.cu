@@ -566,7 +566,7 @@ int build_pcg_units(vmm_ba_engine* e, int ncl, const std::vector<int>& cl_ptr, c
     CU(P.cta_unit.alloc(G + 1)); CU(P.cta_cl_first.alloc(G)); CU(P.cta_part.alloc(G + 1)); CU(P.cl_unit_ptr.alloc(ncl + 1));
     CU(P.rc_part.alloc(std::max<size_t>(6 * (size_t)P.nparts, 1)));
     CU(cudaMemsetAsync(P.rc_part.p, 0, sizeof(double) * std::max<size_t>(6 * (size_t)P.nparts, 1), e->stream));
-    if (!P.phase_ns.p) { CU(P.phase_ns.alloc(8)); CU(cudaMemsetAsync(P.phase_ns.p, 0, 8 * sizeof(unsigned long long), e->stream)); }
+    if (!P.phase_ns.p) { CU(P.phase_ns.alloc(8 + 1024)); CU(cudaMemsetAsync(P.phase_ns.p, 0, (8 + 1024) * sizeof(unsigned long long), e->stream)); }
     if (!P.barrier.p) { CU(P.barrier.alloc(4)); CU(cudaMemsetAsync(P.barrier.p, 0, 4 * sizeof(unsigned), e->stream)); }
     auto up = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, e->stream) : cudaSuccess; };
     CU(up(P.unit_cams.p, cams.data(), sizeof(int) * cams.size()));
@@ -616,6 +616,7 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, b
         if (e->cta_part.n < (size_t)e->sp_grid) CU(e->cta_part.alloc(e->sp_grid));
         d.cta_part = e->cta_part.p;
         d.rank = e->rank; d.world = e->world;
+        { static const char* sk = std::getenv("VMM_BA_DIST_SKIP"); d.debug_skip = sk ? std::atoi(sk) : 0; }
         if (e->world == 1) {
             // split markers on one GPU: the boundary vector is indexed by marker
             d.n_wb = e->seg_big.count > 0 ? 6 * (int)e->Nm : 0;
@@ -1037,7 +1038,9 @@ int build_segments(vmm_ba_engine* e, const std::vector<int>& mptr, const std::ve
     for (int64_t j = 0; j < e->Nm; ++j) {
         const int n = mptr[j + 1] - mptr[j];
         if (!active[j] || n == 0) continue;
-        const bool whole = sharded ? bnd_id[j] < 0 : n <= kSegMaxObs;
+        // VMM_BA_TEST_SPLIT_EVERY=k (tests): every k-th marker goes through the boundary path although it would fit one segment
+        static const int split_every = std::getenv("VMM_BA_TEST_SPLIT_EVERY") ? std::max(1, std::atoi(std::getenv("VMM_BA_TEST_SPLIT_EVERY"))) : 0;
+        const bool whole = sharded ? bnd_id[j] < 0 : (n <= kSegMaxObs && !(split_every && j % split_every == 0));
         if (whole) full.push_back(HostSeg{ SpSeg{ (int)j, 0, n, mptr[j] }, mtile[j] });
         for (int o = 0; o < n; o += kSegRegObs) {
             HostSeg d{ SpSeg{ (int)j, 0, std::min(kSegRegObs, n - o), mptr[j] + o }, mtile[j] + o / kTileObs };
@@ -2518,7 +2521,7 @@ int vmm_ba_profile_enable(vmm_ba_handle e, int on) {
     CU(cudaStreamSynchronize(e->stream));
     profile_resolve(e);
     e->profiling = on != 0;
-    if (e->pcgp.phase_ns.p && on) CU(cudaMemsetAsync(e->pcgp.phase_ns.p, 0, 8 * sizeof(unsigned long long), e->stream));
+    if (e->pcgp.phase_ns.p && on) CU(cudaMemsetAsync(e->pcgp.phase_ns.p, 0, (8 + 1024) * sizeof(unsigned long long), e->stream));
     std::fill(e->prof_ms.begin(), e->prof_ms.end(), 0.0);
     std::fill(e->prof_n.begin(), e->prof_n.end(), 0);
     return VMM_BA_OK;
@@ -2526,12 +2529,17 @@ int vmm_ba_profile_enable(vmm_ba_handle e, int on) {
 
 int vmm_ba_pcg_phase_ns(vmm_ba_handle e, double* out5) {
     if (!e || !out5) return VMM_BA_ERR_INVALID_ARGUMENT;
-    for (int k = 0; k < 5; ++k) out5[k] = 0.0;
+    for (int k = 0; k < 8; ++k) out5[k] = 0.0;
     if (!e->pcgp.phase_ns.p) return VMM_BA_OK;
     CU(cudaSetDevice(e->device));
-    unsigned long long h[8];
-    CU(cudaMemcpy(h, e->pcgp.phase_ns.p, sizeof(h), cudaMemcpyDeviceToHost));
+    std::vector<unsigned long long> h(8 + 1024);
+    CU(cudaMemcpy(h.data(), e->pcgp.phase_ns.p, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost));
     for (int k = 0; k < 5; ++k) out5[k] = (double)h[k];
+    // [5..7]: streamed product per CTA: min, mean, max over the grid
+    const int G = std::min(e->sp_grid, 1024);
+    double mn = 1e300, mx = 0.0, sum = 0.0;
+    for (int b = 0; b < G; ++b) { const double v = (double)h[8 + b]; mn = std::min(mn, v); mx = std::max(mx, v); sum += v; }
+    out5[5] = G > 0 ? mn : 0.0; out5[6] = G > 0 ? sum / G : 0.0; out5[7] = mx;
     return VMM_BA_OK;
 }
 

@@ -52,7 +52,8 @@ struct PcgArgs {
     double tol2;
     int resume;               // 1: continue the solve the previous launch stopped (same system, tighter tolerance): x, r, z, p and the
                               //    scalars it left in `result` are taken up where they were
-    unsigned long long* phase_ns;   // optional (debug / bench): CTA 0 accumulates the time of the phases A, B, C, D, barriers excluded [0..3], barriers [4]
+    unsigned long long* phase_ns;   // optional (debug / bench): CTA 0 accumulates the time of the phases A, B, C, D, barriers excluded [0..3], barriers [4];
+                                    // [8 + b]: time CTA b spent in its streamed product (load balance of phase A)
 };
 
 // The arguments live in constant memory (copied there, stream-ordered, before every launch): every phase — each its own
@@ -155,14 +156,14 @@ __device__ __noinline__ double pcg_phase_update(bool first, double alpha, bool c
                 const double* R = c_pcg.camP + (size_t)cam * CAM_PREP;
                 R0 = R[k]; R1 = R[3 + k]; R2 = R[6 + k];
             }
+            // all operands first, then the stores: the vectors may alias as far as the compiler knows, so a load written
+            // behind a store waits for the store's operands (one L2 round trip each)
             rv = c_pcg.r[idx];
-            if (first) {
-                c_pcg.x[idx] = 0.0;
-            } else {
-                c_pcg.x[idx] += alpha * c_pcg.p[idx];
-                rv -= alpha * c_pcg.q[idx];
-                c_pcg.r[idx] = rv;
-            }
+            double xv = 0.0, pvv = 0.0, qv = 0.0;
+            if (!first) { xv = c_pcg.x[idx]; pvv = c_pcg.p[idx]; qv = c_pcg.q[idx]; }
+            rv -= alpha * qv;
+            c_pcg.x[idx] = xv + alpha * pvv;
+            if (!first) c_pcg.r[idx] = rv;
         }
         const int src = min(6 * g, 26);
         const double r0 = __shfl_sync(0xffffffffu, rv, src), r1 = __shfl_sync(0xffffffffu, rv, src + 1), r2 = __shfl_sync(0xffffffffu, rv, src + 2);
@@ -236,6 +237,7 @@ __device__ __noinline__ double pcg_phase_direction(bool first, double beta, bool
             b0 = __ldg(b); b1 = __ldg(b + 1); b2 = __ldg(b + 2);
             lam = __ldg(c_pcg.lam + idx);
             pv = c_pcg.z[idx];
+            const double p_old = first ? 0.0 : c_pcg.p[idx];   // requested with the other operands (see pcg_phase_update)
             if (coarse && cl >= 0) {
                 const double* R = c_pcg.camP + (size_t)cam * CAM_PREP + 3 * k;
                 const double R0 = R[0], R1 = R[1], R2 = R[2];
@@ -255,7 +257,7 @@ __device__ __noinline__ double pcg_phase_direction(bool first, double beta, bool
                 }
                 pv += (a >= 3 ? -0.5 : -1.0) * (R0 * u0 + R1 * u1 + R2 * u2);
             }
-            if (!first) pv += beta * c_pcg.p[idx];
+            pv += beta * p_old;
             c_pcg.p[idx] = pv;
         }
         const int src = min(6 * g, 26);
@@ -370,8 +372,18 @@ k_pcg_persistent() {
         double* nxt = A.scal + (size_t)(it + 1) * PS_STRIDE;
         if (it >= 0) {
             // ---- A: q -= Es Es^T p ----
+            unsigned long long ta = 0;
+            if (A.phase_ns && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ta));
             pcg_phase_product(sh, sp_ring, ring_used, row + PS_WW);
             ring_used = true;
+            if (A.phase_ns) {
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    unsigned long long tb;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tb));
+                    A.phase_ns[8 + blockIdx.x] += tb - ta;
+                }
+            }
             tick(0);
             if (!grid_barrier(A.barrier, G)) { aborted = true; break; }
             tick(4);

@@ -42,6 +42,7 @@ struct PcgDistArgs {
     uint4* xbuf[kPeerMaxWorld];   // every rank's exchange buffer as mapped here: [X1: 2 parities][world][cap1] [X2: 2 parities][world][cap2]
     size_t cap1, cap2;
     unsigned* seq;            // device-resident sequence base (advanced by the kernel, the same on every rank)
+    int debug_skip;           // test builds only (VMM_BA_DIST_SKIP): bit 0 / 1 / 2 skip the interior / gather / scatter pass (wrong numbers)
 };
 
 __constant__ PcgDistArgs c_pcgd;
@@ -198,10 +199,10 @@ k_pcg_persistent_dist() {
             double* row = A.scal + (size_t)it * PS_STRIDE;
             double* nxt = row + PS_STRIDE;
             // ---- A1 / A2 ----
-            sp_pass_call<SP_FULL>(sh, sp_ring, ring_used, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr,
+            if (!(D.debug_skip & 1)) sp_pass_call<SP_FULL>(sh, sp_ring, ring_used, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr,
                                    -1.0, A.q, row + PS_WW);
             ring_used = ring_used || A.cta_seg[blockIdx.x] < A.cta_seg[blockIdx.x + 1];
-            if (boundary) {
+            if (boundary && !(D.debug_skip & 2)) {
                 sp_pass_call<SP_GATHER>(sh, sp_ring, ring_used, D.bsegs, D.bcta_seg, D.bnseg, D.bslot_desc, D.bnslots_total, A.Es, A.mo_cam, A.p,
                                          D.wbl, 1.0, nullptr, nullptr);
                 ring_used = ring_used || D.bcta_seg[blockIdx.x] < D.bcta_seg[blockIdx.x + 1];
@@ -218,7 +219,7 @@ k_pcg_persistent_dist() {
                 for (unsigned b = 0; b < G; ++b) ww_tot += __ldcg(D.cta_part + b);   // fixed order: the same alpha in every CTA
                 // ---- A3 ----
                 if (boundary) {
-                    sp_pass_call<SP_SCATTER>(sh, sp_ring, ring_used, D.bsegs, D.bcta_seg, D.bnseg, D.bslot_desc, D.bnslots_total, A.Es, A.mo_cam,
+                    if (!(D.debug_skip & 4)) sp_pass_call<SP_SCATTER>(sh, sp_ring, ring_used, D.bsegs, D.bcta_seg, D.bnseg, D.bslot_desc, D.bnslots_total, A.Es, A.mo_cam,
                                               nullptr, D.wb, -1.0, A.q, nullptr);
                     if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
                 }
