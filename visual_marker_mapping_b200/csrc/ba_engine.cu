@@ -581,6 +581,10 @@ int build_pcg_units(vmm_ba_engine* e, int ncl, const std::vector<int>& cl_ptr, c
 
 // The whole PCG solve as one cooperative launch (ba_pcg.cuh).  The result (iterations, relative residual, ok) lands in
 // e->sc and reaches the host with the next read_stats: no host synchronisation inside the linear solve.
+#ifdef VMM_DBG_TRACE
+constexpr size_t kTraceWords = 160 * 64 + 160 * 32;
+unsigned* g_trace_host = nullptr;
+#endif
 int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, bool resume) {
     auto& P = e->pcgp;
     const size_t rows = (size_t)max_it + 2;
@@ -617,6 +621,15 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, b
         d.cta_part = e->cta_part.p;
         d.rank = e->rank; d.world = e->world;
         { static const char* sk = std::getenv("VMM_BA_DIST_SKIP"); d.debug_skip = sk ? std::atoi(sk) : 0; }
+#ifdef VMM_DBG_TRACE
+        if (!g_trace_host) {
+            CU(cudaHostAlloc((void**)&g_trace_host, sizeof(unsigned) * kTraceWords, cudaHostAllocMapped));
+            std::memset(g_trace_host, 0, sizeof(unsigned) * kTraceWords);
+            unsigned* dp = nullptr;
+            CU(cudaHostGetDevicePointer((void**)&dp, g_trace_host, 0));
+            CU(cudaMemcpyToSymbolAsync(g_sp_trace, &dp, sizeof(dp), 0, cudaMemcpyHostToDevice, e->stream));
+        }
+#endif
         if (e->world == 1) {
             // split markers on one GPU: the boundary vector is indexed by marker
             d.n_wb = e->seg_big.count > 0 ? 6 * (int)e->Nm : 0;
@@ -640,6 +653,7 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, b
 }
 
 struct PcgResult { int iterations; bool ok; double rel; };
+
 
 bool pcg_persistent_eligible(const vmm_ba_engine* e) {
     static const bool legacy = std::getenv("VMM_BA_PCG_LEGACY") != nullptr;   // A/B: the five-launches-per-iteration loop of round 1
@@ -2527,6 +2541,9 @@ int vmm_ba_profile_enable(vmm_ba_handle e, int on) {
     return VMM_BA_OK;
 }
 
+#ifdef VMM_DBG_TRACE
+__attribute__((visibility("default"))) int vmm_ba_debug_trace_words(unsigned** p, size_t* n) { *p = g_trace_host; *n = kTraceWords; return 0; }
+#endif
 int vmm_ba_pcg_phase_ns(vmm_ba_handle e, double* out5) {
     if (!e || !out5) return VMM_BA_ERR_INVALID_ARGUMENT;
     for (int k = 0; k < 8; ++k) out5[k] = 0.0;

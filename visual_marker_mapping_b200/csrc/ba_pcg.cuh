@@ -273,16 +273,21 @@ __device__ __noinline__ double pcg_phase_direction(bool first, double beta, bool
 }
 
 // The interior pass of the plain kernel: all arguments from constant memory.
-__device__ __noinline__ void pcg_phase_product(SpShared& sh, unsigned char* sp_ring, bool reinit, double* dot_acc) {
+__device__ __noinline__ void pcg_phase_product(SpShared& sh, unsigned char* sp_ring, bool ring_used, double* dot_acc) {
     const PcgArgs& A = c_pcg;
-    sp_pass<SP_FULL, true>(sh, sp_ring, reinit, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr, -1.0, A.q, dot_acc);
+    sp_pass<SP_FULL, true>(sh, sp_ring, ring_used, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr, -1.0, A.q, dot_acc);
 }
 
+#ifdef VMM_DBG_PASS_INLINE
+#define VMM_PASS_CALL_ATTR __forceinline__
+#else
+#define VMM_PASS_CALL_ATTR __noinline__
+#endif
 template <int MODE>
-__device__ __noinline__ void sp_pass_call(SpShared& sh, unsigned char* sp_ring, bool reinit, const SpSeg* segs, const int* cta_seg, int nseg,
+__device__ VMM_PASS_CALL_ATTR void sp_pass_call(SpShared& sh, unsigned char* sp_ring, bool ring_used, const SpSeg* segs, const int* cta_seg, int nseg,
                                           const int2* slot_desc, int nslots_total, const unsigned char* Es, const int* mo_cam, const double* vin_c,
                                           double* mvec, double sign, double* out_c, double* dot_acc) {
-    sp_pass<MODE, true>(sh, sp_ring, reinit, segs, cta_seg, nseg, slot_desc, nslots_total, Es, mo_cam, vin_c, mvec, sign, out_c, dot_acc);
+    sp_pass<MODE, true>(sh, sp_ring, ring_used, segs, cta_seg, nseg, slot_desc, nslots_total, Es, mo_cam, vin_c, mvec, sign, out_c, dot_acc);
 }
 
 // rc = sum of the restriction partials: all partials into shared memory with independent loads, then summed per cluster.

@@ -154,6 +154,11 @@ __device__ __forceinline__ void pcg_coarse_exchange_apply(const PcgDistArgs& D, 
     }
 }
 
+#ifdef VMM_DBG_TRACE
+#define KT(stage) do { if (g_sp_trace && threadIdx.x == 0) *reinterpret_cast<volatile unsigned*>(g_sp_trace + ((size_t)blockIdx.x * 16 + 15) * 4) = ((unsigned)it << 8) | (unsigned)(stage); } while (0)
+#else
+#define KT(stage) do { } while (0)
+#endif
 template <bool SHARDED>
 __global__ void __launch_bounds__(kSpThreads, 1)
 k_pcg_persistent_dist() {
@@ -199,15 +204,19 @@ k_pcg_persistent_dist() {
             double* row = A.scal + (size_t)it * PS_STRIDE;
             double* nxt = row + PS_STRIDE;
             // ---- A1 / A2 ----
+            KT(1);
             if (!(D.debug_skip & 1)) sp_pass_call<SP_FULL>(sh, sp_ring, ring_used, A.segs, A.cta_seg, A.nseg, A.slot_desc, A.nslots_total, A.Es, A.mo_cam, A.p, nullptr,
                                    -1.0, A.q, row + PS_WW);
             ring_used = ring_used || A.cta_seg[blockIdx.x] < A.cta_seg[blockIdx.x + 1];
+            KT(2);
             if (boundary && !(D.debug_skip & 2)) {
                 sp_pass_call<SP_GATHER>(sh, sp_ring, ring_used, D.bsegs, D.bcta_seg, D.bnseg, D.bslot_desc, D.bnslots_total, A.Es, A.mo_cam, A.p,
                                          D.wbl, 1.0, nullptr, nullptr);
                 ring_used = ring_used || D.bcta_seg[blockIdx.x] < D.bcta_seg[blockIdx.x + 1];
             }
+            KT(3);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            KT(4);
             double pbp_tot = scal[(size_t)it * PS_STRIDE + PS_PBP], ww_tot = scal[(size_t)it * PS_STRIDE + PS_WW];
             if (boundary || SHARDED) {
                 // ---- X1 ----
@@ -218,13 +227,16 @@ k_pcg_persistent_dist() {
                 if (SHARDED) { pbp_tot = __ldcg(D.wb + D.n_wb); ww_tot = __ldcg(D.wb + D.n_wb + 1); }
                 for (unsigned b = 0; b < G; ++b) ww_tot += __ldcg(D.cta_part + b);   // fixed order: the same alpha in every CTA
                 // ---- A3 ----
+                KT(5);
                 if (boundary) {
                     if (!(D.debug_skip & 4)) sp_pass_call<SP_SCATTER>(sh, sp_ring, ring_used, D.bsegs, D.bcta_seg, D.bnseg, D.bslot_desc, D.bnslots_total, A.Es, A.mo_cam,
                                               nullptr, D.wb, -1.0, A.q, nullptr);
+                    KT(6);
                     if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
                 }
             }
             // ---- B ----
+            KT(7);
             const double alpha = (rz_s != 0.0) ? rz_s / (pbp_tot - ww_tot) : 0.0;
             {
                 double rz = pcg_phase_update(false, alpha, coarse, s_acc);
@@ -234,9 +246,11 @@ k_pcg_persistent_dist() {
             }
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
             // ---- X2 + C ----
+            KT(8);
             pcg_coarse_exchange_apply<SHARDED>(D, A, seq0 + (++x2_count), scal[(size_t)(it + 1) * PS_STRIDE + PS_RZ], s_rc, nC);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
             // ---- D ----
+            KT(9);
             const double rz_new = s_rc[nC] + pcg_fixed_dot(s_rc, A.yc, nC, s_red);
             iterations = it + 1;
             rel2 = rz_new / rz0;

@@ -385,8 +385,8 @@ __device__ __forceinline__ double warp_reduce6(const double (&y)[6], int lane) {
 // hence the wait on the full barrier starts only once the producer has issued lap q / kSpRing of that
 // ring position (then the barrier is in the phase of q or the next one).  No fence: shared memory has
 // one copy and the try_wait is control-dependent on the load of s_lap.
-__device__ __forceinline__ int ring_acquire(int q, uint64_t* s_full, const volatile int* s_lap) {
-    const int ring = q % kSpRing, lap = q / kSpRing;
+__device__ __forceinline__ int ring_acquire(int q, uint64_t* s_full, const volatile int* s_lap, const int* s_lap_base) {
+    const int ring = q % kSpRing, lap = s_lap_base[ring] + q / kSpRing;   // laps count from the first pass of the kernel (SpShared::lap_base)
     if ((threadIdx.x & 31) == 0) {
         while (s_lap[ring] <= lap) { }
     }
@@ -395,19 +395,32 @@ __device__ __forceinline__ int ring_acquire(int q, uint64_t* s_full, const volat
     return ring;
 }
 
+#ifdef VMM_DBG_TRACE   // debug builds (tools/): progress words in mapped host memory, readable after a device fault or during a hang
+__device__ unsigned* g_sp_trace = nullptr;   // [CTA][16 warps][4] consumer words, then [CTA][32] producer words at offset 148*64... see SP_TRACE
+#define SP_TRACE(k, v) do { if (g_sp_trace && (threadIdx.x & 31) == 0) { \
+    *reinterpret_cast<volatile unsigned*>(g_sp_trace + ((size_t)blockIdx.x * 16 + (threadIdx.x >> 5)) * 4 + (k)) = (unsigned)(v); } } while (0)
+#define SP_TRACE_P(v) do { if (g_sp_trace) { \
+    *reinterpret_cast<volatile unsigned*>(g_sp_trace + (size_t)160 * 64 + (size_t)blockIdx.x * 32 + (threadIdx.x & 31)) = (unsigned)(v); } } while (0)
+#else
+#define SP_TRACE(k, v) do { } while (0)
+#define SP_TRACE_P(v) do { } while (0)
+#endif
+
 // Shared state of one streamed pass (static shared memory of the calling kernel; the ring itself is dynamic).
 struct SpShared {
     uint64_t full[kSpRing], empty[kSpRing];
     double part[2][kSpGroups][kSpGroupWarps][6];
-    volatile int lap[kSpRing];   // laps the producer has issued per ring position (see ring_acquire)
+    volatile int lap[kSpRing];   // laps the producer has issued per ring position since the barriers were initialised (see ring_acquire)
+    int lap_base[kSpRing];       // ... at the start of the current pass
+    int pass_no;                 // debug builds: passes this CTA has started
 };
 
 // One streamed pass over a segment list, executed by ALL kSpThreads threads of the CTA (consumer groups + producer
-// warp); returns with every thread (no early exits: the persistent PCG kernel goes on to a grid barrier).  `reinit`:
-// the ring barriers have been used by an earlier pass of the same kernel and are invalidated first.
+// warp); returns with every thread (no early exits: the persistent PCG kernel goes on to a grid barrier).  `ring_used`:
+// an earlier pass of the same kernel has initialised the ring barriers of this CTA; their phases are carried on.
 // COHERENT: see load_x6.
 template <int MODE, bool COHERENT>
-__device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bool reinit, const SpSeg* __restrict__ segs,
+__device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bool ring_used, const SpSeg* __restrict__ segs,
                                         const int* __restrict__ cta_seg, int nseg, const int2* __restrict__ slot_desc, int nslots_total,
                                         const unsigned char* __restrict__ Es, const int* __restrict__ mo_cam,
                                         const double* __restrict__ vin_c, double* __restrict__ mvec, double sign,
@@ -419,16 +432,18 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
     const int sb = cta_seg[blockIdx.x], se = cta_seg[blockIdx.x + 1];
     if (sb >= se) return;   // uniform for the CTA
     __syncthreads();        // an earlier pass has left the ring
-    if (tid == 0) {
-        for (int s = 0; s < kSpRing; ++s) {
-            if (reinit) {
-                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&s_full[s])) : "memory");
-                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(&s_empty[s])) : "memory");
-            }
-            mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 1); s_lap[s] = 0;
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // The ring barriers are initialised ONCE per kernel and never again: a pass ends with every slot it issued consumed and
+    // released, so full[r] and empty[r] have both completed lap[r] phases and the next pass simply goes on counting
+    // from there (lap_base).  (Invalidating and re-initialising them per pass — the first version — let a pass start
+    // with an empty barrier in the wrong phase once in a while: the producer then overwrote a slot nobody had read.)
+    if (tid < kSpRing) {
+        if (!ring_used) { mbar_init(&s_full[tid], 1); mbar_init(&s_empty[tid], 1); s_lap[tid] = 0; }
+        sh.lap_base[tid] = ring_used ? s_lap[tid] : 0;
+        if (!ring_used) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+#ifdef VMM_DBG_TRACE
+    if (tid == 0) sh.pass_no = ring_used ? sh.pass_no + 1 : 1;
+#endif
     __syncthreads();
     const int4* seg4 = reinterpret_cast<const int4*>(segs);
     const int slot_base = __ldg(seg4 + sb).y;
@@ -442,8 +457,12 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
         const int2* desc = slot_desc + slot_base;
         unsigned char* dst = sp_ring + (size_t)(lane < kSpRing ? lane : 0) * kSlotBytes;
         int q = (lane < kSpRing) ? lane : nslots;
-        int lap = 0;
+        int lap = (lane < kSpRing) ? sh.lap_base[lane] : 0;   // laps of this ring position since the barriers were initialised
         int2 sd = (q < nslots) ? __ldg(desc + q) : make_int2(0, 0);
+#ifdef VMM_DBG_TRACE
+        const unsigned tp = ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18);
+        SP_TRACE_P(tp | 0x20000u | (unsigned)(nslots & 0xffff));
+#endif
         while (__any_sync(0xffffffffu, q < nslots)) {
             const bool ready = (q < nslots) && (lap == 0 || mbar_test(&s_empty[lane], (uint32_t)(lap - 1) & 1));
             if (ready) {
@@ -451,10 +470,16 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
                 mbar_expect_tx(&s_full[lane], bytes);
                 bulk_g2s(dst, Es + (size_t)sd.x * kTileBytes, bytes, &s_full[lane]);
                 s_lap[lane] = ++lap;   // after the expect_tx in this thread's shared-memory order
+#ifdef VMM_DBG_TRACE
+                SP_TRACE_P(tp | (unsigned)(lap & 0xffff));
+#endif
                 q += kSpRing;
                 if (q < nslots) sd = __ldg(desc + q);
             }
         }
+#ifdef VMM_DBG_TRACE
+        SP_TRACE_P(tp | 0x10000u | (unsigned)(lap & 0xffff));
+#endif
         return;
     }
 
@@ -485,6 +510,12 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
         const bool has0 = wg * 32 < d.nobs, has1 = wg * 32 + kSegRegObs < d.nobs;   // warp-uniform
         const bool v0 = o0 < d.nobs, v1 = o1 < d.nobs;
         SP_TS(0, 0.0);
+#ifdef VMM_DBG_TRACE
+        SP_TRACE(0, ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18) | 1u);
+        SP_TRACE(1, s - sb);
+        SP_TRACE(2, (d.slot0 - slot_base + wg) | (has0 ? 0x80000000u : 0u) | (has1 ? 0x40000000u : 0u));
+        SP_TRACE(3, d.nobs);
+#endif
         // ---- requests that must not wait for the slot: this segment's vector entries, the next one's indices ----
         double x0[6], z[6];
         const int c0 = cam0, c1 = cam1;
@@ -492,7 +523,11 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
             if (v0) load_x6<COHERENT>(vin_c, c0, x0);
         } else {
 #pragma unroll
+#ifdef VMM_DBG_SCATTER_LDG
+            for (int b = 0; b < 6; ++b) z[b] = __ldg(mvec + (size_t)j * 6 + b);
+#else
             for (int b = 0; b < 6; ++b) z[b] = COHERENT ? mvec[(size_t)j * 6 + b] : __ldg(mvec + (size_t)j * 6 + b);
+#endif
         }
         d_cur = d_nxt;
         if (s + 2 * kSpGroups < se) d_nxt = __ldg(seg4 + s + 2 * kSpGroups);
@@ -506,7 +541,7 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
         double y[6] = { 0, 0, 0, 0, 0, 0 };
         SP_TS(1, 0.0);
         if (has1) {   // the tail first: its vector entries die before the register-resident block is loaded
-            ring1 = ring_acquire(d.slot0 - slot_base + wg + kSpGroupWarps, s_full, s_lap);
+            ring1 = ring_acquire(d.slot0 - slot_base + wg + kSpGroupWarps, s_full, s_lap, sh.lap_base);
             slot1 = sp_ring + (size_t)ring1 * kSlotBytes;
             if (MODE != SP_SCATTER && v1) {
                 double x1[6];
@@ -517,7 +552,9 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
             }
         }
         if (has0) {
-            ring0 = ring_acquire(d.slot0 - slot_base + wg, s_full, s_lap);
+            SP_TRACE(0, ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18) | 2u);
+            ring0 = ring_acquire(d.slot0 - slot_base + wg, s_full, s_lap, sh.lap_base);
+            SP_TRACE(0, ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18) | 3u);
             SP_TS(2, 0.0);
             if (v0) {
                 slot_load_e(sp_ring + (size_t)ring0 * kSlotBytes, lane, Er);
@@ -551,7 +588,9 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
             SP_TS(6, z[5]);
         }
         // ---- scatter pass ----
+        SP_TRACE(0, ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18) | 4u);
         if (v0) scatter_e_z(Er, z, sign, out_c + (size_t)c0 * 6);
+        SP_TRACE(0, ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18) | 5u);
         if (MODE == SP_SCATTER && has0) {
             slot_reads_done();
             __syncwarp();
@@ -568,7 +607,12 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
             if (lane == 0) mbar_arrive_relaxed(&s_empty[ring1]);
         }
         SP_TS(7, 0.0);
+        SP_TRACE(0, ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18) | 6u);
+#ifdef VMM_DBG_SCATTER_BAR
+        if (MODE == SP_SCATTER) group_barrier(g);
+#endif
     }
+    SP_TRACE(0, ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18) | 7u);
     if (MODE == SP_FULL && dot_acc && wg == 0) {
         const double dsum = warp_sum(lane < 6 ? dacc : 0.0);
         if (lane == 0) red_add(dot_acc, dsum);
