@@ -359,7 +359,7 @@ def run_b200(args):
             if name in KERNEL_BYTES_PER_TAG_OBS:
                 gbs = KERNEL_BYTES_PER_TAG_OBS[name] * ntol / (ms / n * 1e-3) / 1e9
                 ent.update({"gbs": gbs, "frac_hbm": gbs / peak})
-            elif name == "k_pcg_persistent":
+            elif name in ("k_pcg_persistent", "k_pcg_persistent_dist"):
                 # one launch = one whole PCG solve: every iteration streams the scaled E blocks once (292 B per tag observation);
                 # the grid barriers, the vector updates and the coarse mat-vec of each iteration are inside the measured time
                 per_launch = KERNEL_BYTES_PER_TAG_OBS["k_schur_product<SP_FULL>"] * ntol * pcg_its_prof / max(n, 1)

@@ -288,8 +288,10 @@ int vmm_ba_profile_enable(vmm_ba_handle h, int on);
 /* Phase clock of the persistent PCG kernel, summed over the launches since vmm_ba_profile_enable(h, 1): nanoseconds CTA 0
  * spent in the streamed product, the update + restriction, the coarse mat-vec, the direction [0..3] and in grid
  * barriers (waiting for the slowest CTA included) [4]; [5..7]: the streamed product per CTA, minimum / mean / maximum
- * over the grid (its load balance).  out must hold 8 doubles. */
-int vmm_ba_pcg_phase_ns(vmm_ba_handle h, double* out8);
+ * over the grid (its load balance); [8], [9]: sharded engines / split markers — the exchange of the boundary vector and
+ * the boundary scatter pass ([0] then covers the interior product and the boundary gather pass, [2] the exchange of
+ * the restricted residual and the coarse mat-vec).  out must hold 10 doubles. */
+int vmm_ba_pcg_phase_ns(vmm_ba_handle h, double* out10);
 int vmm_ba_profile_num_kernels(void);
 const char* vmm_ba_profile_kernel_name(int index);
 int vmm_ba_profile_get(vmm_ba_handle h, int index, int64_t* launches, double* total_ms);

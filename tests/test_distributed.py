@@ -108,7 +108,7 @@ def test_two_gpu_solve_matches_one_gpu():
     procs = [ctx.Process(target=_nccl_worker, args=(r, 2, nccl_id, q)) for r in range(2)]
     for p in procs:
         p.start()
-    res = sorted([q.get(timeout=600) for _ in range(2)], key=lambda t: t[0])
+    res = sorted([q.get(timeout=int(os.environ.get("VMM_TEST_2GPU_TIMEOUT_S", "240"))) for _ in range(2)], key=lambda t: t[0])
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
@@ -155,7 +155,7 @@ def test_two_gpu_inexact_solve_reaches_one_gpu_minimum():
     procs = [ctx.Process(target=_nccl_worker_inexact, args=(r, 2, nccl_id, q)) for r in range(2)]
     for p in procs:
         p.start()
-    res = sorted([q.get(timeout=600) for _ in range(2)], key=lambda t: t[0])
+    res = sorted([q.get(timeout=int(os.environ.get("VMM_TEST_2GPU_TIMEOUT_S", "240"))) for _ in range(2)], key=lambda t: t[0])
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0

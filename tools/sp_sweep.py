@@ -25,11 +25,12 @@ with pkg.BundleAdjuster(0) as ba:
     ba.profile_enable(False)
     y1 = ba.schur_multiply(x, 1, 1.0, 1e4, path=1)
     out["paths_agree"] = float(np.abs(y0 - y1).max() / np.abs(y1).max())
-    ba.set_poses(s.cam_q, s.cam_t, s.tag_q, s.tag_t)
-    t0 = time.time(); summ = ba.solve(max_num_iterations=50, loss_kind=1, loss_scale=1.0); dt = time.time() - t0
-    ba.set_poses(s.cam_q, s.cam_t, s.tag_q, s.tag_t)
-    t0 = time.time(); summ = ba.solve(max_num_iterations=50, loss_kind=1, loss_scale=1.0); dt = time.time() - t0
-    out.update({"solve_s": dt, "lm": summ.num_iterations, "pcg": int(summ.pcg_iterations), "cost": summ.final_cost})
+    if not os.environ.get("SP_SWEEP_NO_SOLVE"):
+        ba.set_poses(s.cam_q, s.cam_t, s.tag_q, s.tag_t)
+        t0 = time.time(); summ = ba.solve(max_num_iterations=50, loss_kind=1, loss_scale=1.0); dt = time.time() - t0
+        ba.set_poses(s.cam_q, s.cam_t, s.tag_q, s.tag_t)
+        t0 = time.time(); summ = ba.solve(max_num_iterations=50, loss_kind=1, loss_scale=1.0); dt = time.time() - t0
+        out.update({"solve_s": dt, "lm": summ.num_iterations, "pcg": int(summ.pcg_iterations), "cost": summ.final_cost})
 print(json.dumps(out))
 ''' % ROOT
 from visual_marker_mapping_b200 import synth
@@ -50,3 +51,7 @@ for lib in sorted(glob.glob(os.path.join(ROOT, "tools", "variants", "libvmm_ba_*
             env["VMM_BA_PCG_LEGACY"] = "1"
         r = subprocess.run([sys.executable, child, pk, name + ("/legacy" if legacy == "1" else "/persistent")], env=env, capture_output=True, text=True, timeout=300)
         print(r.stdout.strip() if r.returncode == 0 else json.dumps({"variant": name, "error": r.stderr[-400:]}), flush=True)
+        for line in r.stderr.splitlines():
+            if "[sp timing]" in line:
+                print(json.dumps({"variant": name, "timing": line}), flush=True)
+                break

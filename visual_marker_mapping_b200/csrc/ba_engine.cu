@@ -2546,7 +2546,7 @@ __attribute__((visibility("default"))) int vmm_ba_debug_trace_words(unsigned** p
 #endif
 int vmm_ba_pcg_phase_ns(vmm_ba_handle e, double* out5) {
     if (!e || !out5) return VMM_BA_ERR_INVALID_ARGUMENT;
-    for (int k = 0; k < 8; ++k) out5[k] = 0.0;
+    for (int k = 0; k < 10; ++k) out5[k] = 0.0;
     if (!e->pcgp.phase_ns.p) return VMM_BA_OK;
     CU(cudaSetDevice(e->device));
     std::vector<unsigned long long> h(8 + 1024);
@@ -2557,6 +2557,7 @@ int vmm_ba_pcg_phase_ns(vmm_ba_handle e, double* out5) {
     double mn = 1e300, mx = 0.0, sum = 0.0;
     for (int b = 0; b < G; ++b) { const double v = (double)h[8 + b]; mn = std::min(mn, v); mx = std::max(mx, v); sum += v; }
     out5[5] = G > 0 ? mn : 0.0; out5[6] = G > 0 ? sum / G : 0.0; out5[7] = mx;
+    out5[8] = (double)h[5]; out5[9] = (double)h[6];   // sharded / split-marker kernel: boundary exchange, boundary scatter pass
     return VMM_BA_OK;
 }
 

@@ -90,6 +90,21 @@ __device__ __forceinline__ double pcg_fixed_dot(const double* s_rc, const double
     return t;
 }
 
+// sum of v[0 .. n) in a fixed order, the same bits in every CTA of every rank (see pcg_fixed_dot)
+__device__ __forceinline__ double pcg_fixed_sum(const double* v, int n, double* s_red) {
+    double s = 0.0;
+    for (int k = threadIdx.x; k < n; k += kSpThreads) s += __ldcg(v + k);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < kSpThreads / 32; ++w) t += s_red[w];
+    return t;
+}
+
 // X1: wb = sum over ranks of wbl (+ two scalars in the tail).  Returns the thread's share of sum wb_i^2.
 template <bool SHARDED>
 __device__ __forceinline__ double pcg_exchange_boundary(const PcgDistArgs& D, unsigned seq, double tail0, double tail1) {
@@ -176,6 +191,16 @@ k_pcg_persistent_dist() {
     const unsigned seq0 = SHARDED ? __ldcg(D.seq) : 0u;   // exchanges of this launch: X2 uses seq0 + 1, seq0 + 2, ...; X1 uses seq0 + 1 + it
     unsigned x2_count = 0;
     bool aborted = false, ok = true, ring_used = false;
+    unsigned long long t_prev = 0;
+    // phase clock as in k_pcg_persistent (CTA 0): [0] A1 + A2, [1] B, [2] X2 + C, [3] D, [4] barriers, [5] X1, [6] A3
+    auto tick = [&](int k) {
+        if (A.phase_ns && blockIdx.x == 0 && threadIdx.x == 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (k >= 0) A.phase_ns[k] += now - t_prev;
+            t_prev = now;
+        }
+    };
     int it = 0, iterations = 0;
     double rel2 = 1.0, rz0 = 0.0;
 
@@ -198,6 +223,7 @@ k_pcg_persistent_dist() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // s_rc aliases the ring
     if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
     ok = isfinite(rz0);
+    tick(-1);
     if (ok && rz0 > 0.0) {
         double rz_s = rz0;
         for (it = 0; it < A.max_it; ++it) {
@@ -215,7 +241,9 @@ k_pcg_persistent_dist() {
                 ring_used = ring_used || D.bcta_seg[blockIdx.x] < D.bcta_seg[blockIdx.x + 1];
             }
             KT(3);
+            tick(0);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            tick(4);
             KT(4);
             double pbp_tot = scal[(size_t)it * PS_STRIDE + PS_PBP], ww_tot = scal[(size_t)it * PS_STRIDE + PS_WW];
             if (boundary || SHARDED) {
@@ -223,16 +251,20 @@ k_pcg_persistent_dist() {
                 double sq = pcg_exchange_boundary<SHARDED>(D, seq0 + 1u + (unsigned)it, pbp_tot, ww_tot);
                 sq = cta_sum(sq, s_red);
                 if (threadIdx.x == 0) D.cta_part[blockIdx.x] = sq;
+                tick(5);
                 if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+                tick(4);
                 if (SHARDED) { pbp_tot = __ldcg(D.wb + D.n_wb); ww_tot = __ldcg(D.wb + D.n_wb + 1); }
-                for (unsigned b = 0; b < G; ++b) ww_tot += __ldcg(D.cta_part + b);   // fixed order: the same alpha in every CTA
+                ww_tot += pcg_fixed_sum(D.cta_part, (int)G, s_red);   // fixed order: the same alpha in every CTA of every rank
                 // ---- A3 ----
                 KT(5);
                 if (boundary) {
                     if (!(D.debug_skip & 4)) sp_pass_call<SP_SCATTER>(sh, sp_ring, ring_used, D.bsegs, D.bcta_seg, D.bnseg, D.bslot_desc, D.bnslots_total, A.Es, A.mo_cam,
                                               nullptr, D.wb, -1.0, A.q, nullptr);
                     KT(6);
+                    tick(6);
                     if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+                    tick(4);
                 }
             }
             // ---- B ----
@@ -244,11 +276,15 @@ k_pcg_persistent_dist() {
                 if (threadIdx.x == 0) red_add(nxt + PS_RZ, rz);
                 if (boundary) for (int i = blockIdx.x * kSpThreads + threadIdx.x; i < D.n_wb; i += G * kSpThreads) D.wbl[i] = 0.0;
             }
+            tick(1);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            tick(4);
             // ---- X2 + C ----
             KT(8);
             pcg_coarse_exchange_apply<SHARDED>(D, A, seq0 + (++x2_count), scal[(size_t)(it + 1) * PS_STRIDE + PS_RZ], s_rc, nC);
+            tick(2);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            tick(4);
             // ---- D ----
             KT(9);
             const double rz_new = s_rc[nC] + pcg_fixed_dot(s_rc, A.yc, nC, s_red);
@@ -264,7 +300,9 @@ k_pcg_persistent_dist() {
                 if (threadIdx.x == 0) red_add(nxt + PS_PBP, pq);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            tick(3);
             if (!grid_barrier(A.barrier, G)) { aborted = true; goto finish; }
+            tick(4);
         }
     } else if (ok) {
         rel2 = 0.0;

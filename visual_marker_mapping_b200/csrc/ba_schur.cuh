@@ -466,7 +466,11 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
         while (__any_sync(0xffffffffu, q < nslots)) {
             const bool ready = (q < nslots) && (lap == 0 || mbar_test(&s_empty[lane], (uint32_t)(lap - 1) & 1));
             if (ready) {
+#ifdef VMM_SP_HALF_BYTES   // timing experiment only (tools/): half of every slot is fetched, results are wrong
+                const uint32_t bytes = (uint32_t)sd.y * kTileBytes / 2;
+#else
                 const uint32_t bytes = (uint32_t)sd.y * kTileBytes;
+#endif
                 mbar_expect_tx(&s_full[lane], bytes);
                 bulk_g2s(dst, Es + (size_t)sd.x * kTileBytes, bytes, &s_full[lane]);
                 s_lap[lane] = ++lap;   // after the expect_tx in this thread's shared-memory order

@@ -379,10 +379,10 @@ class BundleAdjuster:
 
     def pcg_phase_ns(self) -> dict:
         """In-kernel phase clock of the persistent PCG since profile_enable(True) (CTA 0)."""
-        v = np.zeros(8)
+        v = np.zeros(10)
         self._check(self._lib.vmm_ba_pcg_phase_ns(self._h, _dp(v)))
         return dict(zip(("product", "update_restrict", "coarse_matvec", "direction", "grid_barriers", "product_cta_min", "product_cta_mean",
-                         "product_cta_max"), (float(x) for x in v)))
+                         "product_cta_max", "boundary_exchange", "boundary_scatter"), (float(x) for x in v)))
 
     def measure_fp64_peak(self) -> float:
         v = C.c_double(0)
