@@ -69,6 +69,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--rj-iters", type=int, default=10)
+    ap.add_argument("--pcg-tolerance", type=float, default=None, help="A/B runs only: override the forcing term of the inexact solve (the default is the library's)")
     return ap.parse_args()
 
 
@@ -250,6 +251,8 @@ def run_b200(args):
     ba.set_stream(stream.cuda_stream)          # run the engine on a torch stream and record on that one
     ba.set_scene(scene)
     opts = dict(loss_kind=pkg.LOSS_HUBER, loss_scale=1.0)
+    if args.pcg_tolerance is not None:
+        opts["pcg_tolerance"] = args.pcg_tolerance
     init = (scene.cam_q, scene.cam_t, scene.tag_q, scene.tag_t)
 
     def pinned(a, dtype):
@@ -441,7 +444,7 @@ def run_b200(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": job_config(scene, args.workload, world),
+            "data": "synthetic", "config": dict(job_config(scene, args.workload, world), **({"pcg_tolerance_override": args.pcg_tolerance} if args.pcg_tolerance is not None else {})),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks.summary(),
             "rj": rj, "kernels": kernels,
             "solve": {"solves_in_timed_region": len(sums), "first_solve": {"iterations": s0.num_iterations, "initial_cost": s0.initial_cost,
