@@ -289,3 +289,39 @@ def test_marker_covariance_at_site_scale_c3(scene_c3, oracle):
     for k, j in enumerate(sel):
         # two exact routes through matrices of condition ~1e9 (the map is anchored at ONE marker): measured 8e-7 relative
         assert np.abs(cov[j] - ref[k]).max() <= 1e-5 * np.abs(ref[k]).max(), (j, cov[j], ref[k])
+
+
+_SPLIT_CHILD = r"""
+import json, sys
+sys.path.insert(0, sys.argv[1])
+import visual_marker_mapping_b200 as pkg
+from visual_marker_mapping_b200 import synth
+s = synth.make_config("c3/8")
+with pkg.BundleAdjuster(0) as ba:
+    ba.set_scene(s)
+    out = []
+    for parity in (1, 0):
+        ba.set_poses(s.cam_q, s.cam_t, s.tag_q, s.tag_t)
+        summ = ba.solve(max_num_iterations=50, loss_kind=pkg.LOSS_HUBER, loss_scale=1.0, parity_mode=parity)
+        out.append({"cost": summ.final_cost, "lm": summ.num_iterations, "pcg": int(summ.pcg_iterations), "msg": summ.message.decode()})
+print(json.dumps(out))
+"""
+
+
+def test_boundary_passes_when_the_ring_laps():
+    """Regression test of the round-2 fault: with every second marker forced through the boundary path of the persistent PCG
+    kernel (VMM_BA_TEST_SPLIT_EVERY, read once per process, hence the child processes) every CTA runs three streamed passes
+    per iteration — interior, boundary gather, boundary scatter — each of them lapping the slot ring several times.  Re-
+    initialising the ring barriers per pass let the scatter pass start on a barrier in the wrong phase (fault or hang,
+    only at this scale).  The solve must equal the one without the forced split."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = {}
+    for label, extra in (("plain", {}), ("split", {"VMM_BA_TEST_SPLIT_EVERY": "2"})):
+        r = subprocess.run([sys.executable, "-c", _SPLIT_CHILD, root], env=dict(os.environ, **extra), capture_output=True, text=True, timeout=240)
+        assert r.returncode == 0, f"{label}: {r.stderr[-600:]}"
+        res[label] = json.loads(r.stdout.strip().splitlines()[-1])
+    for mode in (0, 1):   # parity mode, product mode
+        a, b = res["plain"][mode], res["split"][mode]
+        assert a["lm"] == b["lm"], (a, b)
+        assert abs(a["cost"] - b["cost"]) <= (1e-10 if mode == 0 else 1e-7) * a["cost"], (a, b)

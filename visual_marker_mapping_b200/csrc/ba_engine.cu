@@ -620,8 +620,8 @@ int pcg_solve_persistent(vmm_ba_engine* e, double tol, int max_it, int min_it, b
         if (e->cta_part.n < (size_t)e->sp_grid) CU(e->cta_part.alloc(e->sp_grid));
         d.cta_part = e->cta_part.p;
         d.rank = e->rank; d.world = e->world;
-        { static const char* sk = std::getenv("VMM_BA_DIST_SKIP"); d.debug_skip = sk ? std::atoi(sk) : 0; }
 #ifdef VMM_DBG_TRACE
+        { static const char* sk = std::getenv("VMM_BA_DIST_SKIP"); d.debug_skip = sk ? std::atoi(sk) : 0; }   // debug builds only: wrong numbers
         if (!g_trace_host) {
             CU(cudaHostAlloc((void**)&g_trace_host, sizeof(unsigned) * kTraceWords, cudaHostAllocMapped));
             std::memset(g_trace_host, 0, sizeof(unsigned) * kTraceWords);

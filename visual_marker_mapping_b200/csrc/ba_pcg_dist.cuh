@@ -42,7 +42,7 @@ struct PcgDistArgs {
     uint4* xbuf[kPeerMaxWorld];   // every rank's exchange buffer as mapped here: [X1: 2 parities][world][cap1] [X2: 2 parities][world][cap2]
     size_t cap1, cap2;
     unsigned* seq;            // device-resident sequence base (advanced by the kernel, the same on every rank)
-    int debug_skip;           // test builds only (VMM_BA_DIST_SKIP): bit 0 / 1 / 2 skip the interior / gather / scatter pass (wrong numbers)
+    int debug_skip;           // -DVMM_DBG_TRACE builds only (VMM_BA_DIST_SKIP), 0 otherwise: bit 0 / 1 / 2 skip the interior / gather / scatter pass (wrong numbers)
 };
 
 __constant__ PcgDistArgs c_pcgd;
