@@ -315,6 +315,7 @@ def test_boundary_passes_when_the_ring_laps():
     initialising the ring barriers per pass let the scatter pass start on a barrier in the wrong phase (fault or hang,
     only at this scale).  The solve must equal the one without the forced split."""
     import subprocess
+    import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     res = {}
     for label, extra in (("plain", {}), ("split", {"VMM_BA_TEST_SPLIT_EVERY": "2"})):
