@@ -302,6 +302,34 @@ int vmm_ba_measure_fp64_peak(vmm_ba_handle h, double* tflops);
 /* Measured device-to-device copy bandwidth (GB/s, read+write bytes) with this library's own copy kernel. */
 int vmm_ba_measure_copy_bandwidth(vmm_ba_handle h, size_t bytes, double* gbps);
 
+/* ---- no allocation --------------------------------------------------------------------------------------------- */
+
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * The robust cost of a small problem — sum over corners of 0.5*rho(|r|^2), the number vmm_ba_evaluate returns in
+ * *cost — computed on DEVICE buffers the caller owns, without a handle.  This call performs no cudaMalloc / cudaFree
+ * and calls no allocating library routine: the scratch the engine allocates for this computation (prepared pose blocks,
+ * one cost partial per block) lives in a static __device__ array of the library (499,712 bytes, held by every GPU
+ * that loads the library until the process exits).  Hence the limits, checked before anything is launched
+ * (VMM_BA_ERR_INVALID_ARGUMENT with the numbers in vmm_ba_last_error(NULL)):
+ *     num_cameras <= VMM_BA_NO_ALLOC_MAX_CAMERAS, num_markers <= VMM_BA_NO_ALLOC_MAX_MARKERS,
+ *     num_tag_obs <= VMM_BA_NO_ALLOC_MAX_TAG_OBS.
+ * All d_* pointers are device pointers on `device`, with the layouts of vmm_ba_set_problem (cam_q [4*num_cameras] w,x,y,z;
+ * cam_t [3*..]; tag_wh [2*num_markers]; to_uv [8*num_tag_obs]); the index arrays are NOT validated (they are on the device).
+ * The four kernels are enqueued on cuda_stream (a cudaStream_t, NULL = the default stream) and the call returns without
+ * synchronising; *d_cost (device, one double) is valid once the stream has reached that point.  loss_kind / loss_scale
+ * as in vmm_ba_options.  The static scratch is shared by all calls in the process and keeps the last call's contents
+ * (every call rewrites all it reads): calls that overlap on the GPU — different streams without a dependency — race. */
+#define VMM_BA_NO_ALLOC_MAX_CAMERAS 4096
+#define VMM_BA_NO_ALLOC_MAX_MARKERS 1024
+#define VMM_BA_NO_ALLOC_MAX_TAG_OBS 131072
+int vmm_ba_cost_no_alloc(int device, void* cuda_stream, double fx, double fy, double cx, double cy, const double dist[5],
+                         int64_t num_cameras, const double* d_cam_q, const double* d_cam_t, int64_t num_markers,
+                         const double* d_tag_q, const double* d_tag_t, const double* d_tag_wh, int64_t num_tag_obs,
+                         const int32_t* d_to_cam, const int32_t* d_to_tag, const double* d_to_uv, int loss_kind,
+                         double loss_scale, double* d_cost);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,7 +24,7 @@ NVCC_FLAGS = [
 ]
 
 CUDA_SOURCES = ["ba_engine.cu"]
-CUDA_HEADERS = ["ba_kernels.cuh", "ba_schur.cuh", "ba_coarse.cuh", "ba_pcg.cuh", "ba_pcg_dist.cuh", "ba_coarse_inv.cuh", "ba_stage.cuh", "ba_cov.cuh", "ba_peer.cuh", "ba_math.h", "nccl_dyn.h", os.path.join(REPO, "include", "vmm_ba.h")]
+CUDA_HEADERS = ["ba_kernels.cuh", "ba_schur.cuh", "ba_coarse.cuh", "ba_pcg.cuh", "ba_pcg_dist.cuh", "ba_coarse_inv.cuh", "ba_stage.cuh", "ba_cov.cuh", "ba_peer.cuh", "ba_cov_block.cuh", "ba_no_alloc.cuh", "ba_math.h", "nccl_dyn.h", os.path.join(REPO, "include", "vmm_ba.h")]
 
 
 def _nvcc() -> str:

@@ -2628,3 +2628,6 @@ int vmm_ba_measure_copy_bandwidth(vmm_ba_handle e, size_t bytes, double* gbps) {
 }
 
 }  // extern "C"
+
+// the entry point that allocates nothing (static device scratch; no counterpart in the reference)
+#include "ba_no_alloc.cuh"

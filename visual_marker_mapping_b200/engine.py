@@ -29,7 +29,9 @@ ABI_SYMBOLS = [
     "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_marker_translation_covariance_ex", "vmm_ba_schur_multiply", "vmm_ba_debug_coarse_matrix", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
     "vmm_ba_kernel_launches", "vmm_ba_h2d_bytes", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
     "vmm_ba_pcg_phase_ns", "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
+    "vmm_ba_cost_no_alloc",
 ]
+NO_ALLOC_MAX_CAMERAS, NO_ALLOC_MAX_MARKERS, NO_ALLOC_MAX_TAG_OBS = 4096, 1024, 131072
 
 
 class Options(C.Structure):
@@ -152,6 +154,9 @@ def load_library():
     lib.vmm_ba_profile_kernel_name.restype = C.c_char_p
     lib.vmm_ba_profile_kernel_name.argtypes = [C.c_int]
     lib.vmm_ba_profile_get.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), dp]
+    vp = C.c_void_p
+    lib.vmm_ba_cost_no_alloc.argtypes = [C.c_int, vp, C.c_double, C.c_double, C.c_double, C.c_double, dp, C.c_int64, vp, vp, C.c_int64, vp, vp, vp,
+                                         C.c_int64, vp, vp, vp, C.c_int, C.c_double, vp]
     _lib = lib
     return lib
 
@@ -164,6 +169,22 @@ def default_options(**kw) -> Options:
             raise AttributeError(k)
         setattr(o, k, v)
     return o
+
+
+def cost_no_alloc(device: int, stream: int, intrinsics, num_cameras: int, d_cam_q: int, d_cam_t: int, num_markers: int, d_tag_q: int,
+                  d_tag_t: int, d_tag_wh: int, num_tag_obs: int, d_to_cam: int, d_to_tag: int, d_to_uv: int, loss_kind: int, loss_scale: float,
+                  d_cost: int) -> None:
+    """vmm_ba_cost_no_alloc: the robust cost on the caller's DEVICE buffers (raw device addresses as ints), scratch in the
+    library's static device array; allocates nothing, does not synchronise.  Raises VmmBaError beyond the static limits."""
+    lib = load_library()
+    intr = np.ascontiguousarray(intrinsics, dtype=np.float64)
+    dist = np.ascontiguousarray(intr[4:9])
+    rc = lib.vmm_ba_cost_no_alloc(int(device), C.c_void_p(stream or None), float(intr[0]), float(intr[1]), float(intr[2]), float(intr[3]), _dp(dist),
+                                  int(num_cameras), C.c_void_p(d_cam_q or None), C.c_void_p(d_cam_t or None), int(num_markers), C.c_void_p(d_tag_q or None),
+                                  C.c_void_p(d_tag_t or None), C.c_void_p(d_tag_wh or None), int(num_tag_obs), C.c_void_p(d_to_cam or None),
+                                  C.c_void_p(d_to_tag or None), C.c_void_p(d_to_uv or None), int(loss_kind), float(loss_scale), C.c_void_p(d_cost or None))
+    if rc != 0:
+        raise VmmBaError(f"status {rc}: {lib.vmm_ba_last_error(None).decode()}")
 
 
 def device_count() -> int:
