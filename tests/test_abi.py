@@ -91,3 +91,24 @@ def test_product_never_imports_the_oracle():
                 with open(os.path.join(dirpath, fn), errors="ignore") as f:
                     t = f.read()
                 assert "vmm_oracle" not in t and "from oracle" not in t and "import oracle" not in t, fn
+
+
+def test_no_alloc_entry_checks_its_limits_before_touching_the_device(lib):
+    """vmm_ba_cost_no_alloc (static device scratch, no allocation): sizes beyond the scratch, bad losses and null pointers are
+    refused with a clear text before any CUDA call — so this runs without a GPU."""
+    from visual_marker_mapping_b200 import engine
+    intr = np.arange(1.0, 10.0)
+    ok = dict(num_cameras=4, num_markers=2, num_tag_obs=3)
+    for bad, text in ((dict(num_cameras=engine.NO_ALLOC_MAX_CAMERAS + 1), "exceed the static scratch"),
+                      (dict(num_markers=engine.NO_ALLOC_MAX_MARKERS + 1), "exceed the static scratch"),
+                      (dict(num_tag_obs=engine.NO_ALLOC_MAX_TAG_OBS + 1), "exceed the static scratch"),
+                      (dict(num_cameras=-1), "negative size")):
+        n = dict(ok, **bad)
+        with pytest.raises(pkg.VmmBaError, match=text):
+            engine.cost_no_alloc(0, 0, intr, n["num_cameras"], 8, 8, n["num_markers"], 8, 8, 8, n["num_tag_obs"], 8, 8, 8, pkg.LOSS_HUBER, 1.0, 8)
+    with pytest.raises(pkg.VmmBaError, match="bad loss"):
+        engine.cost_no_alloc(0, 0, intr, 4, 8, 8, 2, 8, 8, 8, 3, 8, 8, 8, 7, 1.0, 8)
+    with pytest.raises(pkg.VmmBaError, match="null"):
+        engine.cost_no_alloc(0, 0, intr, 4, 0, 8, 2, 8, 8, 8, 3, 8, 8, 8, pkg.LOSS_HUBER, 1.0, 8)
+    with pytest.raises(pkg.VmmBaError, match="null"):
+        engine.cost_no_alloc(0, 0, intr, 4, 8, 8, 2, 8, 8, 8, 3, 8, 8, 8, pkg.LOSS_HUBER, 1.0, 0)
