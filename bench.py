@@ -53,10 +53,10 @@ NCU_TRAFFIC_BYTES_C3 = {
     "k_residual_jacobian": 0.299655e9 + 3.268961e9,
     "k_coarse_w": 1.202321e9 + 0.011970e9,
 }
-# k_pcg_persistent (profiles/r02_ncu_pcg.md): the captured launch ran 4 PCG iterations and moved 5.397546 GB + 0.167593 GB, i.e.
-# 1.39 GB per PCG iteration against 1.168 GB of scaled E blocks (the rest: B, M^-1, the camera-space vectors and A_c^-1 of
+# k_pcg_persistent (profiles/r02_ncu_pcg.md): the captured launch ran 47 PCG iterations and moved 61.956590 GB + 1.059650 GB, i.e.
+# 1.341 GB per PCG iteration against 1.168 GB of scaled E blocks (the rest: B, M^-1, the camera-space vectors and A_c^-1 of
 # phases B, C, D); scaled to the iterations of the measured launches below
-NCU_TRAFFIC_BYTES_PER_PCG_ITERATION_C3 = (5.397546e9 + 0.167593e9) / 4
+NCU_TRAFFIC_BYTES_PER_PCG_ITERATION_C3 = (61.956590e9 + 1.059650e9) / 47
 
 
 def parse_args():
@@ -387,7 +387,7 @@ def run_b200(args):
                 if args.workload == "c3" and world == 1:
                     roofline["traffic"] = NCU_TRAFFIC_BYTES_PER_PCG_ITERATION_C3 * pcg_its_prof / max(k["launches"], 1)
                 roofline["note"] = ("one launch = one PCG solve of %.1f iterations on average; per iteration 292 B per tag observation are streamed once; "
-                                    "traffic = DRAM bytes per PCG iteration of the ncu capture (4 iterations, 5.57 GB: profiles/r02_ncu_pcg.md) x the iterations of an average launch here" % (pcg_its_prof / max(k["launches"], 1)))
+                                    "traffic = DRAM bytes per PCG iteration of the ncu capture (47 iterations, 63.0 GB: profiles/r02_ncu_pcg.md) x the iterations of an average launch here" % (pcg_its_prof / max(k["launches"], 1)))
             roofline["rj"] = rj
         # ---- cost check (north_star: the solve reaches the reference's cost): default-tolerance solve, both modes at
         #      function_tolerance 1e-12, and the oracle's exact-Cholesky solve of the same scene (committed fixture) ----

@@ -292,6 +292,9 @@ int vmm_ba_profile_enable(vmm_ba_handle h, int on);
  * the boundary scatter pass ([0] then covers the interior product and the boundary gather pass, [2] the exchange of
  * the restricted residual and the coarse mat-vec).  out must hold 10 doubles. */
 int vmm_ba_pcg_phase_ns(vmm_ba_handle h, double* out10);
+/* The same clock per CTA: nanoseconds CTA b (b < n, at most the grid of the kernel: one CTA per SM) spent in the streamed
+ * product since vmm_ba_profile_enable(h, 1) — what the load-balance model of the segment lists is fitted on (tools/). */
+int vmm_ba_pcg_cta_product_ns(vmm_ba_handle h, double* out, int n);
 int vmm_ba_profile_num_kernels(void);
 const char* vmm_ba_profile_kernel_name(int index);
 int vmm_ba_profile_get(vmm_ba_handle h, int index, int64_t* launches, double* total_ms);

@@ -31,6 +31,16 @@ with pkg.BundleAdjuster(0) as ba:
         ba.set_poses(s.cam_q, s.cam_t, s.tag_q, s.tag_t)
         t0 = time.time(); summ = ba.solve(max_num_iterations=50, loss_kind=1, loss_scale=1.0); dt = time.time() - t0
         out.update({"solve_s": dt, "lm": summ.num_iterations, "pcg": int(summ.pcg_iterations), "cost": summ.final_cost})
+        ba.set_poses(s.cam_q, s.cam_t, s.tag_q, s.tag_t)
+        ba.profile_enable(True)
+        summ = ba.solve(max_num_iterations=50, loss_kind=1, loss_scale=1.0)
+        ph = ba.pcg_phase_ns()
+        n = max(int(summ.pcg_iterations), 1)
+        out["phase_us_per_pcg_iteration"] = {k: round(v / 1e3 / n, 1) for k, v in ph.items() if v}
+        for k, (cnt, ms) in ba.profile().items():
+            if k.startswith("k_pcg_persistent"):
+                out["pcg_kernel_us_per_iteration"] = round(ms * 1e3 / n, 1)
+        ba.profile_enable(False)
 print(json.dumps(out))
 ''' % ROOT
 from visual_marker_mapping_b200 import synth
@@ -45,7 +55,7 @@ for lib in sorted(glob.glob(os.path.join(ROOT, "tools", "variants", "libvmm_ba_*
     name = os.path.basename(lib)[len("libvmm_ba_"):-3]
     if name.startswith("inv"):
         continue
-    for legacy in (("0", "1") if name == "base" else ("0",)):
+    for legacy in (("0", "1") if name == "base" else ("0",)) * int(os.environ.get("SP_SWEEP_REPEAT", "1")):
         env = dict(os.environ, VMM_BA_LIBRARY=lib)
         if legacy == "1":
             env["VMM_BA_PCG_LEGACY"] = "1"

@@ -1012,15 +1012,19 @@ struct HostSeg { SpSeg d; int tile0; };
 int upload_seglist(vmm_ba_engine* e, vmm_ba_engine::SegList& L, std::vector<HostSeg>& hs) {
     std::vector<int2> desc;
     std::vector<SpSeg> segs(hs.size());
-    // a segment costs its slots (HBM time) plus a fixed latency chain: balance the CTAs on both
-    const int kFixed = 3;
+    // A segment costs its slots plus a fixed latency chain, and more when its tail stays in the ring for both halves.  Fitted on
+    // the per-CTA clock of the product phase (tools/balance_fit.py, C3 on B200): 0.60 us per segment + 0.147 us per slot +
+    // 0.57 us per segment with a tail, rms residual 2.9 us of 250 -> in units of slots 4 / 1 / 4.  (Round 1's 3 / 1 / 0 left
+    // the slowest CTA 18 us behind the mean; now 8.)  VMM_BA_SEG_FIXED / VMM_BA_SEG_TAIL override for the study.
+    static const int kFixed = std::getenv("VMM_BA_SEG_FIXED") ? std::atoi(std::getenv("VMM_BA_SEG_FIXED")) : 4;
+    static const int kTail = std::getenv("VMM_BA_SEG_TAIL") ? std::atoi(std::getenv("VMM_BA_SEG_TAIL")) : 4;
     std::vector<int64_t> cost(hs.size() + 1, 0);
     for (size_t i = 0; i < hs.size(); ++i) {
         hs[i].d.slot0 = (int)desc.size();
         const int ntiles = (hs[i].d.nobs + kTileObs - 1) / kTileObs;
         for (int t = 0; t < ntiles; t += kSlotTiles) desc.push_back(make_int2(hs[i].tile0 + t, std::min(kSlotTiles, ntiles - t)));
         segs[i] = hs[i].d;
-        cost[i + 1] = cost[i] + ((int)desc.size() - hs[i].d.slot0) + kFixed;
+        cost[i + 1] = cost[i] + ((int)desc.size() - hs[i].d.slot0) + kFixed + (hs[i].d.nobs > kSegRegObs ? kTail : 0);
     }
     L.nslots = (int)desc.size();
     const int G = e->sp_grid;
@@ -2541,6 +2545,17 @@ int vmm_ba_profile_enable(vmm_ba_handle e, int on) {
     return VMM_BA_OK;
 }
 
+// measurement: nanoseconds every CTA spent in the streamed product of the persistent PCG kernel since vmm_ba_profile_enable(h, 1)
+int vmm_ba_pcg_cta_product_ns(vmm_ba_handle e, double* out, int n) {
+    if (!e || !out || n < 0) return VMM_BA_ERR_INVALID_ARGUMENT;
+    for (int b = 0; b < n; ++b) out[b] = 0.0;
+    if (!e->pcgp.phase_ns.p) return VMM_BA_OK;
+    CU(cudaSetDevice(e->device));
+    std::vector<unsigned long long> h(8 + 1024);
+    CU(cudaMemcpy(h.data(), e->pcgp.phase_ns.p, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost));
+    for (int b = 0; b < std::min(n, std::min(e->sp_grid, 1024)); ++b) out[b] = (double)h[8 + b];
+    return VMM_BA_OK;
+}
 #ifdef VMM_DBG_TRACE
 __attribute__((visibility("default"))) int vmm_ba_debug_trace_words(unsigned** p, size_t* n) { *p = g_trace_host; *n = kTraceWords; return 0; }
 #endif

@@ -284,6 +284,18 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// The same with an L2 eviction policy (createpolicy): the persistent PCG kernel streams the scaled blocks (1.2 GB per pass at
+// C3, ten times the L2) evict-first, so that the camera-space vectors and blocks of the phases between two passes survive in L2.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+                 : "memory");
+}
 // Slot release.  The consumer's reads of the slot (generic proxy, LDS) must be ordered before the producer's next
 // cp.async.bulk into it (async proxy): a cross-proxy fence on shared memory, then the arrive.  The arrive itself is
 // RELAXED — a releasing arrive makes ptxas track every earlier global reduction of the thread (ATOMG with a
@@ -353,6 +365,11 @@ __device__ __forceinline__ void load_x6(const double* __restrict__ v, int cam, d
 // lane's block inside a ring slot (tile = lane / 8, row = lane % 8)
 __device__ __forceinline__ void slot_load_e(const unsigned char* slot, int lane, double2 (&E)[18]) {
     const unsigned char* b = slot + (lane >> 3) * kTileBytes + (lane & 7) * 16;
+#ifdef VMM_SP_EMU32   // timing experiment only (tools/): half the planes are read and kept (the register and shared-memory footprint of an fp32 stream); results are wrong
+#pragma unroll
+    for (int i = 0; i < 9; ++i) { E[i] = *reinterpret_cast<const double2*>(b + i * (kTileObs * 16)); E[i + 9] = E[i]; }
+    return;
+#endif
 #pragma unroll
     for (int i = 0; i < 18; ++i) E[i] = *reinterpret_cast<const double2*>(b + i * (kTileObs * 16));
 }
@@ -459,6 +476,7 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
         int q = (lane < kSpRing) ? lane : nslots;
         int lap = (lane < kSpRing) ? sh.lap_base[lane] : 0;   // laps of this ring position since the barriers were initialised
         int2 sd = (q < nslots) ? __ldg(desc + q) : make_int2(0, 0);
+        const uint64_t l2_evict_first = COHERENT ? l2_policy_evict_first() : 0;
 #ifdef VMM_DBG_TRACE
         const unsigned tp = ((unsigned)sh.pass_no << 20) | ((unsigned)MODE << 18);
         SP_TRACE_P(tp | 0x20000u | (unsigned)(nslots & 0xffff));
@@ -472,13 +490,18 @@ __device__ __forceinline__ void sp_pass(SpShared& sh, unsigned char* sp_ring, bo
                 const uint32_t bytes = (uint32_t)sd.y * kTileBytes;
 #endif
                 mbar_expect_tx(&s_full[lane], bytes);
+#ifdef VMM_SP_NO_L2_HINT   // A/B builds (tools/)
                 bulk_g2s(dst, Es + (size_t)sd.x * kTileBytes, bytes, &s_full[lane]);
+#else
+                if (COHERENT) bulk_g2s_hint(dst, Es + (size_t)sd.x * kTileBytes, bytes, &s_full[lane], l2_evict_first);   // persistent PCG kernels
+                else bulk_g2s(dst, Es + (size_t)sd.x * kTileBytes, bytes, &s_full[lane]);
+#endif
                 s_lap[lane] = ++lap;   // after the expect_tx in this thread's shared-memory order
 #ifdef VMM_DBG_TRACE
                 SP_TRACE_P(tp | (unsigned)(lap & 0xffff));
 #endif
                 q += kSpRing;
-                if (q < nslots) sd = __ldg(desc + q);
+                if (q < nslots) sd = __ldg(desc + q);   // (two laps ahead measured the same: the producer does not wait for descriptors)
             }
         }
 #ifdef VMM_DBG_TRACE

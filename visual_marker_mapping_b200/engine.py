@@ -28,7 +28,7 @@ ABI_SYMBOLS = [
     "vmm_ba_get_poses", "vmm_ba_get_step", "vmm_ba_solve", "vmm_ba_evaluate", "vmm_ba_evaluate_device",
     "vmm_ba_reprojection_error_sums", "vmm_ba_marker_translation_covariance", "vmm_ba_marker_translation_covariance_ex", "vmm_ba_schur_multiply", "vmm_ba_debug_coarse_matrix", "vmm_ba_set_coarse_cluster_size", "vmm_ba_shard_info", "vmm_ba_partition_cameras", "vmm_ba_shard_plan",
     "vmm_ba_kernel_launches", "vmm_ba_h2d_bytes", "vmm_ba_measure_fp64_peak", "vmm_ba_measure_copy_bandwidth",
-    "vmm_ba_pcg_phase_ns", "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
+    "vmm_ba_pcg_phase_ns", "vmm_ba_pcg_cta_product_ns", "vmm_ba_profile_enable", "vmm_ba_profile_num_kernels", "vmm_ba_profile_kernel_name", "vmm_ba_profile_get",
     "vmm_ba_cost_no_alloc",
 ]
 NO_ALLOC_MAX_CAMERAS, NO_ALLOC_MAX_MARKERS, NO_ALLOC_MAX_TAG_OBS = 4096, 1024, 131072
@@ -150,6 +150,7 @@ def load_library():
     lib.vmm_ba_measure_copy_bandwidth.argtypes = [C.c_void_p, C.c_size_t, dp]
     lib.vmm_ba_nccl_unique_id.argtypes = [C.c_void_p, C.c_size_t]
     lib.vmm_ba_pcg_phase_ns.argtypes = [C.c_void_p, dp]
+    lib.vmm_ba_pcg_cta_product_ns.argtypes = [C.c_void_p, dp, C.c_int]
     lib.vmm_ba_profile_enable.argtypes = [C.c_void_p, C.c_int]
     lib.vmm_ba_profile_kernel_name.restype = C.c_char_p
     lib.vmm_ba_profile_kernel_name.argtypes = [C.c_int]
@@ -404,6 +405,11 @@ class BundleAdjuster:
         self._check(self._lib.vmm_ba_pcg_phase_ns(self._h, _dp(v)))
         return dict(zip(("product", "update_restrict", "coarse_matvec", "direction", "grid_barriers", "product_cta_min", "product_cta_mean",
                          "product_cta_max", "boundary_exchange", "boundary_scatter"), (float(x) for x in v)))
+
+    def pcg_cta_product_ns(self, n: int = 148) -> np.ndarray:
+        v = np.zeros(n)
+        self._check(self._lib.vmm_ba_pcg_cta_product_ns(self._h, _dp(v), n))
+        return v
 
     def measure_fp64_peak(self) -> float:
         v = C.c_double(0)
