@@ -102,7 +102,7 @@ typedef struct {
     double pcg_polish_tolerance;          /* forcing term once the solve is in its polishing phase, i.e. after an accepted step
                                              lowered the cost by less than pcg_polish_threshold (relative); 0 = the same tolerance
                                              throughout; default 5e-2.  A loose tolerance is only dangerous while the steps are large. */
-    double pcg_polish_threshold;          /* default 1e-2 */
+    double pcg_polish_threshold;          /* default 0.9: all but the first, large steps */
 } vmm_ba_options;
 
 /* replaces: ceres::Solver::Summary (the reference only prints termination_type / FullReport) */
