@@ -13,6 +13,14 @@ python - "$OUT" <<PY
 import sys; sys.path.insert(0, "$ROOT")
 from visual_marker_mapping_b200 import synth, project_io
 project_io.write_project(synth.make_config("c1"), sys.argv[1] + "/proj")
+import json
+g = json.load(open("$ROOT/tests/golden/pnp_cases.json"))   # the PnP driver reads a plain text list of cases (tests/test_pnp.py)
+K, lines = g["K"], []
+for robust in (0, 1):
+    for c in g["cases"]:
+        lines.append(f"case {len(c['object_points'])} {robust} {K[0][0]!r} {K[1][1]!r} {K[0][2]!r} {K[1][2]!r} " + " ".join(repr(float(d)) for d in g["dist"]))
+        lines += [" ".join(repr(float(v)) for v in list(p) + list(q)) for p, q in zip(c["object_points"], c["image_points"])]
+open(sys.argv[1] + "/pnp_cases.txt", "w").write("\n".join(lines) + "\n")
 PY
 export ASAN_OPTIONS=detect_leaks=1 UBSAN_OPTIONS=print_stacktrace=1:halt_on_error=1
 cd "$OUT"
@@ -25,6 +33,6 @@ cd "$OUT"
 ./host_test_asan bigio big 20000 > t4.log 2>&1
 ./host_test_asan moveorigin proj 3 rt/mo.json > t5.log 2>&1
 ./host_test_asan stats proj > t6.log 2>&1
-./host_test_asan pnp "$ROOT/tests/golden/pnp_cases.json" > t7.log 2>&1
+./host_test_asan pnp pnp_cases.txt > t7.log 2>&1
 if grep -l "Sanitizer\|runtime error" *.log; then echo "sanitizer reports found"; exit 1; fi
 echo "host side clean under ASan + UBSan (10 runs)"
