@@ -112,3 +112,25 @@ def test_no_alloc_entry_checks_its_limits_before_touching_the_device(lib):
         engine.cost_no_alloc(0, 0, intr, 4, 0, 8, 2, 8, 8, 8, 3, 8, 8, 8, pkg.LOSS_HUBER, 1.0, 8)
     with pytest.raises(pkg.VmmBaError, match="null"):
         engine.cost_no_alloc(0, 0, intr, 4, 8, 8, 2, 8, 8, 8, 3, 8, 8, 8, pkg.LOSS_HUBER, 1.0, 0)
+
+
+def test_header_is_plain_c_and_links_from_c99(lib, tmp_path):
+    """The boundary is a C ABI: include/vmm_ba.h must compile with a C compiler (-std=c99 -pedantic, no warnings) and a C program
+    must link against libvmm_ba.so and call it."""
+    import shutil, subprocess
+    cc = shutil.which("gcc")
+    if not cc:
+        pytest.skip("no gcc")
+    src = tmp_path / "c_abi.c"
+    src.write_text('#include "vmm_ba.h"\n#include <stdio.h>\n'
+                   'int main(void) { vmm_ba_options o; vmm_ba_options_init(&o);\n'
+                   '  printf("%d %g %d\\n", vmm_ba_abi_version(), o.pcg_tolerance, VMM_BA_NO_ALLOC_MAX_CAMERAS);\n'
+                   '  return vmm_ba_cost_no_alloc(0, 0, 1, 1, 0, 0, 0, 1, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0, 1, 1.0, 0) == VMM_BA_ERR_INVALID_ARGUMENT ? 0 : 1; }\n')
+    libdir = os.path.dirname(pkg.engine.library_path())
+    r = subprocess.run([cc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"), "-o", str(tmp_path / "c_abi"), str(src),
+                        "-L", libdir, "-lvmm_ba", f"-Wl,-rpath,{libdir}"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(tmp_path / "c_abi")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    version, tol, cams = r.stdout.split()
+    assert int(version) == 2 and float(tol) == 1e-2 and int(cams) == 4096
